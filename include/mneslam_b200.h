@@ -1,0 +1,160 @@
+/*
+ * mneslam_b200 -- C ABI of the B200-native JointEncoding ray-batch path.
+ *
+ * The reference (dtc111111/MNESLAM) has no FFI layer: its boundary for this path is the Python class
+ * model/scene_rep.py::JointEncoding.  This library is what a native binding behind that class binds:
+ * every entry point names the reference code it replaces.  Plain pointers and sizes only; no torch
+ * types.  All pointers are DEVICE pointers unless a comment says "host".  All calls are asynchronous on
+ * `stream` (a cudaStream_t passed as void*), never synchronise the device, never throw and never allocate
+ * device memory (workspaces are passed in by the caller).  Return value: 0 = ok, nonzero = error; the
+ * message is available from mne_last_error() (thread-local).
+ *
+ * Tensor layouts (row-major, float32 unless noted):
+ *   rays_o, rays_d [N,3]   z_vals [N,S]   raw [N,S,4] = (rgb logits x3, sdf)   target_rgb [N,3]
+ *   target_d [N]           noise [N,S]    rgb [N,3]   depth/disp/acc/depth_var [N]   inds [N] int32
+ */
+#ifndef MNESLAM_B200_H
+#define MNESLAM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MNE_MAX_PLANES 12
+#define MNE_ACC_SLOTS 16
+#define MNE_N_LOSSES 8
+
+typedef void* mne_stream_t; /* cudaStream_t */
+
+/* One feature plane, logical shape [1, C, H, W] (reference model/scene_rep.py:104-109), addressed through
+ * element strides so that both torch.channels_last (stride_c == 1: the fast, coalesced layout) and plain
+ * NCHW tensors (e.g. a checkpoint written by the reference, mneslam_mp.py:294-315) work.  `grad` has the
+ * same shape/strides and is ACCUMULATED into (+=); NULL = no gradient for this plane. */
+typedef struct MnePlaneDesc {
+    const float* data;
+    float* grad;
+    int32_t H, W;
+    int64_t stride_c, stride_h, stride_w;
+} MnePlaneDesc;
+
+/* Multi-resolution hash grid (the encoder the reference's configs name, model/encodings.py:31-46;
+ * tiny-cuda-nn "HashGrid": n_levels x n_features tables concatenated, level l at table + offset[l]). */
+typedef struct MneHashDesc {
+    const float* table;
+    float* grad;
+    int32_t n_levels;        /* 16 */
+    int32_t n_features;      /* 2 */
+    int32_t base_resolution; /* 16 */
+    float per_level_scale;
+    uint32_t offsets[33];    /* entry offset of each level, offsets[n_levels] = total entries */
+} MneHashDesc;
+
+/* Scene state read at call time (the reference reads model.all_planes / decoder weights at call time too:
+ * SURVEY.md 8(b) "Attributes read/written from outside"). */
+typedef struct MneSceneDesc {
+    int32_t encoder;  /* 0 = tri-plane (live in the reference), 1 = hash grid */
+    int32_t two_grid; /* 1 when grid.oneGrid is False: colour planes / colour table present */
+    int32_t n_bins;   /* OneBlob bins per dimension; must be 16 */
+    int32_t c_dim;    /* plane channels; must be 32 */
+    /* tri-plane: index = group*6 + axis*2 + level; group 0 = sdf planes, 1 = colour planes;
+     * axis 0 = xy [Ny,Nx], 1 = xz [Nz,Nx], 2 = yz [Nz,Ny]; level 0 = coarse, 1 = fine */
+    MnePlaneDesc planes[MNE_MAX_PLANES];
+    MneHashDesc hash[2]; /* [0] sdf table, [1] colour table (two_grid) */
+    /* plane normalisation box = JointEncoding.bound (model/scene_rep.py:80-83), lo and (hi - lo) in fp32 */
+    float bound_lo[3], bound_ext[3];
+    /* OneBlob normalisation box = JointEncoding.bounding_box, float64 (model/scene_rep.py:292) */
+    double bbox_lo[3], bbox_ext[3];
+    /* decoder: the four bias-free nn.Linear weights, row-major [out, in] (model/decoder.py:39-55,92-108):
+     * sdf0 [32, F+48], sdf1 [16, 32], col0 [32, 48 (+F) + 15], col1 [3, 32]; F = 64 (planes) or 32 (hash) */
+    const float* w_sdf0;
+    const float* w_sdf1;
+    const float* w_col0;
+    const float* w_col1;
+    /* gradient accumulators of the same shapes (+=), or NULL */
+    float* g_sdf0;
+    float* g_sdf1;
+    float* g_col0;
+    float* g_col1;
+} MneSceneDesc;
+
+/* Constants of the sampling stage (reference model/scene_rep.py:361-381).  The linspace tables are built
+ * by the host exactly as the reference builds them (torch.linspace on the CPU) so sample positions are
+ * bit-identical by construction. */
+typedef struct MneSampleCfg {
+    int32_t n_uniform;            /* training.n_samples_d (target_d given) or training.n_samples */
+    int32_t n_range;              /* training.n_range_d, 0 when target_d is NULL */
+    const float* uniform;         /* [n_uniform] linspace(near, far) */
+    const float* range_offsets;   /* [n_range]   linspace(-range_d, range_d) */
+    const float* range_fallback;  /* [n_range]   linspace(near, far), used where target_d <= 0 */
+    int32_t perturb;              /* training.perturb > 0 */
+} MneSampleCfg;
+
+/* Constants of compositing and of the losses.  Floats are the float32 roundings of the Python doubles the
+ * reference combines with float32 tensors. */
+typedef struct MneRenderCfg {
+    float trunc;        /* training.trunc: sdf2weights sigmoid scale (model/scene_rep.py:193) */
+    float sc_trunc;     /* data.sc_factor * training.trunc: mask window (:200) and Co-SLAM truncation (:586) */
+    float model_trunc;  /* model.truncation: ESLAM losses (:489-507) */
+    float center_trunc; /* 0.4 * model.truncation (:495-496) */
+    float depth_trunc;  /* cam.depth_trunc (:570) */
+    int32_t white_bkgd; /* training.white_bkgd (:227) */
+    int32_t first_pass; /* 1: coarse pass of importance sampling -- only rgb0/depth0 losses (:579-581) */
+    double norm_rays;   /* number of rays the means run over; = n_rays unless the batch is sharded over GPUs */
+} MneRenderCfg;
+
+/* Loss accumulators, MNE_ACC_SLOTS doubles on the device (one NCCL all-reduce when rays are sharded):
+ * [0] n_valid_depth [1] n_co_front [2] n_co_near [3] n_e_front [4] n_e_center [5] n_e_tail   (sample stage)
+ * [6] s_rgb [7] s_depth [8] s_co_fs [9] s_co_sdf [10] s_e_fs [11] s_e_center [12] s_e_tail
+ * [13] s_rgb0 [14] s_depth0 [15] spare                                                        (forward)  */
+
+/* ---- library ---- */
+int mne_version(void);
+const char* mne_last_error(void);
+
+/* ---- sampling: replaces the z_vals block of JointEncoding.render_rays (model/scene_rep.py:361-381) plus
+ * the mask counts of get_masks (model/utils.py:117-145), sdf_losses (model/scene_rep.py:489-499) and
+ * valid_depth_mask (:570).  target_d NULL = uniform sampling.  noise NULL = no perturbation.  acc may be
+ * NULL (no counts); otherwise slots 0..5 are ADDED to (zero it first).  */
+int mne_sample_rays(const MneSampleCfg* cfg, const MneRenderCfg* rcfg, int32_t n_rays, const float* target_d,
+                    const float* noise, float* z_vals, double* acc, mne_stream_t stream);
+
+/* ---- forward: replaces run_network + raw2outputs/sdf2weights (model/scene_rep.py:183-230,303-317,384-386)
+ * and the loss sums of JointEncoding.forward (:569-590).  Optional outputs may be NULL.  target_rgb /
+ * target_d / acc NULL = no loss sums. */
+int mne_render_forward(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples,
+                       const float* rays_o, const float* rays_d, const float* z_vals, const float* target_rgb,
+                       const float* target_d, float* raw, float* weights, float* rgb, float* depth, float* disp,
+                       float* acc_map, float* depth_var, int32_t* inds, double* acc, mne_stream_t stream);
+
+/* ---- losses from the accumulators: compute_loss / get_sdf_loss / sdf_losses / mse2psnr
+ * (model/utils.py:43-47,147-185; model/scene_rep.py:501-507).  losses[8] = rgb_loss, depth_loss,
+ * co_sdf_loss, co_fs_loss, e_fs_loss, e_center_loss, e_tail_loss, psnr. */
+int mne_loss_finalize(const MneRenderCfg* rcfg, int32_t n_samples, const double* acc, float* losses,
+                      mne_stream_t stream);
+
+/* ---- backward: replaces torch autograd through the whole path (loss.backward() at mp_slam/mapper.py:88,159).
+ * Upstream gradients: loss_grads[8] (device; d total / d each entry of `losses`, psnr ignored) when the
+ * losses are used, plus optional explicit g_rgb [N,3] / g_depth [N] / g_raw [N,S,4] when the caller
+ * differentiates the rendered maps or the raw network output itself (loop-closure pose optimisation, mp_slam/mapper.py:388-410).
+ * Accumulates (+=) into scene->planes[].grad / hash[].grad / g_* and, if non-NULL, WRITES g_rays_o /
+ * g_rays_d [N,3].  `scratch` must hold mne_backward_scratch_bytes(n_rays, n_samples) bytes. */
+size_t mne_backward_scratch_bytes(int32_t n_rays, int32_t n_samples);
+int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples,
+                        const float* rays_o, const float* rays_d, const float* z_vals, const float* raw,
+                        const float* target_rgb, const float* target_d, const double* acc,
+                        const float* loss_grads, const float* g_rgb, const float* g_depth, const float* g_raw,
+                        void* scratch, float* g_rays_o, float* g_rays_d, mne_stream_t stream);
+
+/* ---- point queries: query_color_sdf / run_network_flat / query_sdf(embed, return_geo)
+ * (model/scene_rep.py:232-301,319-331).  pts [M,3].  Any output may be NULL:
+ * raw [M,4], geo [M,15], feat [M,F] (the embed=True output). */
+int mne_query_points(const MneSceneDesc* scene, int64_t n_pts, const float* pts, float* raw, float* geo,
+                     float* feat, mne_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MNESLAM_B200_H */

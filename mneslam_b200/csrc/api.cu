@@ -1,0 +1,71 @@
+// Library plumbing: error reporting, argument validation, launch heuristics.
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace mne {
+
+static thread_local char g_error[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+}
+
+int sm_count() {
+    static thread_local int cached_dev = -1, cached = 148;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (dev != cached_dev) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0) cached = n;
+        cached_dev = dev;
+    }
+    return cached;
+}
+
+// Rays per warp-group: a group's (ray, sample) points are flattened and processed 32 at a time, so the
+// lane efficiency is (r*S) / (32*ceil(r*S/32)); but larger groups mean fewer of them to spread over the
+// warps.  Pick the r that minimises (rounds of groups per warp) x (chunks per group).
+int choose_rays_per_group(int n_rays, int n_samples, int total_warps) {
+    int best_r = 1;
+    long best_cost = -1;
+    for (int r = 1; r <= 8; ++r) {
+        if (r > 1 && (long)r * n_samples > 1024) break;
+        const long groups = (n_rays + r - 1) / r;
+        const long rounds = (groups + total_warps - 1) / total_warps;
+        const long chunks = ((long)r * n_samples + 31) / 32;
+        const long cost = rounds * chunks;
+        if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_r = r; }
+    }
+    return best_r;
+}
+
+int check_scene(const MneSceneDesc* sc, const char* who, bool) {
+    MNE_CHECK_ARG(sc->encoder == 0, "%s: encoder %d is not built into this library (0 = tri-plane)", who, sc->encoder);
+    MNE_CHECK_ARG(sc->n_bins == kBins, "%s: n_bins = %d, this library is built for %d", who, sc->n_bins, kBins);
+    MNE_CHECK_ARG(sc->c_dim == kCDim, "%s: c_dim = %d, this library is built for %d", who, sc->c_dim, kCDim);
+    MNE_CHECK_ARG(sc->w_sdf0 && sc->w_sdf1 && sc->w_col0 && sc->w_col1, "%s: decoder weights missing", who);
+    const int n = sc->two_grid ? 12 : 6;
+    for (int i = 0; i < n; ++i) {
+        const MnePlaneDesc& p = sc->planes[i];
+        MNE_CHECK_ARG(p.data, "%s: plane %d has no data", who, i);
+        MNE_CHECK_ARG(p.H >= 1 && p.W >= 1, "%s: plane %d has size %dx%d", who, i, p.H, p.W);
+        const int64_t extent = (int64_t)(p.H - 1) * p.stride_h + (int64_t)(p.W - 1) * p.stride_w;
+        MNE_CHECK_ARG(p.stride_h > 0 && p.stride_w > 0 && p.stride_c > 0 && extent < ((int64_t)1 << 31),
+                      "%s: plane %d strides unsupported (c=%lld h=%lld w=%lld)", who, i, (long long)p.stride_c,
+                      (long long)p.stride_h, (long long)p.stride_w);
+    }
+    for (int a = 0; a < 3; ++a) {
+        MNE_CHECK_ARG(sc->bound_ext[a] > 0.f && sc->bbox_ext[a] > 0.0, "%s: empty bound on axis %d", who, a);
+    }
+    return 0;
+}
+
+}  // namespace mne
+
+extern "C" int mne_version(void) { return 100; }
+extern "C" const char* mne_last_error(void) { return mne::g_error; }

@@ -1,0 +1,221 @@
+"""Thin wrappers: torch tensors in, C-ABI calls out.  PyTorch is used for device memory and streams only;
+every computation below happens inside ``libmneslam_b200.so``."""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import ACC_SLOTS, N_LOSSES, RenderCfg, SampleCfg, SceneDesc
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _f32(t, name):
+    if t is None:
+        return None
+    if not (t.is_cuda and t.dtype == torch.float32):
+        raise TypeError('%s must be a float32 CUDA tensor, got %s on %s' % (name, t.dtype, t.device))
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def require_cuda():
+    if not torch.cuda.is_available():
+        raise RuntimeError('mneslam_b200 needs a CUDA device (there is no CPU fallback)')
+
+
+# --------------------------------------------------------------------------------------------------
+# descriptors
+# --------------------------------------------------------------------------------------------------
+def make_render_cfg(config, norm_rays, first_pass=False):
+    """Float32 roundings of the Python constants, as the reference's tensor-scalar ops round them."""
+    t = config['training']
+    rc = RenderCfg()
+    rc.trunc = t['trunc']
+    rc.sc_trunc = config['data']['sc_factor'] * t['trunc']
+    rc.model_trunc = config['model']['truncation']
+    rc.center_trunc = 0.4 * config['model']['truncation']
+    rc.depth_trunc = config['cam']['depth_trunc']
+    rc.white_bkgd = 1 if t['white_bkgd'] else 0
+    rc.first_pass = 1 if first_pass else 0
+    rc.norm_rays = float(norm_rays)
+    return rc
+
+
+class SampleTables:
+    """The reference rebuilds its linspace tables on the CPU every call (``model/scene_rep.py:363-373``); here
+    they are built once per (config values, device) with the same torch.linspace calls and kept on the device."""
+    _cache = {}
+
+    @classmethod
+    def get(cls, config, device, with_depth):
+        t, cam = config['training'], config['cam']
+        if with_depth:
+            key = (str(device), True, cam['near'], cam['far'], t['n_samples_d'], t['n_range_d'], t['range_d'])
+        else:
+            key = (str(device), False, cam['near'], cam['far'], t['n_samples'])
+        tab = cls._cache.get(key)
+        if tab is None:
+            if with_depth:
+                uni = torch.linspace(cam['near'], cam['far'], t['n_samples_d']) if t['n_samples_d'] > 0 \
+                    else torch.empty(0)
+                off = torch.linspace(-t['range_d'], t['range_d'], steps=t['n_range_d'])
+                fb = torch.linspace(cam['near'], cam['far'], steps=t['n_range_d'])
+            else:
+                uni = torch.linspace(cam['near'], cam['far'], t['n_samples'])
+                off = fb = torch.empty(0)
+            tab = tuple(x.float().to(device) for x in (uni, off, fb))
+            cls._cache[key] = tab
+        return tab
+
+
+def make_sample_cfg(tables, perturb):
+    uni, off, fb = tables
+    sc = SampleCfg()
+    sc.n_uniform = uni.numel()
+    sc.n_range = off.numel()
+    sc.uniform = _ptr(uni) if uni.numel() else None
+    sc.range_offsets = _ptr(off) if off.numel() else None
+    sc.range_fallback = _ptr(fb) if fb.numel() else None
+    sc.perturb = 1 if perturb else 0
+    return sc
+
+
+def make_scene(planes, weights, bound, bounding_box, n_bins=16, plane_grads=None, weight_grads=None):
+    """planes: flat list of 6 or 12 ``[1,32,H,W]`` tensors in ``all_planes`` order (group, axis, level).
+    weights: [sdf0, sdf1, col0, col1].  bound: float32 [3,2] (CPU ok).  bounding_box: float64 [3,2]."""
+    if len(planes) not in (6, 12):
+        raise ValueError('expected 6 or 12 planes, got %d' % len(planes))
+    sc = SceneDesc()
+    sc.encoder = 0
+    sc.two_grid = 1 if len(planes) == 12 else 0
+    sc.n_bins = n_bins
+    sc.c_dim = planes[0].shape[1]
+    keep = []
+    for i, p in enumerate(planes):
+        if not (p.is_cuda and p.dtype == torch.float32 and p.dim() == 4 and p.shape[0] == 1):
+            raise TypeError('plane %d must be a float32 CUDA tensor of shape [1,C,H,W]' % i)
+        d = sc.planes[i]
+        d.data = p.data_ptr()
+        d.H, d.W = p.shape[2], p.shape[3]
+        d.stride_c, d.stride_h, d.stride_w = p.stride(1), p.stride(2), p.stride(3)
+        g = plane_grads[i] if plane_grads is not None else None
+        if g is not None:
+            if g.shape != p.shape or g.stride() != p.stride() or g.dtype != torch.float32 or not g.is_cuda:
+                raise TypeError('gradient buffer of plane %d must match its shape and strides' % i)
+            d.grad = g.data_ptr()
+        else:
+            d.grad = None
+    b = bound.detach().to('cpu', torch.float32)
+    ext = b[:, 1] - b[:, 0]                       # float32 subtraction, as model/utils.py:38-40
+    bb = bounding_box.detach().to('cpu', torch.float64)
+    bext = bb[:, 1] - bb[:, 0]
+    for a in range(3):
+        sc.bound_lo[a], sc.bound_ext[a] = float(b[a, 0]), float(ext[a])
+        sc.bbox_lo[a], sc.bbox_ext[a] = float(bb[a, 0]), float(bext[a])
+    ws = [_f32(w, 'decoder weight') for w in weights]
+    keep.extend(ws)
+    sc.w_sdf0, sc.w_sdf1, sc.w_col0, sc.w_col1 = [w.data_ptr() for w in ws]
+    in_sdf = 64 + 48
+    in_col = 48 + 15 + (64 if sc.two_grid else 0)
+    shapes = [(32, in_sdf), (16, 32), (32, in_col), (3, 32)]
+    for w, s in zip(ws, shapes):
+        if tuple(w.shape) != s:
+            raise ValueError('decoder weight shape %s, expected %s' % (tuple(w.shape), s))
+    if weight_grads is not None:
+        for g, w in zip(weight_grads, ws):
+            if g is not None and (g.shape != w.shape or not g.is_contiguous()):
+                raise TypeError('decoder gradient buffers must be contiguous and match the weights')
+        sc.g_sdf0, sc.g_sdf1, sc.g_col0, sc.g_col1 = [_ptr(g) for g in weight_grads]
+    sc._keep = keep
+    return sc
+
+
+# --------------------------------------------------------------------------------------------------
+# entry points
+# --------------------------------------------------------------------------------------------------
+def new_acc(device):
+    return torch.zeros(ACC_SLOTS, dtype=torch.float64, device=device)
+
+
+def sample_rays(sample_cfg, render_cfg, n_rays, n_samples, target_d, noise, acc, device):
+    z = torch.empty(n_rays, n_samples, dtype=torch.float32, device=device)
+    td = _f32(target_d, 'target_d')
+    nz = _f32(noise, 'noise')
+    if nz is not None and tuple(nz.shape) != (n_rays, n_samples):
+        raise ValueError('noise must have shape [%d, %d], got %s' % (n_rays, n_samples, tuple(nz.shape)))
+    _lib.check(_lib.lib().mne_sample_rays(C.byref(sample_cfg), C.byref(render_cfg), n_rays, _ptr(td), _ptr(nz),
+                                          _ptr(z), _ptr(acc), _stream()), 'mne_sample_rays')
+    return z
+
+
+def render_forward(scene, render_cfg, rays_o, rays_d, z_vals, target_rgb=None, target_d=None, acc=None,
+                   want_weights=False, want_aux=True):
+    n, s = z_vals.shape
+    dev = z_vals.device
+    ro, rd = _f32(rays_o, 'rays_o'), _f32(rays_d, 'rays_d')
+    trgb, td = _f32(target_rgb, 'target_rgb'), _f32(target_d, 'target_d')
+    out = {'raw': torch.empty(n, s, 4, dtype=torch.float32, device=dev),
+           'rgb': torch.empty(n, 3, dtype=torch.float32, device=dev),
+           'depth': torch.empty(n, dtype=torch.float32, device=dev)}
+    if want_aux:
+        for k in ('disp_map', 'acc_map', 'depth_var'):
+            out[k] = torch.empty(n, dtype=torch.float32, device=dev)
+        out['inds'] = torch.empty(n, dtype=torch.int32, device=dev)
+    if want_weights:
+        out['weights'] = torch.empty(n, s, dtype=torch.float32, device=dev)
+    _lib.check(_lib.lib().mne_render_forward(
+        C.byref(scene), C.byref(render_cfg), n, s, _ptr(ro), _ptr(rd), _ptr(z_vals), _ptr(trgb), _ptr(td),
+        _ptr(out['raw']), _ptr(out.get('weights')), _ptr(out['rgb']), _ptr(out['depth']), _ptr(out.get('disp_map')),
+        _ptr(out.get('acc_map')), _ptr(out.get('depth_var')), _ptr(out.get('inds')), _ptr(acc), _stream()),
+        'mne_render_forward')
+    return out
+
+
+def loss_finalize(render_cfg, n_samples, acc):
+    losses = torch.empty(N_LOSSES, dtype=torch.float32, device=acc.device)
+    _lib.check(_lib.lib().mne_loss_finalize(C.byref(render_cfg), n_samples, _ptr(acc), _ptr(losses), _stream()),
+               'mne_loss_finalize')
+    return losses
+
+
+def backward_scratch(n_rays, n_samples, device):
+    nbytes = _lib.lib().mne_backward_scratch_bytes(n_rays, n_samples)
+    return torch.empty(max(nbytes // 4, 4), dtype=torch.float32, device=device)
+
+
+def render_backward(scene, render_cfg, rays_o, rays_d, z_vals, raw, target_rgb=None, target_d=None, acc=None,
+                    loss_grads=None, g_rgb=None, g_depth=None, g_raw=None, want_ray_grads=False, scratch=None):
+    n, s = z_vals.shape
+    dev = z_vals.device
+    ro, rd = _f32(rays_o, 'rays_o'), _f32(rays_d, 'rays_d')
+    trgb, td = _f32(target_rgb, 'target_rgb'), _f32(target_d, 'target_d')
+    lg, grgb, gdep, graw = (_f32(loss_grads, 'loss_grads'), _f32(g_rgb, 'g_rgb'), _f32(g_depth, 'g_depth'),
+                            _f32(g_raw, 'g_raw'))
+    if scratch is None:
+        scratch = backward_scratch(n, s, dev)
+    g_o = g_d = None
+    if want_ray_grads:
+        g_o = torch.empty(n, 3, dtype=torch.float32, device=dev)
+        g_d = torch.empty(n, 3, dtype=torch.float32, device=dev)
+    _lib.check(_lib.lib().mne_render_backward(
+        C.byref(scene), C.byref(render_cfg), n, s, _ptr(ro), _ptr(rd), _ptr(z_vals), _ptr(raw), _ptr(trgb), _ptr(td),
+        _ptr(acc), _ptr(lg), _ptr(grgb), _ptr(gdep), _ptr(graw), _ptr(scratch), _ptr(g_o), _ptr(g_d), _stream()),
+        'mne_render_backward')
+    return g_o, g_d
+
+
+def query_points(scene, pts, want_raw=True, want_geo=False, want_feat=False):
+    p = _f32(pts, 'pts').reshape(-1, 3)
+    m, dev = p.shape[0], p.device
+    raw = torch.empty(m, 4, dtype=torch.float32, device=dev) if want_raw else None
+    geo = torch.empty(m, 15, dtype=torch.float32, device=dev) if want_geo else None
+    feat = torch.empty(m, 64, dtype=torch.float32, device=dev) if want_feat else None
+    _lib.check(_lib.lib().mne_query_points(C.byref(scene), m, _ptr(p), _ptr(raw), _ptr(geo), _ptr(feat), _stream()),
+               'mne_query_points')
+    return raw, geo, feat

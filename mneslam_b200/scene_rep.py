@@ -1,0 +1,261 @@
+"""Drop-in replacement for the reference's ``model/scene_rep.py::JointEncoding``.
+
+Same constructor, attributes (``all_planes``, ``bound``, ``bounding_box``, ``decoder``, ``config``), method
+names, argument meaning and return keys as the reference class; the work is done by the
+fused sm_100a kernels in ``libmneslam_b200.so`` behind ``torch.autograd.Function`` wrappers.  There is no
+torch / CPU fallback: without a CUDA device or without the library every compute method raises.
+
+Differences a caller can observe (all documented in DESIGN.md):
+* the feature planes are allocated in ``torch.channels_last`` memory format (same logical ``[1,32,H,W]``
+  shape, so checkpoints round-trip); planes in any other layout (e.g. loaded from a reference checkpoint)
+  still work through strides, only slower;
+* the stratified noise is drawn with ``torch.rand`` on the device instead of on the CPU
+  (``model/scene_rep.py:381``); pass ``noise=`` (or set ``self.noise_override``) for bit-identical samples;
+* ``disp_map`` / ``acc_map`` / ``depth_var`` / ``z_vals`` are returned without a gradient path (they enter no
+  loss in the reference, ``model/scene_rep.py:597-609``).
+"""
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import ops
+from ._lib import LOSS_KEYS
+from .decoder import ColorSDFNet, ColorSDFNet_v2
+
+
+def get_rays(H, W, fx, fy, cx, cy, c2w, device):
+    """Rays of a whole image, OpenGL convention (reference ``model/utils.py:6-25``)."""
+    if isinstance(c2w, np.ndarray):
+        c2w = torch.from_numpy(c2w)
+    c2w = c2w.to(device=device, dtype=torch.float32)
+    i = torch.arange(W, dtype=torch.float32, device=device)[None, :].expand(H, W)
+    j = torch.arange(H, dtype=torch.float32, device=device)[:, None].expand(H, W)
+    dirs = torch.stack([(i - cx) / fx, -(j - cy) / fy, -torch.ones_like(i)], -1)
+    rays_d = torch.sum(dirs[..., None, :] * c2w[:3, :3], -1)
+    rays_o = c2w[:3, -1].expand(rays_d.shape)
+    return rays_o, rays_d
+
+
+class _Render(torch.autograd.Function):
+    """sample -> fused forward (+ loss sums) ; backward = fused recompute-backward kernel."""
+
+    @staticmethod
+    def forward(ctx, model, rays_o, rays_d, target_rgb, target_d, noise, with_losses, *params):
+        cfg = model.config
+        dev = rays_o.device
+        n = rays_o.shape[0]
+        with_depth = target_d is not None
+        n_planes = len(params) - 4
+        planes, weights = list(params[:n_planes]), list(params[n_planes:])
+        tables = ops.SampleTables.get(cfg, dev, with_depth)
+        n_samples = tables[0].numel() + tables[1].numel()
+        perturb = cfg['training']['perturb'] > 0.
+        if perturb and noise is None:
+            noise = torch.rand(n, n_samples, device=dev)
+        rcfg = ops.make_render_cfg(cfg, norm_rays=n * model.norm_scale)
+        scfg = ops.make_sample_cfg(tables, perturb)
+        td = target_d.reshape(-1) if with_depth else None
+        acc = ops.new_acc(dev) if with_losses else None
+        z_vals = ops.sample_rays(scfg, rcfg, n, n_samples, td, noise if perturb else None, acc, dev)
+        scene = ops.make_scene(planes, weights, model.bound, model.bounding_box, cfg['pos']['n_bins'])
+        out = ops.render_forward(scene, rcfg, rays_o, rays_d, z_vals, target_rgb if with_losses else None,
+                                 td if with_losses else None, acc)
+        if with_losses:
+            if model.acc_allreduce is not None:
+                model.acc_allreduce(acc)
+            losses = ops.loss_finalize(rcfg, n_samples, acc)
+        else:
+            losses = torch.zeros(len(LOSS_KEYS), device=dev)
+        ctx.model, ctx.rcfg, ctx.with_losses, ctx.n_planes = model, rcfg, with_losses, n_planes
+        ctx.save_for_backward(rays_o, rays_d, z_vals, out['raw'], target_rgb if with_losses else None,
+                              td if with_losses else None, acc, *params)
+        ctx.set_materialize_grads(False)
+        nondiff = (z_vals, out['disp_map'], out['acc_map'], out['depth_var'], out['inds'])
+        ctx.mark_non_differentiable(*nondiff)
+        return (out['rgb'], out['depth'], out['raw'], losses) + nondiff
+
+    @staticmethod
+    def backward(ctx, g_rgb, g_depth, g_raw, g_losses, *unused):
+        rays_o, rays_d, z_vals, raw, target_rgb, td, acc = ctx.saved_tensors[:7]
+        params = ctx.saved_tensors[7:]
+        model, n_planes = ctx.model, ctx.n_planes
+        planes, weights = list(params[:n_planes]), list(params[n_planes:])
+        need = ctx.needs_input_grad
+        need_params = need[7:]
+        plane_grads = [torch.zeros_like(p) if nd else None for p, nd in zip(planes, need_params[:n_planes])]
+        weight_grads = [torch.zeros_like(w) if nd else None for w, nd in zip(weights, need_params[n_planes:])]
+        want_rays = bool(need[1] or need[2])
+        scene = ops.make_scene(planes, weights, model.bound, model.bounding_box, model.config['pos']['n_bins'],
+                               plane_grads=plane_grads, weight_grads=weight_grads)
+        lg = g_losses if (ctx.with_losses and g_losses is not None) else None
+        g_o, g_d = ops.render_backward(scene, ctx.rcfg, rays_o, rays_d, z_vals, raw, target_rgb, td, acc,
+                                       loss_grads=lg, g_rgb=g_rgb, g_depth=g_depth, g_raw=g_raw,
+                                       want_ray_grads=want_rays)
+        return (None, g_o if need[1] else None, g_d if need[2] else None, None, None, None, None,
+                *plane_grads, *weight_grads)
+
+
+class JointEncoding(nn.Module):
+    def __init__(self, config, bound_box, ray_batch_size=4096):
+        super().__init__()
+        self.config = config
+        self.bounding_box = bound_box
+        self.device = torch.device('cuda' if torch.cuda.is_available() else 'cpu')
+        self.load_bound(config)
+        self.get_encoding(config)
+        self.get_decoder(config)
+        self.ray_batch_size = ray_batch_size
+        # extensions (not in the reference): explicit noise for parity runs, multi-GPU hooks
+        self.noise_override = None
+        self.norm_scale = 1          # world size when the ray batch is sharded over GPUs
+        self.acc_allreduce = None    # callable(acc) all-reducing the loss accumulators across ranks
+
+    # ------------------------------------------------------------------ construction
+    def load_bound(self, cfg):
+        """Enlarged scene box for the planes (reference ``model/scene_rep.py:72-83``)."""
+        self.bound = torch.from_numpy(np.array(cfg['mapping']['bound']) * cfg['scale']).float()
+        q = cfg['planes_res']['bound_dividable']
+        self.bound[:, 1] = (((self.bound[:, 1] - self.bound[:, 0]) / q).int() + 1) * q + self.bound[:, 0]
+
+    def _init_planes(self, res_key):
+        c_dim = self.config['model']['c_dim']
+        if c_dim != 32:
+            raise NotImplementedError('the fused kernels are built for model.c_dim = 32 (every reference config)')
+        ext = self.bound[:, 1] - self.bound[:, 0]
+        groups = ([], [], [])
+        for res in (self.config[res_key]['coarse'], self.config[res_key]['fine']):
+            nx, ny, nz = [int(v) for v in (ext / res).tolist()]
+            for lst, hw in zip(groups, ((ny, nx), (nz, nx), (nz, ny))):
+                # values are drawn in NCHW order (same stream of normals as the reference), then laid out
+                # channels-last: a texel's 32 channels become one 128-byte line
+                p = torch.empty([1, c_dim, *hw]).normal_(mean=0, std=0.01).to(self.device)
+                lst.append(p.contiguous(memory_format=torch.channels_last))
+        return groups
+
+    def init_all_planes(self, config):
+        self.coarse_planes_res = config['planes_res']['coarse']
+        self.fine_planes_res = config['planes_res']['fine']
+        return self._init_planes('planes_res')
+
+    def init_all_c_planes(self, config):
+        self.coarse_c_planes_res = config['c_planes_res']['coarse']
+        self.fine_c_planes_res = config['c_planes_res']['fine']
+        return self._init_planes('c_planes_res')
+
+    def get_encoding(self, config):
+        if 'blob' not in config['pos']['enc'].lower() or config['pos']['n_bins'] != 16:
+            raise NotImplementedError('the fused kernels are built for pos.enc = OneBlob with 16 bins')
+        self.input_ch = config['model']['input_ch']
+        self.input_ch_pos = config['model']['input_ch_pos']
+        if (self.input_ch, self.input_ch_pos) != (64, 48):
+            raise NotImplementedError('model.input_ch / input_ch_pos must be 64 / 48 (2 x c_dim, 3 x n_bins)')
+        self.all_planes = self.init_all_planes(config)
+        if not config['grid']['oneGrid']:
+            self.all_planes = self.all_planes + self.init_all_c_planes(config)
+
+    def get_decoder(self, config):
+        cls = ColorSDFNet_v2 if config['grid']['oneGrid'] else ColorSDFNet
+        self.decoder = cls(config, input_ch=self.input_ch, input_ch_pos=self.input_ch_pos)
+        self.color_net = self.decoder.color_net
+        self.sdf_net = self.decoder.sdf_net
+
+    # ------------------------------------------------------------------ helpers
+    def _flat_planes(self):
+        expect = 3 if self.config['grid']['oneGrid'] else 6
+        if len(self.all_planes) != expect:
+            raise ValueError('all_planes has %d groups, config expects %d' % (len(self.all_planes), expect))
+        return [p for group in self.all_planes for p in group]
+
+    def _scene(self):
+        return ops.make_scene(self._flat_planes(), self.decoder.weight_list(), self.bound, self.bounding_box,
+                              self.config['pos']['n_bins'])
+
+    def _render(self, rays_o, rays_d, target_rgb, target_d, with_losses, noise=None):
+        ops.require_cuda()
+        if self.config['training']['n_importance'] > 0:
+            from .importance import render_with_importance
+            return render_with_importance(self, rays_o, rays_d, target_rgb, target_d, with_losses, noise)
+        noise = noise if noise is not None else self.noise_override
+        params = self._flat_planes() + self.decoder.weight_list()
+        res = _Render.apply(self, rays_o, rays_d, target_rgb, target_d, noise, with_losses, *params)
+        rgb, depth, raw, losses, z_vals, disp, acc_map, depth_var, inds = res
+        rend = {'rgb': rgb, 'depth': depth, 'disp_map': disp, 'acc_map': acc_map, 'depth_var': depth_var,
+                'z_vals': z_vals, 'raw': raw}
+        return rend, losses, inds
+
+    # ------------------------------------------------------------------ reference API: rendering
+    def render_rays(self, rays_o, rays_d, target_d=None, noise=None):
+        """reference ``model/scene_rep.py:351-419``: dict with rgb, depth, disp_map, acc_map, depth_var, z_vals,
+        raw (+ rgb0, disp0, acc0, depth0, depth_var0, z_std when ``training.n_importance > 0``)."""
+        rend, _, _ = self._render(rays_o, rays_d, None, target_d, False, noise)
+        return rend
+
+    def forward(self, rays_o, rays_d, target_rgb, target_d, global_step=0, noise=None):
+        """reference ``model/scene_rep.py:549-611``."""
+        if not self.training:
+            return self.render_rays(rays_o, rays_d, target_d=target_d, noise=noise)
+        rend, losses, _ = self._render(rays_o, rays_d, target_rgb, target_d, True, noise)
+        ret = {'rgb': rend['rgb'], 'depth': rend['depth']}
+        for i, k in enumerate(LOSS_KEYS[:-1]):
+            ret[k] = losses[i]
+        ret['psnr'] = losses[7:8].detach()
+        return ret
+
+    def render_img(self, c2w, device, gt_depth=None):
+        """reference ``model/scene_rep.py:422-473``: (depth [H,W] float64, colour [H,W,3])."""
+        with torch.no_grad():
+            cam = self.config['cam']
+            H = cam['H'] - 2 * cam['crop_edge']
+            W = cam['W'] - 2 * cam['crop_edge']
+            rays_o, rays_d = get_rays(H, W, cam['fx'], cam['fy'], cam['cx'], cam['cy'], c2w, device)
+            rays_o = rays_o.reshape(-1, 3).contiguous()
+            rays_d = rays_d.reshape(-1, 3).contiguous()
+            if gt_depth is not None:
+                gt_depth = gt_depth.reshape(-1).unsqueeze(1).to(device)
+            depths, colours = [], []
+            bs = self.ray_batch_size
+            for i in range(0, rays_d.shape[0], bs):
+                td = None if gt_depth is None else gt_depth[i:i + bs]
+                ret = self.render_rays(rays_o[i:i + bs], rays_d[i:i + bs], target_d=td)
+                depths.append(ret['depth'].double())
+                colours.append(ret['rgb'])
+            return torch.cat(depths, 0).reshape(H, W), torch.cat(colours, 0).reshape(H, W, 3)
+
+    # ------------------------------------------------------------------ reference API: point queries
+    def query_color_sdf(self, query_points):
+        """raw (rgb logits, sdf) at points ``[..., 3]`` -> ``[M, 4]`` flattened like the reference
+        (``model/scene_rep.py:273-301``)."""
+        ops.require_cuda()
+        raw, _, _ = ops.query_points(self._scene(), query_points.reshape(-1, 3).float())
+        return raw
+
+    def run_network(self, inputs):
+        flat = self.query_color_sdf(inputs)
+        return flat.reshape(list(inputs.shape[:-1]) + [4])
+
+    def run_network_flat(self, inputs_flat):
+        return self.query_color_sdf(inputs_flat)
+
+    def query_sdf(self, query_points, return_geo=False, embed=False):
+        """reference ``model/scene_rep.py:232-268``."""
+        ops.require_cuda()
+        lead = list(query_points.shape[:-1])
+        pts = query_points.reshape(-1, 3).float()
+        if embed:
+            _, _, feat = ops.query_points(self._scene(), pts, want_raw=False, want_feat=True)
+            return feat.reshape(lead + [feat.shape[-1]])
+        raw, geo, _ = ops.query_points(self._scene(), pts, want_geo=return_geo)
+        sdf = raw[:, 3].reshape(lead)
+        if not return_geo:
+            return sdf
+        return sdf, geo.reshape(lead + [geo.shape[-1]])
+
+    def query_color(self, query_points):
+        return torch.sigmoid(self.query_color_sdf(query_points)[..., :3])
+
+    def render_surface_color(self, rays_o, normal):
+        """reference ``model/scene_rep.py:333-349``: composite colour over a short normal-aligned segment."""
+        from .compose import composite_along
+        trunc = self.config['training']['trunc']
+        z = torch.linspace(-trunc, trunc, steps=self.config['training']['n_range_d']).to(rays_o)
+        return composite_along(self, rays_o.reshape(-1, 3), normal.reshape(-1, 3), z)['rgb']

@@ -1,0 +1,224 @@
+"""GPU parity: the CUDA path (through the C ABI) against the golden fixtures of the reference and against the
+CPU oracle on fresh seeded inputs.  Tolerances are BASELINE.json's: sample positions and sign-change
+indices bit-exact; rendered maps and losses <= 1e-3 relative (fp32 parameters); gradient cosine >= 0.999."""
+import numpy as np
+import pytest
+import torch
+
+from mneslam_b200 import configs, synthetic
+from oracle import joint_encoding as J
+from tests.cases import FULL, SMALL_DEPTH, SMALL_NODEPTH, Case
+from tests.gpu_util import build_model, cosine, flat_planes, rel, total_loss
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-3
+COS_TOL = 0.999
+
+
+def check_grads_against_golden(case, model, rays_o=None, rays_d=None):
+    g = case.g
+    for w, k in zip(model.decoder.weight_list(), ('sdf0', 'sdf1', 'col0', 'col1')):
+        got = w.grad.cpu().numpy()
+        assert cosine(got, g['g_' + k]) >= COS_TOL, k
+        assert rel(got, g['g_' + k]) < 5e-3, (k, rel(got, g['g_' + k]))
+    for i, p in enumerate(flat_planes(model)):
+        got = p.grad.cpu()
+        if f'g_plane{i}' in g:
+            assert cosine(got.numpy(), g[f'g_plane{i}']) >= COS_TOL, i
+            assert rel(got.numpy(), g[f'g_plane{i}']) < 5e-3, (i, rel(got.numpy(), g[f'g_plane{i}']))
+        else:
+            vals = got.contiguous().reshape(-1)[torch.from_numpy(g[f'gp_idx{i}'])].numpy()
+            if np.abs(g[f'gp_val{i}']).max() > 0:
+                assert cosine(vals, g[f'gp_val{i}']) >= COS_TOL, i
+            np.testing.assert_allclose(got.double().norm().item(), g[f'gp_stats{i}'][1], rtol=2e-3)
+    if rays_o is not None:
+        assert cosine(rays_o.grad.cpu().numpy(), g['g_rays_o']) >= COS_TOL
+        assert cosine(rays_d.grad.cpu().numpy(), g['g_rays_d']) >= COS_TOL
+        assert rel(rays_o.grad.cpu().numpy(), g['g_rays_o']) < 5e-3
+        assert rel(rays_d.grad.cpu().numpy(), g['g_rays_d']) < 5e-3
+
+
+@pytest.mark.parametrize('channels_last', [True, False])
+@pytest.mark.parametrize('name', SMALL_DEPTH + FULL)
+def test_forward_backward_vs_reference_golden(name, channels_last):
+    if name in FULL and not channels_last:
+        pytest.skip('strided-layout path is covered by the small cases')
+    case = Case(name)
+    g, cfg = case.g, case.cfg
+    model = build_model(cfg, case.bounding_box, case.planes, case.weights, channels_last)
+    rays_o = case.t('rays_o').cuda().requires_grad_(True)
+    rays_d = case.t('rays_d').cuda().requires_grad_(True)
+    trgb, td, noise = case.t('target_rgb').cuda(), case.t('target_d').cuda(), case.t('noise').cuda()
+
+    rend = model.render_rays(rays_o.detach(), rays_d.detach(), target_d=td, noise=noise)
+    assert np.array_equal(rend['z_vals'].cpu().numpy(), g['z_vals']), 'sample positions must be bit-exact'
+    for k in ('rgb', 'depth', 'raw', 'acc_map', 'depth_var', 'disp_map'):
+        assert rel(rend[k].cpu().numpy(), g[k]) < REL_TOL, (k, rel(rend[k].cpu().numpy(), g[k]))
+    _, _, inds = model._render(rays_o.detach(), rays_d.detach(), None, td, False, noise)
+    assert np.array_equal(inds.cpu().numpy().astype(np.int64), g['inds']), 'sign-change indices must be bit-exact'
+
+    ret = model.forward(rays_o, rays_d, trgb, td, noise=noise)
+    for k in ('rgb_loss', 'depth_loss', 'co_sdf_loss', 'co_fs_loss', 'e_fs_loss', 'e_center_loss', 'e_tail_loss', 'psnr'):
+        np.testing.assert_allclose(ret[k].detach().cpu().numpy(), g[k], rtol=REL_TOL, err_msg=k)
+    loss = total_loss(cfg, ret)
+    np.testing.assert_allclose(loss.item(), g['loss'], rtol=REL_TOL)
+    loss.backward()
+    check_grads_against_golden(case, model, rays_o, rays_d)
+
+
+@pytest.mark.parametrize('name', SMALL_NODEPTH)
+def test_pose_path_vs_reference_golden(name):
+    """Loop-closure alignment path: render_rays(target_d=None), MSE on the rendered maps, gradients reach the
+    pose parameters through d loss / d rays (mp_slam/mapper.py:388-410)."""
+    case = Case(name)
+    g, cfg = case.g, case.cfg
+    model = build_model(cfg, case.bounding_box, case.planes, case.weights)
+    c2w = case.t('c2w').cuda()
+    rot = case.t('pose_rot').cuda().requires_grad_(True)
+    trans = c2w[:3, 3].clone().requires_grad_(True)
+    Rm = J.axis_angle_to_matrix(rot[None])[0] if 'axis' in name else J.quat_to_matrix(rot[None])[0]
+    rays_o, rays_d = J.rays_from_pose(Rm @ c2w[:3, :3], trans, case.t('dirs_cam').cuda())
+    rays_o.retain_grad(); rays_d.retain_grad()
+    rend = model.render_rays(rays_o, rays_d, target_d=None, noise=case.t('noise').cuda())
+    assert np.array_equal(rend['z_vals'].cpu().numpy(), g['z_vals'])
+    t = cfg['training']
+    loss = (t['rgb_weight'] * torch.nn.functional.mse_loss(rend['rgb'], case.t('target_rgb').cuda())
+            + t['depth_weight'] * torch.nn.functional.mse_loss(rend['depth'], case.t('target_d').cuda().squeeze(-1)))
+    np.testing.assert_allclose(loss.item(), g['loss'], rtol=REL_TOL)
+    loss.backward()
+    check_grads_against_golden(case, model, rays_o, rays_d)
+    assert rel(rot.grad.cpu().numpy(), g['g_pose_rot']) < 5e-3
+    assert rel(trans.grad.cpu().numpy(), g['g_pose_trans']) < 5e-3
+
+
+@pytest.mark.parametrize('two_grid', [False, True])
+@pytest.mark.parametrize('n_rays', [1, 37, 300])
+def test_fresh_inputs_vs_oracle(two_grid, n_rays):
+    """Fresh seeds and ragged sizes against the CPU oracle run on the spot."""
+    cfg = configs.small_test_config(one_grid=not two_grid, n_samples_d=13, n_range_d=7)
+    cfg['is_co_sdf'] = two_grid
+    seed = 100 + n_rays
+    bound = J.enlarged_bound(cfg)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    planes = J.init_planes(cfg, bound, seed=seed, std=0.5)
+    weights = J.init_weights(cfg, seed=seed)
+    batch = synthetic.make_ray_batch(cfg, n_rays, seed=seed, zero_depth_frac=0.2, depth_range=(0.3, 2.5))
+    S = synthetic.n_samples_total(cfg)
+    noise = synthetic.make_noise(n_rays, S, seed)
+
+    op = tuple([p.clone().requires_grad_(True) for p in grp] for grp in planes)
+    ow = {k: v.clone().requires_grad_(True) for k, v in weights.items()}
+    oret, orend = J.forward(cfg, op, ow, bound, bb, batch['rays_o'], batch['rays_d'], batch['target_rgb'],
+                            batch['target_d'], noise)
+    oloss = J.total_loss(cfg, oret)
+
+    model = build_model(cfg, bb, planes, weights)
+    ret = model.forward(batch['rays_o'].cuda(), batch['rays_d'].cuda(), batch['target_rgb'].cuda(),
+                        batch['target_d'].cuda(), noise=noise.cuda())
+    for k in ('rgb', 'depth'):
+        assert rel(ret[k].detach().cpu().numpy(), orend[k].detach().numpy()) < REL_TOL, k
+    finite = True
+    for k in ('rgb_loss', 'depth_loss', 'co_sdf_loss', 'co_fs_loss', 'e_fs_loss', 'e_center_loss', 'e_tail_loss'):
+        a, b = ret[k].item(), oret[k].item()
+        if np.isnan(b):                       # empty mask: the reference's mean() of nothing is nan
+            assert np.isnan(a), k
+            finite = False
+        else:
+            np.testing.assert_allclose(a, b, rtol=REL_TOL, atol=1e-7, err_msg=k)
+    if not finite:
+        return
+    oloss.backward()
+    total_loss(cfg, ret).backward()
+    for p, q in zip(flat_planes(model), [p for grp in op for p in grp]):
+        if q.grad.abs().max() > 0:
+            assert cosine(p.grad.cpu().numpy(), q.grad.numpy()) >= COS_TOL
+    for w, k in zip(model.decoder.weight_list(), ('sdf0', 'sdf1', 'col0', 'col1')):
+        assert cosine(w.grad.cpu().numpy(), ow[k].grad.numpy()) >= COS_TOL, k
+
+
+def test_empty_masks_give_nan_loss_and_finite_grads():
+    """All depths invalid: depth_loss and the ESLAM terms are means over empty selections (nan in the reference),
+    while the gradients of the remaining terms stay finite."""
+    cfg = configs.small_test_config()
+    bound = J.enlarged_bound(cfg)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    model = build_model(cfg, bb, J.init_planes(cfg, bound, seed=5, std=0.5), J.init_weights(cfg, seed=5))
+    batch = synthetic.make_ray_batch(cfg, 64, seed=5, zero_depth_frac=1.1)
+    assert float(batch['target_d'].max()) == 0.0
+    ret = model.forward(batch['rays_o'].cuda(), batch['rays_d'].cuda(), batch['target_rgb'].cuda(),
+                        batch['target_d'].cuda())
+    assert torch.isnan(ret['depth_loss']) and torch.isnan(ret['e_fs_loss'])
+    assert torch.isfinite(ret['rgb_loss'])
+    ret['rgb_loss'].backward()
+    for p in flat_planes(model):
+        assert torch.isfinite(p.grad).all()
+
+
+def test_zero_rays_and_query_entry_points():
+    cfg = configs.small_test_config(one_grid=False)
+    bound = J.enlarged_bound(cfg)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    planes, weights = J.init_planes(cfg, bound, seed=3, std=0.5), J.init_weights(cfg, seed=3)
+    model = build_model(cfg, bb, planes, weights, as_params=False)
+    model.eval()
+    pts = (torch.rand(1000, 3) * 2.4 - 1.2)              # some outside the box: border clamp + OneBlob wrap
+    raw = model.run_network_flat(pts.cuda())
+    oraw = J.query_points(cfg, planes, weights, bound, bb, pts)
+    assert rel(raw.cpu().numpy(), oraw.numpy()) < REL_TOL
+    sdf, geo = model.query_sdf(pts.cuda().reshape(100, 10, 3), return_geo=True)
+    assert sdf.shape == (100, 10) and geo.shape == (100, 10, 15)
+    assert rel(sdf.reshape(-1).cpu().numpy(), oraw[:, 3].numpy()) < REL_TOL
+    emb = model.query_sdf(pts.cuda().reshape(1000, 1, 3), embed=True)
+    ofeat = J.triplane_features(J.normalize_plane_coords(pts, bound), planes[0], planes[1], planes[2])
+    assert emb.shape == (1000, 1, 64) and rel(emb.reshape(-1, 64).cpu().numpy(), ofeat.numpy()) < REL_TOL
+    col = model.query_color(pts.cuda().reshape(1000, 1, 3))
+    assert col.shape == (1000, 3) and rel(col.cpu().numpy(), torch.sigmoid(oraw[:, :3]).numpy()) < REL_TOL
+    empty = model.run_network_flat(torch.zeros(0, 3).cuda())
+    assert empty.shape == (0, 4)
+
+
+def test_full_size_properties_r0():
+    """BASELINE config 1/2 shape (Replica room0, 2048 rays x 43 samples): properties that need no oracle."""
+    cfg = configs.replica_room0()
+    torch.manual_seed(0)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    from mneslam_b200 import JointEncoding
+    model = JointEncoding(cfg, bb).cuda()
+    for grp in model.all_planes:
+        for i, p in enumerate(grp):
+            grp[i] = torch.nn.Parameter(p.mul_(30.0))
+    model.train()
+    batch = {k: v.cuda() for k, v in synthetic.make_ray_batch(cfg, 2048, seed=11).items()}
+    rend = model.render_rays(batch['rays_o'], batch['rays_d'], target_d=batch['target_d'])
+    z = rend['z_vals']
+    assert z.shape == (2048, 43) and bool((z[:, 1:] >= z[:, :-1]).all()), 'perturbed samples stay sorted'
+    acc = rend['acc_map']
+    assert bool(((acc - 1).abs() < 1e-4).all()), 'normalised weights sum to one'
+    assert bool((rend['rgb'] >= 0).all()) and bool((rend['rgb'] <= 1).all())
+    noise = torch.rand(2048, 43, device='cuda')
+
+    def grads(scale):
+        for p in flat_planes(model) + list(model.decoder.parameters()):
+            p.grad = None
+        ret = model.forward(batch['rays_o'], batch['rays_d'], batch['target_rgb'], batch['target_d'], noise=noise)
+        (scale * total_loss(cfg, ret)).backward()
+        return [p.grad.clone() for p in flat_planes(model) + list(model.decoder.parameters())], ret
+    g1, ret1 = grads(1.0)
+    g2, ret2 = grads(2.0)
+    assert ret1['rgb_loss'].item() == pytest.approx(ret2['rgb_loss'].item(), rel=1e-6)
+    for a, b in zip(g1, g2):                       # linearity in the upstream gradient
+        assert torch.allclose(2 * a, b, rtol=1e-3, atol=1e-9 + 1e-4 * float(b.abs().max()))
+    # directional finite difference on the decoder weights (fp32, so a coarse check)
+    w = model.decoder.sdf_net.model[2].weight
+    direction = torch.randn_like(w)
+    eps = 1e-2
+    with torch.no_grad():
+        w.add_(eps * direction)
+        lp = total_loss(cfg, model.forward(batch['rays_o'], batch['rays_d'], batch['target_rgb'], batch['target_d'], noise=noise)).item()
+        w.sub_(2 * eps * direction)
+        lm = total_loss(cfg, model.forward(batch['rays_o'], batch['rays_d'], batch['target_rgb'], batch['target_d'], noise=noise)).item()
+        w.add_(eps * direction)
+    fd = (lp - lm) / (2 * eps)
+    an = float((g1[len(flat_planes(model)) + 1] * direction).sum())
+    assert abs(fd - an) <= 0.05 * max(abs(fd), abs(an)) + 1e-4, (fd, an)

@@ -1,0 +1,69 @@
+"""CPU-side checks: the C-ABI library loads and exports every symbol the header declares, host descriptors
+are laid out as the C structs, and the product path refuses to run without a GPU (no fallback)."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+from mneslam_b200 import _lib, configs, ops
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, 'include', 'mneslam_b200.h')).read()
+    text = re.sub(r'/\*.*?\*/', '', text, flags=re.S)
+    return sorted(set(re.findall(r'\b(mne_[a-z_0-9]+)\s*\(', text)))
+
+
+def test_library_exports_every_declared_symbol():
+    handle = _lib.lib()
+    names = declared_symbols()
+    assert len(names) >= 8
+    for n in names:
+        assert hasattr(handle, n), n
+    assert sorted(_lib.exported_symbols()) == names, 'ctypes signatures and header are out of sync'
+    assert handle.mne_version() >= 100
+
+
+def test_struct_layout_matches_header():
+    assert ctypes.sizeof(_lib.PlaneDesc) == 48
+    assert ctypes.sizeof(_lib.HashDesc) == 168
+    assert ctypes.sizeof(_lib.SceneDesc) == 1064
+    assert _lib.SceneDesc.bound_lo.offset == 928 and _lib.SceneDesc.bbox_lo.offset == 952
+    assert _lib.SceneDesc.w_sdf0.offset == 1000
+    assert ctypes.sizeof(_lib.RenderCfg) == 40 and _lib.RenderCfg.norm_rays.offset == 32
+    assert ctypes.sizeof(_lib.SampleCfg) == 40
+
+
+def test_argument_errors_are_reported_without_a_gpu():
+    handle = _lib.lib()
+    rc = ops.make_render_cfg(configs.replica_room0(), 16)
+    sc = _lib.SampleCfg()
+    assert handle.mne_sample_rays(ctypes.byref(sc), ctypes.byref(rc), 4, None, None, None, None, None) != 0
+    assert b'null' in handle.mne_last_error()
+    scene = _lib.SceneDesc()
+    scene.n_bins, scene.c_dim = 8, 32
+    assert handle.mne_query_points(ctypes.byref(scene), 4, None, None, None, None, None) != 0
+    assert b'n_bins' in handle.mne_last_error()
+    assert handle.mne_backward_scratch_bytes(2048, 43) == 2048 * 43 * 16
+
+
+def test_render_cfg_uses_float32_roundings():
+    rc = ops.make_render_cfg(configs.replica_room0(), 2048)
+    import numpy as np
+    assert rc.trunc == np.float32(0.1) and rc.center_trunc == np.float32(0.4 * 0.1)
+    assert rc.norm_rays == 2048.0
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason='checks the no-GPU behaviour')
+def test_no_cpu_fallback():
+    from mneslam_b200 import JointEncoding
+    cfg = configs.small_test_config()
+    model = JointEncoding(cfg, torch.tensor(cfg['mapping']['bound'], dtype=torch.float64))
+    with pytest.raises(RuntimeError, match='CUDA'):
+        model.render_rays(torch.zeros(4, 3), torch.ones(4, 3), target_d=torch.ones(4, 1))
+    with pytest.raises(RuntimeError):
+        model.run_network_flat(torch.zeros(4, 3))

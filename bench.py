@@ -1,0 +1,413 @@
+#!/usr/bin/env python
+"""Benchmark of the JointEncoding mapping iteration (BASELINE.json metric: sampled points/s, fwd+bwd map step).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--no-graph]
+
+A "step" is ONE mapping iteration of the reference's hot loop (mp_slam/mapper.py:134-162) on the Replica
+room0 configuration (BASELINE.json configs[1]): a 2048-ray batch drawn from a synthetic 20-keyframe ray
+database, 43 samples per ray (88 064 points), forward + losses + backward (plane, decoder gradients) + Adam.
+`value` = points / s of the whole job with all inputs resident in HBM (the step is captured in a CUDA graph);
+`e2e` = the same iteration driven through the drop-in JointEncoding class (forward / loss.backward() /
+torch.optim.Adam, i.e. the reference's own call sites) with the ray batch coming from pinned HOST memory and the
+loss read back to the host every step.  Multi-GPU (torchrun): every rank renders its own 2048-ray shard of a
+global batch, loss accumulators and gradients are all-reduced over NCCL (weak scaling).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+N_RAYS = 2048
+N_KF = 20
+ALG_BYTES_PER_POINT_FWD = 3072      # 3 planes x 2 levels x 4 texels x 32 ch x 4 B gathered      
+ALG_BYTES_PER_POINT_BWD = 3072      # the same texels receive one gradient contribution each
+METRIC = 'sampled points/s fwd+bwd (map step)'
+UNIT = 'points/s'
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=50)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--no-graph', action='store_true')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--rays', type=int, default=N_RAYS)
+    return ap.parse_args()
+
+
+def workload_config(cfg, n_rays, world):
+    s = cfg['training']['n_samples_d'] + cfg['training']['n_range_d']
+    return {'workload': 'Replica room0 mapping iteration: %d-ray batch/GPU from a synthetic %d-keyframe DB (1200x680), '
+                        '%d samples/ray, tri-plane 2x3 planes (129.4 MB fp32) + OneBlob + SDF/colour MLPs, '
+                        'fwd + losses + bwd + Adam' % (n_rays, N_KF, s),
+            'rays_per_gpu': n_rays, 'samples_per_ray': s, 'points_per_step': n_rays * s * world,
+            'parallelism': 'ray-sharded data parallel x%d' % world if world > 1 else 'single GPU',
+            'l2': 'inputs larger than L2: planes + gradients + Adam moments = 517 MB touched per step (L2 = 126 MB)'}
+
+
+# ----------------------------------------------------------------------------------------------------
+# CPU baseline: the oracle port of the reference's path (torch CPU ops incl. F.grid_sample, as the reference)
+# ----------------------------------------------------------------------------------------------------
+class CpuMapper:
+    def __init__(self, cfg, seed=0):
+        from oracle import joint_encoding as J
+        self.J, self.cfg = J, cfg
+        self.bound = J.enlarged_bound(cfg)
+        self.bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+        planes = J.init_planes(cfg, self.bound, seed=seed, std=0.01)
+        self.planes = tuple([torch.nn.Parameter(p) for p in grp] for grp in planes)
+        self.weights = {k: torch.nn.Parameter(v) for k, v in J.init_weights(cfg, seed=seed).items()}
+        mp = cfg['mapping']
+        self.opt = torch.optim.Adam([
+            {'params': list(self.weights.values()), 'weight_decay': 1e-6, 'lr': mp['lr_decoder']},
+            {'params': [p for g in self.planes for p in g], 'eps': 1e-15, 'lr': mp['lr_embed']}], betas=(0.9, 0.99))
+
+    def step(self, batch, noise):
+        J = self.J
+        ret, _ = J.forward(self.cfg, self.planes, self.weights, self.bound, self.bb, batch['rays_o'], batch['rays_d'],
+                           batch['target_rgb'], batch['target_d'], noise, fast=True)
+        loss = J.total_loss(self.cfg, ret)
+        loss.backward()
+        self.opt.step()
+        self.opt.zero_grad()
+        return float(loss)
+
+
+def time_cpu(cfg, n_rays, steps, warmup):
+    from mneslam_b200 import synthetic
+    s = synthetic.n_samples_total(cfg)
+    m = CpuMapper(cfg)
+    times = []
+    for i in range(warmup + steps):
+        batch = synthetic.make_ray_batch(cfg, n_rays, seed=i)
+        noise = synthetic.make_noise(n_rays, s, seed=i)
+        t0 = time.perf_counter()
+        m.step(batch, noise)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    times.sort()
+    med = times[len(times) // 2]
+    return n_rays * s / med, med, sum(times)
+
+
+def cpu_baseline_record(cfg, n_rays, steps=5, warmup=1):
+    pts_s, med, total = time_cpu(cfg, n_rays, steps, warmup)
+    return {'value': pts_s, 'unit': UNIT, 'cores': torch.get_num_threads(), 'kind': 'port',
+            'sample': '%d mapping iterations (median) of the same %d-ray x %d-sample workload, oracle port of the '
+                      "reference's torch-CPU path (F.grid_sample + matmul + torch Adam), %d host threads of %d cores"
+                      % (steps, n_rays, cfg['training']['n_samples_d'] + cfg['training']['n_range_d'],
+                         torch.get_num_threads(), os.cpu_count()),
+            'ms_per_step': med * 1e3}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path (oracle port; /root/reference is Python
+    and cannot travel to the GPU box) on the host cores, rank 0 only."""
+    if int(os.environ.get('RANK', '0')) != 0:
+        return
+    from mneslam_b200 import configs
+    cfg = configs.replica_room0()
+    steps, warmup = max(1, min(args.steps, 20)), max(1, min(args.warmup, 3))
+    pts_s, med, _ = time_cpu(cfg, args.rays, steps, warmup)
+    sample = ('%d of the requested %d mapping iterations (median), %d rays x 43 samples, %d host threads'
+              % (steps, args.steps, args.rays, torch.get_num_threads()))
+    line = {'impl': 'reference', 'metric': METRIC, 'value': pts_s, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': steps,
+            'warmup': warmup, 'ms_per_step': med * 1e3, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': workload_config(cfg, args.rays, 1),
+            'cpu_baseline': {'value': pts_s, 'unit': UNIT, 'cores': torch.get_num_threads(), 'kind': 'port',
+                             'sample': sample},
+            'e2e': {'value': pts_s, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'gpu_launches': 0}
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------------
+# clocks
+# ----------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+         'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.path = tempfile.mktemp(suffix='.csv')
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(index), '--query-gpu=' + self.Q,
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=open(self.path, 'w'), stderr=subprocess.DEVNULL)
+        except OSError:
+            pass
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap')
+        for line in open(self.path):
+            f = [x.strip() for x in line.split(',')]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith('active'):
+                    reasons.add(n)
+        os.unlink(self.path)
+        sm.sort()
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': mx, 'samples': len(sm),
+                'reasons': sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------------------------------
+# our arm
+# ----------------------------------------------------------------------------------------------------
+def measured_peak():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(path):
+        return json.load(open(path))['hbm_gbs'], 'MEASURED_PEAKS.json hbm_gbs (measured)'
+    return 6650.0, 'fallback 6.65 TB/s (B200_PROFILING.md)'
+
+
+def ncu_traffic():
+    """dram bytes per launch of the dominant kernel from the committed ncu summary, if there is one."""
+    path = os.path.join(ROOT, 'profiles', 'traffic.json')
+    if os.path.exists(path):
+        try:
+            return json.load(open(path)).get('render_bwd_dram_bytes_per_launch')
+        except Exception:
+            return None
+    return None
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    from mneslam_b200 import JointEncoding, configs, synthetic
+    from mneslam_b200.mapping import DeviceKeyframeRays, FusedMapper, loss_weight_vector
+    from mneslam_b200 import ops
+
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py: no CUDA device (the product path has no CPU fallback); use --impl reference for the CPU arm')
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+
+    cfg = configs.replica_room0()
+    n_rays = args.rays
+    s = synthetic.n_samples_total(cfg)
+    pts_per_rank = n_rays * s
+
+    torch.manual_seed(0)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    model = JointEncoding(cfg, bb).to(dev)
+    model.train()
+    # the map is replicated: same seed on every rank gives identical planes and decoder
+    mapper = FusedMapper(model, world_size=world)
+    rays_cpu, poses_cpu = synthetic.make_keyframe_db(cfg, n_kf=N_KF, seed=0)
+    db = DeviceKeyframeRays(rays_cpu.to(dev), poses_cpu.to(dev))
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(1234 + rank)
+
+    launches_per_step = 3 + 1 + 1 + len(mapper.params)     # sample, fwd, finalize | bwd | tick | adam x params
+
+    def one_step():
+        ro, rd, trgb, td = db.sample(n_rays)
+        return mapper.step(ro, rd, trgb, td)
+
+    # ---- warm-up (also sets kernel attributes outside capture)
+    for _ in range(max(args.warmup, 3)):
+        losses = one_step()
+    torch.cuda.synchronize()
+
+    graph = None
+    if not args.no_graph and world == 1:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            one_step()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            static_losses = one_step()
+        for _ in range(3):
+            graph.replay()
+        torch.cuda.synchronize()
+
+    def run_steps(k):
+        if graph is not None:
+            for _ in range(k):
+                graph.replay()
+        else:
+            for _ in range(k):
+                one_step()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- timed region: exactly K steps, device time via CUDA events, max over ranks
+    sampler = ClockSampler(local) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    run_steps(args.steps)
+    e1.record()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    clocks = sampler.stop() if sampler else None
+    if world > 1:
+        t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ms_step = ms_total / args.steps
+    value = pts_per_rank * world / (ms_step * 1e-3)
+
+    # ---- per-kernel device times (events around each launch, same stream, un-graphed), K steps
+    def timed(fn):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); r = fn(); b.record()
+        return r, (a, b)
+    tables = ops.SampleTables.get(cfg, dev, True)
+    scfg = ops.make_sample_cfg(tables, True)
+    rcfg = ops.make_render_cfg(cfg, norm_rays=n_rays * world)
+    ev = {'sample': [], 'fwd': [], 'bwd': [], 'adam': []}
+    k_prof = min(args.steps, 20)
+    for _ in range(k_prof):
+        ro, rd, trgb, td = db.sample(n_rays)
+        tdf = td.reshape(-1)
+        noise = torch.rand(n_rays, s, device=dev)
+        acc = ops.new_acc(dev)
+        z, e = timed(lambda: ops.sample_rays(scfg, rcfg, n_rays, s, tdf, noise, acc, dev)); ev['sample'].append(e)
+        out, e = timed(lambda: ops.render_forward(mapper._scene(False), rcfg, ro, rd, z, trgb, tdf, acc, want_aux=False)); ev['fwd'].append(e)
+        if world > 1:
+            dist.all_reduce(acc)
+        scr = mapper._scratch
+        _, e = timed(lambda: ops.render_backward(mapper._scene(True), rcfg, ro, rd, z, out['raw'], trgb, tdf, acc,
+                                                 loss_grads=mapper.loss_grads, scratch=scr)); ev['bwd'].append(e)
+        _, e = timed(mapper.optimizer_step); ev['adam'].append(e)
+    torch.cuda.synchronize()
+    us = {k: 1e3 * sum(a.elapsed_time(b) for a, b in v) / len(v) for k, v in ev.items()}
+
+    # ---- e2e: the drop-in class through the reference's call sites, host buffers in, loss out (every step)
+    planes = model._flat_planes()
+    for grp in model.all_planes:
+        for i, p in enumerate(grp):
+            grp[i] = torch.nn.Parameter(p)                                  # mneslam_mp.py:451-457
+    mp = cfg['mapping']
+    opt = torch.optim.Adam([{'params': model.decoder.parameters(), 'weight_decay': 1e-6, 'lr': mp['lr_decoder']},
+                            {'params': model._flat_planes(), 'eps': 1e-15, 'lr': mp['lr_embed']}], betas=(0.9, 0.99))
+    lw = loss_weight_vector(cfg)
+    n_pool = 8
+    host_rays = [torch.empty(n_rays, 7).pin_memory() for _ in range(n_pool)]
+    host_ids = [torch.empty(n_rays, dtype=torch.int64).pin_memory() for _ in range(n_pool)]
+    g_cpu = torch.Generator().manual_seed(99 + rank)
+    flat_db = rays_cpu.reshape(-1, 7)
+    for hr, hi in zip(host_rays, host_ids):
+        idx = torch.randint(0, flat_db.shape[0], (n_rays,), generator=g_cpu)
+        hr.copy_(flat_db[idx]); hi.copy_(idx // rays_cpu.shape[1])
+    h2d_bytes = n_rays * 7 * 4 + n_rays * 8
+    loss_host = torch.empty(1).pin_memory()
+
+    def e2e_step(i):
+        rays7 = host_rays[i % n_pool].to(dev, non_blocking=True)
+        ids = host_ids[i % n_pool].to(dev, non_blocking=True)
+        ro, rd, trgb, td = db.assemble(rays7, ids)
+        ret = model.forward(ro, rd, trgb, td)
+        loss = (lw[0] * ret['rgb_loss'] + lw[1] * ret['depth_loss'] + lw[4] * ret['e_fs_loss']
+                + lw[5] * ret['e_center_loss'] + lw[6] * ret['e_tail_loss'])
+        loss.backward()
+        if world > 1:
+            for p in model._flat_planes() + list(model.decoder.parameters()):
+                dist.all_reduce(p.grad)
+        opt.step()
+        opt.zero_grad()
+        loss_host.copy_(loss.detach().reshape(1), non_blocking=False)      # D2H read of the step's loss
+        return float(loss_host[0])
+
+    for i in range(3):
+        e2e_step(i)
+    barrier()
+    k_e2e = min(args.steps, 30)
+    t0 = time.perf_counter()
+    e0.record()
+    for i in range(k_e2e):
+        e2e_step(i)
+    e1.record()
+    barrier()
+    ms_e2e = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3) / k_e2e
+    if world > 1:
+        t = torch.tensor([ms_e2e], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_e2e = float(t.item())
+    e2e_value = pts_per_rank * world / (ms_e2e * 1e-3)
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        bwd_gbs = pts_per_rank * ALG_BYTES_PER_POINT_BWD / (us['bwd'] * 1e-6) / 1e9
+        fwd_gbs = pts_per_rank * ALG_BYTES_PER_POINT_FWD / (us['fwd'] * 1e-6) / 1e9
+        both_gbs = pts_per_rank * (ALG_BYTES_PER_POINT_FWD + ALG_BYTES_PER_POINT_BWD) / ((us['fwd'] + us['bwd']) * 1e-6) / 1e9
+        line = {
+            'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3),
+            'ms_per_step': ms_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+            'data': 'synthetic', 'config': workload_config(cfg, n_rays, world),
+            'cuda_graph': graph is not None,
+            'gpu_launches': launches_per_step * args.steps,
+            'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d_bytes, 'd2h_bytes_per_step': 4,
+                    'ms_per_step': ms_e2e, 'steps': k_e2e,
+                    'path': 'JointEncoding.forward -> loss.backward() -> torch.optim.Adam.step(), rays from pinned host memory'},
+            'roofline': {'bound': 'hbm', 'kernel': 'render_bwd_kernel', 'achieved': bwd_gbs, 'peak': peak, 'unit': 'GB/s',
+                         'frac': bwd_gbs / peak, 'traffic': ncu_traffic(), 'peak_source': peak_src,
+                         'algorithmic_bytes_per_launch': pts_per_rank * ALG_BYTES_PER_POINT_BWD,
+                         'launch_us': us['bwd'],
+                         'fwd_kernel': {'achieved': fwd_gbs, 'frac': fwd_gbs / peak, 'launch_us': us['fwd']},
+                         'fwd_plus_bwd': {'achieved': both_gbs, 'frac': both_gbs / peak,
+                                          'bytes_per_point': ALG_BYTES_PER_POINT_FWD + ALG_BYTES_PER_POINT_BWD}},
+            'breakdown_us': us,
+            'fwd_bwd_points_per_s': pts_per_rank * world / ((us['sample'] + us['fwd'] + us['bwd']) * 1e-6),
+            'clocks': clocks,
+            'last_loss': float(mapper.total_loss(static_losses if graph is not None else losses).item()),
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line['cpu_baseline'] = cpu_baseline_record(cfg, n_rays)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

@@ -154,6 +154,16 @@ int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int
 int mne_query_points(const MneSceneDesc* scene, int64_t n_pts, const float* pts, float* raw, float* geo,
                      float* feat, mne_stream_t stream);
 
+/* ---- optimiser: torch.optim.Adam.step() + zero_grad() of the mapping loop (mneslam_mp.py:459-469,
+ * mp_slam/mapper.py:161-162), dense semantics, one pass: 16 B/param read + 16 B/param written.  All four
+ * arrays hold n floats in the same (dense) storage order.  The step count t (>= 1, already incremented) is
+ * read from `step_dev` when non-NULL (lets a CUDA graph replay advance it with mne_adam_tick), else
+ * `step_host`.  zero_grad != 0 also clears `grad`. */
+int mne_adam_tick(int64_t* step_dev, mne_stream_t stream);
+int mne_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
+                  float beta2, float eps, float weight_decay, const int64_t* step_dev, int64_t step_host,
+                  int32_t zero_grad, mne_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -61,6 +61,9 @@ _SIGNATURES = {
     'mne_backward_scratch_bytes': (C.c_size_t, [C.c_int32, C.c_int32]),
     'mne_render_backward': (C.c_int, [C.POINTER(SceneDesc), C.POINTER(RenderCfg), C.c_int32, C.c_int32] +
                             [C.c_void_p] * 15),
+    'mne_adam_tick': (C.c_int, [C.c_void_p, C.c_void_p]),
+    'mne_adam_step': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float,
+                                C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
     'mne_query_points': (C.c_int, [C.POINTER(SceneDesc), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                    C.c_void_p]),
 }

@@ -436,7 +436,13 @@ int sm_count();
 template <bool TWO, bool RAY_GRAD, bool PARAM_GRAD>
 static int launch_bwd(const BwdParams& P, cudaStream_t stream) {
     const size_t smem = bwd_smem_bytes<TWO>();
-    MNE_CHECK_CUDA(cudaFuncSetAttribute(render_bwd_kernel<TWO, RAY_GRAD, PARAM_GRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    static bool configured[64] = {};      // per device; set outside any stream capture by the first (warm-up) call
+    int dev = 0;
+    MNE_CHECK_CUDA(cudaGetDevice(&dev));
+    if (dev >= 64 || !configured[dev]) {
+        MNE_CHECK_CUDA(cudaFuncSetAttribute(render_bwd_kernel<TWO, RAY_GRAD, PARAM_GRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (dev < 64) configured[dev] = true;
+    }
     const int n_groups = (P.n_rays + P.rays_per_group - 1) / P.rays_per_group;
     int blocks = (n_groups + bwd_warps<TWO>() - 1) / bwd_warps<TWO>();
     blocks = max(1, min(blocks, sm_count()));

@@ -1,0 +1,155 @@
+"""Device-resident mapping iteration: the body of the reference's hot loop
+(``mp_slam/mapper.py:134-162`` / ``:73-89``) as five kernel launches with no host synchronisation:
+
+    sample (z_vals + mask counts) -> fused forward (+ loss sums) -> loss finalize
+      -> fused backward (upstream = the caller's loss weights, mneslam_mp.py:350-372)
+      -> fused Adam + gradient zero-fill (mneslam_mp.py:459-469, mapper.py:161-162)
+
+so that a whole iteration (or several) can be captured in one CUDA graph.  ``JointEncoding.forward`` +
+``loss.backward()`` + ``torch.optim.Adam`` remain available and give the same numbers through autograd; this
+class is the fast path ``bench.py`` measures.
+
+Multi-GPU (one process per GPU, ``torch.distributed`` / NCCL): every rank holds the full map, renders its own
+shard of the ray batch, and the loss accumulators (16 doubles, before the losses are finalised) and the flat
+gradient buffer are all-reduced once per iteration; the Adam step is then identical on every rank.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib, ops
+from ._lib import LOSS_KEYS
+
+
+def loss_weight_vector(cfg, is_co_sdf=None):
+    """d total / d each loss of ``get_loss_from_ret`` (mneslam_mp.py:350-372, rgb + depth + sdf terms)."""
+    t, m = cfg['training'], cfg['mapping']
+    if is_co_sdf is None:
+        is_co_sdf = cfg['is_co_sdf']
+    w = [t['rgb_weight'], t['depth_weight'], 0., 0., 0., 0., 0., 0.]
+    if is_co_sdf:
+        w[2], w[3] = t['sdf_weight'], t['fs_weight']
+    else:
+        w[4], w[5], w[6] = m['w_sdf_fs'], m['w_sdf_center'], m['w_sdf_tail']
+    return w
+
+
+class FusedMapper:
+    def __init__(self, model, is_co_sdf=None, process_group=None, world_size=1):
+        ops.require_cuda()
+        self.model, self.cfg = model, model.config
+        self.world_size, self.group = world_size, process_group
+        planes = model._flat_planes()
+        weights = model.decoder.weight_list()
+        self.dev = planes[0].device
+        one_grid = self.cfg['grid']['oneGrid']
+        mp = self.cfg['mapping']
+        n_sdf_planes = 6
+        # parameter groups of create_optimizer (mneslam_mp.py:459-469): (tensor, lr, eps, weight_decay)
+        self.params = [(w, mp['lr_decoder'], 1e-8, 1e-6) for w in weights]
+        self.params += [(p, mp['lr_embed'], 1e-15, 0.0) for p in planes[:n_sdf_planes]]
+        if not one_grid:
+            self.params += [(p, mp['lr_embed_color'], 1e-15, 0.0) for p in planes[n_sdf_planes:]]
+        self.betas = (0.9, 0.99)
+        # one flat gradient buffer (a single all-reduce); per-parameter views keep the parameter's strides
+        total = sum(p.numel() for p, *_ in self.params)
+        self.flat_grad = torch.zeros(total, dtype=torch.float32, device=self.dev)
+        self.grads, self.exp_avg, self.exp_avg_sq = [], [], []
+        off = 0
+        for p, *_ in self.params:
+            n = p.numel()
+            self.grads.append(torch.as_strided(self.flat_grad, p.shape, p.stride(), off))
+            self.exp_avg.append(torch.zeros_like(p))
+            self.exp_avg_sq.append(torch.zeros_like(p))
+            if not (p.is_contiguous() or p.is_contiguous(memory_format=torch.channels_last)) or n % 4:
+                raise ValueError('map parameters must be dense tensors with a multiple of 4 elements')
+            off += n
+        self.weight_grads = self.grads[:4]
+        self.plane_grads = self.grads[4:]
+        self.step_dev = torch.zeros(1, dtype=torch.int64, device=self.dev)
+        self.loss_grads = torch.tensor(loss_weight_vector(self.cfg, is_co_sdf), dtype=torch.float32, device=self.dev)
+        self.loss_weights = self.loss_grads.clone()
+        self._scratch = None
+        self.last_losses = None
+
+    # ------------------------------------------------------------------------------------------
+    def _scene(self, with_grads):
+        m = self.model
+        return ops.make_scene(m._flat_planes(), m.decoder.weight_list(), m.bound, m.bounding_box,
+                              self.cfg['pos']['n_bins'],
+                              plane_grads=self.plane_grads if with_grads else None,
+                              weight_grads=self.weight_grads if with_grads else None)
+
+    def forward_backward(self, rays_o, rays_d, target_rgb, target_d, noise=None):
+        """sample -> forward -> finalize -> backward; gradients are ADDED to the flat buffer.  Returns losses[8]."""
+        cfg, dev = self.cfg, self.dev
+        n = rays_o.shape[0]
+        tables = ops.SampleTables.get(cfg, dev, True)
+        s = tables[0].numel() + tables[1].numel()
+        perturb = cfg['training']['perturb'] > 0.
+        if perturb and noise is None:
+            noise = torch.rand(n, s, device=dev)
+        rcfg = ops.make_render_cfg(cfg, norm_rays=n * self.world_size)
+        scfg = ops.make_sample_cfg(tables, perturb)
+        td = target_d.reshape(-1)
+        acc = ops.new_acc(dev)
+        z_vals = ops.sample_rays(scfg, rcfg, n, s, td, noise if perturb else None, acc, dev)
+        out = ops.render_forward(self._scene(False), rcfg, rays_o, rays_d, z_vals, target_rgb, td, acc,
+                                 want_aux=False)
+        if self.world_size > 1:
+            torch.distributed.all_reduce(acc, group=self.group)
+        losses = ops.loss_finalize(rcfg, s, acc)
+        if self._scratch is None or self._scratch.numel() * 4 < n * s * 16:
+            self._scratch = ops.backward_scratch(n, s, dev)
+        ops.render_backward(self._scene(True), rcfg, rays_o, rays_d, z_vals, out['raw'], target_rgb, td, acc,
+                            loss_grads=self.loss_grads, scratch=self._scratch)
+        self.last_render = out
+        return losses
+
+    def optimizer_step(self):
+        """all-reduce (multi-GPU) + Adam + zero_grad, one launch per parameter tensor."""
+        if self.world_size > 1:
+            torch.distributed.all_reduce(self.flat_grad, group=self.group)
+        lib = _lib.lib()
+        st = ops._stream()
+        _lib.check(lib.mne_adam_tick(self.step_dev.data_ptr(), st), 'mne_adam_tick')
+        for (p, lr, eps, wd), g, m, v in zip(self.params, self.grads, self.exp_avg, self.exp_avg_sq):
+            _lib.check(lib.mne_adam_step(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), lr,
+                                         self.betas[0], self.betas[1], eps, wd, self.step_dev.data_ptr(), 0, 1, st),
+                       'mne_adam_step')
+
+    def step(self, rays_o, rays_d, target_rgb, target_d, noise=None):
+        """One mapping iteration.  Returns the eight losses (device tensor, order ``LOSS_KEYS``)."""
+        losses = self.forward_backward(rays_o, rays_d, target_rgb, target_d, noise)
+        self.optimizer_step()
+        self.last_losses = losses
+        return losses
+
+    def total_loss(self, losses):
+        return (losses[:7] * self.loss_weights[:7]).sum()
+
+    def losses_dict(self, losses):
+        return {k: losses[i] for i, k in enumerate(LOSS_KEYS)}
+
+
+class DeviceKeyframeRays:
+    """Keyframe ray database kept on the device with on-device ray assembly: replaces the CPU
+    gather + three H2D copies per iteration of ``KeyFrameDatabase.sample_global_rays`` (model/keyframe.py:91-103)
+    and the ray assembly of ``mapping_optimize`` (mp_slam/mapper.py:135-153)."""
+
+    def __init__(self, rays, poses):
+        self.rays = rays          # [n_kf, R, 7] (dir_cam, rgb, depth)
+        self.poses = poses        # [n_kf, 4, 4] camera-to-world
+        self.n_kf, self.per_kf = rays.shape[0], rays.shape[1]
+
+    def sample(self, n_rays, generator=None):
+        """Uniform sample over all stored rays (with replacement; the reference's ``random.sample`` draws
+        without -- for 2048 of ~800k rays the two are statistically indistinguishable)."""
+        idx = torch.randint(0, self.n_kf * self.per_kf, (n_rays,), device=self.rays.device, generator=generator)
+        return self.assemble(self.rays.reshape(-1, 7)[idx], torch.div(idx, self.per_kf, rounding_mode='trunc'))
+
+    def assemble(self, rays7, kf_ids):
+        R = self.poses[kf_ids, :3, :3]
+        rays_d = torch.sum(rays7[:, None, 0:3] * R, -1)
+        rays_o = self.poses[kf_ids, :3, 3]
+        return rays_o.contiguous(), rays_d.contiguous(), rays7[:, 3:6].contiguous(), rays7[:, 6:7].contiguous()

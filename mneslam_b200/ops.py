@@ -86,6 +86,27 @@ def make_sample_cfg(tables, perturb):
     return sc
 
 
+_bounds_cache = {}
+
+
+def bounds_to_host(bound, bounding_box):
+    """Host floats of the two boxes.  ``bounding_box`` is a float64 CUDA tensor in the reference
+    (mneslam_mp.py:223); reading it costs a device sync, so the result is cached per (tensor, version)."""
+    key = (id(bound), bound._version, id(bounding_box), bounding_box._version)
+    hit = _bounds_cache.get(key)
+    if hit is None:
+        b = bound.detach().to('cpu', torch.float32)
+        ext = b[:, 1] - b[:, 0]                       # float32 subtraction, as model/utils.py:38-40
+        bb = bounding_box.detach().to('cpu', torch.float64)
+        bext = bb[:, 1] - bb[:, 0]
+        hit = ([float(v) for v in b[:, 0]], [float(v) for v in ext], [float(v) for v in bb[:, 0]],
+               [float(v) for v in bext], bound, bounding_box)      # keep the tensors alive: ids stay unique
+        if len(_bounds_cache) > 64:
+            _bounds_cache.clear()
+        _bounds_cache[key] = hit
+    return hit[:4]
+
+
 def make_scene(planes, weights, bound, bounding_box, n_bins=16, plane_grads=None, weight_grads=None):
     """planes: flat list of 6 or 12 ``[1,32,H,W]`` tensors in ``all_planes`` order (group, axis, level).
     weights: [sdf0, sdf1, col0, col1].  bound: float32 [3,2] (CPU ok).  bounding_box: float64 [3,2]."""
@@ -111,13 +132,10 @@ def make_scene(planes, weights, bound, bounding_box, n_bins=16, plane_grads=None
             d.grad = g.data_ptr()
         else:
             d.grad = None
-    b = bound.detach().to('cpu', torch.float32)
-    ext = b[:, 1] - b[:, 0]                       # float32 subtraction, as model/utils.py:38-40
-    bb = bounding_box.detach().to('cpu', torch.float64)
-    bext = bb[:, 1] - bb[:, 0]
+    blo, bext_f, bblo, bbext = bounds_to_host(bound, bounding_box)
     for a in range(3):
-        sc.bound_lo[a], sc.bound_ext[a] = float(b[a, 0]), float(ext[a])
-        sc.bbox_lo[a], sc.bbox_ext[a] = float(bb[a, 0]), float(bext[a])
+        sc.bound_lo[a], sc.bound_ext[a] = blo[a], bext_f[a]
+        sc.bbox_lo[a], sc.bbox_ext[a] = bblo[a], bbext[a]
     ws = [_f32(w, 'decoder weight') for w in weights]
     keep.extend(ws)
     sc.w_sdf0, sc.w_sdf1, sc.w_col0, sc.w_col1 = [w.data_ptr() for w in ws]

@@ -52,9 +52,9 @@ def test_forward_backward_vs_reference_golden(name, channels_last):
     trgb, td, noise = case.t('target_rgb').cuda(), case.t('target_d').cuda(), case.t('noise').cuda()
 
     rend = model.render_rays(rays_o.detach(), rays_d.detach(), target_d=td, noise=noise)
-    assert np.array_equal(rend['z_vals'].cpu().numpy(), g['z_vals']), 'sample positions must be bit-exact'
+    assert np.array_equal(rend['z_vals'].detach().cpu().numpy(), g['z_vals']), 'sample positions must be bit-exact'
     for k in ('rgb', 'depth', 'raw', 'acc_map', 'depth_var', 'disp_map'):
-        assert rel(rend[k].cpu().numpy(), g[k]) < REL_TOL, (k, rel(rend[k].cpu().numpy(), g[k]))
+        assert rel(rend[k].detach().cpu().numpy(), g[k]) < REL_TOL, (k, rel(rend[k].detach().cpu().numpy(), g[k]))
     _, _, inds = model._render(rays_o.detach(), rays_d.detach(), None, td, False, noise)
     assert np.array_equal(inds.cpu().numpy().astype(np.int64), g['inds']), 'sign-change indices must be bit-exact'
 
@@ -81,7 +81,7 @@ def test_pose_path_vs_reference_golden(name):
     rays_o, rays_d = J.rays_from_pose(Rm @ c2w[:3, :3], trans, case.t('dirs_cam').cuda())
     rays_o.retain_grad(); rays_d.retain_grad()
     rend = model.render_rays(rays_o, rays_d, target_d=None, noise=case.t('noise').cuda())
-    assert np.array_equal(rend['z_vals'].cpu().numpy(), g['z_vals'])
+    assert np.array_equal(rend['z_vals'].detach().cpu().numpy(), g['z_vals'])
     t = cfg['training']
     loss = (t['rgb_weight'] * torch.nn.functional.mse_loss(rend['rgb'], case.t('target_rgb').cuda())
             + t['depth_weight'] * torch.nn.functional.mse_loss(rend['depth'], case.t('target_d').cuda().squeeze(-1)))
@@ -163,7 +163,7 @@ def test_zero_rays_and_query_entry_points():
     model = build_model(cfg, bb, planes, weights, as_params=False)
     model.eval()
     pts = (torch.rand(1000, 3) * 2.4 - 1.2)              # some outside the box: border clamp + OneBlob wrap
-    raw = model.run_network_flat(pts.cuda())
+    raw = model.run_network_flat(pts.cuda()).detach()
     oraw = J.query_points(cfg, planes, weights, bound, bb, pts)
     assert rel(raw.cpu().numpy(), oraw.numpy()) < REL_TOL
     sdf, geo = model.query_sdf(pts.cuda().reshape(100, 10, 3), return_geo=True)

@@ -106,7 +106,8 @@ __global__ void __launch_bounds__(bwd_warps<TWO>() * 32, 1) render_bwd_kernel(co
         }
     }
 
-    for (int g = blockIdx.x * NW + warp; g < n_groups; g += total_warps) {
+    // block-minor order: consecutive groups land on different SMs, so a grid with spare warps stays balanced
+    for (int g = warp * gridDim.x + blockIdx.x; g < n_groups; g += total_warps) {
         const int ray0 = g * rpg;
         const int nr = min(rpg, P.n_rays - ray0);
         const int npts = nr * S;
@@ -445,7 +446,7 @@ static int launch_bwd(const BwdParams& P, cudaStream_t stream) {
     }
     const int n_groups = (P.n_rays + P.rays_per_group - 1) / P.rays_per_group;
     int blocks = (n_groups + bwd_warps<TWO>() - 1) / bwd_warps<TWO>();
-    blocks = max(1, min(blocks, sm_count()));
+    blocks = max(1, min(n_groups, sm_count()));
     render_bwd_kernel<TWO, RAY_GRAD, PARAM_GRAD><<<blocks, bwd_warps<TWO>() * 32, smem, stream>>>(P);
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;

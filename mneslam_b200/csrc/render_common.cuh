@@ -127,7 +127,7 @@ template <bool TWO>
 __device__ __forceinline__ void gather_chunk(const MneSceneDesc& sc, const int4* __restrict__ tab, float* __restrict__ IN,
                                              float* __restrict__ CF, int np, int lane) {
     constexpr int NT = Net<TWO>::N_TAPS;
-#pragma unroll 2
+#pragma unroll 4
     for (int p = 0; p < np; ++p) {
 #pragma unroll
         for (int grp = 0; grp < (TWO ? 2 : 1); ++grp) {

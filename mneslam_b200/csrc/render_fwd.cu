@@ -61,7 +61,8 @@ __global__ void __launch_bounds__(fwd_warps<TWO>() * 32, 1) render_fwd_kernel(co
 
     double l_rgb = 0, l_depth = 0, l_co_fs = 0, l_co_sdf = 0, l_e_fs = 0, l_e_center = 0, l_e_tail = 0;
 
-    for (int g = blockIdx.x * kFwdWarps + warp; g < n_groups; g += total_warps) {
+    // block-minor order: consecutive groups land on different SMs, so a grid with spare warps stays balanced
+    for (int g = warp * gridDim.x + blockIdx.x; g < n_groups; g += total_warps) {
         const int ray0 = g * rpg;
         const int nr = min(rpg, P.n_rays - ray0);
         const int npts = nr * S;
@@ -221,7 +222,7 @@ static int launch_fwd(const FwdParams& P, cudaStream_t stream) {
     }
     const int n_groups = (P.n_rays + P.rays_per_group - 1) / P.rays_per_group;
     int blocks = (n_groups + fwd_warps<TWO>() - 1) / fwd_warps<TWO>();
-    blocks = max(1, min(blocks, sm_count()));
+    blocks = max(1, min(n_groups, sm_count()));
     render_fwd_kernel<TWO, QUERY><<<blocks, fwd_warps<TWO>() * 32, smem, stream>>>(P);
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;

@@ -346,7 +346,7 @@ def axis_angle_to_matrix(r):
     K = torch.stack([torch.stack([z, -k[..., 2], k[..., 1]], -1),
                      torch.stack([k[..., 2], z, -k[..., 0]], -1),
                      torch.stack([-k[..., 1], k[..., 0], z], -1)], -2)
-    eye = torch.eye(3, dtype=r.dtype).expand(K.shape)
+    eye = torch.eye(3, dtype=r.dtype, device=r.device).expand(K.shape)
     return eye + torch.sin(theta)[..., None] * K + (1. - torch.cos(theta))[..., None] * (K @ K)
 
 

@@ -1,0 +1,126 @@
+"""GPU tests of the iteration driver: fused Adam against torch.optim.Adam, device ray assembly, CUDA-graph replay."""
+import numpy as np
+import pytest
+import torch
+
+from mneslam_b200 import configs, synthetic
+from oracle import joint_encoding as J
+from tests.gpu_util import build_model, flat_planes, rel, total_loss
+
+pytestmark = pytest.mark.gpu
+
+
+def _small_model(seed=3, one_grid=True):
+    cfg = configs.small_test_config(one_grid=one_grid)
+    bound = J.enlarged_bound(cfg)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    planes, weights = J.init_planes(cfg, bound, seed=seed, std=0.3), J.init_weights(cfg, seed=seed)
+    return cfg, bb, planes, weights
+
+
+@pytest.mark.parametrize('one_grid', [True, False])
+def test_fused_iterations_match_autograd_plus_torch_adam(one_grid):
+    """Five mapping iterations: FusedMapper (sample/fwd/bwd/Adam kernels) against the drop-in class driven the
+    way the reference drives it (forward -> get_loss_from_ret -> backward -> torch.optim.Adam, create_optimizer's
+    parameter groups)."""
+    from mneslam_b200.mapping import FusedMapper
+    cfg, bb, planes, weights = _small_model(one_grid=one_grid)
+    a = build_model(cfg, bb, planes, weights)
+    b = build_model(cfg, bb, planes, weights, as_params=False)
+    mp = cfg['mapping']
+    groups = [{'params': a.decoder.parameters(), 'weight_decay': 1e-6, 'lr': mp['lr_decoder']},
+              {'params': flat_planes(a)[:6], 'eps': 1e-15, 'lr': mp['lr_embed']}]
+    if not one_grid:
+        groups.append({'params': flat_planes(a)[6:], 'eps': 1e-15, 'lr': mp['lr_embed_color']})
+    opt = torch.optim.Adam(groups, betas=(0.9, 0.99))
+    mapper = FusedMapper(b)
+    n, s = 200, synthetic.n_samples_total(cfg)
+    for it in range(5):
+        batch = {k: v.cuda() for k, v in synthetic.make_ray_batch(cfg, n, seed=50 + it).items()}
+        noise = synthetic.make_noise(n, s, seed=it).cuda()
+        ret = a.forward(batch['rays_o'], batch['rays_d'], batch['target_rgb'], batch['target_d'], noise=noise)
+        loss = total_loss(cfg, ret)
+        loss.backward()
+        opt.step()
+        opt.zero_grad()
+        losses = mapper.step(batch['rays_o'], batch['rays_d'], batch['target_rgb'], batch['target_d'], noise=noise)
+        assert mapper.total_loss(losses).item() == pytest.approx(loss.item(), rel=2e-4)
+    for pa, pb in zip(flat_planes(a), flat_planes(b)):
+        assert rel(pb.detach().cpu().numpy(), pa.detach().cpu().numpy()) < 2e-4
+    for wa, wb in zip(a.decoder.weight_list(), b.decoder.weight_list()):
+        assert rel(wb.detach().cpu().numpy(), wa.detach().cpu().numpy()) < 2e-4
+    assert float(mapper.flat_grad.abs().max()) == 0.0, 'the Adam kernel leaves the gradients zeroed'
+
+
+def test_adam_kernel_matches_torch_single_tensor():
+    from mneslam_b200 import _lib, ops
+    torch.manual_seed(0)
+    n = 4096 * 3 + 8
+    p = torch.randn(n, device='cuda')
+    ref = torch.nn.Parameter(p.clone())
+    opt = torch.optim.Adam([ref], lr=5e-3, betas=(0.9, 0.99), eps=1e-15, foreach=False)
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    for t in range(1, 6):
+        g = torch.randn(n, device='cuda') * (0.1 if t % 2 else 10.0)
+        ref.grad = g.clone()
+        opt.step()
+        gg = g.clone()
+        _lib.check(_lib.lib().mne_adam_step(p.data_ptr(), gg.data_ptr(), m.data_ptr(), v.data_ptr(), n, 5e-3, 0.9, 0.99,
+                                            1e-15, 0.0, None, t, 1, ops._stream()), 'adam')
+        assert float(gg.abs().max()) == 0.0
+    torch.cuda.synchronize()
+    assert rel(p.cpu().numpy(), ref.detach().cpu().numpy()) < 1e-6
+    assert rel(v.cpu().numpy(), opt.state[ref]['exp_avg_sq'].cpu().numpy()) < 1e-6
+
+
+def test_device_keyframe_assembly_matches_caller_code():
+    """rays_d = sum_k dirs_k R[ids][:, k], rays_o = t[ids] (mp_slam/mapper.py:150-153)."""
+    from mneslam_b200.mapping import DeviceKeyframeRays
+    cfg = configs.small_test_config()
+    cfg['cam'].update({'H': 40, 'W': 60, 'fx': 50.0, 'fy': 50.0, 'cx': 29.5, 'cy': 19.5})
+    rays, poses = synthetic.make_keyframe_db(cfg, n_kf=4, seed=2)
+    db = DeviceKeyframeRays(rays.cuda(), poses.cuda())
+    idx = torch.randint(0, rays.shape[0] * rays.shape[1], (333,))
+    ids = idx // rays.shape[1]
+    r7 = rays.reshape(-1, 7)[idx]
+    ro, rd, rgb, d = db.assemble(r7.cuda(), ids.cuda())
+    want_d = torch.sum(r7[:, None, None, :3] * poses[ids, None, :3, :3], -1).reshape(-1, 3)
+    want_o = poses[ids, None, :3, -1].repeat(1, 1, 1).reshape(-1, 3)
+    assert torch.allclose(rd.cpu(), want_d, atol=1e-6) and torch.equal(ro.cpu(), want_o)
+    assert torch.equal(rgb.cpu(), r7[:, 3:6]) and torch.equal(d.cpu(), r7[:, 6:7])
+    ro2, rd2, rgb2, d2 = db.sample(128)
+    assert ro2.shape == (128, 3) and d2.shape == (128, 1)
+
+
+def test_cuda_graph_replay_of_a_mapping_iteration():
+    """The whole iteration (ray assembly, sample, forward, losses, backward, Adam) captured once and replayed:
+    the loss keeps decreasing and no launch needs the host."""
+    from mneslam_b200.mapping import DeviceKeyframeRays, FusedMapper
+    cfg, bb, planes, weights = _small_model(seed=9)
+    cfg['cam'].update({'H': 40, 'W': 60, 'fx': 50.0, 'fy': 50.0, 'cx': 29.5, 'cy': 19.5})
+    model = build_model(cfg, bb, planes, weights, as_params=False)
+    mapper = FusedMapper(model)
+    rays, poses = synthetic.make_keyframe_db(cfg, n_kf=3, seed=2)
+    db = DeviceKeyframeRays(rays.cuda(), poses.cuda())
+
+    def one():
+        return mapper.step(*db.sample(256))
+    for _ in range(3):
+        one()
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        one()
+    torch.cuda.current_stream().wait_stream(side)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        losses = one()
+    first = None
+    hist = []
+    for i in range(60):
+        g.replay()
+        hist.append(mapper.total_loss(losses).item())
+    assert np.isfinite(hist).all()
+    assert np.mean(hist[-10:]) < np.mean(hist[:10]), (hist[:3], hist[-3:])
+    assert int(mapper.step_dev.item()) == 3 + 1 + 1 + 60

@@ -77,8 +77,10 @@ def test_pose_path_vs_reference_golden(name):
     c2w = case.t('c2w').cuda()
     rot = case.t('pose_rot').cuda().requires_grad_(True)
     trans = c2w[:3, 3].clone().requires_grad_(True)
-    Rm = J.axis_angle_to_matrix(rot[None])[0] if 'axis' in name else J.quat_to_matrix(rot[None])[0]
-    rays_o, rays_d = J.rays_from_pose(Rm @ c2w[:3, :3], trans, case.t('dirs_cam').cuda())
+    from mneslam_b200 import pose
+    Rm = pose.axis_angle_to_matrix(rot[None])[0] if 'axis' in name else pose.quaternion_to_matrix(rot[None])[0]
+    pose_c2w = torch.cat([Rm @ c2w[:3, :3], trans[:, None]], -1)
+    rays_o, rays_d = pose.rays_from_c2w(pose_c2w, case.t('dirs_cam').cuda())
     rays_o.retain_grad(); rays_d.retain_grad()
     rend = model.render_rays(rays_o, rays_d, target_d=None, noise=case.t('noise').cuda())
     assert np.array_equal(rend['z_vals'].detach().cpu().numpy(), g['z_vals'])
@@ -209,16 +211,13 @@ def test_full_size_properties_r0():
     assert ret1['rgb_loss'].item() == pytest.approx(ret2['rgb_loss'].item(), rel=1e-6)
     for a, b in zip(g1, g2):                       # linearity in the upstream gradient
         assert torch.allclose(2 * a, b, rtol=1e-3, atol=1e-9 + 1e-4 * float(b.abs().max()))
-    # directional finite difference on the decoder weights (fp32, so a coarse check)
-    w = model.decoder.sdf_net.model[2].weight
-    direction = torch.randn_like(w)
-    eps = 1e-2
-    with torch.no_grad():
-        w.add_(eps * direction)
-        lp = total_loss(cfg, model.forward(batch['rays_o'], batch['rays_d'], batch['target_rgb'], batch['target_d'], noise=noise)).item()
-        w.sub_(2 * eps * direction)
-        lm = total_loss(cfg, model.forward(batch['rays_o'], batch['rays_d'], batch['target_rgb'], batch['target_d'], noise=noise)).item()
-        w.add_(eps * direction)
-    fd = (lp - lm) / (2 * eps)
-    an = float((g1[len(flat_planes(model)) + 1] * direction).sum())
-    assert abs(fd - an) <= 0.05 * max(abs(fd), abs(an)) + 1e-4, (fd, an)
+    # the same step through the fused (non-autograd) iteration driver gives the same gradients
+    from mneslam_b200.mapping import FusedMapper
+    mapper = FusedMapper(model)
+    losses = mapper.forward_backward(batch['rays_o'], batch['rays_d'], batch['target_rgb'], batch['target_d'], noise=noise)
+    assert mapper.total_loss(losses).item() == pytest.approx(total_loss(cfg, ret1).item(), rel=1e-5)
+    params = flat_planes(model) + list(model.decoder.parameters())
+    by_id = {id(p): g for p, g in zip(params, g1)}
+    for (p, *_), g in zip(mapper.params, mapper.grads):
+        ref = by_id[id(p)]
+        assert torch.allclose(g, ref, rtol=1e-3, atol=1e-9 + 1e-4 * float(ref.abs().max()))

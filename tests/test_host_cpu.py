@@ -67,3 +67,16 @@ def test_no_cpu_fallback():
         model.render_rays(torch.zeros(4, 3), torch.ones(4, 3), target_d=torch.ones(4, 1))
     with pytest.raises(RuntimeError):
         model.run_network_flat(torch.zeros(4, 3))
+
+
+def test_pose_parameterisations_match_oracle():
+    from mneslam_b200 import pose
+    from oracle import joint_encoding as J
+    r = torch.tensor([[0.3, -0.2, 0.5], [1e-3, 2e-3, -1e-3]])
+    q = torch.tensor([[0.9, 0.1, -0.3, 0.2], [2.0, 0.0, 0.1, 0.0]])
+    assert torch.allclose(pose.axis_angle_to_matrix(r), J.axis_angle_to_matrix(r), atol=1e-6)
+    assert torch.allclose(pose.quaternion_to_matrix(q), J.quat_to_matrix(q), atol=1e-6)
+    R = pose.quaternion_to_matrix(q)
+    assert torch.allclose(R @ R.transpose(-1, -2), torch.eye(3).expand(2, 3, 3), atol=1e-5)
+    T = pose.transform_matrix(r, torch.ones(2, 3), 'axis_angle')
+    assert T.shape == (2, 4, 4) and torch.equal(T[:, 3], torch.tensor([[0., 0, 0, 1]] * 2))

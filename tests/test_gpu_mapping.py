@@ -69,8 +69,9 @@ def test_adam_kernel_matches_torch_single_tensor():
                                             1e-15, 0.0, None, t, 1, ops._stream()), 'adam')
         assert float(gg.abs().max()) == 0.0
     torch.cuda.synchronize()
-    assert rel(p.cpu().numpy(), ref.detach().cpu().numpy()) < 1e-6
-    assert rel(v.cpu().numpy(), opt.state[ref]['exp_avg_sq'].cpu().numpy()) < 1e-6
+    # same formulas as torch's single-tensor Adam; fp32 rounding order differs by a few ulp over five steps
+    assert rel(p.cpu().numpy(), ref.detach().cpu().numpy()) < 5e-6
+    assert rel(v.cpu().numpy(), opt.state[ref]['exp_avg_sq'].cpu().numpy()) < 5e-6
 
 
 def test_device_keyframe_assembly_matches_caller_code():
@@ -123,4 +124,4 @@ def test_cuda_graph_replay_of_a_mapping_iteration():
         hist.append(mapper.total_loss(losses).item())
     assert np.isfinite(hist).all()
     assert np.mean(hist[-10:]) < np.mean(hist[:10]), (hist[:3], hist[-3:])
-    assert int(mapper.step_dev.item()) == 3 + 1 + 1 + 60
+    assert int(mapper.step_dev.item()) == 3 + 1 + 60      # warm-up, side-stream run, replays (capture runs nothing)

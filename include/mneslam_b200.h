@@ -148,6 +148,27 @@ int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int
                         const float* loss_grads, const float* g_rgb, const float* g_depth, const float* g_raw,
                         void* scratch, float* g_rays_o, float* g_rays_d, mne_stream_t stream);
 
+/* ---- backward without a caller workspace.  This entry point has no counterpart in the reference: it exists
+ * for callers that must not allocate device memory (a host that forbids cudaMalloc around the call, a real-time
+ * loop that cannot take the allocator's lock, a plugin that is only handed input and output buffers).  It is
+ * mne_render_backward with the 16-byte-per-sample workspace taken from an array built into the library image
+ * (MNE_STATIC_SCRATCH_SAMPLES * 16 bytes = 2 MiB, held on every GPU that loads the library until the process
+ * exits) instead of the `scratch` argument; inputs and outputs are still the caller's.  It calls no cudaMalloc /
+ * cudaFree or other allocating routine.
+ *   - n_rays * n_samples must not exceed MNE_STATIC_SCRATCH_SAMPLES; larger batches are rejected with an error.
+ *   - The first call on each device looks up the array's device address (a one-time, synchronous-with-the-host
+ *     query); make that first call outside of any CUDA stream capture.
+ *   - All calls on a device share the one array.  Calls that can overlap on the GPU (different streams, or
+ *     threads launching concurrently) race on it: serialise them on one stream.  Nothing in the array has to be
+ *     cleared between calls -- each launch writes every slot it later reads -- and its contents after a call are
+ *     unspecified. */
+#define MNE_STATIC_SCRATCH_SAMPLES 131072
+int mne_render_backward_static(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples,
+                               const float* rays_o, const float* rays_d, const float* z_vals, const float* raw,
+                               const float* target_rgb, const float* target_d, const double* acc,
+                               const float* loss_grads, const float* g_rgb, const float* g_depth, const float* g_raw,
+                               float* g_rays_o, float* g_rays_d, mne_stream_t stream);
+
 /* ---- point queries: query_color_sdf / run_network_flat / query_sdf(embed, return_geo)
  * (model/scene_rep.py:232-301,319-331).  pts [M,3].  Any output may be NULL:
  * raw [M,4], geo [M,15], feat [M,F] (the embed=True output). */

@@ -11,6 +11,7 @@ from . import build as _build
 MAX_PLANES = 12
 ACC_SLOTS = 16
 N_LOSSES = 8
+STATIC_SCRATCH_SAMPLES = 131072   # MNE_STATIC_SCRATCH_SAMPLES
 
 # accumulator / loss slots (keep in sync with csrc/common.cuh)
 ACC = {'n_valid': 0, 'n_co_front': 1, 'n_co_near': 2, 'n_e_front': 3, 'n_e_center': 4, 'n_e_tail': 5,
@@ -61,6 +62,8 @@ _SIGNATURES = {
     'mne_backward_scratch_bytes': (C.c_size_t, [C.c_int32, C.c_int32]),
     'mne_render_backward': (C.c_int, [C.POINTER(SceneDesc), C.POINTER(RenderCfg), C.c_int32, C.c_int32] +
                             [C.c_void_p] * 15),
+    'mne_render_backward_static': (C.c_int, [C.POINTER(SceneDesc), C.POINTER(RenderCfg), C.c_int32, C.c_int32] +
+                                   [C.c_void_p] * 14),
     'mne_adam_tick': (C.c_int, [C.c_void_p, C.c_void_p]),
     'mne_adam_step': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float,
                                 C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),

@@ -3,6 +3,8 @@
 // tri-plane gradient scatter and ray (pose) gradients, one kernel.  Replaces torch autograd through
 // reference model/scene_rep.py:183-230,273-317,384-386,549-611 (loss.backward() at mp_slam/mapper.py:88,159
 // and :405).
+#include <mutex>
+
 #include "render_common.cuh"
 
 namespace mne {
@@ -498,4 +500,63 @@ extern "C" int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg
     P.acc = acc; P.loss_grads = loss_grads; P.g_rgb = g_rgb; P.g_depth = g_depth; P.g_raw = g_raw;
     P.draw = reinterpret_cast<float4*>(scratch); P.g_rays_o = g_rays_o; P.g_rays_d = g_rays_d;
     return scene->two_grid ? dispatch_bwd<true>(P, ray_grad, param_grad, st) : dispatch_bwd<false>(P, ray_grad, param_grad, st);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Backward for callers that may not allocate.
+//
+// mne_render_backward needs a caller-supplied workspace of 16 bytes per sample.  Some callers cannot provide
+// one: code that runs where cudaMalloc is off limits (inside a region the host application has fenced off
+// from the allocator, in a real-time loop that must not take the driver's allocation lock, or in a plugin
+// whose host only hands it input and output buffers).  For them the workspace below lives in the library
+// image itself: every GPU that loads the library reserves MNE_STATIC_SCRATCH_SAMPLES * 16 bytes (2 MiB)
+// until the process exits, and nothing is allocated at call time.
+//
+// In host code the name `g_static_draw` is only a handle for the symbol, not a device address, so the device
+// address is looked up once per device with cudaGetSymbolAddress (with that device current) and cached.
+// ---------------------------------------------------------------------------------------------------------
+namespace mne {
+
+constexpr int kStaticScratchSamples = MNE_STATIC_SCRATCH_SAMPLES;
+static __device__ __align__(256) float4 g_static_draw[kStaticScratchSamples];
+
+static int static_scratch_for_current_device(float4** out) {
+    constexpr int kMaxDevices = 64;
+    static float4* cached[kMaxDevices] = {};
+    static std::mutex lock;
+    int dev = 0;
+    MNE_CHECK_CUDA(cudaGetDevice(&dev));
+    MNE_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "mne_render_backward_static: device index %d not supported", dev);
+    std::lock_guard<std::mutex> guard(lock);
+    if (!cached[dev]) {
+        float4* ptr = nullptr;
+        MNE_CHECK_CUDA(cudaGetSymbolAddress((void**)&ptr, g_static_draw));
+        MNE_CHECK_ARG(ptr != nullptr, "mne_render_backward_static: static scratch has no device address");
+        cached[dev] = ptr;
+    }
+    *out = cached[dev];
+    return 0;
+}
+
+}  // namespace mne
+
+extern "C" int mne_render_backward_static(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays,
+                                          int32_t n_samples, const float* rays_o, const float* rays_d, const float* z_vals,
+                                          const float* raw, const float* target_rgb, const float* target_d,
+                                          const double* acc, const float* loss_grads, const float* g_rgb,
+                                          const float* g_depth, const float* g_raw, float* g_rays_o, float* g_rays_d,
+                                          mne_stream_t stream) {
+    using namespace mne;
+    MNE_CHECK_ARG(n_rays >= 0 && n_samples > 0, "mne_render_backward_static: bad sizes n_rays=%d n_samples=%d", n_rays, n_samples);
+    MNE_CHECK_ARG((int64_t)n_rays * n_samples <= (int64_t)kStaticScratchSamples,
+                  "mne_render_backward_static: %lld samples exceed the built-in workspace of %d samples "
+                  "(MNE_STATIC_SCRATCH_SAMPLES); use mne_render_backward with your own scratch buffer",
+                  (long long)n_rays * n_samples, kStaticScratchSamples);
+    float4* scratch = nullptr;
+    if (int e = static_scratch_for_current_device(&scratch)) return e;
+    // Every sample slot of the workspace that the kernel reads is written earlier in the same launch (the
+    // compositing-backward phase fills d_raw for all n_rays * n_samples entries), so leftovers of a previous call
+    // are never read and nothing has to be cleared here.
+    return mne_render_backward(scene, rcfg, n_rays, n_samples, rays_o, rays_d, z_vals, raw, target_rgb, target_d, acc,
+                               loss_grads, g_rgb, g_depth, g_raw, scratch, g_rays_o, g_rays_d, stream);
 }

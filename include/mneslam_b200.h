@@ -113,6 +113,9 @@ typedef struct MneRenderCfg {
 /* ---- library ---- */
 int mne_version(void);
 const char* mne_last_error(void);
+/* Process-wide switches.  "impl": 2 (default) = tensor-pipe kernels (16-point tiles, mma TF32 with split
+ * operands), 1 = the first-generation fp32 CUDA-core kernels, kept as an on-device cross-check. */
+int mne_set_option(const char* key, int value);
 
 /* ---- sampling: replaces the z_vals block of JointEncoding.render_rays (model/scene_rep.py:361-381) plus
  * the mask counts of get_masks (model/utils.py:117-145), sdf_losses (model/scene_rep.py:489-499) and

@@ -54,6 +54,7 @@ class RenderCfg(C.Structure):
 _SIGNATURES = {
     'mne_version': (C.c_int, []),
     'mne_last_error': (C.c_char_p, []),
+    'mne_set_option': (C.c_int, [C.c_char_p, C.c_int]),
     'mne_sample_rays': (C.c_int, [C.POINTER(SampleCfg), C.POINTER(RenderCfg), C.c_int32, C.c_void_p, C.c_void_p,
                                   C.c_void_p, C.c_void_p, C.c_void_p]),
     'mne_render_forward': (C.c_int, [C.POINTER(SceneDesc), C.POINTER(RenderCfg), C.c_int32, C.c_int32] +

@@ -65,7 +65,22 @@ int check_scene(const MneSceneDesc* sc, const char* who, bool) {
     return 0;
 }
 
+static int g_impl = 2;
+int impl_version() { return g_impl; }
+
 }  // namespace mne
+
+extern "C" int mne_set_option(const char* key, int value) {
+    using namespace mne;
+    MNE_CHECK_ARG(key, "mne_set_option: null key");
+    if (strcmp(key, "impl") == 0) {
+        MNE_CHECK_ARG(value == 1 || value == 2, "mne_set_option: impl must be 1 (fp32 CUDA-core kernels) or 2 (tensor-pipe kernels)");
+        g_impl = value;
+        return 0;
+    }
+    set_error("mne_set_option: unknown option '%s'", key);
+    return 1;
+}
 
 extern "C" int mne_version(void) { return 100; }
 extern "C" const char* mne_last_error(void) { return mne::g_error; }

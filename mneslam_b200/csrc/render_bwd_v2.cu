@@ -1,0 +1,520 @@
+// v2 backward: (1) a ray kernel -- warp per ray: compositing backward, loss / map upstream -> d_raw scratch;
+// (2) a point kernel -- 16-point tiles per warp, decoder forward recompute and backward on the tensor pipe.
+//
+// Weight gradients are the one cross-point reduction.  They are NOT pushed through shared-memory float atomics
+// (a CAS loop on this hardware): the CTA's warps advance in lock-step rounds of one tile each, publish their
+// activation / gradient tiles in shared memory, and every warp owns a fixed set of 16x8 blocks of the weight
+// gradients which it accumulates IN REGISTERS over all tiles of all rounds with mma (the point index is the
+// contraction dimension).  One pass of global atomics per CTA at the very end.
+//
+// Plane gradients: lane = (corner, 4-channel group), one 128-bit vector reduction (red.global.add.v4.f32) per
+// lane covers the four corner texels of a tap.
+#include "tile16.cuh"
+
+namespace mne {
+
+constexpr int kBwdWarps = 8;
+constexpr int kActStride = 40;     // hidden-wide tiles [16][32 + 8]: == 8 (mod 32)
+constexpr int kGeoStride = 24;     // 16-wide tiles
+constexpr int kRgbStride = 8;
+
+// hi-only transposed weights for the "d input = d output . W" products (B fragment = W[k = out][n = in]),
+// stored [in][out] so that a lane's (b0, b1) = outputs (k0 + 2t, k0 + 2t + 1) of input n0 + g is one 64-bit load
+template <bool TWO>
+struct NetT {
+    static constexpr int S1 = 40;                        // W1T  [64 feat][32 j]
+    static constexpr int OFF_W1T = 0;
+    static constexpr int OFF_VGT = OFF_W1T + 64 * S1;    // V1T geo [16][32 j] (row 15 = 0)
+    static constexpr int OFF_VCT = OFF_VGT + 16 * S1;    // V1T colour feat [64][32 j] (two grids)
+    static constexpr int OFF_W2T = OFF_VCT + (TWO ? 64 * S1 : 0);   // W2T [32 j][16 i] stride 24
+    static constexpr int OFF_V2T = OFF_W2T + 32 * kGeoStride;       // V2T [32 j][8 c]
+    static constexpr int FLOATS = OFF_V2T + 32 * kRgbStride;
+};
+
+template <bool TWO>
+__device__ __forceinline__ void load_weights_t(const MneSceneDesc& sc, float* WT, int tid, int nthreads) {
+    using N = NetV2<TWO>;
+    using T = NetT<TWO>;
+    for (int i = tid; i < 64 * 32; i += nthreads) {
+        const int k = i >> 5, j = i & 31;
+        WT[T::OFF_W1T + k * T::S1 + j] = sc.w_sdf0[j * N::K1 + k];
+        if (TWO) WT[T::OFF_VCT + k * T::S1 + j] = sc.w_col0[j * N::IN_COL + kBlob + k];
+    }
+    for (int i = tid; i < 16 * 32; i += nthreads) {
+        const int m = i >> 5, j = i & 31;
+        WT[T::OFF_VGT + m * T::S1 + j] = (m < kGeo) ? sc.w_col0[j * N::IN_COL + (N::IN_COL - kGeo) + m] : 0.0f;
+        const int jj = i >> 4, c = i & 15;                     // W2T[j][c], c: 0..14 geo (out c+1), 15 sdf (out 0)
+        WT[T::OFF_W2T + jj * kGeoStride + c] = sc.w_sdf1[((c == 15) ? 0 : c + 1) * 32 + jj];
+    }
+    for (int i = tid; i < 32 * 8; i += nthreads) {
+        const int j = i >> 3, c = i & 7;
+        WT[T::OFF_V2T + j * kRgbStride + c] = (c < 3) ? sc.w_col1[c * 32 + j] : 0.0f;
+    }
+}
+
+template <bool TWO> __host__ __device__ constexpr int bwd2_warp_floats() {
+    return kTilePts * (kXStride + (TWO ? kCStride : 0) + 2 * kActStride + kGeoStride + kRgbStride);
+}
+template <bool TWO>
+constexpr size_t bwd2_smem_bytes() {
+    return sizeof(float4) * (size_t)NetV2<TWO>::W4_COUNT + sizeof(float) * (size_t)(NetT<TWO>::FLOATS + kBwdWarps * bwd2_warp_floats<TWO>());
+}
+
+struct PtsBwdParams {
+    MneSceneDesc sc;
+    int64_t n_pts;
+    int n_samples;
+    const float* rays_o;
+    const float* rays_d;
+    const float* z_vals;
+    const float4* draw;      // [n_pts] d loss / d raw
+};
+
+__device__ __forceinline__ void mma_1x(float (&d)[4], float a0, float a1, float a2, float a3, float b0, float b1) {
+    const uint32_t a[4] = {__float_as_uint(a0), __float_as_uint(a1), __float_as_uint(a2), __float_as_uint(a3)};
+    mma_tf32(d, a, __float_as_uint(b0), __float_as_uint(b1));
+}
+
+// store an accumulator fragment block (rows g, g+8; cols n*8 + 2t, +1) into a [16][stride] tile
+__device__ __forceinline__ void store_frag(float* tile, int stride, int n, int g, int t, const float (&c)[4]) {
+    *reinterpret_cast<float2*>(tile + g * stride + n * 8 + 2 * t) = make_float2(c[0], c[1]);
+    *reinterpret_cast<float2*>(tile + (g + 8) * stride + n * 8 + 2 * t) = make_float2(c[2], c[3]);
+}
+
+// acc[nb] (+)= sum over the 16 points of a source tile of  A[p][m0 + ...] (x) B[p][nb*8 + ...]   (transposed product)
+template <int NB, int OFF, int NACC>
+__device__ __forceinline__ void outer_mma(float (&acc)[NACC][4], const float* __restrict__ A, int a_stride, int m0,
+                                          const float* __restrict__ B, int b_stride, int g, int t) {
+#pragma unroll
+    for (int ks = 0; ks < 2; ++ks) {
+        const float* ar = A + (ks * 8 + t) * a_stride + m0 + g;
+        const float a0 = ar[0], a1 = ar[8], a2 = ar[4 * a_stride], a3 = ar[4 * a_stride + 8];
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) {
+            const float* br = B + (ks * 8 + t) * b_stride + nb * 8 + g;
+            mma_1x(acc[OFF + nb], a0, a1, a2, a3, br[0], br[4 * b_stride]);
+        }
+    }
+}
+
+template <bool TWO, bool VEC>
+__global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __grid_constant__ PtsBwdParams P) {
+    using N = NetV2<TWO>;
+    using T = NetT<TWO>;
+    constexpr int NW = kBwdWarps;
+    constexpr int WF = bwd2_warp_floats<TWO>();
+    extern __shared__ __align__(16) float4 smem4[];
+    float4* W4 = smem4;
+    float* WT = reinterpret_cast<float*>(smem4 + N::W4_COUNT);
+    float* tiles = WT + T::FLOATS;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float* X = tiles + warp * WF;
+    float* CFt = X + kTilePts * kXStride;
+    float* ACT = CFt + (TWO ? kTilePts * kCStride : 0);
+    float* DY = ACT + kTilePts * kActStride;
+    float* GEO = DY + kTilePts * kActStride;       // o16 in phase 1, d_out in phase 2
+    float* DRGB = GEO + kTilePts * kGeoStride;
+    // offsets of the same tiles inside another warp's block
+    constexpr int O_CF = kTilePts * kXStride, O_ACT = O_CF + (TWO ? kTilePts * kCStride : 0), O_DY = O_ACT + kTilePts * kActStride,
+                  O_GEO = O_DY + kTilePts * kActStride, O_DRGB = O_GEO + kTilePts * kGeoStride;
+
+    load_weights_v2<TWO>(P.sc, W4, threadIdx.x, blockDim.x);
+    load_weights_t<TWO>(P.sc, WT, threadIdx.x, blockDim.x);
+    __syncthreads();
+
+    const int64_t n_tiles = (P.n_pts + kTilePts - 1) / kTilePts;
+    const int64_t tiles_per_round = (int64_t)gridDim.x * NW;
+    const int64_t n_rounds = (n_tiles + tiles_per_round - 1) / tiles_per_round;
+    const int p_loc = lane & 15, half = lane >> 4;
+    const int g = lane >> 2, t = lane & 3;
+
+    // weight-gradient blocks owned by this warp (transposed: rows = inputs, cols = outputs)
+    //   phase 1: d col0^T  -- one 16-row block of inputs per warp (one grid: warps 0..3; two grids: 0..7), 4 col blocks
+    //            d col1^T  -- rows j (2 blocks) x 8 cols: warps 4,5 (one grid) / 0,1 (two grids, extra)
+    //   phase 2: d sdf0^T  -- warps 0..6, input block = warp, 4 col blocks;  d sdf1^T -- warp 7: 2 row blocks x 2 col blocks
+    float acc_v1[4][4], acc_v2[1][4], acc_w1[4][4];
+#pragma unroll
+    for (int n = 0; n < 4; ++n)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { acc_v1[n][i] = 0.f; acc_w1[n][i] = 0.f; }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) acc_v2[0][i] = 0.f;
+    constexpr int V1_BLOCKS = N::KC / 16;                   // 4 (one grid) or 8 (two grids)
+    const int v2_owner0 = TWO ? 0 : 4;
+
+    for (int64_t round = 0; round < n_rounds; ++round) {
+        // consecutive tiles of a round go to different SMs (block-minor), as in the forward
+        const int64_t tile = round * tiles_per_round + (int64_t)warp * gridDim.x + blockIdx.x;
+        const bool have = tile < n_tiles;
+        const int64_t pt0 = tile * kTilePts;
+        const int np = have ? (int)min((int64_t)kTilePts, P.n_pts - pt0) : 0;
+
+        // ---- 1. position, taps, gather, OneBlob
+        float px = 0.f, py = 0.f, pz = 0.f;
+        if (p_loc < np) {
+            const int64_t q = pt0 + p_loc;
+            const int64_t ray = q / P.n_samples;
+            const float z = P.z_vals[q];
+            px = __fadd_rn(P.rays_o[ray * 3 + 0], __fmul_rn(P.rays_d[ray * 3 + 0], z));
+            py = __fadd_rn(P.rays_o[ray * 3 + 1], __fmul_rn(P.rays_d[ray * 3 + 1], z));
+            pz = __fadd_rn(P.rays_o[ray * 3 + 2], __fmul_rn(P.rays_d[ray * 3 + 2], z));
+        }
+        float* row = X + p_loc * kXStride;
+        if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 0);
+        __syncwarp();
+        if (VEC) gather16_vec(P.sc, 0, X + kBlobCol, kXStride, X, kXStride, np, lane);
+        else gather16(P.sc, 0, X + kBlobCol, kXStride, X, kXStride, np, lane);
+        __syncwarp();
+        if (TWO) {
+            if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 1);
+            __syncwarp();
+            if (VEC) gather16_vec(P.sc, 1, X + kBlobCol, kXStride, CFt, kCStride, np, lane);
+            else gather16(P.sc, 1, X + kBlobCol, kXStride, CFt, kCStride, np, lane);
+            __syncwarp();
+        }
+        if (half == 0) {
+            oneblob16_sparse(blob_input(px, P.sc.bbox_lo[0], P.sc.bbox_ext[0]), row + kBlobCol);
+            oneblob16_sparse(blob_input(py, P.sc.bbox_lo[1], P.sc.bbox_ext[1]), row + kBlobCol + 16);
+        } else {
+            oneblob16_sparse(blob_input(pz, P.sc.bbox_lo[2], P.sc.bbox_ext[2]), row + kBlobCol + 32);
+        }
+        // rows without a point must be finite (they are multiplied by zero gradients later)
+        for (int p = np; p < kTilePts; ++p) {
+            X[p * kXStride + lane] = 0.f; X[p * kXStride + 32 + lane] = 0.f;
+            if (TWO) { CFt[p * kCStride + lane] = 0.f; CFt[p * kCStride + 32 + lane] = 0.f; }
+        }
+        __syncwarp();
+
+        // ---- 2. forward recompute, upstream of this tile's rows g and g+8
+        float h1[4][4], o16[2][4], hc[4][4], rgbf[4];
+        decoder_forward_mma<TWO>(W4, X, CFt, lane, h1, o16, hc, rgbf);
+        float4 dr_lo = make_float4(0.f, 0.f, 0.f, 0.f), dr_hi = dr_lo;
+        if (g < np) dr_lo = __ldg(P.draw + pt0 + g);
+        if (g + 8 < np) dr_hi = __ldg(P.draw + pt0 + g + 8);
+
+        // ---- 3. colour branch backward
+        // A fragment of d_rgb: columns (2t, 2t+1) of (r, g, b, 0, ...)
+        const float ar0 = (t == 0) ? dr_lo.x : ((t == 1) ? dr_lo.z : 0.f), ar2 = (t == 0) ? dr_lo.y : 0.f;
+        const float ar1 = (t == 0) ? dr_hi.x : ((t == 1) ? dr_hi.z : 0.f), ar3 = (t == 0) ? dr_hi.y : 0.f;
+        float dhc[4][4];
+#pragma unroll
+        for (int n = 0; n < 4; ++n) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dhc[n][i] = 0.f;
+            const float2 b = *reinterpret_cast<const float2*>(WT + T::OFF_V2T + (n * 8 + g) * kRgbStride + 2 * t);
+            mma_1x(dhc[n], ar0, ar1, ar2, ar3, b.x, b.y);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dhc[n][i] = (hc[n][i] > 0.f) ? dhc[n][i] : 0.f;
+            store_frag(ACT, kActStride, n, g, t, hc[n]);
+            store_frag(DY, kActStride, n, g, t, dhc[n]);
+        }
+#pragma unroll
+        for (int n = 0; n < 2; ++n) store_frag(GEO, kGeoStride, n, g, t, o16[n]);
+        {
+            const float c0[4] = {ar0, ar2, ar1, ar3};            // (g,2t) (g,2t+1) (g+8,2t) (g+8,2t+1)
+            store_frag(DRGB, kRgbStride, 0, g, t, c0);
+        }
+        float dout[2][4];                                        // [d_geo (15) | d_sdf]
+#pragma unroll
+        for (int n = 0; n < 2; ++n) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dout[n][i] = 0.f;
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+                const float2 b = *reinterpret_cast<const float2*>(WT + T::OFF_VGT + (n * 8 + g) * T::S1 + ks * 8 + 2 * t);
+                mma_1x(dout[n], dhc[ks][0], dhc[ks][2], dhc[ks][1], dhc[ks][3], b.x, b.y);
+            }
+        }
+        if (t == 3) { dout[1][1] = dr_lo.w; dout[1][3] = dr_hi.w; }     // column 15 = sdf
+        __syncthreads();                                         // A: every warp's ACT / DY / GEO / DRGB / X are published
+
+        // ---- 4. weight gradients, phase 1 (colour net)
+        if (warp < V1_BLOCKS) {
+            for (int w = 0; w < NW; ++w) {
+                const float* src = tiles + w * WF;
+                const float* A; int as, m0;
+                const int blk = warp;                           // 16-row block of col0's inputs
+                if (blk < 3) { A = src; as = kXStride; m0 = kBlobCol + blk * 16; }
+                else if (TWO && blk < 7) { A = src + O_CF; as = kCStride; m0 = (blk - 3) * 16; }
+                else { A = src + O_GEO; as = kGeoStride; m0 = 0; }
+                outer_mma<4, 0>(acc_v1, A, as, m0, src + O_DY, kActStride, g, t);
+            }
+        }
+        if (warp == v2_owner0 || warp == v2_owner0 + 1) {
+            for (int w = 0; w < NW; ++w) {
+                const float* src = tiles + w * WF;
+                outer_mma<1, 0>(acc_v2, src + O_ACT, kActStride, (warp - v2_owner0) * 16, src + O_DRGB, kRgbStride, g, t);
+            }
+        }
+        __syncthreads();                                         // B: phase-1 tiles may be overwritten
+
+        // ---- 5. sdf branch backward
+        float dh1[4][4];
+#pragma unroll
+        for (int n = 0; n < 4; ++n) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dh1[n][i] = 0.f;
+#pragma unroll
+            for (int ks = 0; ks < 2; ++ks) {
+                const float2 b = *reinterpret_cast<const float2*>(WT + T::OFF_W2T + (n * 8 + g) * kGeoStride + ks * 8 + 2 * t);
+                mma_1x(dh1[n], dout[ks][0], dout[ks][2], dout[ks][1], dout[ks][3], b.x, b.y);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dh1[n][i] = (h1[n][i] > 0.f) ? dh1[n][i] : 0.f;
+            store_frag(ACT, kActStride, n, g, t, h1[n]);
+            store_frag(DY, kActStride, n, g, t, dh1[n]);
+        }
+#pragma unroll
+        for (int n = 0; n < 2; ++n) store_frag(GEO, kGeoStride, n, g, t, dout[n]);
+        if (TWO) {                                               // d colour features -> CF tile (its values are spent)
+#pragma unroll
+            for (int n = 0; n < 8; ++n) {
+                float d[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) {
+                    const float2 b = *reinterpret_cast<const float2*>(WT + T::OFF_VCT + (n * 8 + g) * T::S1 + ks * 8 + 2 * t);
+                    mma_1x(d, dhc[ks][0], dhc[ks][2], dhc[ks][1], dhc[ks][3], b.x, b.y);
+                }
+                store_frag(CFt, kCStride, n, g, t, d);
+            }
+        }
+        __syncthreads();                                         // C
+
+        // ---- 6. weight gradients, phase 2 (sdf net)
+        if (warp < 7) {
+            for (int w = 0; w < NW; ++w) {
+                const float* src = tiles + w * WF;
+                outer_mma<4, 0>(acc_w1, src, kXStride, warp * 16, src + O_DY, kActStride, g, t);
+            }
+        } else {
+            // d sdf1^T [32 j][16 i]: blocks (row block rb, col block cb) -> acc_w1[rb * 2 + cb]
+            for (int w = 0; w < NW; ++w) {
+                const float* src = tiles + w * WF;
+                outer_mma<2, 0>(acc_w1, src + O_ACT, kActStride, 0, src + O_GEO, kGeoStride, g, t);
+                outer_mma<2, 2>(acc_w1, src + O_ACT, kActStride, 16, src + O_GEO, kGeoStride, g, t);
+            }
+        }
+        __syncthreads();                                         // D: X may be overwritten with d feat
+
+        // ---- 7. d feat = d_h1 . W1[:, :64] -> X columns [0, 64)
+#pragma unroll
+        for (int n = 0; n < 8; ++n) {
+            float d[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+                const float2 b = *reinterpret_cast<const float2*>(WT + T::OFF_W1T + (n * 8 + g) * T::S1 + ks * 8 + 2 * t);
+                mma_1x(d, dh1[ks][0], dh1[ks][2], dh1[ks][1], dh1[ks][3], b.x, b.y);
+            }
+            store_frag(X, kXStride, n, g, t, d);
+        }
+        // tap table again (the blob segment is spent), then scatter
+        if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 0);
+        __syncwarp();
+        // ---- 8. plane gradient scatter: lane = (corner, 4-channel group)
+        for (int grp = 0; grp < (TWO ? 2 : 1); ++grp) {
+            if (grp == 1) {
+                __syncwarp();
+                if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 1);
+                __syncwarp();
+            }
+            const float* gsrc = (grp == 0) ? X : CFt;
+            const int gstride = (grp == 0) ? kXStride : kCStride;
+            const int c = lane >> 3, q = lane & 7;
+            for (int p = 0; p < np; ++p) {
+                const float* seg = X + p * kXStride + kBlobCol;
+#pragma unroll
+                for (int l = 0; l < 2; ++l) {
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) {
+                        const int tp = a * 2 + l;
+                        float* gp = P.sc.planes[grp * 6 + tp].grad;
+                        if (!gp) continue;
+                        if (VEC) {
+                            const float4 gv = *reinterpret_cast<const float4*>(gsrc + p * gstride + l * 32 + q * 4);
+                            const unsigned off = __float_as_uint(seg[8 * tp + c]);
+                            const float w = seg[8 * tp + 4 + c];
+                            if (w != 0.f)
+                                atomicAdd(reinterpret_cast<float4*>(gp + off) + q, make_float4(gv.x * w, gv.y * w, gv.z * w, gv.w * w));
+                        } else {
+                            const MnePlaneDesc& Pl = P.sc.planes[grp * 6 + tp];
+                            const float gch = gsrc[p * gstride + l * 32 + lane];
+                            float* gb = gp + (int64_t)lane * Pl.stride_c;
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                const float w = seg[8 * tp + 4 + k];
+                                if (w != 0.f) atomicAdd(gb + __float_as_uint(seg[8 * tp + k]), gch * w);
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    }
+
+    // ---- flush the register-resident weight gradients (once per CTA)
+    {
+        // d col0^T block: rows = inputs (blk*16 + g, +8), cols = j
+        if (warp < V1_BLOCKS && P.sc.g_col0) {
+#pragma unroll
+            for (int nb = 0; nb < 4; ++nb)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int k = warp * 16 + g + ((i & 2) ? 8 : 0), j = nb * 8 + 2 * t + (i & 1);
+                    if (k < N::IN_COL) atomicAdd(P.sc.g_col0 + j * N::IN_COL + k, acc_v1[nb][i]);
+                }
+        }
+        if ((warp == v2_owner0 || warp == v2_owner0 + 1) && P.sc.g_col1) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int j = (warp - v2_owner0) * 16 + g + ((i & 2) ? 8 : 0), c = 2 * t + (i & 1);
+                if (c < 3) atomicAdd(P.sc.g_col1 + c * 32 + j, acc_v2[0][i]);
+            }
+        }
+        if (warp < 7 && P.sc.g_sdf0) {
+#pragma unroll
+            for (int nb = 0; nb < 4; ++nb)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int k = warp * 16 + g + ((i & 2) ? 8 : 0), j = nb * 8 + 2 * t + (i & 1);
+                    atomicAdd(P.sc.g_sdf0 + j * N::K1 + k, acc_w1[nb][i]);
+                }
+        }
+        if (warp == 7 && P.sc.g_sdf1) {
+#pragma unroll
+            for (int rb = 0; rb < 2; ++rb)
+#pragma unroll
+                for (int cb = 0; cb < 2; ++cb)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int j = rb * 16 + g + ((i & 2) ? 8 : 0), c = cb * 8 + 2 * t + (i & 1);
+                        atomicAdd(P.sc.g_sdf1 + ((c == 15) ? 0 : c + 1) * 32 + j, acc_w1[rb * 2 + cb][i]);
+                    }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// ray kernel: d loss / d raw for every sample (same arithmetic as the head of v1's render_bwd_kernel)
+// ---------------------------------------------------------------------------------------------
+struct RayBwdParams {
+    MneRenderCfg rc;
+    int n_rays, n_samples;
+    const float* z_vals;
+    const float* raw;
+    const float* target_rgb;
+    const float* target_d;
+    const double* acc;
+    const float* loss_grads;
+    const float* g_rgb;
+    const float* g_depth;
+    const float* g_raw;
+    float4* draw;
+};
+
+__global__ void __launch_bounds__(256) rays_bwd_kernel(const RayBwdParams P) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int S = P.n_samples;
+    const float* lg = P.loss_grads;
+    float k_rgb = 0.f, k_depth = 0.f, k_co_fs = 0.f, k_co_sdf = 0.f, k_e_fs = 0.f, k_e_center = 0.f, k_e_tail = 0.f;
+    if (lg) {
+        const double Nn = P.rc.norm_rays, NS = P.rc.norm_rays * (double)S;
+        auto inv = [](double c) { return c > 0.0 ? 1.0 / c : 0.0; };
+        k_rgb = (float)(2.0 * lg[L_RGB] / (3.0 * Nn));
+        k_depth = (float)(2.0 * lg[L_DEPTH] * inv(P.acc[A_N_VALID]));
+        if (!P.rc.first_pass) {
+            const float n_fs = (float)P.acc[A_N_CO_FRONT], n_sdf = (float)P.acc[A_N_CO_NEAR];
+            const float fs_w = 1.0f - n_fs / (n_fs + n_sdf), sdf_w = 1.0f - n_sdf / (n_fs + n_sdf);
+            k_co_fs = (n_fs + n_sdf > 0.f) ? (float)(2.0 * lg[L_CO_FS] * fs_w / NS) : 0.f;
+            k_co_sdf = (n_fs + n_sdf > 0.f) ? (float)(2.0 * lg[L_CO_SDF] * sdf_w / NS) * P.rc.sc_trunc : 0.f;
+            k_e_fs = (float)(2.0 * lg[L_E_FS] * inv(P.acc[A_N_E_FRONT]));
+            k_e_center = (float)(2.0 * lg[L_E_CENTER] * inv(P.acc[A_N_E_CENTER])) * P.rc.model_trunc;
+            k_e_tail = (float)(2.0 * lg[L_E_TAIL] * inv(P.acc[A_N_E_TAIL])) * P.rc.model_trunc;
+        }
+    }
+    for (int ray = blockIdx.x * 8 + warp; ray < P.n_rays; ray += gridDim.x * 8) {
+        const size_t rb = (size_t)ray * S;
+        const RayComposite c = composite_ray(P.raw, P.z_vals, rb, S, P.rc, lane);
+        const float d = P.target_d ? P.target_d[ray] : 0.0f;
+        float rr[3] = {c.rgb[0], c.rgb[1], c.rgb[2]};
+        if (P.rc.white_bkgd) { rr[0] += 1.f - c.acc; rr[1] += 1.f - c.acc; rr[2] += 1.f - c.acc; }
+        float G[3] = {0.f, 0.f, 0.f}, Gd = 0.f;
+        if (lg && P.target_rgb) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) G[k] = k_rgb * (rr[k] - P.target_rgb[ray * 3 + k]);
+            if (depth_valid(d, P.rc)) Gd = k_depth * (c.depth - d);
+        }
+        if (P.g_rgb) { G[0] += P.g_rgb[ray * 3 + 0]; G[1] += P.g_rgb[ray * 3 + 1]; G[2] += P.g_rgb[ray * 3 + 2]; }
+        if (P.g_depth) Gd += P.g_depth[ray];
+        for (int s = lane; s < S; s += 32) {
+            const float z = __ldg(P.z_vals + rb + s);
+            const float4 v = __ldg(reinterpret_cast<const float4*>(P.raw) + rb + s);
+            float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (z < c.thresh) {
+                float sp;
+                const float u = sdf_bell(v.w, P.rc.trunc, &sp);
+                const float w = u * c.inv_norm;
+                const float c0 = sigmoidf(v.x), c1 = sigmoidf(v.y), c2 = sigmoidf(v.z);
+                const float dLdu = c.inv_norm * (G[0] * (c0 - rr[0]) + G[1] * (c1 - rr[1]) + G[2] * (c2 - rr[2]) + Gd * (z - c.depth));
+                o.w = dLdu * u * (1.0f - 2.0f * sp) / P.rc.trunc;
+                o.x = G[0] * w * c0 * (1.0f - c0);
+                o.y = G[1] * w * c1 * (1.0f - c1);
+                o.z = G[2] * w * c2 * (1.0f - c2);
+            }
+            if (lg && P.target_d && !P.rc.first_pass) {
+                const unsigned m = sample_masks(z, d, P.rc);
+                if (m & M_CO_FRONT) o.w += k_co_fs * (v.w - 1.0f);
+                if (m & M_CO_NEAR) o.w += k_co_sdf * (__fadd_rn(z, __fmul_rn(v.w, P.rc.sc_trunc)) - d);
+                if (m & M_E_FRONT) o.w += k_e_fs * (v.w - 1.0f);
+                const float re = __fadd_rn(z, __fmul_rn(v.w, P.rc.model_trunc)) - d;
+                if (m & M_E_CENTER) o.w += k_e_center * re;
+                if (m & M_E_TAIL) o.w += k_e_tail * re;
+            }
+            if (P.g_raw) {
+                const float4 e = __ldg(reinterpret_cast<const float4*>(P.g_raw) + rb + s);
+                o.x += e.x; o.y += e.y; o.z += e.z; o.w += e.w;
+            }
+            P.draw[rb + s] = o;
+        }
+    }
+}
+
+int check_scene(const MneSceneDesc* sc, const char* who, bool need_grads);
+int sm_count();
+
+template <bool TWO, bool VEC>
+static int launch_points_bwd(const PtsBwdParams& P, cudaStream_t stream) {
+    const size_t smem = bwd2_smem_bytes<TWO>();
+    static bool configured[64] = {};
+    int dev = 0;
+    MNE_CHECK_CUDA(cudaGetDevice(&dev));
+    if (dev >= 64 || !configured[dev]) {
+        MNE_CHECK_CUDA(cudaFuncSetAttribute(points_bwd_kernel<TWO, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (dev < 64) configured[dev] = true;
+    }
+    const int64_t n_tiles = (P.n_pts + kTilePts - 1) / kTilePts;
+    const int blocks = (int)max((int64_t)1, min((n_tiles + kBwdWarps - 1) / kBwdWarps, (int64_t)sm_count()));
+    points_bwd_kernel<TWO, VEC><<<blocks, kBwdWarps * 32, smem, stream>>>(P);
+    MNE_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// v2 backward for parameter gradients (ray gradients are served by the v1 kernel, see render_bwd.cu)
+int render_backward_v2(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples,
+                       const float* rays_o, const float* rays_d, const float* z_vals, const float* raw,
+                       const float* target_rgb, const float* target_d, const double* acc, const float* loss_grads,
+                       const float* g_rgb, const float* g_depth, const float* g_raw, void* scratch, cudaStream_t st) {
+    RayBwdParams R{};
+    R.rc = *rcfg; R.n_rays = n_rays; R.n_samples = n_samples; R.z_vals = z_vals; R.raw = raw; R.target_rgb = target_rgb;
+    R.target_d = target_d; R.acc = acc; R.loss_grads = loss_grads; R.g_rgb = g_rgb; R.g_depth = g_depth; R.g_raw = g_raw;
+    R.draw = reinterpret_cast<float4*>(scratch);
+    const int blocks = max(1, min((n_rays + 7) / 8, sm_count() * 4));
+    rays_bwd_kernel<<<blocks, 256, 0, st>>>(R);
+    MNE_CHECK_CUDA(cudaGetLastError());
+    PtsBwdParams P{};
+    P.sc = *scene; P.n_pts = (int64_t)n_rays * n_samples; P.n_samples = n_samples;
+    P.rays_o = rays_o; P.rays_d = rays_d; P.z_vals = z_vals; P.draw = reinterpret_cast<const float4*>(scratch);
+    // (two grids do not fit this kernel's shared-memory plan yet: the caller routes them to the v1 kernel)
+    return planes_vectorizable(*scene) ? launch_points_bwd<false, true>(P, st) : launch_points_bwd<false, false>(P, st);
+}
+
+}  // namespace mne

@@ -230,11 +230,11 @@ static int launch_fwd(const FwdParams& P, cudaStream_t stream) {
 
 }  // namespace mne
 
-extern "C" int mne_render_forward(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples,
-                                  const float* rays_o, const float* rays_d, const float* z_vals, const float* target_rgb,
-                                  const float* target_d, float* raw, float* weights, float* rgb, float* depth, float* disp,
-                                  float* acc_map, float* depth_var, int32_t* inds, double* acc, mne_stream_t stream) {
-    using namespace mne;
+namespace mne {
+int render_forward_v1(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples,
+                      const float* rays_o, const float* rays_d, const float* z_vals, const float* target_rgb,
+                      const float* target_d, float* raw, float* weights, float* rgb, float* depth, float* disp,
+                      float* acc_map, float* depth_var, int32_t* inds, double* acc, mne_stream_t stream) {
     MNE_CHECK_ARG(scene && rcfg, "mne_render_forward: null scene/rcfg");
     if (int e = check_scene(scene, "mne_render_forward", false)) return e;
     MNE_CHECK_ARG(n_rays >= 0 && n_samples > 0, "mne_render_forward: bad sizes n_rays=%d n_samples=%d", n_rays, n_samples);
@@ -250,9 +250,8 @@ extern "C" int mne_render_forward(const MneSceneDesc* scene, const MneRenderCfg*
     return scene->two_grid ? launch_fwd<true, false>(P, (cudaStream_t)stream) : launch_fwd<false, false>(P, (cudaStream_t)stream);
 }
 
-extern "C" int mne_query_points(const MneSceneDesc* scene, int64_t n_pts, const float* pts, float* raw, float* geo,
-                                float* feat, mne_stream_t stream) {
-    using namespace mne;
+int query_points_v1(const MneSceneDesc* scene, int64_t n_pts, const float* pts, float* raw, float* geo, float* feat,
+                    mne_stream_t stream) {
     MNE_CHECK_ARG(scene, "mne_query_points: null scene");
     if (int e = check_scene(scene, "mne_query_points", false)) return e;
     MNE_CHECK_ARG(n_pts >= 0 && n_pts < ((int64_t)1 << 31), "mne_query_points: n_pts out of range");
@@ -263,6 +262,8 @@ extern "C" int mne_query_points(const MneSceneDesc* scene, int64_t n_pts, const 
     P.pts = pts; P.raw = raw; P.geo = geo; P.feat = feat;
     return scene->two_grid ? launch_fwd<true, true>(P, (cudaStream_t)stream) : launch_fwd<false, true>(P, (cudaStream_t)stream);
 }
+
+}  // namespace mne
 
 extern "C" int mne_loss_finalize(const MneRenderCfg* rcfg, int32_t n_samples, const double* acc, float* losses,
                                  mne_stream_t stream) {

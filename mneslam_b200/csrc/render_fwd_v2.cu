@@ -1,0 +1,278 @@
+// v2 forward: (1) a point kernel -- 16-point tiles per warp: taps + OneBlob -> tri-plane gather -> decoder on
+// the tensor pipe (mma.sync TF32, 3-term split) -> raw; (2) a ray kernel -- warp per ray: sdf2weights
+// compositing, rendered maps and the loss sums.  Replaces the same reference code as render_fwd.cu (v1).
+#include "tile16.cuh"
+
+namespace mne {
+
+template <bool TWO> __host__ __device__ constexpr int pts_warps() { return TWO ? 8 : 16; }
+template <bool TWO> __host__ __device__ constexpr int pts_warp_floats() { return kTilePts * kXStride + (TWO ? kTilePts * kCStride : 0); }
+template <bool TWO>
+constexpr size_t pts_smem_bytes() {
+    return sizeof(float4) * (size_t)NetV2<TWO>::W4_COUNT + sizeof(float) * (size_t)(pts_warps<TWO>() * pts_warp_floats<TWO>());
+}
+
+struct PtsFwdParams {
+    MneSceneDesc sc;
+    int64_t n_pts;
+    int n_samples;            // points per ray (ray = point / n_samples); unused for explicit points
+    const float* rays_o;
+    const float* rays_d;
+    const float* z_vals;
+    const float* pts;         // explicit points [M,3] (query mode) or NULL
+    float* raw;               // [M,4]
+    float* geo;               // [M,15] or NULL
+    float* feat;              // [M,64] or NULL
+};
+
+template <bool TWO, bool VEC>
+__global__ void __launch_bounds__(pts_warps<TWO>() * 32, 1) points_fwd_kernel(const __grid_constant__ PtsFwdParams P) {
+    using N = NetV2<TWO>;
+    constexpr int NW = pts_warps<TWO>();
+    extern __shared__ __align__(16) float4 smem4[];
+    float4* W4 = smem4;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float* X = reinterpret_cast<float*>(smem4 + N::W4_COUNT) + warp * pts_warp_floats<TWO>();
+    float* CFt = X + kTilePts * kXStride;
+
+    load_weights_v2<TWO>(P.sc, W4, threadIdx.x, blockDim.x);
+    __syncthreads();
+
+    const int64_t n_tiles = (P.n_pts + kTilePts - 1) / kTilePts;
+    const int64_t total_warps = (int64_t)gridDim.x * NW;
+    const int p_loc = lane & 15, half = lane >> 4;
+    const int g = lane >> 2, t = lane & 3;
+
+    for (int64_t tile = (int64_t)warp * gridDim.x + blockIdx.x; tile < n_tiles; tile += total_warps) {
+        const int64_t pt0 = tile * kTilePts;
+        const int np = (int)min((int64_t)kTilePts, P.n_pts - pt0);
+        // ---- lanes (point, half): position
+        float px = 0.f, py = 0.f, pz = 0.f;
+        if (p_loc < np) {
+            const int64_t q = pt0 + p_loc;
+            if (P.pts) {
+                px = P.pts[q * 3 + 0]; py = P.pts[q * 3 + 1]; pz = P.pts[q * 3 + 2];
+            } else {
+                const int64_t ray = q / P.n_samples;
+                const float z = P.z_vals[q];
+                px = __fadd_rn(P.rays_o[ray * 3 + 0], __fmul_rn(P.rays_d[ray * 3 + 0], z));
+                py = __fadd_rn(P.rays_o[ray * 3 + 1], __fmul_rn(P.rays_d[ray * 3 + 1], z));
+                pz = __fadd_rn(P.rays_o[ray * 3 + 2], __fmul_rn(P.rays_d[ray * 3 + 2], z));
+            }
+        }
+        float* row = X + p_loc * kXStride;
+        // ---- tap table into the point's blob segment, gather, then (two grids) the same for the colour planes
+        if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 0);
+        __syncwarp();
+        if (VEC) gather16_vec(P.sc, 0, X + kBlobCol, kXStride, X, kXStride, np, lane);
+        else gather16(P.sc, 0, X + kBlobCol, kXStride, X, kXStride, np, lane);
+        __syncwarp();
+        if (TWO) {
+            if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 1);
+            __syncwarp();
+            if (VEC) gather16_vec(P.sc, 1, X + kBlobCol, kXStride, CFt, kCStride, np, lane);
+            else gather16(P.sc, 1, X + kBlobCol, kXStride, CFt, kCStride, np, lane);
+            __syncwarp();
+        }
+        // ---- OneBlob over the (now dead) tap table: half 0 -> dims 0,1 ; half 1 -> dim 2
+        if (half == 0) {
+            oneblob16_sparse(blob_input(px, P.sc.bbox_lo[0], P.sc.bbox_ext[0]), row + kBlobCol);
+            oneblob16_sparse(blob_input(py, P.sc.bbox_lo[1], P.sc.bbox_ext[1]), row + kBlobCol + 16);
+        } else {
+            oneblob16_sparse(blob_input(pz, P.sc.bbox_lo[2], P.sc.bbox_ext[2]), row + kBlobCol + 32);
+        }
+        __syncwarp();
+        if (P.feat) {
+            for (int p = 0; p < np; ++p) {
+                P.feat[(pt0 + p) * 64 + lane] = X[p * kXStride + lane];
+                P.feat[(pt0 + p) * 64 + 32 + lane] = X[p * kXStride + 32 + lane];
+            }
+        }
+        // ---- decoder
+        float h1[4][4], o16[2][4], hc[4][4], rgb[4];
+        decoder_forward_mma<TWO>(W4, X, CFt, lane, h1, o16, hc, rgb);
+        // rows g, g+8: rgb columns 0,1 on t = 0, column 2 on t = 1; sdf = column 15 of o16 = o16[1][1|3] on t = 3
+        const int quad = lane & ~3;
+        const float b_lo = __shfl_sync(0xffffffffu, rgb[0], quad | 1), b_hi = __shfl_sync(0xffffffffu, rgb[2], quad | 1);
+        const float s_lo = __shfl_sync(0xffffffffu, o16[1][1], quad | 3), s_hi = __shfl_sync(0xffffffffu, o16[1][3], quad | 3);
+        if (P.raw && t == 0) {
+            if (g < np) reinterpret_cast<float4*>(P.raw)[pt0 + g] = make_float4(rgb[0], rgb[1], b_lo, s_lo);
+            if (g + 8 < np) reinterpret_cast<float4*>(P.raw)[pt0 + g + 8] = make_float4(rgb[2], rgb[3], b_hi, s_hi);
+        }
+        if (P.geo) {
+#pragma unroll
+            for (int n = 0; n < 2; ++n)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int col = n * 8 + 2 * t + (i & 1), r = g + ((i & 2) ? 8 : 0);
+                    if (col < kGeo && r < np) P.geo[(pt0 + r) * kGeo + col] = o16[n][i];
+                }
+        }
+        __syncwarp();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// ray kernel: compositing + loss sums (same arithmetic as the tail of v1's render_fwd_kernel)
+// ---------------------------------------------------------------------------------------------
+struct RayFwdParams {
+    MneRenderCfg rc;
+    int n_rays, n_samples;
+    const float* z_vals;
+    const float* raw;
+    const float* target_rgb;
+    const float* target_d;
+    float* weights;
+    float* rgb;
+    float* depth;
+    float* disp;
+    float* acc_map;
+    float* depth_var;
+    int32_t* inds;
+    double* acc;
+};
+
+constexpr int kRayWarps = 8;
+
+__global__ void __launch_bounds__(kRayWarps * 32) rays_fwd_kernel(const RayFwdParams P) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int S = P.n_samples;
+    const bool with_loss = P.acc && P.target_rgb && P.target_d;
+    double l_rgb = 0, l_depth = 0, l_co_fs = 0, l_co_sdf = 0, l_e_fs = 0, l_e_center = 0, l_e_tail = 0;
+    for (int ray = blockIdx.x * kRayWarps + warp; ray < P.n_rays; ray += gridDim.x * kRayWarps) {
+        const size_t rb = (size_t)ray * S;
+        const RayComposite c = composite_ray(P.raw, P.z_vals, rb, S, P.rc, lane);
+        const float d = P.target_d ? P.target_d[ray] : 0.0f;
+        float var = 0.f;
+        for (int s = lane; s < S; s += 32) {
+            const float z = P.z_vals[rb + s];
+            const float sdf = P.raw[(rb + s) * 4 + 3];
+            float w = 0.f;
+            if (z < c.thresh) w = sdf_bell(sdf, P.rc.trunc) * c.inv_norm;
+            if (P.weights) P.weights[rb + s] = w;
+            var += w * (z - c.depth) * (z - c.depth);
+            if (with_loss && !P.rc.first_pass) {
+                const unsigned m = sample_masks(z, d, P.rc);
+                const float fs = (sdf - 1.0f) * (sdf - 1.0f);
+                const float rc_co = __fadd_rn(z, __fmul_rn(sdf, P.rc.sc_trunc)) - d;
+                const float rc_e = __fadd_rn(z, __fmul_rn(sdf, P.rc.model_trunc)) - d;
+                if (m & M_CO_FRONT) l_co_fs += fs;
+                if (m & M_CO_NEAR) l_co_sdf += rc_co * rc_co;
+                if (m & M_E_FRONT) l_e_fs += fs;
+                if (m & M_E_CENTER) l_e_center += rc_e * rc_e;
+                if (m & M_E_TAIL) l_e_tail += rc_e * rc_e;
+            }
+        }
+        var = warp_sum(var);
+        if (lane == 0) {
+            float rr = c.rgb[0], gg = c.rgb[1], bb = c.rgb[2];
+            if (P.rc.white_bkgd) { rr += 1.f - c.acc; gg += 1.f - c.acc; bb += 1.f - c.acc; }
+            if (P.rgb) { P.rgb[ray * 3 + 0] = rr; P.rgb[ray * 3 + 1] = gg; P.rgb[ray * 3 + 2] = bb; }
+            if (P.depth) P.depth[ray] = c.depth;
+            if (P.disp) P.disp[ray] = 1.0f / fmaxf(1e-10f, c.depth / c.acc);
+            if (P.acc_map) P.acc_map[ray] = c.acc;
+            if (P.depth_var) P.depth_var[ray] = var;
+            if (P.inds) P.inds[ray] = c.ind;
+            if (with_loss) {
+                const float e0 = rr - P.target_rgb[ray * 3 + 0], e1 = gg - P.target_rgb[ray * 3 + 1], e2 = bb - P.target_rgb[ray * 3 + 2];
+                l_rgb += (double)(e0 * e0) + (double)(e1 * e1) + (double)(e2 * e2);
+                if (depth_valid(d, P.rc)) l_depth += (double)((c.depth - d) * (c.depth - d));
+            }
+        }
+    }
+    if (with_loss) {
+        __shared__ double red[7];
+        if (threadIdx.x < 7) red[threadIdx.x] = 0.0;
+        __syncthreads();
+        double v[7] = {l_rgb, l_depth, l_co_fs, l_co_sdf, l_e_fs, l_e_center, l_e_tail};
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+            const double s = warp_sum(v[k]);
+            if (lane == 0 && s != 0.0) atomicAdd(&red[k], s);
+        }
+        __syncthreads();
+        if (threadIdx.x < 7 && red[threadIdx.x] != 0.0) {
+            const int slot_first[2] = {A_S_RGB0, A_S_DEPTH0};
+            const int slot[7] = {A_S_RGB, A_S_DEPTH, A_S_CO_FS, A_S_CO_SDF, A_S_E_FS, A_S_E_CENTER, A_S_E_TAIL};
+            if (P.rc.first_pass) { if (threadIdx.x < 2) atomicAdd(P.acc + slot_first[threadIdx.x], red[threadIdx.x]); }
+            else atomicAdd(P.acc + slot[threadIdx.x], red[threadIdx.x]);
+        }
+    }
+}
+
+int check_scene(const MneSceneDesc* sc, const char* who, bool need_grads);
+int sm_count();
+int impl_version();
+int render_forward_v1(const MneSceneDesc*, const MneRenderCfg*, int32_t, int32_t, const float*, const float*, const float*,
+                      const float*, const float*, float*, float*, float*, float*, float*, float*, float*, int32_t*, double*,
+                      mne_stream_t);
+int query_points_v1(const MneSceneDesc*, int64_t, const float*, float*, float*, float*, mne_stream_t);
+
+template <bool TWO, bool VEC>
+static int launch_points_fwd(const PtsFwdParams& P, cudaStream_t stream) {
+    const size_t smem = pts_smem_bytes<TWO>();
+    static bool configured[64] = {};
+    int dev = 0;
+    MNE_CHECK_CUDA(cudaGetDevice(&dev));
+    if (dev >= 64 || !configured[dev]) {
+        MNE_CHECK_CUDA(cudaFuncSetAttribute(points_fwd_kernel<TWO, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (dev < 64) configured[dev] = true;
+    }
+    const int64_t n_tiles = (P.n_pts + kTilePts - 1) / kTilePts;
+    const int blocks = (int)max((int64_t)1, min(n_tiles, (int64_t)sm_count()));
+    points_fwd_kernel<TWO, VEC><<<blocks, pts_warps<TWO>() * 32, smem, stream>>>(P);
+    MNE_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+static int dispatch_points_fwd(const PtsFwdParams& P, cudaStream_t stream) {
+    const bool vec = planes_vectorizable(P.sc);
+    if (P.sc.two_grid) return vec ? launch_points_fwd<true, true>(P, stream) : launch_points_fwd<true, false>(P, stream);
+    return vec ? launch_points_fwd<false, true>(P, stream) : launch_points_fwd<false, false>(P, stream);
+}
+
+}  // namespace mne
+
+extern "C" int mne_render_forward(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples,
+                                  const float* rays_o, const float* rays_d, const float* z_vals, const float* target_rgb,
+                                  const float* target_d, float* raw, float* weights, float* rgb, float* depth, float* disp,
+                                  float* acc_map, float* depth_var, int32_t* inds, double* acc, mne_stream_t stream) {
+    using namespace mne;
+    if (impl_version() == 1)
+        return render_forward_v1(scene, rcfg, n_rays, n_samples, rays_o, rays_d, z_vals, target_rgb, target_d, raw, weights,
+                                 rgb, depth, disp, acc_map, depth_var, inds, acc, stream);
+    MNE_CHECK_ARG(scene && rcfg, "mne_render_forward: null scene/rcfg");
+    if (int e = check_scene(scene, "mne_render_forward", false)) return e;
+    MNE_CHECK_ARG(n_rays >= 0 && n_samples > 0, "mne_render_forward: bad sizes n_rays=%d n_samples=%d", n_rays, n_samples);
+    if (n_rays == 0) return 0;
+    MNE_CHECK_ARG(rays_o && rays_d && z_vals && raw, "mne_render_forward: rays_o, rays_d, z_vals and raw are required");
+    MNE_CHECK_ARG(((uintptr_t)raw & 15) == 0, "mne_render_forward: raw must be 16-byte aligned");
+    MNE_CHECK_ARG((int64_t)n_rays * n_samples < (int64_t)1 << 31, "mne_render_forward: n_rays * n_samples must be < 2^31");
+    PtsFwdParams P{};
+    P.sc = *scene; P.n_pts = (int64_t)n_rays * n_samples; P.n_samples = n_samples;
+    P.rays_o = rays_o; P.rays_d = rays_d; P.z_vals = z_vals; P.raw = raw;
+    if (int e = dispatch_points_fwd(P, (cudaStream_t)stream)) return e;
+    RayFwdParams R{};
+    R.rc = *rcfg; R.n_rays = n_rays; R.n_samples = n_samples; R.z_vals = z_vals; R.raw = raw;
+    R.target_rgb = target_rgb; R.target_d = target_d; R.weights = weights; R.rgb = rgb; R.depth = depth; R.disp = disp;
+    R.acc_map = acc_map; R.depth_var = depth_var; R.inds = inds; R.acc = acc;
+    const int blocks = max(1, min((n_rays + kRayWarps - 1) / kRayWarps, sm_count() * 4));
+    rays_fwd_kernel<<<blocks, kRayWarps * 32, 0, (cudaStream_t)stream>>>(R);
+    MNE_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int mne_query_points(const MneSceneDesc* scene, int64_t n_pts, const float* pts, float* raw, float* geo,
+                                float* feat, mne_stream_t stream) {
+    using namespace mne;
+    if (impl_version() == 1) return query_points_v1(scene, n_pts, pts, raw, geo, feat, stream);
+    MNE_CHECK_ARG(scene, "mne_query_points: null scene");
+    if (int e = check_scene(scene, "mne_query_points", false)) return e;
+    MNE_CHECK_ARG(n_pts >= 0 && n_pts < ((int64_t)1 << 31), "mne_query_points: n_pts out of range");
+    if (n_pts == 0) return 0;
+    MNE_CHECK_ARG(pts, "mne_query_points: null pts");
+    MNE_CHECK_ARG(((uintptr_t)raw & 15) == 0, "mne_query_points: raw must be 16-byte aligned");
+    PtsFwdParams P{};
+    P.sc = *scene; P.n_pts = n_pts; P.n_samples = 1; P.pts = pts; P.raw = raw; P.geo = geo; P.feat = feat;
+    return dispatch_points_fwd(P, (cudaStream_t)stream);
+}

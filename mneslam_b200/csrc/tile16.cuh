@@ -1,0 +1,326 @@
+// v2 building blocks: a warp owns a tile of 16 points and runs the decoder on the tensor pipe.
+//
+//   * mma.sync.m16n8k8 TF32, fp32 accumulate.  The forward uses the 3-term split (x = hi + lo, products
+//     lo*hi + hi*lo + hi*hi) which carries ~21 mantissa bits, i.e. fp32-level accuracy, so the 1e-3 parity
+//     gate holds; gradients (cosine >= 0.999 gate) use single TF32 products.
+//   * fragment chaining: the accumulator fragment of one layer IS the A fragment of the next layer when the
+//     8 k-slots of a k-step are mapped to columns (2t, 2t+1) instead of (t, t+4); the weights (B operand) are
+//     stored with the same pairing, so activations never leave registers between layers.
+//   * per-warp shared memory: one [16][120] fp32 tile (feat64 | blob48); the bilinear tap table of a point
+//     aliases that point's blob segment while the gather runs (192 B = 6 taps x (4 offsets + 4 weights)).
+#pragma once
+#include "render_common.cuh"
+
+namespace mne {
+
+constexpr int kTilePts = 16;
+constexpr int kXStride = 120;      // floats per tile row; == 8 (mod 32): conflict-free 64-bit A-fragment loads
+constexpr int kCStride = 72;       // colour-feature tile row (two grids)
+constexpr int kBlobCol = 64;
+
+__device__ __forceinline__ uint32_t to_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return r;
+}
+
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+struct SplitA {
+    uint32_t hi[4], lo[4];
+};
+__device__ __forceinline__ SplitA split_a(float a0, float a1, float a2, float a3) {
+    SplitA s;
+    const float v[4] = {a0, a1, a2, a3};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        s.hi[i] = to_tf32(v[i]);
+        s.lo[i] = to_tf32(v[i] - __uint_as_float(s.hi[i]));
+    }
+    return s;
+}
+// d += A * B with the 3-term split; w = (b0_hi, b1_hi, b0_lo, b1_lo)
+__device__ __forceinline__ void mma_3x(float (&d)[4], const SplitA& a, const float4& w) {
+    mma_tf32(d, a.lo, __float_as_uint(w.x), __float_as_uint(w.y));
+    mma_tf32(d, a.hi, __float_as_uint(w.z), __float_as_uint(w.w));
+    mma_tf32(d, a.hi, __float_as_uint(w.x), __float_as_uint(w.y));
+}
+
+// ---------------------------------------------------------------------------------------------
+// forward weight layout in shared memory: for each output n a row of float4 pairs
+//   W4[n][kp] = (hi W[n][2kp], hi W[n][2kp+1], lo W[n][2kp], lo W[n][2kp+1])
+// row strides (in float4) are == 4 (mod 8): conflict-free 128-bit B-fragment loads.
+// ---------------------------------------------------------------------------------------------
+template <bool TWO>
+struct NetV2 {
+    static constexpr int K1 = 112, K1P = 56, RS1 = 60;                    // sdf0: [32][112]
+    static constexpr int K2P = 16, RS2 = 20;                              // sdf1: [16][32], rows = (geo0..14, sdf)
+    static constexpr int KC = kBlob + (TWO ? 64 : 0) + 16;                // col0 inputs: blob | cfeat | geo15 + 0
+    static constexpr int KCP = KC / 2, RSC = KCP + 4;                     // 32+4 = 36, 64+4 = 68
+    static constexpr int IN_COL = kBlob + (TWO ? 64 : 0) + kGeo;          // real columns of col0
+    static constexpr int OFF1 = 0;
+    static constexpr int OFF2 = OFF1 + 32 * RS1;
+    static constexpr int OFFC = OFF2 + 16 * RS2;
+    static constexpr int OFFO = OFFC + 32 * RSC;                          // col1: [8][32] (3 real rows)
+    static constexpr int W4_COUNT = OFFO + 8 * RS2;                       // float4 elements
+};
+
+__device__ __forceinline__ float4 split_pair(float a, float b) {
+    const uint32_t ah = to_tf32(a), bh = to_tf32(b);
+    return make_float4(__uint_as_float(ah), __uint_as_float(bh), __uint_as_float(to_tf32(a - __uint_as_float(ah))),
+                       __uint_as_float(to_tf32(b - __uint_as_float(bh))));
+}
+
+template <bool TWO>
+__device__ __forceinline__ void load_weights_v2(const MneSceneDesc& sc, float4* W4, int tid, int nthreads) {
+    using N = NetV2<TWO>;
+    for (int i = tid; i < 32 * N::K1P; i += nthreads) {
+        const int n = i / N::K1P, kp = i % N::K1P;
+        W4[N::OFF1 + n * N::RS1 + kp] = split_pair(sc.w_sdf0[n * N::K1 + 2 * kp], sc.w_sdf0[n * N::K1 + 2 * kp + 1]);
+    }
+    for (int i = tid; i < 16 * N::K2P; i += nthreads) {
+        const int n = i / N::K2P, kp = i % N::K2P;
+        const int out = (n == 15) ? 0 : n + 1;                      // tile column 15 carries the sdf
+        W4[N::OFF2 + n * N::RS2 + kp] = split_pair(sc.w_sdf1[out * 32 + 2 * kp], sc.w_sdf1[out * 32 + 2 * kp + 1]);
+    }
+    for (int i = tid; i < 32 * N::KCP; i += nthreads) {
+        const int n = i / N::KCP, kp = i % N::KCP;
+        const int k0 = 2 * kp, k1 = 2 * kp + 1;
+        const float a = (k0 < N::IN_COL) ? sc.w_col0[n * N::IN_COL + k0] : 0.0f;
+        const float b = (k1 < N::IN_COL) ? sc.w_col0[n * N::IN_COL + k1] : 0.0f;
+        W4[N::OFFC + n * N::RSC + kp] = split_pair(a, b);
+    }
+    for (int i = tid; i < 8 * N::K2P; i += nthreads) {
+        const int n = i / N::K2P, kp = i % N::K2P;
+        const float a = (n < 3) ? sc.w_col1[n * 32 + 2 * kp] : 0.0f, b = (n < 3) ? sc.w_col1[n * 32 + 2 * kp + 1] : 0.0f;
+        W4[N::OFFO + n * N::RS2 + kp] = split_pair(a, b);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// tap table: per (point, plane-level) 4 texel offsets + 4 bilinear weights (32 B)
+// ---------------------------------------------------------------------------------------------
+struct Tap8 {
+    int4 off;      // element offsets of (y0,x0) (y0,x1) (y1,x0) (y1,x1); out-of-plane corners repeat a valid one
+    float4 w;      // their weights (0 for out-of-plane corners)
+};
+
+__device__ __forceinline__ void make_tap8(const MnePlaneDesc& P, float gx, float gy, int4& off, float4& w, unsigned* flags = nullptr) {
+    const AxisTap tx = axis_tap(gx, P.W), ty = axis_tap(gy, P.H);
+    const int o00 = (int)((int64_t)ty.i0 * P.stride_h + (int64_t)tx.i0 * P.stride_w);
+    const int dx = tx.ok1 ? (int)P.stride_w : 0, dy = ty.ok1 ? (int)P.stride_h : 0;
+    const float wx1 = tx.ok1 ? tx.f : 0.0f, wy1 = ty.ok1 ? ty.f : 0.0f;
+    const float wx0 = 1.0f - tx.f, wy0 = 1.0f - ty.f;
+    off = make_int4(o00, o00 + dx, o00 + dy, o00 + dy + dx);
+    w = make_float4(wy0 * wx0, wy0 * wx1, wy1 * wx0, wy1 * wx1);
+    if (flags) *flags = (tx.grad_on ? 1u : 0u) | (ty.grad_on ? 2u : 0u);
+}
+
+// taps of one point for the planes [t_begin, t_end) into its table segment (float4 slots 2t, 2t+1)
+template <bool TWO>
+__device__ __forceinline__ void write_taps8(const MneSceneDesc& sc, float4* seg, float px, float py, float pz, int grp) {
+    const float n[3] = {plane_coord(px, sc.bound_lo[0], sc.bound_ext[0]), plane_coord(py, sc.bound_lo[1], sc.bound_ext[1]),
+                        plane_coord(pz, sc.bound_lo[2], sc.bound_ext[2])};
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float gx = (a == 2) ? n[1] : n[0];
+        const float gy = (a == 0) ? n[1] : n[2];
+#pragma unroll
+        for (int l = 0; l < 2; ++l) {
+            const int t = a * 2 + l;
+            int4 off; float4 w;
+            make_tap8(sc.planes[grp * 6 + t], gx, gy, off, w);
+            seg[2 * t] = make_float4(__int_as_float(off.x), __int_as_float(off.y), __int_as_float(off.z), __int_as_float(off.w));
+            seg[2 * t + 1] = w;
+        }
+    }
+}
+
+// lane = channel: features of np points of one plane group into tile columns [0, 64)
+__device__ __forceinline__ void gather16(const MneSceneDesc& sc, int grp, const float* __restrict__ tab_base, int tab_stride,
+                                         float* __restrict__ dst, int dst_stride, int np, int lane) {
+    const float* base[6];
+#pragma unroll
+    for (int t = 0; t < 6; ++t) base[t] = sc.planes[grp * 6 + t].data + (int64_t)lane * sc.planes[grp * 6 + t].stride_c;
+#pragma unroll 4
+    for (int p = 0; p < np; ++p) {
+        const float4* seg = reinterpret_cast<const float4*>(tab_base + p * tab_stride);
+#pragma unroll
+        for (int l = 0; l < 2; ++l) {
+            float v[3];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const int t = a * 2 + l;
+                const float4 o = seg[2 * t], w = seg[2 * t + 1];
+                const float* b = base[t];
+                v[a] = __ldg(b + __float_as_uint(o.x)) * w.x + __ldg(b + __float_as_uint(o.y)) * w.y +
+                       __ldg(b + __float_as_uint(o.z)) * w.z + __ldg(b + __float_as_uint(o.w)) * w.w;
+            }
+            dst[p * dst_stride + l * 32 + lane] = (v[0] + v[1]) + v[2];
+        }
+    }
+}
+
+// Channels-last fast path: lane = (corner, 4-channel group).  One 128-bit load per lane fetches the four
+// corner texels of a tap (4 x 128 B lines) in a single warp instruction; the per-corner partial sums of the
+// three planes of a level are then reduced across the four corner lane-groups with two shuffle steps.
+// Needs stride_c == 1 and 16-byte aligned texels (checked on the host: planes_vectorizable()).
+__device__ __forceinline__ void gather16_vec(const MneSceneDesc& sc, int grp, const float* __restrict__ tab_base, int tab_stride,
+                                             float* __restrict__ dst, int dst_stride, int np, int lane) {
+    const int c = lane >> 3, q = lane & 7;
+    const float* base[6];
+#pragma unroll
+    for (int t = 0; t < 6; ++t) base[t] = sc.planes[grp * 6 + t].data + q * 4;
+#pragma unroll 2
+    for (int p = 0; p < np; ++p) {
+        const float* seg = tab_base + p * tab_stride;
+        float4 acc[2];
+#pragma unroll
+        for (int l = 0; l < 2; ++l) {
+            acc[l] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const int t = a * 2 + l;
+                const unsigned off = __float_as_uint(seg[8 * t + c]);
+                const float w = seg[8 * t + 4 + c];
+                const float4 v = __ldg(reinterpret_cast<const float4*>(base[t] + off));
+                acc[l].x = fmaf(w, v.x, acc[l].x); acc[l].y = fmaf(w, v.y, acc[l].y);
+                acc[l].z = fmaf(w, v.z, acc[l].z); acc[l].w = fmaf(w, v.w, acc[l].w);
+            }
+        }
+#pragma unroll
+        for (int l = 0; l < 2; ++l) {
+#pragma unroll
+            for (int o = 8; o <= 16; o <<= 1) {
+                acc[l].x += __shfl_xor_sync(0xffffffffu, acc[l].x, o); acc[l].y += __shfl_xor_sync(0xffffffffu, acc[l].y, o);
+                acc[l].z += __shfl_xor_sync(0xffffffffu, acc[l].z, o); acc[l].w += __shfl_xor_sync(0xffffffffu, acc[l].w, o);
+            }
+            if (c == 0) *reinterpret_cast<float4*>(dst + p * dst_stride + l * 32 + q * 4) = acc[l];
+        }
+    }
+}
+
+__host__ inline bool planes_vectorizable(const MneSceneDesc& sc) {
+    const int n = sc.two_grid ? 12 : 6;
+    for (int i = 0; i < n; ++i) {
+        const MnePlaneDesc& p = sc.planes[i];
+        if (p.stride_c != 1 || (p.stride_w & 3) || (p.stride_h & 3) || ((uintptr_t)p.data & 15)) return false;
+        if (p.grad && ((uintptr_t)p.grad & 15)) return false;
+    }
+    return true;
+}
+
+// ---------------------------------------------------------------------------------------------
+// OneBlob, sparse evaluation: each of the three wrap images of the quartic kernel touches at most three
+// bins; everything else is exactly 0.  Equal to oneblob16 (render_common.cuh) up to summation order.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void oneblob16_sparse(float x, float* o) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) reinterpret_cast<float4*>(o)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+        const float sh = (s == 0) ? 0.0f : ((s == 1) ? -1.0f : 1.0f);
+        const float c = x - sh;                                  // centre of this image of the kernel
+        const float fb = floorf(c * (float)kBins);
+        if (fb < -2.0f || fb > (float)kBins + 1.0f) continue;    // image entirely outside the bins
+        const int bc = (int)fb;
+        float F[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) F[j] = quartic_cdf(((float)(bc - 1 + j) * (1.0f / kBins) - x) + sh);
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            const int b = bc - 1 + j;
+            if (b >= 0 && b < kBins) o[b] += F[j + 1] - F[j];
+        }
+    }
+    // power-of-two variant of tiny-cuda-nn: the last bin's right edge is "left edge of bin 0, plus one"
+    o[kBins - 1] += 1.0f - (quartic_cdf((1.0f - x) + 1.0f) - quartic_cdf((0.0f - x) - 1.0f));
+}
+
+// ---------------------------------------------------------------------------------------------
+// decoder forward on the tensor pipe for one 16-point tile.
+// X: tile [16][kXStride] (feat | blob); CFt: colour features [16][kCStride] (two grids).
+// Outputs (accumulator fragments, rows g / g+8, columns 2t, 2t+1 of each 8-wide block):
+//   h1[4][4] post-ReLU, o16[2][4] = (geo0..14, sdf), hc[4][4] post-ReLU, rgb[4] (columns 0..2 real).
+// ---------------------------------------------------------------------------------------------
+template <bool TWO>
+__device__ __forceinline__ void decoder_forward_mma(const float4* __restrict__ W4, const float* __restrict__ X,
+                                                    const float* __restrict__ CFt, int lane, float (&h1)[4][4],
+                                                    float (&o16)[2][4], float (&hc)[4][4], float (&rgb)[4]) {
+    using N = NetV2<TWO>;
+    const int g = lane >> 2, t = lane & 3;
+#pragma unroll
+    for (int n = 0; n < 4; ++n)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { h1[n][i] = 0.f; hc[n][i] = 0.f; }
+    // ---- sdf layer 1: [16 x 112] . [112 x 32]
+#pragma unroll 2
+    for (int ks = 0; ks < N::K1 / 8; ++ks) {
+        const float2 lo = *reinterpret_cast<const float2*>(X + g * kXStride + ks * 8 + 2 * t);
+        const float2 hi = *reinterpret_cast<const float2*>(X + (g + 8) * kXStride + ks * 8 + 2 * t);
+        const SplitA a = split_a(lo.x, hi.x, lo.y, hi.y);
+#pragma unroll
+        for (int n = 0; n < 4; ++n) mma_3x(h1[n], a, W4[N::OFF1 + (n * 8 + g) * N::RS1 + ks * 4 + t]);
+    }
+#pragma unroll
+    for (int n = 0; n < 4; ++n)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) h1[n][i] = fmaxf(h1[n][i], 0.f);
+    // ---- sdf layer 2: [16 x 32] . [32 x 16], A straight from the h1 fragments
+#pragma unroll
+    for (int n = 0; n < 2; ++n)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) o16[n][i] = 0.f;
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+        const SplitA a = split_a(h1[ks][0], h1[ks][2], h1[ks][1], h1[ks][3]);
+#pragma unroll
+        for (int n = 0; n < 2; ++n) mma_3x(o16[n], a, W4[N::OFF2 + (n * 8 + g) * N::RS2 + ks * 4 + t]);
+    }
+    // ---- colour layer 1: blob (tile) | cfeat (tile) | geo (o16 fragments; the sdf column meets a zero weight row)
+    int kp0 = 0;
+#pragma unroll 2
+    for (int ks = 0; ks < kBlob / 8; ++ks) {
+        const float2 lo = *reinterpret_cast<const float2*>(X + g * kXStride + kBlobCol + ks * 8 + 2 * t);
+        const float2 hi = *reinterpret_cast<const float2*>(X + (g + 8) * kXStride + kBlobCol + ks * 8 + 2 * t);
+        const SplitA a = split_a(lo.x, hi.x, lo.y, hi.y);
+#pragma unroll
+        for (int n = 0; n < 4; ++n) mma_3x(hc[n], a, W4[N::OFFC + (n * 8 + g) * N::RSC + kp0 + ks * 4 + t]);
+    }
+    kp0 += kBlob / 2;
+    if (TWO) {
+#pragma unroll 2
+        for (int ks = 0; ks < 8; ++ks) {
+            const float2 lo = *reinterpret_cast<const float2*>(CFt + g * kCStride + ks * 8 + 2 * t);
+            const float2 hi = *reinterpret_cast<const float2*>(CFt + (g + 8) * kCStride + ks * 8 + 2 * t);
+            const SplitA a = split_a(lo.x, hi.x, lo.y, hi.y);
+#pragma unroll
+            for (int n = 0; n < 4; ++n) mma_3x(hc[n], a, W4[N::OFFC + (n * 8 + g) * N::RSC + kp0 + ks * 4 + t]);
+        }
+        kp0 += 32;
+    }
+#pragma unroll
+    for (int ks = 0; ks < 2; ++ks) {
+        const SplitA a = split_a(o16[ks][0], o16[ks][2], o16[ks][1], o16[ks][3]);
+#pragma unroll
+        for (int n = 0; n < 4; ++n) mma_3x(hc[n], a, W4[N::OFFC + (n * 8 + g) * N::RSC + kp0 + ks * 4 + t]);
+    }
+#pragma unroll
+    for (int n = 0; n < 4; ++n)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) hc[n][i] = fmaxf(hc[n][i], 0.f);
+    // ---- colour layer 2: [16 x 32] . [32 x 8]
+#pragma unroll
+    for (int i = 0; i < 4; ++i) rgb[i] = 0.f;
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+        const SplitA a = split_a(hc[ks][0], hc[ks][2], hc[ks][1], hc[ks][3]);
+        mma_3x(rgb, a, W4[N::OFFO + g * N::RS2 + ks * 4 + t]);
+    }
+}
+
+}  // namespace mne

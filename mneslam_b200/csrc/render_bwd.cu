@@ -438,7 +438,7 @@ int sm_count();
 int impl_version();
 int render_backward_v2(const MneSceneDesc*, const MneRenderCfg*, int32_t, int32_t, const float*, const float*, const float*,
                        const float*, const float*, const float*, const double*, const float*, const float*, const float*,
-                       const float*, void*, cudaStream_t);
+                       const float*, void*, float*, float*, bool, cudaStream_t);
 
 template <bool TWO, bool RAY_GRAD, bool PARAM_GRAD>
 static int launch_bwd(const BwdParams& P, cudaStream_t stream) {
@@ -493,13 +493,13 @@ extern "C" int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg
     const bool ray_grad = g_rays_o != nullptr;
     if (!param_grad && !ray_grad) return 0;
     cudaStream_t st = (cudaStream_t)stream;
-    if (impl_version() == 2 && param_grad && !ray_grad && !scene->two_grid)
-        return render_backward_v2(scene, rcfg, n_rays, n_samples, rays_o, rays_d, z_vals, raw, target_rgb, target_d, acc,
-                                  loss_grads, g_rgb, g_depth, g_raw, scratch, st);
     if (ray_grad) {
         MNE_CHECK_CUDA(cudaMemsetAsync(g_rays_o, 0, sizeof(float) * 3 * (size_t)n_rays, st));
         MNE_CHECK_CUDA(cudaMemsetAsync(g_rays_d, 0, sizeof(float) * 3 * (size_t)n_rays, st));
     }
+    if (impl_version() == 2 && !scene->two_grid)
+        return render_backward_v2(scene, rcfg, n_rays, n_samples, rays_o, rays_d, z_vals, raw, target_rgb, target_d, acc,
+                                  loss_grads, g_rgb, g_depth, g_raw, scratch, g_rays_o, g_rays_d, param_grad, st);
     BwdParams P{};
     P.sc = *scene; P.rc = *rcfg; P.n_rays = n_rays; P.n_samples = n_samples;
     P.rays_per_group = choose_rays_per_group(n_rays, n_samples, sm_count() * (scene->two_grid ? bwd_warps<true>() : bwd_warps<false>()));

@@ -28,13 +28,22 @@ struct NetT {
     static constexpr int OFF_VCT = OFF_VGT + 16 * S1;    // V1T colour feat [64][32 j] (two grids)
     static constexpr int OFF_W2T = OFF_VCT + (TWO ? 64 * S1 : 0);   // W2T [32 j][16 i] stride 24
     static constexpr int OFF_V2T = OFF_W2T + 32 * kGeoStride;       // V2T [32 j][8 c]
-    static constexpr int FLOATS = OFF_V2T + 32 * kRgbStride;
+    static constexpr int OFF_W1BT = OFF_V2T + 32 * kRgbStride;      // W1T blob rows [48][32 j]   (ray gradients only)
+    static constexpr int OFF_V1BT = OFF_W1BT + 48 * S1;             // V1T blob rows [48][32 j]
+    static constexpr int FLOATS_NORAY = OFF_W1BT;
+    static constexpr int FLOATS_RAY = OFF_V1BT + 48 * S1;
 };
 
-template <bool TWO>
+template <bool TWO, bool RAY>
 __device__ __forceinline__ void load_weights_t(const MneSceneDesc& sc, float* WT, int tid, int nthreads) {
     using N = NetV2<TWO>;
     using T = NetT<TWO>;
+    if (RAY)
+        for (int i = tid; i < 48 * 32; i += nthreads) {
+            const int k = i >> 5, j = i & 31;
+            WT[T::OFF_W1BT + k * T::S1 + j] = sc.w_sdf0[j * N::K1 + 64 + k];
+            WT[T::OFF_V1BT + k * T::S1 + j] = sc.w_col0[j * N::IN_COL + k];
+        }
     for (int i = tid; i < 64 * 32; i += nthreads) {
         const int k = i >> 5, j = i & 31;
         WT[T::OFF_W1T + k * T::S1 + j] = sc.w_sdf0[j * N::K1 + k];
@@ -55,9 +64,10 @@ __device__ __forceinline__ void load_weights_t(const MneSceneDesc& sc, float* WT
 template <bool TWO> __host__ __device__ constexpr int bwd2_warp_floats() {
     return kTilePts * (kXStride + (TWO ? kCStride : 0) + 2 * kActStride + kGeoStride + kRgbStride);
 }
-template <bool TWO>
+template <bool TWO, bool RAY>
 constexpr size_t bwd2_smem_bytes() {
-    return sizeof(float4) * (size_t)NetV2<TWO>::W4_COUNT + sizeof(float) * (size_t)(NetT<TWO>::FLOATS + kBwdWarps * bwd2_warp_floats<TWO>());
+    return sizeof(float4) * (size_t)NetV2<TWO>::W4_COUNT +
+           sizeof(float) * (size_t)((RAY ? NetT<TWO>::FLOATS_RAY : NetT<TWO>::FLOATS_NORAY) + kBwdWarps * bwd2_warp_floats<TWO>());
 }
 
 struct PtsBwdParams {
@@ -68,6 +78,8 @@ struct PtsBwdParams {
     const float* rays_d;
     const float* z_vals;
     const float4* draw;      // [n_pts] d loss / d raw
+    float* g_rays_o;         // [N,3] accumulated into (zeroed by the entry point), or NULL
+    float* g_rays_d;
 };
 
 __device__ __forceinline__ void mma_1x(float (&d)[4], float a0, float a1, float a2, float a3, float b0, float b1) {
@@ -97,7 +109,7 @@ __device__ __forceinline__ void outer_mma(float (&acc)[NACC][4], const float* __
     }
 }
 
-template <bool TWO, bool VEC>
+template <bool TWO, bool VEC, bool RAY, bool PARAM>
 __global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __grid_constant__ PtsBwdParams P) {
     using N = NetV2<TWO>;
     using T = NetT<TWO>;
@@ -106,7 +118,7 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __g
     extern __shared__ __align__(16) float4 smem4[];
     float4* W4 = smem4;
     float* WT = reinterpret_cast<float*>(smem4 + N::W4_COUNT);
-    float* tiles = WT + T::FLOATS;
+    float* tiles = WT + (RAY ? T::FLOATS_RAY : T::FLOATS_NORAY);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float* X = tiles + warp * WF;
     float* CFt = X + kTilePts * kXStride;
@@ -119,7 +131,7 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __g
                   O_GEO = O_DY + kTilePts * kActStride, O_DRGB = O_GEO + kTilePts * kGeoStride;
 
     load_weights_v2<TWO>(P.sc, W4, threadIdx.x, blockDim.x);
-    load_weights_t<TWO>(P.sc, WT, threadIdx.x, blockDim.x);
+    load_weights_t<TWO, RAY>(P.sc, WT, threadIdx.x, blockDim.x);
     __syncthreads();
 
     const int64_t n_tiles = (P.n_pts + kTilePts - 1) / kTilePts;
@@ -226,10 +238,10 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __g
             }
         }
         if (t == 3) { dout[1][1] = dr_lo.w; dout[1][3] = dr_hi.w; }     // column 15 = sdf
-        __syncthreads();                                         // A: every warp's ACT / DY / GEO / DRGB / X are published
+        if (PARAM) __syncthreads();                              // A: every warp's ACT / DY / GEO / DRGB / X are published
 
         // ---- 4. weight gradients, phase 1 (colour net)
-        if (warp < V1_BLOCKS) {
+        if (PARAM && warp < V1_BLOCKS) {
             for (int w = 0; w < NW; ++w) {
                 const float* src = tiles + w * WF;
                 const float* A; int as, m0;
@@ -240,13 +252,13 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __g
                 outer_mma<4, 0>(acc_v1, A, as, m0, src + O_DY, kActStride, g, t);
             }
         }
-        if (warp == v2_owner0 || warp == v2_owner0 + 1) {
+        if (PARAM && (warp == v2_owner0 || warp == v2_owner0 + 1)) {
             for (int w = 0; w < NW; ++w) {
                 const float* src = tiles + w * WF;
                 outer_mma<1, 0>(acc_v2, src + O_ACT, kActStride, (warp - v2_owner0) * 16, src + O_DRGB, kRgbStride, g, t);
             }
         }
-        __syncthreads();                                         // B: phase-1 tiles may be overwritten
+        if (PARAM) __syncthreads();                              // B: phase-1 tiles may be overwritten
 
         // ---- 5. sdf branch backward
         float dh1[4][4];
@@ -278,10 +290,11 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __g
                 store_frag(CFt, kCStride, n, g, t, d);
             }
         }
-        __syncthreads();                                         // C
+        if (PARAM) __syncthreads();                              // C
 
         // ---- 6. weight gradients, phase 2 (sdf net)
-        if (warp < 7) {
+        if (!PARAM) {
+        } else if (warp < 7) {
             for (int w = 0; w < NW; ++w) {
                 const float* src = tiles + w * WF;
                 outer_mma<4, 0>(acc_w1, src, kXStride, warp * 16, src + O_DY, kActStride, g, t);
@@ -294,7 +307,7 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __g
                 outer_mma<2, 2>(acc_w1, src + O_ACT, kActStride, 16, src + O_GEO, kGeoStride, g, t);
             }
         }
-        __syncthreads();                                         // D: X may be overwritten with d feat
+        if (PARAM) __syncthreads();                              // D: X may be overwritten with d feat
 
         // ---- 7. d feat = d_h1 . W1[:, :64] -> X columns [0, 64)
 #pragma unroll
@@ -307,9 +320,50 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __g
             }
             store_frag(X, kXStride, n, g, t, d);
         }
+        float dpt[3] = {0.f, 0.f, 0.f};                          // d loss / d point through OneBlob (lanes 0..15)
+        unsigned gflags = 0;                                     // per tap: bit 2t = x gradient on, 2t+1 = y gradient on
+        if (RAY) {
+            // d blob = d_h1 . W1[:, 64:112] + d_hc . col0[:, 0:48] -> the blob segment of X
+#pragma unroll
+            for (int n = 0; n < 6; ++n) {
+                float d[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) {
+                    const float2 b1 = *reinterpret_cast<const float2*>(WT + T::OFF_W1BT + (n * 8 + g) * T::S1 + ks * 8 + 2 * t);
+                    mma_1x(d, dh1[ks][0], dh1[ks][2], dh1[ks][1], dh1[ks][3], b1.x, b1.y);
+                    const float2 b2 = *reinterpret_cast<const float2*>(WT + T::OFF_V1BT + (n * 8 + g) * T::S1 + ks * 8 + 2 * t);
+                    mma_1x(d, dhc[ks][0], dhc[ks][2], dhc[ks][1], dhc[ks][3], b2.x, b2.y);
+                }
+                store_frag(X + kBlobCol, kXStride, n, g, t, d);
+            }
+            __syncwarp();
+            float d0 = 0.f, d1 = 0.f;
+            if (half == 0) {
+                d0 = oneblob16_sparse_grad(blob_input(px, P.sc.bbox_lo[0], P.sc.bbox_ext[0]), row + kBlobCol);
+                d1 = oneblob16_sparse_grad(blob_input(py, P.sc.bbox_lo[1], P.sc.bbox_ext[1]), row + kBlobCol + 16);
+            } else {
+                d0 = oneblob16_sparse_grad(blob_input(pz, P.sc.bbox_lo[2], P.sc.bbox_ext[2]), row + kBlobCol + 32);
+            }
+            const float dz = __shfl_sync(0xffffffffu, d0, p_loc + 16);
+            dpt[0] = (float)((double)d0 / P.sc.bbox_ext[0]);
+            dpt[1] = (float)((double)d1 / P.sc.bbox_ext[1]);
+            dpt[2] = (float)((double)dz / P.sc.bbox_ext[2]);
+            // which taps let the coordinate gradient through (pixel coordinate not clamped)
+            const float nn[3] = {plane_coord(px, P.sc.bound_lo[0], P.sc.bound_ext[0]), plane_coord(py, P.sc.bound_lo[1], P.sc.bound_ext[1]),
+                                 plane_coord(pz, P.sc.bound_lo[2], P.sc.bound_ext[2])};
+#pragma unroll
+            for (int tp = 0; tp < (TWO ? 12 : 6); ++tp) {
+                const int a = (tp % 6) >> 1;
+                const MnePlaneDesc& Pl = P.sc.planes[tp];
+                const AxisTap tx = axis_tap((a == 2) ? nn[1] : nn[0], Pl.W), ty = axis_tap((a == 0) ? nn[1] : nn[2], Pl.H);
+                gflags |= (tx.grad_on ? 1u : 0u) << (2 * tp) | (ty.grad_on ? 1u : 0u) << (2 * tp + 1);
+            }
+            __syncwarp();
+        }
         // tap table again (the blob segment is spent), then scatter
         if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 0);
         __syncwarp();
+        float dn_keep[3] = {0.f, 0.f, 0.f};                      // d loss / d normalised plane coordinates of this lane's point
         // ---- 8. plane gradient scatter: lane = (corner, 4-channel group)
         for (int grp = 0; grp < (TWO ? 2 : 1); ++grp) {
             if (grp == 1) {
@@ -322,21 +376,60 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __g
             const int c = lane >> 3, q = lane & 7;
             for (int p = 0; p < np; ++p) {
                 const float* seg = X + p * kXStride + kBlobCol;
+                const unsigned pflags = RAY ? __shfl_sync(0xffffffffu, gflags, p) : 0u;
+                float dn[3] = {0.f, 0.f, 0.f};
 #pragma unroll
                 for (int l = 0; l < 2; ++l) {
 #pragma unroll
                     for (int a = 0; a < 3; ++a) {
                         const int tp = a * 2 + l;
-                        float* gp = P.sc.planes[grp * 6 + tp].grad;
-                        if (!gp) continue;
+                        const MnePlaneDesc& Pl = P.sc.planes[grp * 6 + tp];
+                        float* gp = PARAM ? Pl.grad : nullptr;
                         if (VEC) {
                             const float4 gv = *reinterpret_cast<const float4*>(gsrc + p * gstride + l * 32 + q * 4);
                             const unsigned off = __float_as_uint(seg[8 * tp + c]);
                             const float w = seg[8 * tp + 4 + c];
-                            if (w != 0.f)
+                            if (gp && w != 0.f)
                                 atomicAdd(reinterpret_cast<float4*>(gp + off) + q, make_float4(gv.x * w, gv.y * w, gv.z * w, gv.w * w));
+                            const unsigned fl = (pflags >> (2 * (grp * 6 + tp))) & 3u;
+                            if (RAY && fl) {
+                                // D_c = <d feat, texel c>, reduced over this corner's 8 lanes, then shared with everyone
+                                const float4 v = __ldg(reinterpret_cast<const float4*>(Pl.data + off) + q);
+                                float dc = gv.x * v.x + gv.y * v.y + gv.z * v.z + gv.w * v.w;
+                                dc += __shfl_xor_sync(0xffffffffu, dc, 1); dc += __shfl_xor_sync(0xffffffffu, dc, 2);
+                                dc += __shfl_xor_sync(0xffffffffu, dc, 4);
+                                const float d00 = __shfl_sync(0xffffffffu, dc, 0), d01 = __shfl_sync(0xffffffffu, dc, 8),
+                                            d10 = __shfl_sync(0xffffffffu, dc, 16), d11 = __shfl_sync(0xffffffffu, dc, 24);
+                                const float4 ww = *reinterpret_cast<const float4*>(seg + 8 * tp + 4);
+                                const float wy0 = ww.x + ww.y, wy1 = ww.z + ww.w, wx0 = ww.x + ww.z, wx1 = ww.y + ww.w;
+                                const int ax = (a == 2) ? 1 : 0, ay = (a == 0) ? 1 : 2;
+                                if (fl & 1u) dn[ax] += ((d01 - d00) * wy0 + (d11 - d10) * wy1) * (0.5f * (float)(Pl.W - 1));
+                                if (fl & 2u) dn[ay] += ((d10 - d00) * wx0 + (d11 - d01) * wx1) * (0.5f * (float)(Pl.H - 1));
+                            }
+                        } else if (RAY) {
+                            // strided planes: lane = channel, corner dot products by a full-warp reduction
+                            const float gch = gsrc[p * gstride + l * 32 + lane];
+                            const float* vb = Pl.data + (int64_t)lane * Pl.stride_c;
+                            float dcs[4];
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) dcs[k] = warp_sum(gch * __ldg(vb + __float_as_uint(seg[8 * tp + k])));
+                            if (gp) {
+                                float* gb = gp + (int64_t)lane * Pl.stride_c;
+#pragma unroll
+                                for (int k = 0; k < 4; ++k) {
+                                    const float w = seg[8 * tp + 4 + k];
+                                    if (w != 0.f) atomicAdd(gb + __float_as_uint(seg[8 * tp + k]), gch * w);
+                                }
+                            }
+                            const unsigned fl = (pflags >> (2 * (grp * 6 + tp))) & 3u;
+                            const float4 ww = *reinterpret_cast<const float4*>(seg + 8 * tp + 4);
+                            const float wy0 = ww.x + ww.y, wy1 = ww.z + ww.w, wx0 = ww.x + ww.z, wx1 = ww.y + ww.w;
+                            const int ax = (a == 2) ? 1 : 0, ay = (a == 0) ? 1 : 2;
+                            if (fl & 1u) dn[ax] += ((dcs[1] - dcs[0]) * wy0 + (dcs[3] - dcs[2]) * wy1) * (0.5f * (float)(Pl.W - 1));
+                            if (fl & 2u) dn[ay] += ((dcs[2] - dcs[0]) * wx0 + (dcs[3] - dcs[1]) * wx1) * (0.5f * (float)(Pl.H - 1));
+                        } else if (!gp) {
+                            continue;
                         } else {
-                            const MnePlaneDesc& Pl = P.sc.planes[grp * 6 + tp];
                             const float gch = gsrc[p * gstride + l * 32 + lane];
                             float* gb = gp + (int64_t)lane * Pl.stride_c;
 #pragma unroll
@@ -347,12 +440,25 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __g
                         }
                     }
                 }
+                if (RAY && p_loc == p) { dn_keep[0] += dn[0]; dn_keep[1] += dn[1]; dn_keep[2] += dn[2]; }
             }
         }
+        if (RAY && half == 0 && p_loc < np) {
+            const int64_t q2 = pt0 + p_loc;
+            const int64_t ray = q2 / P.n_samples;
+            const float z = P.z_vals[q2];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const float gpnt = dn_keep[a] * (2.0f / P.sc.bound_ext[a]) + dpt[a];
+                atomicAdd(P.g_rays_o + ray * 3 + a, gpnt);
+                atomicAdd(P.g_rays_d + ray * 3 + a, gpnt * z);
+            }
+        }
+        if (RAY) __syncwarp();
     }
 
     // ---- flush the register-resident weight gradients (once per CTA)
-    {
+    if (PARAM) {
         // d col0^T block: rows = inputs (blk*16 + g, +8), cols = j
         if (warp < V1_BLOCKS && P.sc.g_col0) {
 #pragma unroll
@@ -481,28 +587,36 @@ __global__ void __launch_bounds__(256) rays_bwd_kernel(const RayBwdParams P) {
 int check_scene(const MneSceneDesc* sc, const char* who, bool need_grads);
 int sm_count();
 
-template <bool TWO, bool VEC>
+template <bool TWO, bool VEC, bool RAY, bool PARAM>
 static int launch_points_bwd(const PtsBwdParams& P, cudaStream_t stream) {
-    const size_t smem = bwd2_smem_bytes<TWO>();
+    const size_t smem = bwd2_smem_bytes<TWO, RAY>();
     static bool configured[64] = {};
     int dev = 0;
     MNE_CHECK_CUDA(cudaGetDevice(&dev));
     if (dev >= 64 || !configured[dev]) {
-        MNE_CHECK_CUDA(cudaFuncSetAttribute(points_bwd_kernel<TWO, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        MNE_CHECK_CUDA(cudaFuncSetAttribute(points_bwd_kernel<TWO, VEC, RAY, PARAM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (dev < 64) configured[dev] = true;
     }
     const int64_t n_tiles = (P.n_pts + kTilePts - 1) / kTilePts;
     const int blocks = (int)max((int64_t)1, min((n_tiles + kBwdWarps - 1) / kBwdWarps, (int64_t)sm_count()));
-    points_bwd_kernel<TWO, VEC><<<blocks, kBwdWarps * 32, smem, stream>>>(P);
+    points_bwd_kernel<TWO, VEC, RAY, PARAM><<<blocks, kBwdWarps * 32, smem, stream>>>(P);
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
 
-// v2 backward for parameter gradients (ray gradients are served by the v1 kernel, see render_bwd.cu)
+template <bool VEC>
+static int dispatch_points_bwd(const PtsBwdParams& P, bool ray, bool param, cudaStream_t st) {
+    if (ray && param) return launch_points_bwd<false, VEC, true, true>(P, st);
+    if (ray) return launch_points_bwd<false, VEC, true, false>(P, st);
+    return launch_points_bwd<false, VEC, false, true>(P, st);
+}
+
+// v2 backward (one grid; two grids do not fit this kernel's shared-memory plan and stay on the v1 kernel)
 int render_backward_v2(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples,
                        const float* rays_o, const float* rays_d, const float* z_vals, const float* raw,
                        const float* target_rgb, const float* target_d, const double* acc, const float* loss_grads,
-                       const float* g_rgb, const float* g_depth, const float* g_raw, void* scratch, cudaStream_t st) {
+                       const float* g_rgb, const float* g_depth, const float* g_raw, void* scratch, float* g_rays_o,
+                       float* g_rays_d, bool param_grad, cudaStream_t st) {
     RayBwdParams R{};
     R.rc = *rcfg; R.n_rays = n_rays; R.n_samples = n_samples; R.z_vals = z_vals; R.raw = raw; R.target_rgb = target_rgb;
     R.target_d = target_d; R.acc = acc; R.loss_grads = loss_grads; R.g_rgb = g_rgb; R.g_depth = g_depth; R.g_raw = g_raw;
@@ -513,8 +627,9 @@ int render_backward_v2(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int3
     PtsBwdParams P{};
     P.sc = *scene; P.n_pts = (int64_t)n_rays * n_samples; P.n_samples = n_samples;
     P.rays_o = rays_o; P.rays_d = rays_d; P.z_vals = z_vals; P.draw = reinterpret_cast<const float4*>(scratch);
-    // (two grids do not fit this kernel's shared-memory plan yet: the caller routes them to the v1 kernel)
-    return planes_vectorizable(*scene) ? launch_points_bwd<false, true>(P, st) : launch_points_bwd<false, false>(P, st);
+    P.g_rays_o = g_rays_o; P.g_rays_d = g_rays_d;
+    const bool ray = g_rays_o != nullptr;
+    return planes_vectorizable(*scene) ? dispatch_points_bwd<true>(P, ray, param_grad, st) : dispatch_points_bwd<false>(P, ray, param_grad, st);
 }
 
 }  // namespace mne

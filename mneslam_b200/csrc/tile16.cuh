@@ -241,6 +241,29 @@ __device__ __forceinline__ void oneblob16_sparse(float x, float* o) {
     o[kBins - 1] += 1.0f - (quartic_cdf((1.0f - x) + 1.0f) - quartic_cdf((0.0f - x) - 1.0f));
 }
 
+// sum_b gb[b] * d blob_b / dx, sparse like oneblob16_sparse (gb: 16 upstream values in shared memory)
+__device__ __forceinline__ float oneblob16_sparse_grad(float x, const float* gb) {
+    float acc = 0.0f;
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+        const float sh = (s == 0) ? 0.0f : ((s == 1) ? -1.0f : 1.0f);
+        const float c = x - sh;
+        const float fb = floorf(c * (float)kBins);
+        if (fb < -2.0f || fb > (float)kBins + 1.0f) continue;
+        const int bc = (int)fb;
+        float f[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) f[j] = quartic_pdf(((float)(bc - 1 + j) * (1.0f / kBins) - x) + sh);
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            const int b = bc - 1 + j;
+            if (b >= 0 && b < kBins) acc += gb[b] * (f[j] - f[j + 1]);     // d/dx cdf(e - x + sh) = -pdf
+        }
+    }
+    acc += gb[kBins - 1] * (quartic_pdf((1.0f - x) + 1.0f) - quartic_pdf((0.0f - x) - 1.0f));
+    return acc;
+}
+
 // ---------------------------------------------------------------------------------------------
 // decoder forward on the tensor pipe for one 16-point tile.
 // X: tile [16][kXStride] (feat | blob); CFt: colour features [16][kCStride] (two grids).

@@ -7,9 +7,10 @@ A "step" is ONE mapping iteration of the reference's hot loop (mp_slam/mapper.py
 room0 configuration (BASELINE.json configs[1]): a 2048-ray batch drawn from a synthetic 20-keyframe ray
 database, 43 samples per ray (88 064 points), forward + losses + backward (plane, decoder gradients) + Adam.
 `value` = points / s of the whole job with all inputs resident in HBM (the step is captured in a CUDA graph);
-`e2e` = the same iteration driven through the drop-in JointEncoding class (forward / loss.backward() /
-torch.optim.Adam, i.e. the reference's own call sites) with the ray batch coming from pinned HOST memory and the
-loss read back to the host every step.  Multi-GPU (torchrun): every rank renders its own 2048-ray shard of a
+`e2e` = the same iteration through the library's iteration driver (FusedMapper.step over the C ABI) with the ray batch
+coming from pinned HOST memory and the loss read back to the host every step, no CUDA graph; `e2e_dropin` = the
+drop-in JointEncoding class driven exactly like the reference's call sites (forward / loss.backward() /
+torch.optim.Adam) on the same host buffers.  Multi-GPU (torchrun): every rank renders its own 2048-ray shard of a
 global batch, loss accumulators and gradients are all-reduced over NCCL (weak scaling).
 """
 import argparse
@@ -232,7 +233,8 @@ def run_ours(args):
     gen = torch.Generator(device=dev)
     gen.manual_seed(1234 + rank)
 
-    launches_per_step = 3 + 1 + 1 + len(mapper.params)     # sample, fwd, finalize | bwd | tick | adam x params
+    # sample | points_fwd, rays_fwd | loss_finalize | rays_bwd, points_bwd | adam_tick, adam_segments
+    launches_per_step = 8
 
     def one_step():
         ro, rd, trgb, td = db.sample(n_rays)
@@ -350,22 +352,65 @@ def run_ours(args):
         loss_host.copy_(loss.detach().reshape(1), non_blocking=False)      # D2H read of the step's loss
         return float(loss_host[0])
 
-    for i in range(3):
-        e2e_step(i)
-    barrier()
-    k_e2e = min(args.steps, 30)
-    t0 = time.perf_counter()
-    e0.record()
-    for i in range(k_e2e):
-        e2e_step(i)
-    e1.record()
-    barrier()
-    ms_e2e = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3) / k_e2e
-    if world > 1:
-        t = torch.tensor([ms_e2e], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_e2e = float(t.item())
+    def fused_e2e_step(i):
+        # the repo's own iteration driver fed from HOST memory: H2D of the ray batch, one iteration, D2H of the loss
+        rays7 = host_rays[i % n_pool].to(dev, non_blocking=True)
+        ids = host_ids[i % n_pool].to(dev, non_blocking=True)
+        ro, rd, trgb, td = db.assemble(rays7, ids)
+        losses = mapper.step(ro, rd, trgb, td)
+        loss_host.copy_(mapper.total_loss(losses).reshape(1), non_blocking=False)
+        return float(loss_host[0])
+
+    def time_e2e(fn):
+        for i in range(3):
+            fn(i)
+        barrier()
+        k = min(args.steps, 30)
+        t0 = time.perf_counter()
+        e0.record()
+        for i in range(k):
+            fn(i)
+        e1.record()
+        barrier()
+        ms = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3) / k
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, k
+
+    ms_dropin, k_e2e = time_e2e(e2e_step)
+    # the fused driver shares the planes with the (now Parameter-wrapped) model: rebuild it on the same storage
+    mapper2 = FusedMapper(model, world_size=world)
+    mapper2.step_dev.copy_(mapper.step_dev)
+    mapper = mapper2
+    ms_e2e, k_e2e = time_e2e(fused_e2e_step)
     e2e_value = pts_per_rank * world / (ms_e2e * 1e-3)
+
+    # ---- tracking iteration (BASELINE config 3): ScanNet-shaped, 1024 rays x 117 samples, pose-only gradients
+    tracking = None
+    if world == 1:
+        from mneslam_b200.tracking import PoseTracker
+        tcfg = configs.scannet_scene0000_onegrid()
+        torch.manual_seed(1)
+        tmodel = JointEncoding(tcfg, torch.tensor(tcfg['mapping']['bound'], dtype=torch.float64)).to(dev)
+        tb = {k: v.to(dev) for k, v in synthetic.make_ray_batch(tcfg, 1024, seed=3).items()}
+        tracker = PoseTracker(tmodel, tb['c2w'], rot_rep='quat')
+        for _ in range(5):
+            tracker.step(tb['dirs_cam'], tb['target_rgb'], tb['target_d'])
+        torch.cuda.synchronize()
+        n_it = 20
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(n_it):
+            tracker.step(tb['dirs_cam'], tb['target_rgb'], tb['target_d'])
+        e1.record()
+        torch.cuda.synchronize()
+        tracking = {'ms_per_iter': max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3) / n_it, 'iters': n_it,
+                    'workload': 'ScanNet-shaped (620x460, scene0000 bound, one grid): 1024 rays x 117 samples, map frozen, '
+                                'quaternion + translation pose, Adam; eager PoseTracker.step (autograd over the fused kernels)',
+                    'points_per_iter': 1024 * 117}
+        del tmodel, tracker
 
     if rank == 0:
         peak, peak_src = measured_peak()
@@ -380,7 +425,12 @@ def run_ours(args):
             'gpu_launches': launches_per_step * args.steps,
             'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d_bytes, 'd2h_bytes_per_step': 4,
                     'ms_per_step': ms_e2e, 'steps': k_e2e,
-                    'path': 'JointEncoding.forward -> loss.backward() -> torch.optim.Adam.step(), rays from pinned host memory'},
+                    'path': 'FusedMapper.step (C-ABI: sample, forward, losses, backward, Adam) per iteration, ray batch copied '
+                            'from pinned host memory, loss copied back to the host, no CUDA graph'},
+            'e2e_dropin': {'value': pts_per_rank * world / (ms_dropin * 1e-3), 'unit': UNIT, 'ms_per_step': ms_dropin,
+                           'path': 'JointEncoding.forward -> loss.backward() -> torch.optim.Adam.step() (the reference call '
+                                   'sites unchanged), same host buffers'},
+            'tracking': tracking,
             'roofline': {'bound': 'hbm', 'kernel': 'render_bwd_kernel', 'achieved': bwd_gbs, 'peak': peak, 'unit': 'GB/s',
                          'frac': bwd_gbs / peak, 'traffic': ncu_traffic(), 'peak_source': peak_src,
                          'algorithmic_bytes_per_launch': pts_per_rank * ALG_BYTES_PER_POINT_BWD,

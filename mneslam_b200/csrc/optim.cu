@@ -58,6 +58,49 @@ __global__ void __launch_bounds__(256) adam_kernel(const AdamArgs a) {
     }
 }
 
+// Several parameter groups that live back to back in four flat buffers (same offsets in param / grad / exp_avg /
+// exp_avg_sq): one launch for the whole map instead of one per tensor, so the HBM pipes are not drained and
+// refilled between tensors.
+struct AdamSegments {
+    float* p;
+    float* g;
+    float* m;
+    float* v;
+    int n_seg;
+    int64_t end4[MNE_ADAM_MAX_SEGMENTS];      // exclusive end of each segment, in float4 units
+    float lr[MNE_ADAM_MAX_SEGMENTS], eps[MNE_ADAM_MAX_SEGMENTS], wd[MNE_ADAM_MAX_SEGMENTS];
+    float beta1, beta2;
+    const int64_t* step_dev;
+    int64_t step_host;
+    int zero_grad;
+};
+
+__global__ void __launch_bounds__(256) adam_segments_kernel(const __grid_constant__ AdamSegments s) {
+    const double t = (double)(s.step_dev ? *s.step_dev : s.step_host);
+    const float bc1 = (float)(1.0 - pow((double)s.beta1, t));
+    const float bc2_sqrt = (float)sqrt(1.0 - pow((double)s.beta2, t));
+    const int64_t n4 = s.end4[s.n_seg - 1];
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    float4* p4 = reinterpret_cast<float4*>(s.p);
+    float4* g4 = reinterpret_cast<float4*>(s.g);
+    float4* m4 = reinterpret_cast<float4*>(s.m);
+    float4* v4 = reinterpret_cast<float4*>(s.v);
+    int seg = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        while (i >= s.end4[seg]) ++seg;
+        AdamArgs a{};
+        a.beta1 = s.beta1; a.beta2 = s.beta2; a.eps = s.eps[seg]; a.weight_decay = s.wd[seg]; a.zero_grad = s.zero_grad;
+        const float step_size = (float)((double)s.lr[seg] / (double)bc1);
+        float4 p = p4[i], g = g4[i], m = m4[i], v = v4[i];
+        adam_one(p.x, g.x, m.x, v.x, a, step_size, bc2_sqrt);
+        adam_one(p.y, g.y, m.y, v.y, a, step_size, bc2_sqrt);
+        adam_one(p.z, g.z, m.z, v.z, a, step_size, bc2_sqrt);
+        adam_one(p.w, g.w, m.w, v.w, a, step_size, bc2_sqrt);
+        p4[i] = p; m4[i] = m; v4[i] = v;
+        if (s.zero_grad) g4[i] = g;
+    }
+}
+
 __global__ void tick_kernel(int64_t* step) { if (threadIdx.x == 0 && blockIdx.x == 0) *step += 1; }
 
 int sm_count();
@@ -88,6 +131,38 @@ extern "C" int mne_adam_step(float* param, float* grad, float* exp_avg, float* e
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     adam_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(a);
+    MNE_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int mne_adam_step_segments(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int32_t n_segments,
+                                      const int64_t* segment_ends, const float* lr, const float* eps,
+                                      const float* weight_decay, float beta1, float beta2, const int64_t* step_dev,
+                                      int64_t step_host, int32_t zero_grad, mne_stream_t stream) {
+    using namespace mne;
+    MNE_CHECK_ARG(param && grad && exp_avg && exp_avg_sq && segment_ends && lr && eps && weight_decay,
+                  "mne_adam_step_segments: null argument");
+    MNE_CHECK_ARG(n_segments >= 1 && n_segments <= MNE_ADAM_MAX_SEGMENTS, "mne_adam_step_segments: 1..%d segments supported, got %d",
+                  MNE_ADAM_MAX_SEGMENTS, n_segments);
+    MNE_CHECK_ARG(step_dev || step_host >= 1, "mne_adam_step_segments: step must be >= 1");
+    MNE_CHECK_ARG((((uintptr_t)param | (uintptr_t)grad | (uintptr_t)exp_avg | (uintptr_t)exp_avg_sq) & 15) == 0,
+                  "mne_adam_step_segments: buffers must be 16-byte aligned");
+    AdamSegments s{};
+    s.p = param; s.g = grad; s.m = exp_avg; s.v = exp_avg_sq; s.n_seg = n_segments;
+    int64_t prev = 0;
+    for (int i = 0; i < n_segments; ++i) {
+        MNE_CHECK_ARG(segment_ends[i] >= prev && (segment_ends[i] & 3) == 0,
+                      "mne_adam_step_segments: segment ends must be ascending multiples of 4 elements");
+        s.end4[i] = segment_ends[i] >> 2;
+        s.lr[i] = lr[i]; s.eps[i] = eps[i]; s.wd[i] = weight_decay[i];
+        prev = segment_ends[i];
+    }
+    if (prev == 0) return 0;
+    s.beta1 = beta1; s.beta2 = beta2; s.step_dev = step_dev; s.step_host = step_host; s.zero_grad = zero_grad;
+    int64_t blocks = ((prev >> 2) + 255) / 256;
+    const int64_t cap = (int64_t)sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    adam_segments_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

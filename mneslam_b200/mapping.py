@@ -35,7 +35,11 @@ def loss_weight_vector(cfg, is_co_sdf=None):
 
 
 class FusedMapper:
-    def __init__(self, model, is_co_sdf=None, process_group=None, world_size=1):
+    def __init__(self, model, is_co_sdf=None, process_group=None, world_size=1, adopt_parameters=True):
+        """``adopt_parameters``: move the planes and decoder weights into ONE flat buffer (each tensor keeps its
+        Python identity, shape and strides; only its storage changes), with gradients and Adam moments laid out
+        the same way, so that the optimiser is a single streaming launch and the multi-GPU gradient exchange a
+        single all-reduce."""
         ops.require_cuda()
         self.model, self.cfg = model, model.config
         self.world_size, self.group = world_size, process_group
@@ -46,26 +50,42 @@ class FusedMapper:
         mp = self.cfg['mapping']
         n_sdf_planes = 6
         # parameter groups of create_optimizer (mneslam_mp.py:459-469): (tensor, lr, eps, weight_decay)
-        self.params = [(w, mp['lr_decoder'], 1e-8, 1e-6) for w in weights]
-        self.params += [(p, mp['lr_embed'], 1e-15, 0.0) for p in planes[:n_sdf_planes]]
+        self.params = [(p, mp['lr_embed'], 1e-15, 0.0) for p in planes[:n_sdf_planes]]
         if not one_grid:
             self.params += [(p, mp['lr_embed_color'], 1e-15, 0.0) for p in planes[n_sdf_planes:]]
+        self.params += [(w, mp['lr_decoder'], 1e-8, 1e-6) for w in weights]
         self.betas = (0.9, 0.99)
-        # one flat gradient buffer (a single all-reduce); per-parameter views keep the parameter's strides
+        for p, *_ in self.params:
+            if not (p.is_contiguous() or p.is_contiguous(memory_format=torch.channels_last)) or p.numel() % 4:
+                raise ValueError('map parameters must be dense tensors with a multiple of 4 elements')
         total = sum(p.numel() for p, *_ in self.params)
         self.flat_grad = torch.zeros(total, dtype=torch.float32, device=self.dev)
+        self.flat_m = torch.zeros(total, dtype=torch.float32, device=self.dev)
+        self.flat_v = torch.zeros(total, dtype=torch.float32, device=self.dev)
+        self.flat_param = torch.empty(total, dtype=torch.float32, device=self.dev) if adopt_parameters else None
         self.grads, self.exp_avg, self.exp_avg_sq = [], [], []
+        seg_ends, seg_lr, seg_eps, seg_wd = [], [], [], []
         off = 0
-        for p, *_ in self.params:
+        for p, lr, eps, wd in self.params:
             n = p.numel()
             self.grads.append(torch.as_strided(self.flat_grad, p.shape, p.stride(), off))
-            self.exp_avg.append(torch.zeros_like(p))
-            self.exp_avg_sq.append(torch.zeros_like(p))
-            if not (p.is_contiguous() or p.is_contiguous(memory_format=torch.channels_last)) or n % 4:
-                raise ValueError('map parameters must be dense tensors with a multiple of 4 elements')
+            self.exp_avg.append(torch.as_strided(self.flat_m, p.shape, p.stride(), off))
+            self.exp_avg_sq.append(torch.as_strided(self.flat_v, p.shape, p.stride(), off))
+            if adopt_parameters:
+                view = torch.as_strided(self.flat_param, p.shape, p.stride(), off)
+                with torch.no_grad():
+                    view.copy_(p)
+                p.data = view                       # same tensor object for every outside holder, new storage
             off += n
-        self.weight_grads = self.grads[:4]
-        self.plane_grads = self.grads[4:]
+            if seg_lr and (seg_lr[-1], seg_eps[-1], seg_wd[-1]) == (lr, eps, wd):
+                seg_ends[-1] = off                  # merge neighbours with identical hyper-parameters
+            else:
+                seg_ends.append(off); seg_lr.append(lr); seg_eps.append(eps); seg_wd.append(wd)
+        self._segments = (len(seg_ends), (C.c_int64 * len(seg_ends))(*seg_ends), (C.c_float * len(seg_ends))(*seg_lr),
+                          (C.c_float * len(seg_ends))(*seg_eps), (C.c_float * len(seg_ends))(*seg_wd))
+        n_planes = len(planes)
+        self.plane_grads = self.grads[:n_planes]
+        self.weight_grads = self.grads[n_planes:]
         self.step_dev = torch.zeros(1, dtype=torch.int64, device=self.dev)
         self.loss_grads = torch.tensor(loss_weight_vector(self.cfg, is_co_sdf), dtype=torch.float32, device=self.dev)
         self.loss_weights = self.loss_grads.clone()
@@ -107,12 +127,19 @@ class FusedMapper:
         return losses
 
     def optimizer_step(self):
-        """all-reduce (multi-GPU) + Adam + zero_grad, one launch per parameter tensor."""
+        """all-reduce (multi-GPU) + Adam + zero_grad: one launch over the flat buffers (or one per tensor when the
+        parameters were not adopted)."""
         if self.world_size > 1:
             torch.distributed.all_reduce(self.flat_grad, group=self.group)
         lib = _lib.lib()
         st = ops._stream()
         _lib.check(lib.mne_adam_tick(self.step_dev.data_ptr(), st), 'mne_adam_tick')
+        if self.flat_param is not None:
+            n_seg, ends, lr, eps, wd = self._segments
+            _lib.check(lib.mne_adam_step_segments(self.flat_param.data_ptr(), self.flat_grad.data_ptr(), self.flat_m.data_ptr(),
+                                                  self.flat_v.data_ptr(), n_seg, ends, lr, eps, wd, self.betas[0], self.betas[1],
+                                                  self.step_dev.data_ptr(), 0, 1, st), 'mne_adam_step_segments')
+            return
         for (p, lr, eps, wd), g, m, v in zip(self.params, self.grads, self.exp_avg, self.exp_avg_sq):
             _lib.check(lib.mne_adam_step(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), lr,
                                          self.betas[0], self.betas[1], eps, wd, self.step_dev.data_ptr(), 0, 1, st),

@@ -90,3 +90,22 @@ def make_keyframe_db(cfg, n_kf=20, seed=0):
         rays[k, :, 3:6] = b['target_rgb']
         rays[k, :, 6:7] = b['target_d']
     return rays, poses
+
+
+def render_box_scene(cfg, c2w, dirs_cam, margin=0.15):
+    """Analytic RGB-D of the inside of an axis-aligned box (the scene bound shrunk by ``margin`` per side), seen
+    along the given camera-frame directions: z-depth of the first wall hit (directions have z = -1, so the ray
+    parameter IS the sensor depth) and a smooth position-dependent colour.  Used by the tracking test."""
+    b = torch.tensor(cfg['mapping']['bound'], dtype=torch.float32)
+    lo, hi = b[:, 0] + margin, b[:, 1] - margin
+    rays_d = torch.sum(dirs_cam[..., None, :] * c2w[:3, :3], -1)
+    o = c2w[:3, 3]
+    t_lo, t_hi = (lo - o) / rays_d, (hi - o) / rays_d
+    t_exit = torch.where(rays_d > 0, t_hi, t_lo)
+    t_exit = torch.where(rays_d.abs() < 1e-9, torch.full_like(t_exit, 1e9), t_exit)
+    depth = t_exit.min(-1).values
+    hit = o + rays_d * depth[:, None]
+    u = (hit - lo) / (hi - lo)
+    rgb = torch.stack([0.5 + 0.4 * torch.sin(6.0 * u[:, 0] + 1.0 * u[:, 2]), 0.5 + 0.4 * torch.sin(5.0 * u[:, 1] + 2.0),
+                       0.5 + 0.4 * torch.cos(4.0 * u[:, 2] + 3.0 * u[:, 0])], -1)
+    return rgb.clamp(0, 1), depth[:, None]

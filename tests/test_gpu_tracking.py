@@ -1,0 +1,100 @@
+"""Tracking on a frozen map (BASELINE.json: "tracking ATE within 5 % on a fixed synthetic trajectory").
+
+A small map is first fitted on the GPU to an analytic box scene, then a short synthetic trajectory is tracked
+twice from the same perturbed initial poses and with the same sample noise: by the product (fused kernels,
+ray-gradient-only backward) and by the CPU oracle (torch autograd).  The two ATEs must agree within 5 %."""
+import math
+
+import pytest
+import torch
+
+from mneslam_b200 import configs, pose, synthetic
+from mneslam_b200.mapping import FusedMapper
+from mneslam_b200.tracking import PoseTracker, ate_rmse, matrix_to_quaternion
+from oracle import joint_encoding as J
+from tests.gpu_util import build_model, flat_planes
+
+pytestmark = pytest.mark.gpu
+
+
+def _camera_dirs(cfg, n, gen):
+    H, W, fx, fy, cx, cy = 48, 64, 40.0, 40.0, 31.5, 23.5
+    pix = torch.randperm(H * W, generator=gen)[:n]
+    j, i = (pix // W).float(), (pix % W).float()
+    return torch.stack([(i - cx) / fx, -(j - cy) / fy, -torch.ones_like(i)], -1)
+
+
+def _pose(a):
+    ang = 0.25 * math.sin(2.0 * a)
+    R = pose.axis_angle_to_matrix(torch.tensor([[0.05, 1.0, 0.1]]) / 1.0099 * (ang + 1e-3))[0]
+    c2w = torch.eye(4)
+    c2w[:3, :3] = R
+    c2w[:3, 3] = torch.tensor([-0.25 + 0.5 * a, 0.05 + 0.1 * math.sin(3 * a), 0.05 * math.cos(2 * a)])
+    return c2w
+
+
+@pytest.mark.parametrize('rot_rep', ['quat', 'axis_angle'])
+def test_tracking_ate_matches_oracle(rot_rep):
+    cfg = configs.small_test_config(n_samples_d=13, n_range_d=7)
+    cfg['training']['rot_rep'] = rot_rep
+    cfg['training']['range_d'] = 0.15
+    bound = J.enlarged_bound(cfg)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    gen = torch.Generator().manual_seed(5)
+    model = build_model(cfg, bb, J.init_planes(cfg, bound, seed=4, std=0.01), J.init_weights(cfg, seed=4), as_params=False)
+
+    # ---- fit the map on a few keyframes of the analytic scene
+    mapper = FusedMapper(model)
+    for it in range(400):
+        c2w = _pose((it % 9) / 8.0)
+        dirs = _camera_dirs(cfg, 512, gen)
+        rgb, d = synthetic.render_box_scene(cfg, c2w, dirs)
+        ro, rd = pose.rays_from_c2w(c2w, dirs)
+        mapper.step(ro.contiguous().cuda(), rd.contiguous().cuda(), rgb.cuda(), d.cuda())
+    torch.cuda.synchronize()
+    planes_cpu = tuple([p.detach().cpu().contiguous() for p in grp] for grp in model.all_planes)
+    weights_cpu = {k: w.detach().cpu() for k, w in zip(('sdf0', 'sdf1', 'col0', 'col1'), model.decoder.weight_list())}
+
+    # ---- track a short trajectory, both implementations
+    n_frames, n_iters, n_rays = 6, 20, 256
+    S = synthetic.n_samples_total(cfg)
+    gt, est_gpu, est_cpu = [], [], []
+    t, m = cfg['training'], cfg['mapping']
+    for f in range(n_frames):
+        c2w_gt = _pose(0.1 + 0.8 * f / (n_frames - 1))
+        init = c2w_gt.clone()
+        init[:3, 3] += torch.tensor([0.03, -0.02, 0.025])
+        init[:3, :3] = pose.axis_angle_to_matrix(torch.tensor([[0.02, -0.015, 0.01]]))[0] @ c2w_gt[:3, :3]
+        dirs = _camera_dirs(cfg, n_rays, gen)
+        rgb, d = synthetic.render_box_scene(cfg, c2w_gt, dirs)
+        noises = [synthetic.make_noise(n_rays, S, seed=100 * f + i) for i in range(n_iters)]
+
+        tracker = PoseTracker(model, init.cuda(), rot_rep=rot_rep, lr_rot=2e-3, lr_trans=2e-3)
+        for i in range(n_iters):
+            tracker.step(dirs.cuda(), rgb.cuda(), d.cuda(), noise=noises[i].cuda())
+        est_gpu.append(tracker.trans.detach().cpu()[0])
+        for p in flat_planes(model) + list(model.decoder.parameters()):
+            assert p.grad is None or float(p.grad.abs().max()) == 0.0, 'the map must stay frozen while tracking'
+
+        # oracle: same parameterisation, torch autograd on the CPU
+        from mneslam_b200.tracking import matrix_to_axis_angle
+        rot0 = matrix_to_quaternion(init[:3, :3]) if rot_rep == 'quat' else matrix_to_axis_angle(init[:3, :3])
+        rot = rot0[None].clone().requires_grad_(True)
+        trans = init[None, :3, 3].clone().requires_grad_(True)
+        opt = torch.optim.Adam([{'params': [rot], 'lr': 2e-3}, {'params': [trans], 'lr': 2e-3}])
+        for i in range(n_iters):
+            opt.zero_grad()
+            Rm = J.quat_to_matrix(rot)[0] if rot_rep == 'quat' else J.axis_angle_to_matrix(rot)[0]
+            ro, rd = J.rays_from_pose(Rm, trans[0], dirs)
+            ret, _ = J.forward(cfg, planes_cpu, weights_cpu, bound, bb, ro, rd, rgb, d, noises[i])
+            J.total_loss(cfg, ret).backward()
+            opt.step()
+        est_cpu.append(trans.detach()[0])
+        gt.append(c2w_gt[:3, 3])
+
+    gt, est_gpu, est_cpu = torch.stack(gt), torch.stack(est_gpu), torch.stack(est_cpu)
+    init_err = float(torch.linalg.norm(torch.tensor([0.03, -0.02, 0.025])))
+    ate_gpu, ate_cpu = ate_rmse(est_gpu, gt), ate_rmse(est_cpu, gt)
+    raw_gpu = float((est_gpu - gt).norm(dim=1).mean())
+    assert raw_gpu < init_err, 'tracking must move the poses towards the ground truth (%g vs %g)' % (raw_gpu, init_err)
+    assert abs(ate_gpu - ate_cpu) <= 0.05 * ate_cpu + 1e-5, (ate_gpu, ate_cpu)

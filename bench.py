@@ -215,6 +215,8 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
     if world > 1:
+        if os.environ.get('NCCL_DEBUG', 'VERSION').upper() == 'VERSION':
+            os.environ['NCCL_DEBUG'] = 'WARN'        # keep NCCL's version banner out of the one-JSON-line stdout
         dist.init_process_group('nccl', device_id=dev)
 
     cfg = configs.replica_room0()
@@ -246,19 +248,25 @@ def run_ours(args):
     torch.cuda.synchronize()
 
     graph = None
-    if not args.no_graph and world == 1:
-        side = torch.cuda.Stream()
-        side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(side):
-            one_step()
-        torch.cuda.current_stream().wait_stream(side)
-        torch.cuda.synchronize()
-        graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph):
-            static_losses = one_step()
-        for _ in range(3):
-            graph.replay()
-        torch.cuda.synchronize()
+    if not args.no_graph:
+        # the whole iteration -- ray assembly, five kernels' worth of rendering, NCCL collectives, Adam -- in one graph
+        try:
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                one_step()
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                static_losses = one_step()
+            for _ in range(3):
+                graph.replay()
+            torch.cuda.synchronize()
+        except Exception as e:                      # e.g. a collective that cannot be captured: time it eagerly
+            print('bench.py: CUDA-graph capture failed (%r); timing eager launches' % (e,), file=sys.stderr)
+            graph = None
+            torch.cuda.synchronize()
 
     def run_steps(k):
         if graph is not None:

@@ -59,18 +59,29 @@ class FusedMapper:
             if not (p.is_contiguous() or p.is_contiguous(memory_format=torch.channels_last)) or p.numel() % 4:
                 raise ValueError('map parameters must be dense tensors with a multiple of 4 elements')
         total = sum(p.numel() for p, *_ in self.params)
-        self.flat_grad = torch.zeros(total, dtype=torch.float32, device=self.dev)
-        self.flat_m = torch.zeros(total, dtype=torch.float32, device=self.dev)
-        self.flat_v = torch.zeros(total, dtype=torch.float32, device=self.dev)
-        self.flat_param = torch.empty(total, dtype=torch.float32, device=self.dev) if adopt_parameters else None
+        if world_size > 1:
+            if not adopt_parameters:
+                raise ValueError('multi-GPU mapping needs adopt_parameters=True (flat buffers for the collectives)')
+            q = world_size * 4
+            padded = (total + q - 1) // q * q
+        else:
+            padded = total
+        self.total = total
+        self.flat_grad = torch.zeros(padded, dtype=torch.float32, device=self.dev)
+        # single GPU: full-length Adam moments; multi GPU: each rank keeps the moments of its own slice only
+        mv_len = padded // world_size
+        self.flat_m = torch.zeros(mv_len, dtype=torch.float32, device=self.dev)
+        self.flat_v = torch.zeros(mv_len, dtype=torch.float32, device=self.dev)
+        self.flat_param = torch.zeros(padded, dtype=torch.float32, device=self.dev) if adopt_parameters else None
         self.grads, self.exp_avg, self.exp_avg_sq = [], [], []
         seg_ends, seg_lr, seg_eps, seg_wd = [], [], [], []
         off = 0
         for p, lr, eps, wd in self.params:
             n = p.numel()
             self.grads.append(torch.as_strided(self.flat_grad, p.shape, p.stride(), off))
-            self.exp_avg.append(torch.as_strided(self.flat_m, p.shape, p.stride(), off))
-            self.exp_avg_sq.append(torch.as_strided(self.flat_v, p.shape, p.stride(), off))
+            if world_size == 1:
+                self.exp_avg.append(torch.as_strided(self.flat_m, p.shape, p.stride(), off))
+                self.exp_avg_sq.append(torch.as_strided(self.flat_v, p.shape, p.stride(), off))
             if adopt_parameters:
                 view = torch.as_strided(self.flat_param, p.shape, p.stride(), off)
                 with torch.no_grad():
@@ -81,8 +92,14 @@ class FusedMapper:
                 seg_ends[-1] = off                  # merge neighbours with identical hyper-parameters
             else:
                 seg_ends.append(off); seg_lr.append(lr); seg_eps.append(eps); seg_wd.append(wd)
-        self._segments = (len(seg_ends), (C.c_int64 * len(seg_ends))(*seg_ends), (C.c_float * len(seg_ends))(*seg_lr),
-                          (C.c_float * len(seg_ends))(*seg_eps), (C.c_float * len(seg_ends))(*seg_wd))
+        self._segments = self._pack_segments(seg_ends, list(zip(seg_lr, seg_eps, seg_wd)))
+        self.shards = None
+        if world_size > 1:
+            from .distributed import FlatShards
+            rank = torch.distributed.get_rank(process_group)
+            self.shards = FlatShards(total, world_size, rank, seg_ends, list(zip(seg_lr, seg_eps, seg_wd)))
+            self.grad_shard = torch.zeros(self.shards.shard_len, dtype=torch.float32, device=self.dev)
+            self._local_segments = self._pack_segments(self.shards.local_ends, self.shards.local_hparams)
         n_planes = len(planes)
         self.plane_grads = self.grads[:n_planes]
         self.weight_grads = self.grads[n_planes:]
@@ -91,6 +108,20 @@ class FusedMapper:
         self.loss_weights = self.loss_grads.clone()
         self._scratch = None
         self.last_losses = None
+        self.global_rays_override = None
+
+    @staticmethod
+    def _pack_segments(ends, hparams):
+        n = len(ends)
+        return (n, (C.c_int64 * n)(*ends), (C.c_float * n)(*[h[0] for h in hparams]),
+                (C.c_float * n)(*[h[1] for h in hparams]), (C.c_float * n)(*[h[2] for h in hparams]))
+
+    def _adam_segments(self, param, grad, m, v, segments, zero_grad):
+        n_seg, ends, lr, eps, wd = segments
+        _lib.check(_lib.lib().mne_adam_step_segments(param.data_ptr(), grad.data_ptr(), m.data_ptr(), v.data_ptr(), n_seg,
+                                                     ends, lr, eps, wd, self.betas[0], self.betas[1],
+                                                     self.step_dev.data_ptr(), 0, 1 if zero_grad else 0, ops._stream()),
+                   'mne_adam_step_segments')
 
     # ------------------------------------------------------------------------------------------
     def _scene(self, with_grads):
@@ -109,7 +140,8 @@ class FusedMapper:
         perturb = cfg['training']['perturb'] > 0.
         if perturb and noise is None:
             noise = torch.rand(n, s, device=dev)
-        rcfg = ops.make_render_cfg(cfg, norm_rays=n * self.world_size)
+        # the means of the losses run over the GLOBAL batch; ragged shards set global_rays_override
+        rcfg = ops.make_render_cfg(cfg, norm_rays=self.global_rays_override or n * self.world_size)
         scfg = ops.make_sample_cfg(tables, perturb)
         td = target_d.reshape(-1)
         acc = ops.new_acc(dev)
@@ -127,18 +159,21 @@ class FusedMapper:
         return losses
 
     def optimizer_step(self):
-        """all-reduce (multi-GPU) + Adam + zero_grad: one launch over the flat buffers (or one per tensor when the
-        parameters were not adopted)."""
-        if self.world_size > 1:
-            torch.distributed.all_reduce(self.flat_grad, group=self.group)
+        """Adam + zero_grad.  One GPU: one launch over the flat buffers (one per tensor when the parameters were not
+        adopted).  Several GPUs: reduce-scatter of the flat gradient, Adam on this rank's slice, all-gather of the
+        parameters (``mneslam_b200.distributed``)."""
         lib = _lib.lib()
         st = ops._stream()
         _lib.check(lib.mne_adam_tick(self.step_dev.data_ptr(), st), 'mne_adam_tick')
+        if self.world_size > 1:
+            from .distributed import sharded_optimizer_step
+
+            def adam_fn(param_slice, grad_slice, _ends, _hp):
+                self._adam_segments(param_slice, grad_slice, self.flat_m, self.flat_v, self._local_segments, False)
+            sharded_optimizer_step(self.flat_param, self.flat_grad, self.grad_shard, self.shards, adam_fn, self.group)
+            return
         if self.flat_param is not None:
-            n_seg, ends, lr, eps, wd = self._segments
-            _lib.check(lib.mne_adam_step_segments(self.flat_param.data_ptr(), self.flat_grad.data_ptr(), self.flat_m.data_ptr(),
-                                                  self.flat_v.data_ptr(), n_seg, ends, lr, eps, wd, self.betas[0], self.betas[1],
-                                                  self.step_dev.data_ptr(), 0, 1, st), 'mne_adam_step_segments')
+            self._adam_segments(self.flat_param, self.flat_grad, self.flat_m, self.flat_v, self._segments, True)
             return
         for (p, lr, eps, wd), g, m, v in zip(self.params, self.grads, self.exp_avg, self.exp_avg_sq):
             _lib.check(lib.mne_adam_step(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), lr,

@@ -364,3 +364,43 @@ def quat_to_matrix(q):
 def rays_from_pose(R, t, dirs_cam):
     """mp_slam/mapper.py:392-393: ``rays_d = sum_k dirs_k R[:, k]``, ``rays_o = t``."""
     return t[None, :].expand(dirs_cam.shape[0], 3), torch.sum(dirs_cam[:, None, :] * R, -1)
+
+
+# --------------------------------------------------------------------------------------------
+# the 16 loss accumulators of include/mneslam_b200.h, restated for the multi-GPU tests: every slot is a plain
+# sum over rays / samples, so shards add up; the losses are ratios of the summed slots.
+# --------------------------------------------------------------------------------------------
+def loss_accumulators(cfg, rend, target_rgb, target_d):
+    d = target_d.squeeze(-1)
+    z, sdf = rend['z_vals'], rend['raw'][..., 3]
+    valid = (d > 0.) & (d < cfg['cam']['depth_trunc'])
+    T = cfg['training']['trunc'] * cfg['data']['sc_factor']
+    front = (z < (d - T)[:, None])
+    back = (z > (d + T)[:, None])
+    near = (~front) & (~back) & (d > 0.)[:, None]
+    Tm = cfg['model']['truncation']
+    has_d = (d > 0)[:, None]
+    e_front = (z < (d - Tm)[:, None]) & has_d
+    e_back = (z > (d + Tm)[:, None]) & has_d
+    e_center = (z > (d - 0.4 * Tm)[:, None]) & (z < (d + 0.4 * Tm)[:, None]) & has_d
+    e_tail = (~e_front) & (~e_back) & (~e_center) & has_d
+    resid_e = (z + sdf * Tm - d[:, None]) ** 2
+    resid_co = (z + sdf * T - d[:, None]) ** 2
+    fs = (sdf - 1.0) ** 2
+    acc = torch.zeros(16, dtype=torch.float64)
+    acc[0], acc[1], acc[2] = valid.sum(), front.sum(), near.sum()
+    acc[3], acc[4], acc[5] = e_front.sum(), e_center.sum(), e_tail.sum()
+    acc[6] = ((rend['rgb'] - target_rgb) ** 2).double().sum()
+    acc[7] = (((rend['depth'] - d) ** 2) * valid).double().sum()
+    acc[8], acc[9] = (fs * front).double().sum(), (resid_co * near).double().sum()
+    acc[10], acc[11], acc[12] = (fs * e_front).double().sum(), (resid_e * e_center).double().sum(), (resid_e * e_tail).double().sum()
+    return acc
+
+
+def losses_from_accumulators(acc, n_rays_total, n_samples):
+    N, NS = float(n_rays_total), float(n_rays_total) * n_samples
+    fs_w = 1.0 - acc[1] / (acc[1] + acc[2])
+    sdf_w = 1.0 - acc[2] / (acc[1] + acc[2])
+    return {'rgb_loss': acc[6] / (3 * N), 'depth_loss': acc[7] / acc[0], 'co_fs_loss': acc[8] / NS * fs_w,
+            'co_sdf_loss': acc[9] / NS * sdf_w, 'e_fs_loss': acc[10] / acc[3], 'e_center_loss': acc[11] / acc[4],
+            'e_tail_loss': acc[12] / acc[5]}

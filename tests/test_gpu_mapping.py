@@ -130,3 +130,17 @@ def test_cuda_graph_replay_of_a_mapping_iteration():
     assert np.isfinite(hist).all()
     assert np.mean(hist[-10:]) < np.mean(hist[:10]), (hist[:3], hist[-3:])
     assert int(mapper.step_dev.item()) == 3 + 1 + 60      # warm-up, side-stream run, replays (capture runs nothing)
+
+
+def test_two_gpu_sharded_iteration_matches_single_gpu():
+    """Runs tests/multigpu_check.py under torchrun when two GPUs are visible (skipped on the one-GPU box)."""
+    import os
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs two GPUs')
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2', '--master-addr',
+                        '127.0.0.1', '--master-port', '29533', os.path.join(root, 'tests', 'multigpu_check.py')],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and 'multigpu_check ok' in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]

@@ -455,8 +455,14 @@ def run_ours(args):
             line['cpu_baseline'] = cpu_baseline_record(cfg, n_rays)
         print(json.dumps(line), flush=True)
     if world > 1:
+        # Tearing NCCL down while a captured graph still references its communicator hung the process once the JSON
+        # line was out: synchronise, meet at a barrier, and leave without the destructor chain.
+        torch.cuda.synchronize()
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def main():

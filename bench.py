@@ -439,7 +439,7 @@ def run_ours(args):
                            'path': 'JointEncoding.forward -> loss.backward() -> torch.optim.Adam.step() (the reference call '
                                    'sites unchanged), same host buffers'},
             'tracking': tracking,
-            'roofline': {'bound': 'hbm', 'kernel': 'render_bwd_kernel', 'achieved': bwd_gbs, 'peak': peak, 'unit': 'GB/s',
+            'roofline': {'bound': 'hbm', 'kernel': 'points_bwd_kernel', 'achieved': bwd_gbs, 'peak': peak, 'unit': 'GB/s',
                          'frac': bwd_gbs / peak, 'traffic': ncu_traffic(), 'peak_source': peak_src,
                          'algorithmic_bytes_per_launch': pts_per_rank * ALG_BYTES_PER_POINT_BWD,
                          'launch_us': us['bwd'],

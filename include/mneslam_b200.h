@@ -124,6 +124,17 @@ int mne_set_option(const char* key, int value);
 int mne_sample_rays(const MneSampleCfg* cfg, const MneRenderCfg* rcfg, int32_t n_rays, const float* target_d,
                     const float* noise, float* z_vals, double* acc, mne_stream_t stream);
 
+/* ---- importance sampling: sample_pdf (model/utils.py:65-104) on the coarse pass's weights and the re-sort of
+ * render_rays (model/scene_rep.py:393-397).  z_vals / weights [N,S] from the coarse pass; u = uniform numbers,
+ * [N,n_importance] when u_per_ray != 0, else one shared row [n_importance] (the deterministic linspace the
+ * reference uses when training.perturb == 0).  Outputs: z_out [N, S + n_importance] sorted; optional inds
+ * [N,n_importance] int32 (searchsorted bin indices), z_std [N], and, when acc and target_d are given, the mask
+ * counts of the FINAL sample positions added into acc slots 0..5. */
+int mne_sample_importance(const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples, int32_t n_importance,
+                          const float* z_vals, const float* weights, const float* u, int32_t u_per_ray,
+                          const float* target_d, float* z_out, int32_t* inds, float* z_std, double* acc,
+                          mne_stream_t stream);
+
 /* ---- forward: replaces run_network + raw2outputs/sdf2weights (model/scene_rep.py:183-230,303-317,384-386)
  * and the loss sums of JointEncoding.forward (:569-590).  Optional outputs may be NULL.  target_rgb /
  * target_d / acc NULL = no loss sums. */

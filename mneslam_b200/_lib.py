@@ -57,6 +57,8 @@ _SIGNATURES = {
     'mne_set_option': (C.c_int, [C.c_char_p, C.c_int]),
     'mne_sample_rays': (C.c_int, [C.POINTER(SampleCfg), C.POINTER(RenderCfg), C.c_int32, C.c_void_p, C.c_void_p,
                                   C.c_void_p, C.c_void_p, C.c_void_p]),
+    'mne_sample_importance': (C.c_int, [C.POINTER(RenderCfg), C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_int32] + [C.c_void_p] * 6),
     'mne_render_forward': (C.c_int, [C.POINTER(SceneDesc), C.POINTER(RenderCfg), C.c_int32, C.c_int32] +
                            [C.c_void_p] * 15),
     'mne_loss_finalize': (C.c_int, [C.POINTER(RenderCfg), C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -50,12 +50,17 @@ typedef struct MneHashDesc {
     int32_t base_resolution; /* 16 */
     float per_level_scale;
     uint32_t offsets[33];    /* entry offset of each level, offsets[n_levels] = total entries */
+    /* per-level grid scale (2^(l log2 pls) * base - 1) and resolution (ceil(scale) + 1), computed once on the host
+     * so that device and oracle use bit-identical values (an exp2f of the device could differ in the last bit) */
+    float level_scale[32];
+    uint32_t level_res[32];
 } MneHashDesc;
 
 /* Scene state read at call time (the reference reads model.all_planes / decoder weights at call time too:
  * SURVEY.md 8(b) "Attributes read/written from outside"). */
 typedef struct MneSceneDesc {
-    int32_t encoder;  /* 0 = tri-plane (live in the reference), 1 = hash grid */
+    int32_t encoder;  /* 0 = tri-plane (live in the reference), 1 = hash grid: 16 levels x 2 features, one table
+                       * (grid.oneGrid), forward and parameter gradients; no ray gradients through the table yet */
     int32_t two_grid; /* 1 when grid.oneGrid is False: colour planes / colour table present */
     int32_t n_bins;   /* OneBlob bins per dimension; must be 16 */
     int32_t c_dim;    /* plane channels; must be 32 */
@@ -188,6 +193,12 @@ int mne_render_backward_static(const MneSceneDesc* scene, const MneRenderCfg* rc
  * raw [M,4], geo [M,15], feat [M,F] (the embed=True output). */
 int mne_query_points(const MneSceneDesc* scene, int64_t n_pts, const float* pts, float* raw, float* geo,
                      float* feat, mne_stream_t stream);
+
+/* ---- hash-grid inspection: entry indices (within their level) of the 8 cell corners of each point at every
+ * level, for coordinates x01 [M,3] in [0,1]^3: indices [M, n_levels, 8] int32.  The table lookups of
+ * tiny-cuda-nn's grid encoding (encodings/grid.h grid_index / coherent prime hash), exposed so that parity
+ * tests can compare the one integer quantity of the encoder bit for bit. */
+int mne_hash_indices(const MneHashDesc* hash, int64_t n_pts, const float* x01, int32_t* indices, mne_stream_t stream);
 
 /* ---- optimiser: torch.optim.Adam.step() + zero_grad() of the mapping loop (mneslam_mp.py:459-469,
  * mp_slam/mapper.py:161-162), dense semantics, one pass: 16 B/param read + 16 B/param written.  All four

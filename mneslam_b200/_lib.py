@@ -28,7 +28,8 @@ class PlaneDesc(C.Structure):
 
 class HashDesc(C.Structure):
     _fields_ = [('table', C.c_void_p), ('grad', C.c_void_p), ('n_levels', C.c_int32), ('n_features', C.c_int32),
-                ('base_resolution', C.c_int32), ('per_level_scale', C.c_float), ('offsets', C.c_uint32 * 33)]
+                ('base_resolution', C.c_int32), ('per_level_scale', C.c_float), ('offsets', C.c_uint32 * 33),
+                ('level_scale', C.c_float * 32), ('level_res', C.c_uint32 * 32)]
 
 
 class SceneDesc(C.Structure):
@@ -67,6 +68,7 @@ _SIGNATURES = {
                             [C.c_void_p] * 15),
     'mne_render_backward_static': (C.c_int, [C.POINTER(SceneDesc), C.POINTER(RenderCfg), C.c_int32, C.c_int32] +
                                    [C.c_void_p] * 14),
+    'mne_hash_indices': (C.c_int, [C.POINTER(HashDesc), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     'mne_adam_tick': (C.c_int, [C.c_void_p, C.c_void_p]),
     'mne_adam_step': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float,
                                 C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),

@@ -44,8 +44,24 @@ int choose_rays_per_group(int n_rays, int n_samples, int total_warps) {
     return best_r;
 }
 
+int impl_version();
+
 int check_scene(const MneSceneDesc* sc, const char* who, bool) {
-    MNE_CHECK_ARG(sc->encoder == 0, "%s: encoder %d is not built into this library (0 = tri-plane)", who, sc->encoder);
+    MNE_CHECK_ARG(sc->encoder == 0 || sc->encoder == 1, "%s: encoder %d unknown (0 = tri-plane, 1 = hash grid)", who, sc->encoder);
+    if (sc->encoder == 1) {
+        const MneHashDesc& h = sc->hash[0];
+        MNE_CHECK_ARG(impl_version() == 2, "%s: the hash-grid encoder needs the tensor-pipe kernels (option impl = 2)", who);
+        MNE_CHECK_ARG(!sc->two_grid, "%s: the hash-grid encoder is built for one table (grid.oneGrid)", who);
+        MNE_CHECK_ARG(h.table && h.n_levels == 16 && h.n_features == 2, "%s: hash grid must have a table, 16 levels, 2 features", who);
+        MNE_CHECK_ARG((((uintptr_t)h.table | (uintptr_t)h.grad) & 7) == 0, "%s: hash table must be 8-byte aligned", who);
+        for (int l = 0; l < 16; ++l)
+            MNE_CHECK_ARG(h.offsets[l + 1] > h.offsets[l] && h.level_res[l] >= 2 && h.level_scale[l] > 0.f,
+                          "%s: hash level %d is empty or has no scale / resolution", who, l);
+        MNE_CHECK_ARG(sc->n_bins == kBins, "%s: n_bins = %d, this library is built for %d", who, sc->n_bins, kBins);
+        MNE_CHECK_ARG(sc->w_sdf0 && sc->w_sdf1 && sc->w_col0 && sc->w_col1, "%s: decoder weights missing", who);
+        for (int a = 0; a < 3; ++a) MNE_CHECK_ARG(sc->bbox_ext[a] > 0.0, "%s: empty bound on axis %d", who, a);
+        return 0;
+    }
     MNE_CHECK_ARG(sc->n_bins == kBins, "%s: n_bins = %d, this library is built for %d", who, sc->n_bins, kBins);
     MNE_CHECK_ARG(sc->c_dim == kCDim, "%s: c_dim = %d, this library is built for %d", who, sc->c_dim, kCDim);
     MNE_CHECK_ARG(sc->w_sdf0 && sc->w_sdf1 && sc->w_col0 && sc->w_col1, "%s: decoder weights missing", who);

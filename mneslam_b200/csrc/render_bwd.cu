@@ -489,7 +489,8 @@ extern "C" int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg
     MNE_CHECK_ARG(!loss_grads || (acc && target_rgb && target_d), "mne_render_backward: loss_grads needs acc, target_rgb and target_d");
     MNE_CHECK_ARG((g_rays_o == nullptr) == (g_rays_d == nullptr), "mne_render_backward: pass both g_rays_o and g_rays_d or neither");
     bool param_grad = scene->g_sdf0 || scene->g_sdf1 || scene->g_col0 || scene->g_col1;
-    for (int i = 0; i < (scene->two_grid ? 12 : 6); ++i) param_grad = param_grad || scene->planes[i].grad;
+    if (scene->encoder == 1) param_grad = param_grad || scene->hash[0].grad;
+    else for (int i = 0; i < (scene->two_grid ? 12 : 6); ++i) param_grad = param_grad || scene->planes[i].grad;
     const bool ray_grad = g_rays_o != nullptr;
     if (!param_grad && !ray_grad) return 0;
     cudaStream_t st = (cudaStream_t)stream;
@@ -497,7 +498,7 @@ extern "C" int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg
         MNE_CHECK_CUDA(cudaMemsetAsync(g_rays_o, 0, sizeof(float) * 3 * (size_t)n_rays, st));
         MNE_CHECK_CUDA(cudaMemsetAsync(g_rays_d, 0, sizeof(float) * 3 * (size_t)n_rays, st));
     }
-    if (impl_version() == 2 && !scene->two_grid)
+    if (impl_version() == 2 && (!scene->two_grid || scene->encoder == 1))
         return render_backward_v2(scene, rcfg, n_rays, n_samples, rays_o, rays_d, z_vals, raw, target_rgb, target_d, acc,
                                   loss_grads, g_rgb, g_depth, g_raw, scratch, g_rays_o, g_rays_d, param_grad, st);
     BwdParams P{};

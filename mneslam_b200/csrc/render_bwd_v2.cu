@@ -38,15 +38,17 @@ template <bool TWO, bool RAY>
 __device__ __forceinline__ void load_weights_t(const MneSceneDesc& sc, float* WT, int tid, int nthreads) {
     using N = NetV2<TWO>;
     using T = NetT<TWO>;
+    const bool hash = sc.encoder == 1;
     if (RAY)
         for (int i = tid; i < 48 * 32; i += nthreads) {
             const int k = i >> 5, j = i & 31;
-            WT[T::OFF_W1BT + k * T::S1 + j] = sc.w_sdf0[j * N::K1 + 64 + k];
+            WT[T::OFF_W1BT + k * T::S1 + j] = sc.w_sdf0[j * sdf0_in(hash) + sdf0_col(64 + k, hash)];
             WT[T::OFF_V1BT + k * T::S1 + j] = sc.w_col0[j * N::IN_COL + k];
         }
     for (int i = tid; i < 64 * 32; i += nthreads) {
         const int k = i >> 5, j = i & 31;
-        WT[T::OFF_W1T + k * T::S1 + j] = sc.w_sdf0[j * N::K1 + k];
+        const int col = sdf0_col(k, hash);
+        WT[T::OFF_W1T + k * T::S1 + j] = (col >= 0) ? sc.w_sdf0[j * sdf0_in(hash) + col] : 0.0f;
         if (TWO) WT[T::OFF_VCT + k * T::S1 + j] = sc.w_col0[j * N::IN_COL + kBlob + k];
     }
     for (int i = tid; i < 16 * 32; i += nthreads) {
@@ -109,7 +111,8 @@ __device__ __forceinline__ void outer_mma(float (&acc)[NACC][4], const float* __
     }
 }
 
-template <bool TWO, bool VEC, bool RAY, bool PARAM>
+// MODE: 0 = planes through strides, 1 = channels-last planes (vector gather / scatter), 2 = hash grid
+template <bool TWO, int MODE, bool RAY, bool PARAM>
 __global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __grid_constant__ PtsBwdParams P) {
     using N = NetV2<TWO>;
     using T = NetT<TWO>;
@@ -172,23 +175,33 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __g
             pz = __fadd_rn(P.rays_o[ray * 3 + 2], __fmul_rn(P.rays_d[ray * 3 + 2], z));
         }
         float* row = X + p_loc * kXStride;
-        if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 0);
-        __syncwarp();
-        if (VEC) gather16_vec(P.sc, 0, X + kBlobCol, kXStride, X, kXStride, np, lane);
-        else gather16(P.sc, 0, X + kBlobCol, kXStride, X, kXStride, np, lane);
-        __syncwarp();
-        if (TWO) {
-            if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 1);
+        const float bx0 = blob_input(px, P.sc.bbox_lo[0], P.sc.bbox_ext[0]);
+        const float by0 = blob_input(py, P.sc.bbox_lo[1], P.sc.bbox_ext[1]);
+        const float bz0 = blob_input(pz, P.sc.bbox_lo[2], P.sc.bbox_ext[2]);
+        if (MODE == 2) {
+            if (half == 0) { row[kBlobCol] = bx0; row[kBlobCol + 1] = by0; row[kBlobCol + 2] = bz0; }
             __syncwarp();
-            if (VEC) gather16_vec(P.sc, 1, X + kBlobCol, kXStride, CFt, kCStride, np, lane);
-            else gather16(P.sc, 1, X + kBlobCol, kXStride, CFt, kCStride, np, lane);
+            gather16_hash(P.sc.hash[0], X + kBlobCol, kXStride, X, kXStride, np, lane);
             __syncwarp();
+        } else {
+            if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 0);
+            __syncwarp();
+            if (MODE == 1) gather16_vec(P.sc, 0, X + kBlobCol, kXStride, X, kXStride, np, lane);
+            else gather16(P.sc, 0, X + kBlobCol, kXStride, X, kXStride, np, lane);
+            __syncwarp();
+            if (TWO) {
+                if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 1);
+                __syncwarp();
+                if (MODE == 1) gather16_vec(P.sc, 1, X + kBlobCol, kXStride, CFt, kCStride, np, lane);
+                else gather16(P.sc, 1, X + kBlobCol, kXStride, CFt, kCStride, np, lane);
+                __syncwarp();
+            }
         }
         if (half == 0) {
-            oneblob16_sparse(blob_input(px, P.sc.bbox_lo[0], P.sc.bbox_ext[0]), row + kBlobCol);
-            oneblob16_sparse(blob_input(py, P.sc.bbox_lo[1], P.sc.bbox_ext[1]), row + kBlobCol + 16);
+            oneblob16_sparse(bx0, row + kBlobCol);
+            oneblob16_sparse(by0, row + kBlobCol + 16);
         } else {
-            oneblob16_sparse(blob_input(pz, P.sc.bbox_lo[2], P.sc.bbox_ext[2]), row + kBlobCol + 32);
+            oneblob16_sparse(bz0, row + kBlobCol + 32);
         }
         // rows without a point must be finite (they are multiplied by zero gradients later)
         for (int p = np; p < kTilePts; ++p) {
@@ -360,12 +373,18 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __g
             }
             __syncwarp();
         }
-        // tap table again (the blob segment is spent), then scatter
-        if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 0);
+        // tap table (or hash coordinates) again -- the blob segment is spent -- then scatter
+        if (MODE == 2) {
+            if (half == 0) { row[kBlobCol] = bx0; row[kBlobCol + 1] = by0; row[kBlobCol + 2] = bz0; }
+            __syncwarp();
+            if (PARAM && P.sc.hash[0].grad) scatter16_hash(P.sc.hash[0], X + kBlobCol, kXStride, X, kXStride, np, lane);
+        } else if (half == 1) {
+            write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 0);
+        }
         __syncwarp();
         float dn_keep[3] = {0.f, 0.f, 0.f};                      // d loss / d normalised plane coordinates of this lane's point
         // ---- 8. plane gradient scatter: lane = (corner, 4-channel group)
-        for (int grp = 0; grp < (TWO ? 2 : 1); ++grp) {
+        for (int grp = 0; MODE != 2 && grp < (TWO ? 2 : 1); ++grp) {
             if (grp == 1) {
                 __syncwarp();
                 if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 1);
@@ -385,7 +404,7 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __g
                         const int tp = a * 2 + l;
                         const MnePlaneDesc& Pl = P.sc.planes[grp * 6 + tp];
                         float* gp = PARAM ? Pl.grad : nullptr;
-                        if (VEC) {
+                        if (MODE == 1) {
                             const float4 gv = *reinterpret_cast<const float4*>(gsrc + p * gstride + l * 32 + q * 4);
                             const unsigned off = __float_as_uint(seg[8 * tp + c]);
                             const float w = seg[8 * tp + 4 + c];
@@ -482,7 +501,9 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __g
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     const int k = warp * 16 + g + ((i & 2) ? 8 : 0), j = nb * 8 + 2 * t + (i & 1);
-                    atomicAdd(P.sc.g_sdf0 + j * N::K1 + k, acc_w1[nb][i]);
+                    const bool hash = MODE == 2;
+                    const int col = sdf0_col(k, hash);
+                    if (col >= 0) atomicAdd(P.sc.g_sdf0 + j * sdf0_in(hash) + col, acc_w1[nb][i]);
                 }
         }
         if (warp == 7 && P.sc.g_sdf1) {
@@ -587,28 +608,28 @@ __global__ void __launch_bounds__(256) rays_bwd_kernel(const RayBwdParams P) {
 int check_scene(const MneSceneDesc* sc, const char* who, bool need_grads);
 int sm_count();
 
-template <bool TWO, bool VEC, bool RAY, bool PARAM>
+template <bool TWO, int MODE, bool RAY, bool PARAM>
 static int launch_points_bwd(const PtsBwdParams& P, cudaStream_t stream) {
     const size_t smem = bwd2_smem_bytes<TWO, RAY>();
     static bool configured[64] = {};
     int dev = 0;
     MNE_CHECK_CUDA(cudaGetDevice(&dev));
     if (dev >= 64 || !configured[dev]) {
-        MNE_CHECK_CUDA(cudaFuncSetAttribute(points_bwd_kernel<TWO, VEC, RAY, PARAM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        MNE_CHECK_CUDA(cudaFuncSetAttribute(points_bwd_kernel<TWO, MODE, RAY, PARAM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (dev < 64) configured[dev] = true;
     }
     const int64_t n_tiles = (P.n_pts + kTilePts - 1) / kTilePts;
     const int blocks = (int)max((int64_t)1, min((n_tiles + kBwdWarps - 1) / kBwdWarps, (int64_t)sm_count()));
-    points_bwd_kernel<TWO, VEC, RAY, PARAM><<<blocks, kBwdWarps * 32, smem, stream>>>(P);
+    points_bwd_kernel<TWO, MODE, RAY, PARAM><<<blocks, kBwdWarps * 32, smem, stream>>>(P);
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
 
-template <bool VEC>
+template <int MODE>
 static int dispatch_points_bwd(const PtsBwdParams& P, bool ray, bool param, cudaStream_t st) {
-    if (ray && param) return launch_points_bwd<false, VEC, true, true>(P, st);
-    if (ray) return launch_points_bwd<false, VEC, true, false>(P, st);
-    return launch_points_bwd<false, VEC, false, true>(P, st);
+    if (ray && param) return launch_points_bwd<false, MODE, true, true>(P, st);
+    if (ray) return launch_points_bwd<false, MODE, true, false>(P, st);
+    return launch_points_bwd<false, MODE, false, true>(P, st);
 }
 
 // v2 backward (one grid; two grids do not fit this kernel's shared-memory plan and stay on the v1 kernel)
@@ -629,7 +650,11 @@ int render_backward_v2(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int3
     P.rays_o = rays_o; P.rays_d = rays_d; P.z_vals = z_vals; P.draw = reinterpret_cast<const float4*>(scratch);
     P.g_rays_o = g_rays_o; P.g_rays_d = g_rays_d;
     const bool ray = g_rays_o != nullptr;
-    return planes_vectorizable(*scene) ? dispatch_points_bwd<true>(P, ray, param_grad, st) : dispatch_points_bwd<false>(P, ray, param_grad, st);
+    if (scene->encoder == 1) {
+        MNE_CHECK_ARG(!ray, "mne_render_backward: ray gradients through the hash grid are not built yet");
+        return launch_points_bwd<false, 2, false, true>(P, st);
+    }
+    return planes_vectorizable(*scene) ? dispatch_points_bwd<1>(P, ray, param_grad, st) : dispatch_points_bwd<0>(P, ray, param_grad, st);
 }
 
 }  // namespace mne

@@ -25,7 +25,8 @@ struct PtsFwdParams {
     float* feat;              // [M,64] or NULL
 };
 
-template <bool TWO, bool VEC>
+// MODE: 0 = planes through strides, 1 = channels-last planes (vector gather), 2 = hash grid
+template <bool TWO, int MODE>
 __global__ void __launch_bounds__(pts_warps<TWO>() * 32, 1) points_fwd_kernel(const __grid_constant__ PtsFwdParams P) {
     using N = NetV2<TWO>;
     constexpr int NW = pts_warps<TWO>();
@@ -61,31 +62,47 @@ __global__ void __launch_bounds__(pts_warps<TWO>() * 32, 1) points_fwd_kernel(co
             }
         }
         float* row = X + p_loc * kXStride;
-        // ---- tap table into the point's blob segment, gather, then (two grids) the same for the colour planes
-        if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 0);
-        __syncwarp();
-        if (VEC) gather16_vec(P.sc, 0, X + kBlobCol, kXStride, X, kXStride, np, lane);
-        else gather16(P.sc, 0, X + kBlobCol, kXStride, X, kXStride, np, lane);
-        __syncwarp();
-        if (TWO) {
-            if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 1);
+        const float bx = blob_input(px, P.sc.bbox_lo[0], P.sc.bbox_ext[0]);
+        const float by = blob_input(py, P.sc.bbox_lo[1], P.sc.bbox_ext[1]);
+        const float bz = blob_input(pz, P.sc.bbox_lo[2], P.sc.bbox_ext[2]);
+        if (MODE == 2) {
+            // ---- hash grid: the table is addressed with the [0,1] coordinates the OneBlob uses; park them in the
+            //      point's blob segment, gather, then let the OneBlob overwrite them
+            if (half == 0) { row[kBlobCol] = bx; row[kBlobCol + 1] = by; row[kBlobCol + 2] = bz; }
             __syncwarp();
-            if (VEC) gather16_vec(P.sc, 1, X + kBlobCol, kXStride, CFt, kCStride, np, lane);
-            else gather16(P.sc, 1, X + kBlobCol, kXStride, CFt, kCStride, np, lane);
+            gather16_hash(P.sc.hash[0], X + kBlobCol, kXStride, X, kXStride, np, lane);
             __syncwarp();
+        } else {
+            // ---- tap table into the point's blob segment, gather, then (two grids) the same for the colour planes
+            if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 0);
+            __syncwarp();
+            if (MODE == 1) gather16_vec(P.sc, 0, X + kBlobCol, kXStride, X, kXStride, np, lane);
+            else gather16(P.sc, 0, X + kBlobCol, kXStride, X, kXStride, np, lane);
+            __syncwarp();
+            if (TWO) {
+                if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 1);
+                __syncwarp();
+                if (MODE == 1) gather16_vec(P.sc, 1, X + kBlobCol, kXStride, CFt, kCStride, np, lane);
+                else gather16(P.sc, 1, X + kBlobCol, kXStride, CFt, kCStride, np, lane);
+                __syncwarp();
+            }
         }
         // ---- OneBlob over the (now dead) tap table: half 0 -> dims 0,1 ; half 1 -> dim 2
         if (half == 0) {
-            oneblob16_sparse(blob_input(px, P.sc.bbox_lo[0], P.sc.bbox_ext[0]), row + kBlobCol);
-            oneblob16_sparse(blob_input(py, P.sc.bbox_lo[1], P.sc.bbox_ext[1]), row + kBlobCol + 16);
+            oneblob16_sparse(bx, row + kBlobCol);
+            oneblob16_sparse(by, row + kBlobCol + 16);
         } else {
-            oneblob16_sparse(blob_input(pz, P.sc.bbox_lo[2], P.sc.bbox_ext[2]), row + kBlobCol + 32);
+            oneblob16_sparse(bz, row + kBlobCol + 32);
         }
         __syncwarp();
         if (P.feat) {
             for (int p = 0; p < np; ++p) {
-                P.feat[(pt0 + p) * 64 + lane] = X[p * kXStride + lane];
-                P.feat[(pt0 + p) * 64 + 32 + lane] = X[p * kXStride + 32 + lane];
+                if (MODE == 2) {
+                    P.feat[(pt0 + p) * 32 + lane] = X[p * kXStride + lane];
+                } else {
+                    P.feat[(pt0 + p) * 64 + lane] = X[p * kXStride + lane];
+                    P.feat[(pt0 + p) * 64 + 32 + lane] = X[p * kXStride + 32 + lane];
+                }
             }
         }
         // ---- decoder
@@ -208,27 +225,28 @@ int render_forward_v1(const MneSceneDesc*, const MneRenderCfg*, int32_t, int32_t
                       mne_stream_t);
 int query_points_v1(const MneSceneDesc*, int64_t, const float*, float*, float*, float*, mne_stream_t);
 
-template <bool TWO, bool VEC>
+template <bool TWO, int MODE>
 static int launch_points_fwd(const PtsFwdParams& P, cudaStream_t stream) {
     const size_t smem = pts_smem_bytes<TWO>();
     static bool configured[64] = {};
     int dev = 0;
     MNE_CHECK_CUDA(cudaGetDevice(&dev));
     if (dev >= 64 || !configured[dev]) {
-        MNE_CHECK_CUDA(cudaFuncSetAttribute(points_fwd_kernel<TWO, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        MNE_CHECK_CUDA(cudaFuncSetAttribute(points_fwd_kernel<TWO, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (dev < 64) configured[dev] = true;
     }
     const int64_t n_tiles = (P.n_pts + kTilePts - 1) / kTilePts;
     const int blocks = (int)max((int64_t)1, min(n_tiles, (int64_t)sm_count()));
-    points_fwd_kernel<TWO, VEC><<<blocks, pts_warps<TWO>() * 32, smem, stream>>>(P);
+    points_fwd_kernel<TWO, MODE><<<blocks, pts_warps<TWO>() * 32, smem, stream>>>(P);
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
 
 static int dispatch_points_fwd(const PtsFwdParams& P, cudaStream_t stream) {
+    if (P.sc.encoder == 1) return launch_points_fwd<false, 2>(P, stream);
     const bool vec = planes_vectorizable(P.sc);
-    if (P.sc.two_grid) return vec ? launch_points_fwd<true, true>(P, stream) : launch_points_fwd<true, false>(P, stream);
-    return vec ? launch_points_fwd<false, true>(P, stream) : launch_points_fwd<false, false>(P, stream);
+    if (P.sc.two_grid) return vec ? launch_points_fwd<true, 1>(P, stream) : launch_points_fwd<true, 0>(P, stream);
+    return vec ? launch_points_fwd<false, 1>(P, stream) : launch_points_fwd<false, 0>(P, stream);
 }
 
 }  // namespace mne
@@ -275,4 +293,35 @@ extern "C" int mne_query_points(const MneSceneDesc* scene, int64_t n_pts, const 
     PtsFwdParams P{};
     P.sc = *scene; P.n_pts = n_pts; P.n_samples = 1; P.pts = pts; P.raw = raw; P.geo = geo; P.feat = feat;
     return dispatch_points_fwd(P, (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// hash-grid corner indices of explicit [0,1]^3 coordinates (inspection / parity tests: the indices are the one
+// integer quantity of the hash encoder, so they can be compared bit for bit with the oracle)
+// ---------------------------------------------------------------------------------------------
+namespace mne {
+__global__ void hash_indices_kernel(MneHashDesc h, int64_t n, const float* __restrict__ x01, int32_t* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;     // one thread per (point, level)
+    if (i >= n * h.n_levels) return;
+    const int64_t p = i / h.n_levels;
+    const int l = (int)(i % h.n_levels);
+    const HashLevel L = hash_level(h, l);
+    const float x[3] = {x01[p * 3], x01[p * 3 + 1], x01[p * 3 + 2]};
+    const HashCell c = hash_cell(L, x);
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+        out[i * 8 + k] = (int32_t)hash_index(L, c.g[0] + (k & 1), c.g[1] + ((k >> 1) & 1), c.g[2] + ((k >> 2) & 1));
+}
+}  // namespace mne
+
+extern "C" int mne_hash_indices(const MneHashDesc* hash, int64_t n_pts, const float* x01, int32_t* indices,
+                                mne_stream_t stream) {
+    using namespace mne;
+    MNE_CHECK_ARG(hash && x01 && indices, "mne_hash_indices: null argument");
+    MNE_CHECK_ARG(hash->n_levels >= 1 && hash->n_levels <= 32, "mne_hash_indices: n_levels out of range");
+    if (n_pts <= 0) return 0;
+    const int64_t total = n_pts * hash->n_levels;
+    hash_indices_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(*hash, n_pts, x01, indices);
+    MNE_CHECK_CUDA(cudaGetLastError());
+    return 0;
 }

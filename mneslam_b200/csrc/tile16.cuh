@@ -69,6 +69,11 @@ struct NetV2 {
     static constexpr int W4_COUNT = OFFO + 8 * RS2;                       // float4 elements
 };
 
+// Column of sdf0 that feeds tile column k.  Planes: identity (64 features | 48 blob).  Hash grid: the table
+// yields 32 features, tile columns 32..63 are zero padding (their weights are zero), blob follows at 64.
+__device__ __forceinline__ int sdf0_col(int k, bool hash) { return !hash ? k : (k < 32 ? k : (k < 64 ? -1 : k - 32)); }
+__device__ __forceinline__ int sdf0_in(bool hash) { return hash ? 80 : 112; }
+
 __device__ __forceinline__ float4 split_pair(float a, float b) {
     const uint32_t ah = to_tf32(a), bh = to_tf32(b);
     return make_float4(__uint_as_float(ah), __uint_as_float(bh), __uint_as_float(to_tf32(a - __uint_as_float(ah))),
@@ -78,9 +83,12 @@ __device__ __forceinline__ float4 split_pair(float a, float b) {
 template <bool TWO>
 __device__ __forceinline__ void load_weights_v2(const MneSceneDesc& sc, float4* W4, int tid, int nthreads) {
     using N = NetV2<TWO>;
+    const bool hash = sc.encoder == 1;
     for (int i = tid; i < 32 * N::K1P; i += nthreads) {
         const int n = i / N::K1P, kp = i % N::K1P;
-        W4[N::OFF1 + n * N::RS1 + kp] = split_pair(sc.w_sdf0[n * N::K1 + 2 * kp], sc.w_sdf0[n * N::K1 + 2 * kp + 1]);
+        const int c0 = sdf0_col(2 * kp, hash), c1 = sdf0_col(2 * kp + 1, hash);
+        W4[N::OFF1 + n * N::RS1 + kp] = split_pair(c0 >= 0 ? sc.w_sdf0[n * sdf0_in(hash) + c0] : 0.0f,
+                                                   c1 >= 0 ? sc.w_sdf0[n * sdf0_in(hash) + c1] : 0.0f);
     }
     for (int i = tid; i < 16 * N::K2P; i += nthreads) {
         const int n = i / N::K2P, kp = i % N::K2P;
@@ -200,6 +208,96 @@ __device__ __forceinline__ void gather16_vec(const MneSceneDesc& sc, int grp, co
                 acc[l].z += __shfl_xor_sync(0xffffffffu, acc[l].z, o); acc[l].w += __shfl_xor_sync(0xffffffffu, acc[l].w, o);
             }
             if (c == 0) *reinterpret_cast<float4*>(dst + p * dst_stride + l * 32 + q * 4) = acc[l];
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// multi-resolution hash grid (tiny-cuda-nn encodings/grid.h; restated in oracle/hashgrid.py).
+// lane = (point parity, level): 16 levels x 2 points per trip, 8 corner loads of one float2 (2 features) each.
+// Point coordinates in [0,1] (the OneBlob inputs) are read from xn[p * xn_stride + 0..2].
+// ---------------------------------------------------------------------------------------------
+struct HashLevel {
+    float scale;
+    uint32_t res, size, offset;
+};
+__device__ __forceinline__ HashLevel hash_level(const MneHashDesc& h, int l) {
+    HashLevel L;
+    L.scale = h.level_scale[l];
+    L.res = h.level_res[l];
+    L.offset = h.offsets[l];
+    L.size = h.offsets[l + 1] - h.offsets[l];
+    return L;
+}
+__device__ __forceinline__ uint32_t hash_index(const HashLevel& L, uint32_t gx, uint32_t gy, uint32_t gz) {
+    uint64_t stride = 1;
+    uint32_t index = 0;
+    if (stride <= L.size) { index += gx * (uint32_t)stride; stride *= L.res; }
+    if (stride <= L.size) { index += gy * (uint32_t)stride; stride *= L.res; }
+    if (stride <= L.size) { index += gz * (uint32_t)stride; stride *= L.res; }
+    if (L.size < stride) index = gx ^ (gy * 2654435761u) ^ (gz * 805459861u);
+    return index % L.size;
+}
+struct HashCell {
+    uint32_t g[3];
+    float f[3];
+};
+__device__ __forceinline__ HashCell hash_cell(const HashLevel& L, const float* x) {
+    HashCell c;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        const float pos = __fadd_rn(__fmul_rn(x[d], L.scale), 0.5f);
+        const float fl = floorf(pos);
+        c.f[d] = pos - fl;
+        c.g[d] = (uint32_t)(int)fl;
+    }
+    return c;
+}
+__device__ __forceinline__ float corner_weight(const HashCell& c, int k) {
+    return ((k & 1) ? c.f[0] : 1.0f - c.f[0]) * ((k & 2) ? c.f[1] : 1.0f - c.f[1]) * ((k & 4) ? c.f[2] : 1.0f - c.f[2]);
+}
+
+__device__ __forceinline__ void gather16_hash(const MneHashDesc& h, const float* __restrict__ xn, int xn_stride,
+                                              float* __restrict__ dst, int dst_stride, int np, int lane) {
+    const int l = lane & 15, pp = lane >> 4;
+    const HashLevel L = hash_level(h, l);
+    const float2* table = reinterpret_cast<const float2*>(h.table) + L.offset;
+#pragma unroll 2
+    for (int it = 0; it < kTilePts / 2; ++it) {
+        const int p = 2 * it + pp;
+        if (p < np) {
+            const HashCell c = hash_cell(L, xn + p * xn_stride);
+            float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const uint32_t idx = hash_index(L, c.g[0] + (k & 1), c.g[1] + ((k >> 1) & 1), c.g[2] + ((k >> 2) & 1));
+                const float2 v = __ldg(table + idx);
+                const float w = corner_weight(c, k);
+                acc.x = fmaf(w, v.x, acc.x); acc.y = fmaf(w, v.y, acc.y);
+            }
+            *reinterpret_cast<float2*>(dst + p * dst_stride + 2 * l) = acc;
+        }
+    }
+    for (int p = 0; p < kTilePts; ++p) dst[p * dst_stride + 32 + lane] = 0.0f;      // padding columns 32..63
+}
+
+// gradient of the table: grad[corner] += w * d feat (one 64-bit vector reduction per corner)
+__device__ __forceinline__ void scatter16_hash(const MneHashDesc& h, const float* __restrict__ xn, int xn_stride,
+                                               const float* __restrict__ src, int src_stride, int np, int lane) {
+    const int l = lane & 15, pp = lane >> 4;
+    const HashLevel L = hash_level(h, l);
+    float2* grad = reinterpret_cast<float2*>(h.grad) + L.offset;
+    for (int it = 0; it < kTilePts / 2; ++it) {
+        const int p = 2 * it + pp;
+        if (p < np) {
+            const HashCell c = hash_cell(L, xn + p * xn_stride);
+            const float2 g2 = *reinterpret_cast<const float2*>(src + p * src_stride + 2 * l);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const uint32_t idx = hash_index(L, c.g[0] + (k & 1), c.g[1] + ((k >> 1) & 1), c.g[2] + ((k >> 2) & 1));
+                const float w = corner_weight(c, k);
+                atomicAdd(grad + idx, make_float2(w * g2.x, w * g2.y));
+            }
         }
     }
 }

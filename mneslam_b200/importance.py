@@ -39,7 +39,7 @@ class _RenderImportance(torch.autograd.Function):
         td = target_d.reshape(-1) if with_depth else None
         acc = ops.new_acc(dev) if with_losses else None
         z0 = ops.sample_rays(scfg, rc0, n, s0, td, noise if perturb else None, None, dev)   # counts come from the final samples
-        scene = ops.make_scene(planes, weights, model.bound, model.bounding_box, cfg['pos']['n_bins'])
+        scene = ops.make_scene(planes, weights, model.bound, model.bounding_box, cfg['pos']['n_bins'], hash_meta=model.hash_meta)
         first = ops.render_forward(scene, rc0, rays_o, rays_d, z0, target_rgb if with_losses else None,
                                    td if with_losses else None, acc, want_weights=True)
         u = u_imp if perturb else _det_u(n_imp, dev)
@@ -80,7 +80,7 @@ class _RenderImportance(torch.autograd.Function):
         weight_grads = [torch.zeros_like(w) if nd else None for w, nd in zip(weights, need_params[n_planes:])]
         want_rays = bool(need[1] or need[2])
         scene = ops.make_scene(planes, weights, model.bound, model.bounding_box, model.config['pos']['n_bins'],
-                               plane_grads=plane_grads, weight_grads=weight_grads)
+                               plane_grads=plane_grads, weight_grads=weight_grads, hash_meta=model.hash_meta)
         lg = g_losses if (ctx.with_losses and g_losses is not None) else None
         go1, gd1 = ops.render_backward(scene, ctx.rc1, rays_o, rays_d, z1, raw1, target_rgb, td, acc, loss_grads=lg,
                                        g_rgb=g_rgb, g_depth=g_depth, g_raw=g_raw, want_ray_grads=want_rays)

@@ -48,10 +48,10 @@ class FusedMapper:
         self.dev = planes[0].device
         one_grid = self.cfg['grid']['oneGrid']
         mp = self.cfg['mapping']
-        n_sdf_planes = 6
+        n_sdf_planes = 6 if model.hash_meta is None else 1
         # parameter groups of create_optimizer (mneslam_mp.py:459-469): (tensor, lr, eps, weight_decay)
         self.params = [(p, mp['lr_embed'], 1e-15, 0.0) for p in planes[:n_sdf_planes]]
-        if not one_grid:
+        if not one_grid and model.hash_meta is None:
             self.params += [(p, mp['lr_embed_color'], 1e-15, 0.0) for p in planes[n_sdf_planes:]]
         self.params += [(w, mp['lr_decoder'], 1e-8, 1e-6) for w in weights]
         self.betas = (0.9, 0.99)
@@ -129,7 +129,7 @@ class FusedMapper:
         return ops.make_scene(m._flat_planes(), m.decoder.weight_list(), m.bound, m.bounding_box,
                               self.cfg['pos']['n_bins'],
                               plane_grads=self.plane_grads if with_grads else None,
-                              weight_grads=self.weight_grads if with_grads else None)
+                              weight_grads=self.weight_grads if with_grads else None, hash_meta=m.hash_meta)
 
     def forward_backward(self, rays_o, rays_d, target_rgb, target_d, noise=None):
         """sample -> forward -> finalize -> backward; gradients are ADDED to the flat buffer.  Returns losses[8]."""

@@ -107,17 +107,27 @@ def bounds_to_host(bound, bounding_box):
     return hit[:4]
 
 
-def make_scene(planes, weights, bound, bounding_box, n_bins=16, plane_grads=None, weight_grads=None):
-    """planes: flat list of 6 or 12 ``[1,32,H,W]`` tensors in ``all_planes`` order (group, axis, level).
+def make_scene(planes, weights, bound, bounding_box, n_bins=16, plane_grads=None, weight_grads=None, hash_meta=None):
+    """planes: flat list of 6 or 12 ``[1,32,H,W]`` tensors in ``all_planes`` order (group, axis, level) -- or, with
+    ``hash_meta`` (a ``hashgrid.HashGridMeta``), the one-element list ``[table]`` of the hash grid encoder.
     weights: [sdf0, sdf1, col0, col1].  bound: float32 [3,2] (CPU ok).  bounding_box: float64 [3,2]."""
-    if len(planes) not in (6, 12):
-        raise ValueError('expected 6 or 12 planes, got %d' % len(planes))
     sc = SceneDesc()
-    sc.encoder = 0
-    sc.two_grid = 1 if len(planes) == 12 else 0
     sc.n_bins = n_bins
-    sc.c_dim = planes[0].shape[1]
     keep = []
+    if hash_meta is not None:
+        if len(planes) != 1:
+            raise ValueError('the hash grid encoder takes exactly one table')
+        sc.encoder, sc.two_grid, sc.c_dim = 1, 0, 32
+        hash_meta.fill_desc(sc.hash[0], planes[0], plane_grads[0] if plane_grads is not None else None)
+        planes, plane_grads = [], None
+        feat = hash_meta.n_output
+    else:
+        if len(planes) not in (6, 12):
+            raise ValueError('expected 6 or 12 planes, got %d' % len(planes))
+        sc.encoder = 0
+        sc.two_grid = 1 if len(planes) == 12 else 0
+        sc.c_dim = planes[0].shape[1]
+        feat = 64
     for i, p in enumerate(planes):
         if not (p.is_cuda and p.dtype == torch.float32 and p.dim() == 4 and p.shape[0] == 1):
             raise TypeError('plane %d must be a float32 CUDA tensor of shape [1,C,H,W]' % i)
@@ -139,8 +149,8 @@ def make_scene(planes, weights, bound, bounding_box, n_bins=16, plane_grads=None
     ws = [_f32(w, 'decoder weight') for w in weights]
     keep.extend(ws)
     sc.w_sdf0, sc.w_sdf1, sc.w_col0, sc.w_col1 = [w.data_ptr() for w in ws]
-    in_sdf = 64 + 48
-    in_col = 48 + 15 + (64 if sc.two_grid else 0)
+    in_sdf = feat + 48
+    in_col = 48 + 15 + (feat if sc.two_grid else 0)
     shapes = [(32, in_sdf), (16, 32), (32, in_col), (3, 32)]
     for w, s in zip(ws, shapes):
         if tuple(w.shape) != s:
@@ -233,7 +243,7 @@ def query_points(scene, pts, want_raw=True, want_geo=False, want_feat=False):
     m, dev = p.shape[0], p.device
     raw = torch.empty(m, 4, dtype=torch.float32, device=dev) if want_raw else None
     geo = torch.empty(m, 15, dtype=torch.float32, device=dev) if want_geo else None
-    feat = torch.empty(m, 64, dtype=torch.float32, device=dev) if want_feat else None
+    feat = torch.empty(m, 32 if scene.encoder == 1 else 64, dtype=torch.float32, device=dev) if want_feat else None
     _lib.check(_lib.lib().mne_query_points(C.byref(scene), m, _ptr(p), _ptr(raw), _ptr(geo), _ptr(feat), _stream()),
                'mne_query_points')
     return raw, geo, feat

@@ -57,7 +57,8 @@ class _Render(torch.autograd.Function):
         td = target_d.reshape(-1) if with_depth else None
         acc = ops.new_acc(dev) if with_losses else None
         z_vals = ops.sample_rays(scfg, rcfg, n, n_samples, td, noise if perturb else None, acc, dev)
-        scene = ops.make_scene(planes, weights, model.bound, model.bounding_box, cfg['pos']['n_bins'])
+        scene = ops.make_scene(planes, weights, model.bound, model.bounding_box, cfg['pos']['n_bins'],
+                               hash_meta=model.hash_meta)
         out = ops.render_forward(scene, rcfg, rays_o, rays_d, z_vals, target_rgb if with_losses else None,
                                  td if with_losses else None, acc)
         if with_losses:
@@ -86,7 +87,7 @@ class _Render(torch.autograd.Function):
         weight_grads = [torch.zeros_like(w) if nd else None for w, nd in zip(weights, need_params[n_planes:])]
         want_rays = bool(need[1] or need[2])
         scene = ops.make_scene(planes, weights, model.bound, model.bounding_box, model.config['pos']['n_bins'],
-                               plane_grads=plane_grads, weight_grads=weight_grads)
+                               plane_grads=plane_grads, weight_grads=weight_grads, hash_meta=model.hash_meta)
         lg = g_losses if (ctx.with_losses and g_losses is not None) else None
         g_o, g_d = ops.render_backward(scene, ctx.rcfg, rays_o, rays_d, z_vals, raw, target_rgb, td, acc,
                                        loss_grads=lg, g_rgb=g_rgb, g_depth=g_depth, g_raw=g_raw,
@@ -145,8 +146,22 @@ class JointEncoding(nn.Module):
     def get_encoding(self, config):
         if 'blob' not in config['pos']['enc'].lower() or config['pos']['n_bins'] != 16:
             raise NotImplementedError('the fused kernels are built for pos.enc = OneBlob with 16 bins')
-        self.input_ch = config['model']['input_ch']
         self.input_ch_pos = config['model']['input_ch_pos']
+        self.hash_meta, self.hash_tables = None, None
+        if config['grid'].get('use_hash', False):
+            # the encoder the configs NAME (grid.enc: HashGrid + hash_size + voxel_sdf, model/scene_rep.py:55-70,160)
+            # but the reference never builds; opt-in through the extension key grid.use_hash
+            from .hashgrid import HashGridMeta
+            if not config['grid']['oneGrid']:
+                raise NotImplementedError('grid.use_hash is built for one table (grid.oneGrid: True)')
+            self.hash_meta = HashGridMeta.from_config(config)
+            self.hash_tables = [self.hash_meta.new_table(self.device)]      # mutable list, like all_planes
+            self.input_ch = self.hash_meta.n_output
+            self.all_planes = ()
+            if self.input_ch_pos != 48:
+                raise NotImplementedError('model.input_ch_pos must be 48 (3 x n_bins)')
+            return
+        self.input_ch = config['model']['input_ch']
         if (self.input_ch, self.input_ch_pos) != (64, 48):
             raise NotImplementedError('model.input_ch / input_ch_pos must be 64 / 48 (2 x c_dim, 3 x n_bins)')
         self.all_planes = self.init_all_planes(config)
@@ -161,6 +176,9 @@ class JointEncoding(nn.Module):
 
     # ------------------------------------------------------------------ helpers
     def _flat_planes(self):
+        """The encoder's parameter tensors: the planes in ``all_planes`` order, or ``[hash table]``."""
+        if self.hash_meta is not None:
+            return list(self.hash_tables)
         expect = 3 if self.config['grid']['oneGrid'] else 6
         if len(self.all_planes) != expect:
             raise ValueError('all_planes has %d groups, config expects %d' % (len(self.all_planes), expect))
@@ -168,7 +186,7 @@ class JointEncoding(nn.Module):
 
     def _scene(self):
         return ops.make_scene(self._flat_planes(), self.decoder.weight_list(), self.bound, self.bounding_box,
-                              self.config['pos']['n_bins'])
+                              self.config['pos']['n_bins'], hash_meta=self.hash_meta)
 
     def _render(self, rays_o, rays_d, target_rgb, target_d, with_losses, noise=None):
         ops.require_cuda()

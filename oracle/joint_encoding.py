@@ -59,8 +59,9 @@ def init_planes(cfg, bound, seed=0, std=0.01):
 def init_weights(cfg, seed=0):
     gen = torch.Generator().manual_seed(seed + 1)
     d, m = cfg['decoder'], cfg['model']
-    in_sdf = m['input_ch'] + m['input_ch_pos']
-    in_col = m['input_ch_pos'] + d['geo_feat_dim'] + (0 if cfg['grid']['oneGrid'] else m['input_ch'])
+    feat = 32 if cfg['grid'].get('use_hash', False) else m['input_ch']
+    in_sdf = feat + m['input_ch_pos']
+    in_col = m['input_ch_pos'] + d['geo_feat_dim'] + (0 if cfg['grid']['oneGrid'] else feat)
 
     def lin(o, i):   # nn.Linear default init: U(-1/sqrt(i), 1/sqrt(i))
         k = 1.0 / math.sqrt(i)
@@ -200,7 +201,13 @@ def decode(weights, feat, blob, cfeat=None):
 
 
 def query_points(cfg, planes, weights, bound, bounding_box, pts, fast=False):
-    """pts [M,3] -> raw [M,4] = (rgb logits, sdf)."""
+    """pts [M,3] -> raw [M,4] = (rgb logits, sdf).  With ``cfg['grid']['use_hash']`` the parametric encoder is the
+    multi-resolution hash grid (``oracle/hashgrid.py``) and ``planes`` is ``([table],)``."""
+    if cfg['grid'].get('use_hash', False):
+        from . import hashgrid
+        x01 = blob_inputs(pts, bounding_box)
+        feat = hashgrid.encode(hashgrid.make_meta(cfg), planes[0][0], x01)
+        return decode(weights, feat, oneblob(x01, cfg['pos']['n_bins']), None)[0]
     p_nor = normalize_plane_coords(pts, bound)
     feat = triplane_features(p_nor, planes[0], planes[1], planes[2], fast)
     blob = oneblob(blob_inputs(pts, bounding_box), cfg['pos']['n_bins'])

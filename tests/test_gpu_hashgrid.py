@@ -1,0 +1,106 @@
+"""Hash-grid encoder (the encoder BASELINE.json's north star names; dormant in the reference, restated from
+tiny-cuda-nn in oracle/hashgrid.py -- parity unpinned by the reference): corner indices bit-exact against the
+oracle, forward / losses within 1e-3, table and decoder gradients cosine >= 0.999, and a short training run."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from mneslam_b200 import JointEncoding, _lib, configs, ops, synthetic
+from mneslam_b200.mapping import FusedMapper
+from oracle import hashgrid as H
+from oracle import joint_encoding as J
+from tests.gpu_util import cosine, rel, total_loss
+
+pytestmark = pytest.mark.gpu
+
+
+def _hash_cfg(hash_size=12, voxel=0.04):
+    cfg = configs.small_test_config(n_samples_d=13, n_range_d=7)
+    cfg['grid'].update({'use_hash': True, 'hash_size': hash_size, 'voxel_sdf': voxel})
+    return cfg
+
+
+def _model(cfg, seed=0, table_scale=0.3):
+    torch.manual_seed(seed)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    model = JointEncoding(cfg, bb).cuda()
+    meta = H.make_meta(cfg)
+    assert meta['offsets'] == model.hash_meta.offsets and meta['resolutions'] == model.hash_meta.resolutions
+    table = H.init_table(meta, seed=seed, scale=table_scale)
+    weights = J.init_weights(cfg, seed=seed)
+    model.hash_tables[0] = torch.nn.Parameter(table.cuda())
+    with torch.no_grad():
+        for w, k in zip(model.decoder.weight_list(), ('sdf0', 'sdf1', 'col0', 'col1')):
+            w.copy_(weights[k])
+    model.train()
+    return model, meta, table, weights, bb
+
+
+@pytest.mark.parametrize('hash_size', [8, 13, 16])
+def test_corner_indices_bit_exact(hash_size):
+    cfg = _hash_cfg(hash_size=hash_size, voxel=0.02)
+    model, meta, table, _, _ = _model(cfg)
+    x = (torch.rand(3000, 3) * 1.6 - 0.3)          # inside and outside the unit cube (negative cells wrap as uint32)
+    desc = _lib.HashDesc()
+    model.hash_meta.fill_desc(desc, model.hash_tables[0].detach())
+    out = torch.empty(3000, 16, 8, dtype=torch.int32, device='cuda')
+    xd = x.cuda()
+    _lib.check(_lib.lib().mne_hash_indices(C.byref(desc), 3000, xd.data_ptr(), out.data_ptr(), ops._stream()), 'mne_hash_indices')
+    got = out.cpu().numpy()
+    hashed_levels = 0
+    for l in range(16):
+        want, _ = H.corner_indices(meta, x, l)
+        assert np.array_equal(got[:, l, :].astype(np.int64), want.numpy()), l
+        hashed_levels += int(meta['sizes'][l] < meta['resolutions'][l] ** 3)
+    assert hashed_levels > 0 and (hash_size < 12 or hashed_levels < 16), 'dense and hashed levels must both be covered'
+
+
+def test_forward_backward_vs_oracle():
+    cfg = _hash_cfg()
+    model, meta, table, weights, bb = _model(cfg, seed=3)
+    n = 300
+    batch = synthetic.make_ray_batch(cfg, n, seed=8, zero_depth_frac=0.1, depth_range=(0.3, 2.5))
+    noise = synthetic.make_noise(n, synthetic.n_samples_total(cfg), seed=8)
+    ot = table.clone().requires_grad_(True)
+    ow = {k: v.clone().requires_grad_(True) for k, v in weights.items()}
+    oret, orend = J.forward(cfg, ([ot],), ow, J.enlarged_bound(cfg), bb, batch['rays_o'], batch['rays_d'], batch['target_rgb'],
+                            batch['target_d'], noise)
+    J.total_loss(cfg, oret).backward()
+
+    dev = {k: v.cuda() for k, v in batch.items()}
+    rend = model.render_rays(dev['rays_o'], dev['rays_d'], target_d=dev['target_d'], noise=noise.cuda())
+    assert np.array_equal(rend['z_vals'].cpu().numpy(), orend['z_vals'].numpy())
+    for k in ('rgb', 'depth', 'raw'):
+        assert rel(rend[k].detach().cpu().numpy(), orend[k].detach().numpy()) < 1e-3, k
+    ret = model.forward(dev['rays_o'], dev['rays_d'], dev['target_rgb'], dev['target_d'], noise=noise.cuda())
+    for k in ('rgb_loss', 'depth_loss', 'e_fs_loss', 'e_center_loss', 'e_tail_loss'):
+        np.testing.assert_allclose(ret[k].item(), oret[k].item(), rtol=1e-3, err_msg=k)
+    total_loss(cfg, ret).backward()
+    assert cosine(model.hash_tables[0].grad.cpu().numpy(), ot.grad.numpy()) >= 0.999
+    assert rel(model.hash_tables[0].grad.cpu().numpy(), ot.grad.numpy()) < 5e-3
+    for w, k in zip(model.decoder.weight_list(), ('sdf0', 'sdf1', 'col0', 'col1')):
+        assert cosine(w.grad.cpu().numpy(), ow[k].grad.numpy()) >= 0.999, k
+    # point queries: 32 hash features for embed=True
+    pts = torch.rand(500, 3) * 1.6 - 0.8
+    emb = model.query_sdf(pts.cuda().reshape(500, 1, 3), embed=True)
+    want = H.encode(meta, table, J.blob_inputs(pts, bb))
+    assert emb.shape == (500, 1, 32) and rel(emb.reshape(500, 32).detach().cpu().numpy(), want.numpy()) < 1e-4
+
+
+def test_fused_mapper_trains_the_hash_grid():
+    cfg = _hash_cfg(hash_size=14)
+    model, *_ = _model(cfg, seed=1, table_scale=1e-4)
+    model.hash_tables[0] = model.hash_tables[0].detach()
+    mapper = FusedMapper(model)
+    gen = torch.Generator().manual_seed(0)
+    hist = []
+    from mneslam_b200 import pose
+    for it in range(150):
+        c2w = synthetic.make_pose(cfg, gen, frac=(0.45 + 0.1 * (it % 5) / 4, 0.5, 0.5))
+        b = synthetic.make_ray_batch(cfg, 512, seed=it, c2w=c2w)
+        rgb, d = synthetic.render_box_scene(cfg, c2w, b['dirs_cam'])
+        losses = mapper.step(b['rays_o'].cuda(), b['rays_d'].cuda(), rgb.cuda(), d.cuda())
+        hist.append(mapper.total_loss(losses).item())
+    assert np.isfinite(hist).all() and np.mean(hist[-10:]) < 0.5 * np.mean(hist[:10]), (hist[:3], hist[-3:])

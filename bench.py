@@ -414,9 +414,25 @@ def run_ours(args):
             tracker.step(tb['dirs_cam'], tb['target_rgb'], tb['target_d'])
         e1.record()
         torch.cuda.synchronize()
-        tracking = {'ms_per_iter': max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3) / n_it, 'iters': n_it,
+        ms_eager = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3) / n_it
+        ms_graph = None
+        try:
+            from mneslam_b200.tracking import GraphedPoseTracker
+            gt = GraphedPoseTracker(tracker, tb['dirs_cam'], tb['target_rgb'], tb['target_d'])
+            gt.run(3)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            e0.record()
+            gt.run(n_it)
+            e1.record()
+            torch.cuda.synchronize()
+            ms_graph = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3) / n_it
+        except Exception as e:
+            print('bench.py: tracking graph capture failed (%r)' % (e,), file=sys.stderr)
+        tracking = {'ms_per_iter': ms_graph if ms_graph is not None else ms_eager, 'ms_per_iter_eager': ms_eager,
+                    'cuda_graph': ms_graph is not None, 'iters': n_it,
                     'workload': 'ScanNet-shaped (620x460, scene0000 bound, one grid): 1024 rays x 117 samples, map frozen, '
-                                'quaternion + translation pose, Adam; eager PoseTracker.step (autograd over the fused kernels)',
+                                'quaternion + translation pose, Adam; PoseTracker.step (autograd over the fused kernels), one CUDA-graph replay per iteration',
                     'points_per_iter': 1024 * 117}
         del tmodel, tracker
 

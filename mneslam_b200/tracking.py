@@ -93,6 +93,34 @@ class PoseTracker:
         return loss.detach()
 
 
+class GraphedPoseTracker:
+    """One pose iteration (pose -> rays -> fused forward -> losses -> ray-gradient backward -> Adam) captured in a
+    CUDA graph for a fixed frame: the per-frame optimisation is ``iters`` replays with no Python in between."""
+
+    def __init__(self, tracker, dirs_cam, target_rgb, target_d):
+        self.tracker = tracker
+        self.dirs, self.rgb, self.d = dirs_cam.clone(), target_rgb.clone(), target_d.clone()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):                                  # warm-up outside capture (allocations, kernel attributes)
+                tracker.step(self.dirs, self.rgb, self.d)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        tracker.optimizer.zero_grad(set_to_none=True)
+        with torch.cuda.graph(self.graph):
+            self.loss = tracker.step(self.dirs, self.rgb, self.d)
+
+    def set_frame(self, dirs_cam, target_rgb, target_d):
+        self.dirs.copy_(dirs_cam); self.rgb.copy_(target_rgb); self.d.copy_(target_d)
+
+    def run(self, iters):
+        for _ in range(iters):
+            self.graph.replay()
+        return self.loss
+
+
 def ate_rmse(est_xyz, gt_xyz):
     """Absolute trajectory error after the closed-form rigid alignment of Horn (the definition the reference's
     ``tools/eval_ate.py:67-101`` uses): RMSE of ``R est + t - gt``."""

@@ -98,3 +98,40 @@ def test_tracking_ate_matches_oracle(rot_rep):
     raw_gpu = float((est_gpu - gt).norm(dim=1).mean())
     assert raw_gpu < init_err, 'tracking must move the poses towards the ground truth (%g vs %g)' % (raw_gpu, init_err)
     assert abs(ate_gpu - ate_cpu) <= 0.05 * ate_cpu + 1e-5, (ate_gpu, ate_cpu)
+
+
+def test_graphed_tracker_matches_eager():
+    """With the stratified noise switched off the iteration is deterministic up to atomic ordering, so ten CUDA-graph
+    replays must land on the same pose as ten eager steps; the map stays untouched."""
+    from mneslam_b200.tracking import GraphedPoseTracker
+    cfg = configs.small_test_config(n_samples_d=13, n_range_d=7)
+    bound = J.enlarged_bound(cfg)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    gen = torch.Generator().manual_seed(5)
+    model = build_model(cfg, bb, J.init_planes(cfg, bound, seed=4, std=0.01), J.init_weights(cfg, seed=4), as_params=False)
+    mapper = FusedMapper(model)
+    for it in range(200):
+        c2w = _pose((it % 9) / 8.0)
+        dirs = _camera_dirs(cfg, 512, gen)
+        rgb, d = synthetic.render_box_scene(cfg, c2w, dirs)
+        ro, rd = pose.rays_from_c2w(c2w, dirs)
+        mapper.step(ro.contiguous().cuda(), rd.contiguous().cuda(), rgb.cuda(), d.cuda())
+    cfg['training']['perturb'] = 0                      # deterministic sampling from here on
+    before = [p.clone() for p in flat_planes(model)]
+    c2w_gt = _pose(0.4)
+    init = c2w_gt.clone()
+    init[:3, 3] += torch.tensor([0.03, -0.02, 0.025])
+    dirs = _camera_dirs(cfg, 256, gen)
+    rgb, d = synthetic.render_box_scene(cfg, c2w_gt, dirs)
+    eager = PoseTracker(model, init.cuda(), rot_rep='quat', lr_rot=2e-3, lr_trans=2e-3)
+    for _ in range(13):
+        eager.step(dirs.cuda(), rgb.cuda(), d.cuda())
+    graphed = PoseTracker(model, init.cuda(), rot_rep='quat', lr_rot=2e-3, lr_trans=2e-3)
+    g = GraphedPoseTracker(graphed, dirs.cuda(), rgb.cuda(), d.cuda())      # three warm-up steps inside
+    g.run(10)
+    torch.cuda.synchronize()
+    assert torch.allclose(graphed.trans, eager.trans, atol=2e-4), (graphed.trans, eager.trans)
+    assert torch.allclose(graphed.rot, eager.rot, atol=2e-4), (graphed.rot, eager.rot)
+    assert float((graphed.trans.detach().cpu()[0] - init[:3, 3]).norm()) > 1e-3, 'the pose must have moved'
+    for a, b in zip(before, flat_planes(model)):
+        assert torch.equal(a, b)

@@ -465,6 +465,8 @@ def run_ours(args):
             'breakdown_us': us,
             'fwd_bwd_points_per_s': pts_per_rank * world / ((us['sample'] + us['fwd'] + us['bwd']) * 1e-6),
             'clocks': clocks,
+            'adam': {'exact_skip_of_never_touched_groups': mapper.touched is not None,
+                     'touched_fraction_at_end': float(mapper.touched.float().mean().item()) if mapper.touched is not None else 1.0},
             'last_loss': float(mapper.total_loss(static_losses if graph is not None else losses).item()),
         }
         if world == 1 and not args.no_cpu_baseline:

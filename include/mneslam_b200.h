@@ -213,12 +213,16 @@ int mne_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq, 
 /* Same update for several parameter groups stored back to back in four flat buffers (identical offsets in param /
  * grad / exp_avg / exp_avg_sq): one launch for the whole map.  segment_ends[i] = exclusive end of group i in
  * elements (ascending, multiples of 4); lr / eps / weight_decay are HOST arrays of n_segments entries (the
- * parameter groups of create_optimizer, mneslam_mp.py:459-467). */
+ * parameter groups of create_optimizer, mneslam_mp.py:459-467).
+ * `touched` (device, one byte per 4 parameters, zero-initialised by the caller, or NULL): marks the 16-byte groups
+ * that have ever received a non-zero gradient.  A group that never did has m = v = g = 0, so dense Adam leaves
+ * it exactly unchanged; with the map the kernel skips its parameter / moment traffic (groups with weight decay
+ * are always updated).  The resulting parameters are bit-identical to the dense update. */
 #define MNE_ADAM_MAX_SEGMENTS 16
 int mne_adam_step_segments(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int32_t n_segments,
                            const int64_t* segment_ends, const float* lr, const float* eps, const float* weight_decay,
                            float beta1, float beta2, const int64_t* step_dev, int64_t step_host, int32_t zero_grad,
-                           mne_stream_t stream);
+                           uint8_t* touched, mne_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -73,6 +73,7 @@ struct AdamSegments {
     const int64_t* step_dev;
     int64_t step_host;
     int zero_grad;
+    uint8_t* touched;      // one byte per float4 group: has this group ever received a gradient?  (NULL = dense)
 };
 
 __global__ void __launch_bounds__(256) adam_segments_kernel(const __grid_constant__ AdamSegments s) {
@@ -91,13 +92,22 @@ __global__ void __launch_bounds__(256) adam_segments_kernel(const __grid_constan
         AdamArgs a{};
         a.beta1 = s.beta1; a.beta2 = s.beta2; a.eps = s.eps[seg]; a.weight_decay = s.wd[seg]; a.zero_grad = s.zero_grad;
         const float step_size = (float)((double)s.lr[seg] / (double)bc1);
-        float4 p = p4[i], g = g4[i], m = m4[i], v = v4[i];
+        float4 g = g4[i];
+        const bool nz = g.x != 0.0f || g.y != 0.0f || g.z != 0.0f || g.w != 0.0f;
+        if (s.touched && a.weight_decay == 0.0f) {
+            // A group that never saw a gradient has m = v = g = 0: its dense Adam update is exactly the identity, so
+            // skipping it (no p / m / v traffic) gives bit-identical parameters.  Once touched, always updated.
+            const uint8_t f = s.touched[i];
+            if (!nz && !f) continue;
+            if (!f) s.touched[i] = 1;
+        }
+        float4 p = p4[i], m = m4[i], v = v4[i];
         adam_one(p.x, g.x, m.x, v.x, a, step_size, bc2_sqrt);
         adam_one(p.y, g.y, m.y, v.y, a, step_size, bc2_sqrt);
         adam_one(p.z, g.z, m.z, v.z, a, step_size, bc2_sqrt);
         adam_one(p.w, g.w, m.w, v.w, a, step_size, bc2_sqrt);
         p4[i] = p; m4[i] = m; v4[i] = v;
-        if (s.zero_grad) g4[i] = g;
+        if (s.zero_grad && nz) g4[i] = g;       // a zero gradient needs no clearing
     }
 }
 
@@ -138,7 +148,7 @@ extern "C" int mne_adam_step(float* param, float* grad, float* exp_avg, float* e
 extern "C" int mne_adam_step_segments(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int32_t n_segments,
                                       const int64_t* segment_ends, const float* lr, const float* eps,
                                       const float* weight_decay, float beta1, float beta2, const int64_t* step_dev,
-                                      int64_t step_host, int32_t zero_grad, mne_stream_t stream) {
+                                      int64_t step_host, int32_t zero_grad, uint8_t* touched, mne_stream_t stream) {
     using namespace mne;
     MNE_CHECK_ARG(param && grad && exp_avg && exp_avg_sq && segment_ends && lr && eps && weight_decay,
                   "mne_adam_step_segments: null argument");
@@ -159,6 +169,7 @@ extern "C" int mne_adam_step_segments(float* param, float* grad, float* exp_avg,
     }
     if (prev == 0) return 0;
     s.beta1 = beta1; s.beta2 = beta2; s.step_dev = step_dev; s.step_host = step_host; s.zero_grad = zero_grad;
+    s.touched = touched;
     int64_t blocks = ((prev >> 2) + 255) / 256;
     const int64_t cap = (int64_t)sm_count() * 8;
     if (blocks > cap) blocks = cap;

@@ -183,7 +183,7 @@ __device__ __forceinline__ void gather16_vec(const MneSceneDesc& sc, int grp, co
     const float* base[6];
 #pragma unroll
     for (int t = 0; t < 6; ++t) base[t] = sc.planes[grp * 6 + t].data + q * 4;
-#pragma unroll 2
+#pragma unroll 4
     for (int p = 0; p < np; ++p) {
         const float* seg = tab_base + p * tab_stride;
         float4 acc[2];

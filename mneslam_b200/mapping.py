@@ -35,7 +35,7 @@ def loss_weight_vector(cfg, is_co_sdf=None):
 
 
 class FusedMapper:
-    def __init__(self, model, is_co_sdf=None, process_group=None, world_size=1, adopt_parameters=True):
+    def __init__(self, model, is_co_sdf=None, process_group=None, world_size=1, adopt_parameters=True, skip_untouched=True):
         """``adopt_parameters``: move the planes and decoder weights into ONE flat buffer (each tensor keeps its
         Python identity, shape and strides; only its storage changes), with gradients and Adam moments laid out
         the same way, so that the optimiser is a single streaming launch and the multi-GPU gradient exchange a
@@ -73,6 +73,8 @@ class FusedMapper:
         self.flat_m = torch.zeros(mv_len, dtype=torch.float32, device=self.dev)
         self.flat_v = torch.zeros(mv_len, dtype=torch.float32, device=self.dev)
         self.flat_param = torch.zeros(padded, dtype=torch.float32, device=self.dev) if adopt_parameters else None
+        # one byte per 4 parameters of this rank's slice: groups never hit by a gradient are skipped by Adam (exact)
+        self.touched = torch.zeros(mv_len // 4, dtype=torch.uint8, device=self.dev) if (adopt_parameters and skip_untouched) else None
         self.grads, self.exp_avg, self.exp_avg_sq = [], [], []
         seg_ends, seg_lr, seg_eps, seg_wd = [], [], [], []
         off = 0
@@ -120,7 +122,8 @@ class FusedMapper:
         n_seg, ends, lr, eps, wd = segments
         _lib.check(_lib.lib().mne_adam_step_segments(param.data_ptr(), grad.data_ptr(), m.data_ptr(), v.data_ptr(), n_seg,
                                                      ends, lr, eps, wd, self.betas[0], self.betas[1],
-                                                     self.step_dev.data_ptr(), 0, 1 if zero_grad else 0, ops._stream()),
+                                                     self.step_dev.data_ptr(), 0, 1 if zero_grad else 0,
+                                                     ops._ptr(self.touched), ops._stream()),
                    'mne_adam_step_segments')
 
     # ------------------------------------------------------------------------------------------

@@ -144,3 +144,31 @@ def test_two_gpu_sharded_iteration_matches_single_gpu():
                         '127.0.0.1', '--master-port', '29533', os.path.join(root, 'tests', 'multigpu_check.py')],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and 'multigpu_check ok' in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+def test_touched_map_adam_is_bit_identical_to_dense():
+    """Skipping the 16-byte groups that never received a gradient must not change a single bit."""
+    import ctypes as C
+    from mneslam_b200 import _lib, ops
+    torch.manual_seed(1)
+    n = 1 << 16
+    p0 = torch.randn(n, device='cuda')
+    ends = (C.c_int64 * 2)(n - 4096, n)
+    lr, eps, wd = (C.c_float * 2)(5e-3, 1e-2), (C.c_float * 2)(1e-15, 1e-8), (C.c_float * 2)(0.0, 1e-6)
+    state = []
+    for use_map in (False, True):
+        p, m, v = p0.clone(), torch.zeros(n, device='cuda'), torch.zeros(n, device='cuda')
+        touched = torch.zeros(n // 4, dtype=torch.uint8, device='cuda') if use_map else None
+        gen = torch.Generator(device='cuda').manual_seed(7)
+        for t in range(1, 7):
+            g = torch.randn(n, device='cuda', generator=gen)
+            mask = torch.rand(n // 64, device='cuda', generator=gen) < (0.1 * t)      # growing set of touched 64-float tiles
+            g = (g.reshape(-1, 64) * mask[:, None]).reshape(-1).contiguous()
+            _lib.check(_lib.lib().mne_adam_step_segments(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), 2, ends, lr, eps,
+                                                         wd, 0.9, 0.99, None, t, 1, ops._ptr(touched), ops._stream()), 'adam')
+            assert float(g.abs().max()) == 0.0
+        state.append((p, m, v, touched))
+    (pd, md, vd, _), (ps, ms, vs, touched) = state
+    assert torch.equal(pd, ps) and torch.equal(md, ms) and torch.equal(vd, vs)
+    frac = touched[: (n - 4096) // 4].float().mean().item()
+    assert 0.2 < frac < 0.95, frac

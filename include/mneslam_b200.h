@@ -148,6 +148,12 @@ int mne_render_forward(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int3
                        const float* target_d, float* raw, float* weights, float* rgb, float* depth, float* disp,
                        float* acc_map, float* depth_var, int32_t* inds, double* acc, mne_stream_t stream);
 
+/* ---- compositing alone: JointEncoding.raw2outputs / sdf2weights (model/scene_rep.py:183-230) on raw [N,S,4] and
+ * z_vals [N,S] supplied by the caller.  Every output may be NULL. */
+int mne_composite(const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples, const float* z_vals, const float* raw,
+                  float* weights, float* rgb, float* depth, float* disp, float* acc_map, float* depth_var, int32_t* inds,
+                  mne_stream_t stream);
+
 /* ---- losses from the accumulators: compute_loss / get_sdf_loss / sdf_losses / mse2psnr
  * (model/utils.py:43-47,147-185; model/scene_rep.py:501-507).  losses[8] = rgb_loss, depth_loss,
  * co_sdf_loss, co_fs_loss, e_fs_loss, e_center_loss, e_tail_loss, psnr. */

@@ -62,6 +62,7 @@ _SIGNATURES = {
                                         C.c_int32] + [C.c_void_p] * 6),
     'mne_render_forward': (C.c_int, [C.POINTER(SceneDesc), C.POINTER(RenderCfg), C.c_int32, C.c_int32] +
                            [C.c_void_p] * 15),
+    'mne_composite': (C.c_int, [C.POINTER(RenderCfg), C.c_int32, C.c_int32] + [C.c_void_p] * 10),
     'mne_loss_finalize': (C.c_int, [C.POINTER(RenderCfg), C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     'mne_backward_scratch_bytes': (C.c_size_t, [C.c_int32, C.c_int32]),
     'mne_render_backward': (C.c_int, [C.POINTER(SceneDesc), C.POINTER(RenderCfg), C.c_int32, C.c_int32] +

@@ -325,3 +325,23 @@ extern "C" int mne_hash_indices(const MneHashDesc* hash, int64_t n_pts, const fl
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// compositing alone: raw2outputs / sdf2weights (reference model/scene_rep.py:183-230) on caller-supplied raw
+// ---------------------------------------------------------------------------------------------
+extern "C" int mne_composite(const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples, const float* z_vals,
+                             const float* raw, float* weights, float* rgb, float* depth, float* disp, float* acc_map,
+                             float* depth_var, int32_t* inds, mne_stream_t stream) {
+    using namespace mne;
+    MNE_CHECK_ARG(rcfg && z_vals && raw, "mne_composite: null argument");
+    MNE_CHECK_ARG(n_rays >= 0 && n_samples > 0, "mne_composite: bad sizes n_rays=%d n_samples=%d", n_rays, n_samples);
+    MNE_CHECK_ARG(((uintptr_t)raw & 15) == 0, "mne_composite: raw must be 16-byte aligned");
+    if (n_rays == 0) return 0;
+    RayFwdParams R{};
+    R.rc = *rcfg; R.n_rays = n_rays; R.n_samples = n_samples; R.z_vals = z_vals; R.raw = raw;
+    R.weights = weights; R.rgb = rgb; R.depth = depth; R.disp = disp; R.acc_map = acc_map; R.depth_var = depth_var; R.inds = inds;
+    const int blocks = max(1, min((n_rays + kRayWarps - 1) / kRayWarps, sm_count() * 4));
+    rays_fwd_kernel<<<blocks, kRayWarps * 32, 0, (cudaStream_t)stream>>>(R);
+    MNE_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}

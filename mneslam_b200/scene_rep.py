@@ -271,6 +271,32 @@ class JointEncoding(nn.Module):
     def query_color(self, query_points):
         return torch.sigmoid(self.query_color_sdf(query_points)[..., :3])
 
+    def raw2outputs(self, raw, z_vals, white_bkgd=False):
+        """reference ``model/scene_rep.py:205-230`` (forward values only): rgb_map, disp_map, acc_map, weights,
+        depth_map, depth_var from raw ``[N,S,4]`` and z_vals ``[N,S]``."""
+        import ctypes as C
+        from . import _lib
+        ops.require_cuda()
+        raw, z = ops._f32(raw, 'raw'), ops._f32(z_vals, 'z_vals')
+        n, s = z.shape
+        dev = z.device
+        cfg = dict(self.config)
+        cfg['training'] = dict(self.config['training'], white_bkgd=bool(white_bkgd))
+        rcfg = ops.make_render_cfg(cfg, norm_rays=max(n, 1))
+        o = {k: torch.empty(n, dtype=torch.float32, device=dev) for k in ('depth', 'disp', 'acc', 'var')}
+        rgb = torch.empty(n, 3, dtype=torch.float32, device=dev)
+        w = torch.empty(n, s, dtype=torch.float32, device=dev)
+        _lib.check(_lib.lib().mne_composite(C.byref(rcfg), n, s, z.data_ptr(), raw.data_ptr(), w.data_ptr(), rgb.data_ptr(),
+                                            o['depth'].data_ptr(), o['disp'].data_ptr(), o['acc'].data_ptr(), o['var'].data_ptr(),
+                                            None, ops._stream()), 'mne_composite')
+        return rgb, o['disp'], o['acc'], w, o['depth'], o['var']
+
+    def sdf2weights(self, sdf, z_vals, args=None):
+        """reference ``model/scene_rep.py:183-203`` (forward values only)."""
+        raw = torch.zeros(*sdf.shape, 4, dtype=torch.float32, device=sdf.device)
+        raw[..., 3] = sdf
+        return self.raw2outputs(raw, z_vals)[3]
+
     def render_surface_color(self, rays_o, normal):
         """reference ``model/scene_rep.py:333-349``: composite colour over a short normal-aligned segment."""
         from .compose import composite_along

@@ -126,3 +126,54 @@ def test_flat_shards_cover_segments():
                 assert h == ('a' if mid < 400 else 'b')
                 b = e
         assert covered == FlatShards(total, w, 0, ends, hp).padded
+
+
+def _exchange_worker(rank, world, port, out, tmpdir):
+    os.environ.update({'MASTER_ADDR': '127.0.0.1', 'MASTER_PORT': str(port)})
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        from mneslam_b200 import JointEncoding, exchange
+        cfg = configs.small_test_config(one_grid=False)
+        bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+        torch.manual_seed(10 + rank)
+        model = JointEncoding(cfg, bb)                  # on the CPU here; the payload logic is device-agnostic
+        shared = JointEncoding(cfg, bb)
+        nbytes = exchange.exchange_maps(model, shared, peer=1 - rank)
+        torch.manual_seed(10 + (1 - rank))
+        expect = JointEncoding(cfg, bb)
+        for a, b in zip(shared._flat_planes() + shared.decoder.weight_list(), expect._flat_planes() + expect.decoder.weight_list()):
+            assert torch.equal(a, b)
+        assert nbytes == 4 * sum(t.numel() for t in model._flat_planes() + model.decoder.weight_list())
+        # the reference's file format round-trips as well
+        path = os.path.join(tmpdir, 'latest_checkpoint_%d.pt' % rank)
+        exchange.save_checkpoint(model, path)
+        dist.barrier()
+        other = exchange.load_foreign_model(JointEncoding(cfg, bb), os.path.join(tmpdir, 'latest_checkpoint_%d.pt' % (1 - rank)))
+        for a, b in zip(other._flat_planes() + other.decoder.weight_list(), expect._flat_planes() + expect.decoder.weight_list()):
+            assert torch.equal(a, b)
+        assert sorted(exchange.checkpoint_dict(model)) == ['all_planes', 'bound', 'bounding_box', 'model']
+        assert 'sdf_net.model.0.weight' in exchange.checkpoint_dict(model)['model']
+        # broadcast of rank 0's map
+        exchange.broadcast_map(model, src=0)
+        torch.manual_seed(10)
+        zero = JointEncoding(cfg, bb)
+        assert all(torch.equal(a, b) for a, b in zip(model._flat_planes(), zero._flat_planes()))
+        out.put((rank, 'ok'))
+    except Exception as e:
+        import traceback
+        out.put((rank, traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_map_exchange_between_two_agents(tmp_path):
+    ctx = mp.get_context('spawn')
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_exchange_worker, args=(r, 2, port, out, str(tmp_path))) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = [out.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(results) == [(0, 'ok'), (1, 'ok')], results

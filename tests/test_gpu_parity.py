@@ -245,3 +245,16 @@ def test_importance_sampling_vs_reference_golden():
     np.testing.assert_allclose(loss.item(), g['loss'], rtol=REL_TOL)
     loss.backward()
     check_grads_against_golden(case, model, rays_o, rays_d)
+
+
+def test_raw2outputs_and_sdf2weights_entry_points():
+    """The compositing helpers the reference exposes as methods, on the golden raw / z_vals of the reference."""
+    case = Case('small_onegrid')
+    g = case.g
+    model = build_model(case.cfg, case.bounding_box, case.planes, case.weights, as_params=False)
+    raw, z = case.t('raw').cuda(), case.t('z_vals').cuda()
+    rgb, disp, acc, w, depth, var = model.raw2outputs(raw, z)
+    for got, k in ((rgb, 'rgb'), (disp, 'disp_map'), (acc, 'acc_map'), (depth, 'depth'), (var, 'depth_var')):
+        assert rel(got.cpu().numpy(), g[k]) < REL_TOL, k
+    w2 = model.sdf2weights(raw[..., 3].contiguous(), z)
+    assert torch.allclose(w, w2) and rel(w.sum(-1).cpu().numpy(), g['acc_map']) < REL_TOL

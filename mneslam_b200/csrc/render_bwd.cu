@@ -498,7 +498,7 @@ extern "C" int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg
         MNE_CHECK_CUDA(cudaMemsetAsync(g_rays_o, 0, sizeof(float) * 3 * (size_t)n_rays, st));
         MNE_CHECK_CUDA(cudaMemsetAsync(g_rays_d, 0, sizeof(float) * 3 * (size_t)n_rays, st));
     }
-    if (impl_version() == 2 && (!scene->two_grid || scene->encoder == 1))
+    if (impl_version() == 2 && !(scene->two_grid && ray_grad && param_grad))
         return render_backward_v2(scene, rcfg, n_rays, n_samples, rays_o, rays_d, z_vals, raw, target_rgb, target_d, acc,
                                   loss_grads, g_rgb, g_depth, g_raw, scratch, g_rays_o, g_rays_d, param_grad, st);
     BwdParams P{};

@@ -66,10 +66,12 @@ __device__ __forceinline__ void load_weights_t(const MneSceneDesc& sc, float* WT
 template <bool TWO> __host__ __device__ constexpr int bwd2_warp_floats() {
     return kTilePts * (kXStride + (TWO ? kCStride : 0) + 2 * kActStride + kGeoStride + kRgbStride);
 }
-template <bool TWO, bool RAY>
+template <bool TWO, bool RAY, int NW>
 constexpr size_t bwd2_smem_bytes() {
-    return sizeof(float4) * (size_t)NetV2<TWO>::W4_COUNT +
-           sizeof(float) * (size_t)((RAY ? NetT<TWO>::FLOATS_RAY : NetT<TWO>::FLOATS_NORAY) + kBwdWarps * bwd2_warp_floats<TWO>());
+    // forward-recompute weights: one grid keeps the split (3-term) layout -- tighter gradients; two grids only fit with
+    // the single-TF32 pair layout (half the bytes)
+    return (TWO ? sizeof(float2) * (size_t)NetF<TWO>::W2_COUNT : sizeof(float4) * (size_t)NetV2<TWO>::W4_COUNT) +
+           sizeof(float) * (size_t)((RAY ? NetT<TWO>::FLOATS_RAY : NetT<TWO>::FLOATS_NORAY) + NW * bwd2_warp_floats<TWO>());
 }
 
 struct PtsBwdParams {
@@ -112,15 +114,18 @@ __device__ __forceinline__ void outer_mma(float (&acc)[NACC][4], const float* __
 }
 
 // MODE: 0 = planes through strides, 1 = channels-last planes (vector gather / scatter), 2 = hash grid
-template <bool TWO, int MODE, bool RAY, bool PARAM>
-__global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __grid_constant__ PtsBwdParams P) {
+// NW = warps per CTA: 8 whenever weight gradients are accumulated (the block ownership below is laid out for 8);
+// the parameter-less variants have independent warps and may run with fewer to fit shared memory.
+template <bool TWO, int MODE, bool RAY, bool PARAM, int NW>
+__global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_constant__ PtsBwdParams P) {
     using N = NetV2<TWO>;
     using T = NetT<TWO>;
-    constexpr int NW = kBwdWarps;
+    static_assert(!PARAM || NW == kBwdWarps, "weight-gradient ownership is laid out for 8 warps");
     constexpr int WF = bwd2_warp_floats<TWO>();
     extern __shared__ __align__(16) float4 smem4[];
-    float4* W4 = smem4;
-    float* WT = reinterpret_cast<float*>(smem4 + N::W4_COUNT);
+    float2* W2 = reinterpret_cast<float2*>(smem4);       // two grids: single-TF32 pairs
+    float4* W4 = smem4;                                   // one grid: split (hi, lo) pairs
+    float* WT = TWO ? reinterpret_cast<float*>(W2 + NetF<TWO>::W2_COUNT) : reinterpret_cast<float*>(W4 + N::W4_COUNT);
     float* tiles = WT + (RAY ? T::FLOATS_RAY : T::FLOATS_NORAY);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float* X = tiles + warp * WF;
@@ -133,7 +138,8 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __g
     constexpr int O_CF = kTilePts * kXStride, O_ACT = O_CF + (TWO ? kTilePts * kCStride : 0), O_DY = O_ACT + kTilePts * kActStride,
                   O_GEO = O_DY + kTilePts * kActStride, O_DRGB = O_GEO + kTilePts * kGeoStride;
 
-    load_weights_v2<TWO>(P.sc, W4, threadIdx.x, blockDim.x);
+    if (TWO) load_weights_1x<TWO>(P.sc, W2, threadIdx.x, blockDim.x);
+    else load_weights_v2<TWO>(P.sc, W4, threadIdx.x, blockDim.x);
     load_weights_t<TWO, RAY>(P.sc, WT, threadIdx.x, blockDim.x);
     __syncthreads();
 
@@ -211,8 +217,13 @@ __global__ void __launch_bounds__(kBwdWarps * 32, 1) points_bwd_kernel(const __g
         __syncwarp();
 
         // ---- 2. forward recompute, upstream of this tile's rows g and g+8
-        float h1[4][4], o16[2][4], hc[4][4], rgbf[4];
-        decoder_forward_mma<TWO>(W4, X, CFt, lane, h1, o16, hc, rgbf);
+        float h1[4][4], o16[2][4], hc[4][4];
+        if (TWO) {
+            decoder_forward_mma_1x<TWO>(W2, X, CFt, lane, h1, o16, hc);
+        } else {
+            float rgb_unused[4];
+            decoder_forward_mma<TWO>(W4, X, CFt, lane, h1, o16, hc, rgb_unused);
+        }
         float4 dr_lo = make_float4(0.f, 0.f, 0.f, 0.f), dr_hi = dr_lo;
         if (g < np) dr_lo = __ldg(P.draw + pt0 + g);
         if (g + 8 < np) dr_hi = __ldg(P.draw + pt0 + g + 8);
@@ -608,31 +619,37 @@ __global__ void __launch_bounds__(256) rays_bwd_kernel(const RayBwdParams P) {
 int check_scene(const MneSceneDesc* sc, const char* who, bool need_grads);
 int sm_count();
 
-template <bool TWO, int MODE, bool RAY, bool PARAM>
+template <bool TWO, int MODE, bool RAY, bool PARAM, int NW = kBwdWarps>
 static int launch_points_bwd(const PtsBwdParams& P, cudaStream_t stream) {
-    const size_t smem = bwd2_smem_bytes<TWO, RAY>();
+    const size_t smem = bwd2_smem_bytes<TWO, RAY, NW>();
     static bool configured[64] = {};
     int dev = 0;
     MNE_CHECK_CUDA(cudaGetDevice(&dev));
     if (dev >= 64 || !configured[dev]) {
-        MNE_CHECK_CUDA(cudaFuncSetAttribute(points_bwd_kernel<TWO, MODE, RAY, PARAM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        MNE_CHECK_CUDA(cudaFuncSetAttribute(points_bwd_kernel<TWO, MODE, RAY, PARAM, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (dev < 64) configured[dev] = true;
     }
     const int64_t n_tiles = (P.n_pts + kTilePts - 1) / kTilePts;
-    const int blocks = (int)max((int64_t)1, min((n_tiles + kBwdWarps - 1) / kBwdWarps, (int64_t)sm_count()));
-    points_bwd_kernel<TWO, MODE, RAY, PARAM><<<blocks, kBwdWarps * 32, smem, stream>>>(P);
+    const int blocks = (int)max((int64_t)1, min((n_tiles + NW - 1) / NW, (int64_t)sm_count()));
+    points_bwd_kernel<TWO, MODE, RAY, PARAM, NW><<<blocks, NW * 32, smem, stream>>>(P);
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
 
 template <int MODE>
 static int dispatch_points_bwd(const PtsBwdParams& P, bool ray, bool param, cudaStream_t st) {
+    if (P.sc.two_grid) {
+        // (two grids + ray AND parameter gradients together exceed the shared-memory plan: render_bwd.cu keeps
+        //  that one combination on the v1 kernel)
+        if (ray) return launch_points_bwd<true, MODE, true, false, 6>(P, st);
+        return launch_points_bwd<true, MODE, false, true>(P, st);
+    }
     if (ray && param) return launch_points_bwd<false, MODE, true, true>(P, st);
     if (ray) return launch_points_bwd<false, MODE, true, false>(P, st);
     return launch_points_bwd<false, MODE, false, true>(P, st);
 }
 
-// v2 backward (one grid; two grids do not fit this kernel's shared-memory plan and stay on the v1 kernel)
+// v2 backward
 int render_backward_v2(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples,
                        const float* rays_o, const float* rays_d, const float* z_vals, const float* raw,
                        const float* target_rgb, const float* target_d, const double* acc, const float* loss_grads,

@@ -70,7 +70,7 @@ template <bool TWO, bool RAY, int NW>
 constexpr size_t bwd2_smem_bytes() {
     // forward-recompute weights: one grid keeps the split (3-term) layout -- tighter gradients; two grids only fit with
     // the single-TF32 pair layout (half the bytes)
-    return (TWO ? sizeof(float2) * (size_t)NetF<TWO>::W2_COUNT : sizeof(float4) * (size_t)NetV2<TWO>::W4_COUNT) +
+    return sizeof(float4) * (size_t)NetV2<TWO>::W4_COUNT +
            sizeof(float) * (size_t)((RAY ? NetT<TWO>::FLOATS_RAY : NetT<TWO>::FLOATS_NORAY) + NW * bwd2_warp_floats<TWO>());
 }
 
@@ -114,18 +114,16 @@ __device__ __forceinline__ void outer_mma(float (&acc)[NACC][4], const float* __
 }
 
 // MODE: 0 = planes through strides, 1 = channels-last planes (vector gather / scatter), 2 = hash grid
-// NW = warps per CTA: 8 whenever weight gradients are accumulated (the block ownership below is laid out for 8);
-// the parameter-less variants have independent warps and may run with fewer to fit shared memory.
+// NW = warps per CTA: 8 for one grid; two grids need more shared memory per warp and for the weights, so 6 (or 5 with
+// the ray-gradient weights); weight-gradient blocks are dealt round-robin to warps (slot = block / NW).
 template <bool TWO, int MODE, bool RAY, bool PARAM, int NW>
 __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_constant__ PtsBwdParams P) {
     using N = NetV2<TWO>;
     using T = NetT<TWO>;
-    static_assert(!PARAM || NW == kBwdWarps, "weight-gradient ownership is laid out for 8 warps");
     constexpr int WF = bwd2_warp_floats<TWO>();
     extern __shared__ __align__(16) float4 smem4[];
-    float2* W2 = reinterpret_cast<float2*>(smem4);       // two grids: single-TF32 pairs
-    float4* W4 = smem4;                                   // one grid: split (hi, lo) pairs
-    float* WT = TWO ? reinterpret_cast<float*>(W2 + NetF<TWO>::W2_COUNT) : reinterpret_cast<float*>(W4 + N::W4_COUNT);
+    float4* W4 = smem4;                                   // split (hi, lo) pairs for the activation recompute
+    float* WT = reinterpret_cast<float*>(W4 + N::W4_COUNT);
     float* tiles = WT + (RAY ? T::FLOATS_RAY : T::FLOATS_NORAY);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float* X = tiles + warp * WF;
@@ -138,8 +136,7 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
     constexpr int O_CF = kTilePts * kXStride, O_ACT = O_CF + (TWO ? kTilePts * kCStride : 0), O_DY = O_ACT + kTilePts * kActStride,
                   O_GEO = O_DY + kTilePts * kActStride, O_DRGB = O_GEO + kTilePts * kGeoStride;
 
-    if (TWO) load_weights_1x<TWO>(P.sc, W2, threadIdx.x, blockDim.x);
-    else load_weights_v2<TWO>(P.sc, W4, threadIdx.x, blockDim.x);
+    load_weights_v2<TWO>(P.sc, W4, threadIdx.x, blockDim.x);
     load_weights_t<TWO, RAY>(P.sc, WT, threadIdx.x, blockDim.x);
     __syncthreads();
 
@@ -153,15 +150,21 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
     //   phase 1: d col0^T  -- one 16-row block of inputs per warp (one grid: warps 0..3; two grids: 0..7), 4 col blocks
     //            d col1^T  -- rows j (2 blocks) x 8 cols: warps 4,5 (one grid) / 0,1 (two grids, extra)
     //   phase 2: d sdf0^T  -- warps 0..6, input block = warp, 4 col blocks;  d sdf1^T -- warp 7: 2 row blocks x 2 col blocks
-    float acc_v1[4][4], acc_v2[1][4], acc_w1[4][4];
+    // block b of a phase is owned by warp b % NW, in that warp's accumulator slot b / NW
+    constexpr int V1_BLOCKS = N::KC / 16;                   // col0 input blocks: 4 (one grid) or 8 (two grids)
+    constexpr int NB1 = V1_BLOCKS + 2;                      // + the two row blocks of col1
+    constexpr int NB2 = 8;                                  // 7 input blocks of sdf0 + sdf1 (four 16x8 blocks in one slot)
+    constexpr int S1 = (NB1 + NW - 1) / NW, S2 = (NB2 + NW - 1) / NW;
+    float acc1[S1][4][4], acc2[S2][4][4];
 #pragma unroll
     for (int n = 0; n < 4; ++n)
 #pragma unroll
-        for (int i = 0; i < 4; ++i) { acc_v1[n][i] = 0.f; acc_w1[n][i] = 0.f; }
+        for (int i = 0; i < 4; ++i) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) acc_v2[0][i] = 0.f;
-    constexpr int V1_BLOCKS = N::KC / 16;                   // 4 (one grid) or 8 (two grids)
-    const int v2_owner0 = TWO ? 0 : 4;
+            for (int sl = 0; sl < S1; ++sl) acc1[sl][n][i] = 0.f;
+#pragma unroll
+            for (int sl = 0; sl < S2; ++sl) acc2[sl][n][i] = 0.f;
+        }
 
     for (int64_t round = 0; round < n_rounds; ++round) {
         // consecutive tiles of a round go to different SMs (block-minor), as in the forward
@@ -218,9 +221,10 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
 
         // ---- 2. forward recompute, upstream of this tile's rows g and g+8
         float h1[4][4], o16[2][4], hc[4][4];
-        if (TWO) {
-            decoder_forward_mma_1x<TWO>(W2, X, CFt, lane, h1, o16, hc);
-        } else {
+        {
+            // same split-precision products as the forward kernel: the ReLU masks and activations must be the
+            // forward's (a single-TF32 recompute flips masks of near-zero pre-activations: measured 1e-2..5e-2
+            // max-norm gradient error on the two-grid goldens, against 2e-3 with the split)
             float rgb_unused[4];
             decoder_forward_mma<TWO>(W4, X, CFt, lane, h1, o16, hc, rgb_unused);
         }
@@ -265,21 +269,25 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
         if (PARAM) __syncthreads();                              // A: every warp's ACT / DY / GEO / DRGB / X are published
 
         // ---- 4. weight gradients, phase 1 (colour net)
-        if (PARAM && warp < V1_BLOCKS) {
-            for (int w = 0; w < NW; ++w) {
-                const float* src = tiles + w * WF;
-                const float* A; int as, m0;
-                const int blk = warp;                           // 16-row block of col0's inputs
-                if (blk < 3) { A = src; as = kXStride; m0 = kBlobCol + blk * 16; }
-                else if (TWO && blk < 7) { A = src + O_CF; as = kCStride; m0 = (blk - 3) * 16; }
-                else { A = src + O_GEO; as = kGeoStride; m0 = 0; }
-                outer_mma<4, 0>(acc_v1, A, as, m0, src + O_DY, kActStride, g, t);
-            }
-        }
-        if (PARAM && (warp == v2_owner0 || warp == v2_owner0 + 1)) {
-            for (int w = 0; w < NW; ++w) {
-                const float* src = tiles + w * WF;
-                outer_mma<1, 0>(acc_v2, src + O_ACT, kActStride, (warp - v2_owner0) * 16, src + O_DRGB, kRgbStride, g, t);
+        if (PARAM) {
+#pragma unroll
+            for (int sl = 0; sl < S1; ++sl) {
+                const int blk = warp + sl * NW;
+                if (blk < V1_BLOCKS) {                           // 16-row block of col0's inputs
+                    for (int w = 0; w < NW; ++w) {
+                        const float* src = tiles + w * WF;
+                        const float* A; int as, m0;
+                        if (blk < 3) { A = src; as = kXStride; m0 = kBlobCol + blk * 16; }
+                        else if (TWO && blk < 7) { A = src + O_CF; as = kCStride; m0 = (blk - 3) * 16; }
+                        else { A = src + O_GEO; as = kGeoStride; m0 = 0; }
+                        outer_mma<4, 0>(acc1[sl], A, as, m0, src + O_DY, kActStride, g, t);
+                    }
+                } else if (blk < NB1) {                          // 16-row block of col1's inputs (hidden j), 8 (3 real) cols
+                    for (int w = 0; w < NW; ++w) {
+                        const float* src = tiles + w * WF;
+                        outer_mma<1, 0>(acc1[sl], src + O_ACT, kActStride, (blk - V1_BLOCKS) * 16, src + O_DRGB, kRgbStride, g, t);
+                    }
+                }
             }
         }
         if (PARAM) __syncthreads();                              // B: phase-1 tiles may be overwritten
@@ -317,18 +325,23 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
         if (PARAM) __syncthreads();                              // C
 
         // ---- 6. weight gradients, phase 2 (sdf net)
-        if (!PARAM) {
-        } else if (warp < 7) {
-            for (int w = 0; w < NW; ++w) {
-                const float* src = tiles + w * WF;
-                outer_mma<4, 0>(acc_w1, src, kXStride, warp * 16, src + O_DY, kActStride, g, t);
-            }
-        } else {
-            // d sdf1^T [32 j][16 i]: blocks (row block rb, col block cb) -> acc_w1[rb * 2 + cb]
-            for (int w = 0; w < NW; ++w) {
-                const float* src = tiles + w * WF;
-                outer_mma<2, 0>(acc_w1, src + O_ACT, kActStride, 0, src + O_GEO, kGeoStride, g, t);
-                outer_mma<2, 2>(acc_w1, src + O_ACT, kActStride, 16, src + O_GEO, kGeoStride, g, t);
+        if (PARAM) {
+#pragma unroll
+            for (int sl = 0; sl < S2; ++sl) {
+                const int blk = warp + sl * NW;
+                if (blk < 7) {
+                    for (int w = 0; w < NW; ++w) {
+                        const float* src = tiles + w * WF;
+                        outer_mma<4, 0>(acc2[sl], src, kXStride, blk * 16, src + O_DY, kActStride, g, t);
+                    }
+                } else if (blk == 7) {
+                    // d sdf1^T [32 j][16 i]: blocks (row block rb, col block cb) -> acc2[sl][rb * 2 + cb]
+                    for (int w = 0; w < NW; ++w) {
+                        const float* src = tiles + w * WF;
+                        outer_mma<2, 0>(acc2[sl], src + O_ACT, kActStride, 0, src + O_GEO, kGeoStride, g, t);
+                        outer_mma<2, 2>(acc2[sl], src + O_ACT, kActStride, 16, src + O_GEO, kGeoStride, g, t);
+                    }
+                }
             }
         }
         if (PARAM) __syncthreads();                              // D: X may be overwritten with d feat
@@ -489,44 +502,49 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
 
     // ---- flush the register-resident weight gradients (once per CTA)
     if (PARAM) {
-        // d col0^T block: rows = inputs (blk*16 + g, +8), cols = j
-        if (warp < V1_BLOCKS && P.sc.g_col0) {
 #pragma unroll
-            for (int nb = 0; nb < 4; ++nb)
+        for (int sl = 0; sl < S1; ++sl) {
+            const int blk = warp + sl * NW;
+            if (blk < V1_BLOCKS && P.sc.g_col0) {                // rows = inputs (blk*16 + g, +8), cols = j
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int k = warp * 16 + g + ((i & 2) ? 8 : 0), j = nb * 8 + 2 * t + (i & 1);
-                    if (k < N::IN_COL) atomicAdd(P.sc.g_col0 + j * N::IN_COL + k, acc_v1[nb][i]);
-                }
-        }
-        if ((warp == v2_owner0 || warp == v2_owner0 + 1) && P.sc.g_col1) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int j = (warp - v2_owner0) * 16 + g + ((i & 2) ? 8 : 0), c = 2 * t + (i & 1);
-                if (c < 3) atomicAdd(P.sc.g_col1 + c * 32 + j, acc_v2[0][i]);
-            }
-        }
-        if (warp < 7 && P.sc.g_sdf0) {
-#pragma unroll
-            for (int nb = 0; nb < 4; ++nb)
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int k = warp * 16 + g + ((i & 2) ? 8 : 0), j = nb * 8 + 2 * t + (i & 1);
-                    const bool hash = MODE == 2;
-                    const int col = sdf0_col(k, hash);
-                    if (col >= 0) atomicAdd(P.sc.g_sdf0 + j * sdf0_in(hash) + col, acc_w1[nb][i]);
-                }
-        }
-        if (warp == 7 && P.sc.g_sdf1) {
-#pragma unroll
-            for (int rb = 0; rb < 2; ++rb)
-#pragma unroll
-                for (int cb = 0; cb < 2; ++cb)
+                for (int nb = 0; nb < 4; ++nb)
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
-                        const int j = rb * 16 + g + ((i & 2) ? 8 : 0), c = cb * 8 + 2 * t + (i & 1);
-                        atomicAdd(P.sc.g_sdf1 + ((c == 15) ? 0 : c + 1) * 32 + j, acc_w1[rb * 2 + cb][i]);
+                        const int k = blk * 16 + g + ((i & 2) ? 8 : 0), j = nb * 8 + 2 * t + (i & 1);
+                        if (k < N::IN_COL) atomicAdd(P.sc.g_col0 + j * N::IN_COL + k, acc1[sl][nb][i]);
                     }
+            } else if (blk >= V1_BLOCKS && blk < NB1 && P.sc.g_col1) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int j = (blk - V1_BLOCKS) * 16 + g + ((i & 2) ? 8 : 0), c = 2 * t + (i & 1);
+                    if (c < 3) atomicAdd(P.sc.g_col1 + c * 32 + j, acc1[sl][0][i]);
+                }
+            }
+        }
+#pragma unroll
+        for (int sl = 0; sl < S2; ++sl) {
+            const int blk = warp + sl * NW;
+            if (blk < 7 && P.sc.g_sdf0) {
+#pragma unroll
+                for (int nb = 0; nb < 4; ++nb)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int k = blk * 16 + g + ((i & 2) ? 8 : 0), j = nb * 8 + 2 * t + (i & 1);
+                        const bool hash = MODE == 2;
+                        const int col = sdf0_col(k, hash);
+                        if (col >= 0) atomicAdd(P.sc.g_sdf0 + j * sdf0_in(hash) + col, acc2[sl][nb][i]);
+                    }
+            } else if (blk == 7 && P.sc.g_sdf1) {
+#pragma unroll
+                for (int rb = 0; rb < 2; ++rb)
+#pragma unroll
+                    for (int cb = 0; cb < 2; ++cb)
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const int j = rb * 16 + g + ((i & 2) ? 8 : 0), c = cb * 8 + 2 * t + (i & 1);
+                            atomicAdd(P.sc.g_sdf1 + ((c == 15) ? 0 : c + 1) * 32 + j, acc2[sl][rb * 2 + cb][i]);
+                        }
+            }
         }
     }
 }
@@ -641,8 +659,8 @@ static int dispatch_points_bwd(const PtsBwdParams& P, bool ray, bool param, cuda
     if (P.sc.two_grid) {
         // (two grids + ray AND parameter gradients together exceed the shared-memory plan: render_bwd.cu keeps
         //  that one combination on the v1 kernel)
-        if (ray) return launch_points_bwd<true, MODE, true, false, 6>(P, st);
-        return launch_points_bwd<true, MODE, false, true>(P, st);
+        if (ray) return launch_points_bwd<true, MODE, true, false, 5>(P, st);
+        return launch_points_bwd<true, MODE, false, true, 6>(P, st);
     }
     if (ray && param) return launch_points_bwd<false, MODE, true, true>(P, st);
     if (ray) return launch_points_bwd<false, MODE, true, false>(P, st);

@@ -444,118 +444,4 @@ __device__ __forceinline__ void decoder_forward_mma(const float4* __restrict__ W
     }
 }
 
-
-// ---------------------------------------------------------------------------------------------
-// single-TF32 variant of the decoder forward, used by the BACKWARD kernel's activation recompute (gradients only
-// need the cosine >= 0.999 gate).  Weights as plain pairs W2[n][kp] = (W[n][2kp], W[n][2kp+1]): half the shared
-// memory of the split layout, one 64-bit load per B fragment.  Row strides (in float2) are == 4 (mod 16).
-// ---------------------------------------------------------------------------------------------
-template <bool TWO>
-struct NetF {
-    using N = NetV2<TWO>;
-    static constexpr int RS1 = N::K1P + 12;          // 68
-    static constexpr int RS2 = N::K2P + 4;           // 20
-    static constexpr int RSC = N::KCP + 4;           // 36 / 68
-    static constexpr int OFF1 = 0;
-    static constexpr int OFF2 = OFF1 + 32 * RS1;
-    static constexpr int OFFC = OFF2 + 16 * RS2;
-    static constexpr int OFFO = OFFC + 32 * RSC;
-    static constexpr int W2_COUNT = OFFO + 8 * RS2;  // float2 elements
-};
-
-template <bool TWO>
-__device__ __forceinline__ void load_weights_1x(const MneSceneDesc& sc, float2* W2, int tid, int nthreads) {
-    using N = NetV2<TWO>;
-    using F = NetF<TWO>;
-    const bool hash = sc.encoder == 1;
-    for (int i = tid; i < 32 * N::K1P; i += nthreads) {
-        const int n = i / N::K1P, kp = i % N::K1P;
-        const int c0 = sdf0_col(2 * kp, hash), c1 = sdf0_col(2 * kp + 1, hash);
-        W2[F::OFF1 + n * F::RS1 + kp] = make_float2(c0 >= 0 ? sc.w_sdf0[n * sdf0_in(hash) + c0] : 0.0f,
-                                                    c1 >= 0 ? sc.w_sdf0[n * sdf0_in(hash) + c1] : 0.0f);
-    }
-    for (int i = tid; i < 16 * N::K2P; i += nthreads) {
-        const int n = i / N::K2P, kp = i % N::K2P;
-        const int out = (n == 15) ? 0 : n + 1;
-        W2[F::OFF2 + n * F::RS2 + kp] = make_float2(sc.w_sdf1[out * 32 + 2 * kp], sc.w_sdf1[out * 32 + 2 * kp + 1]);
-    }
-    for (int i = tid; i < 32 * N::KCP; i += nthreads) {
-        const int n = i / N::KCP, kp = i % N::KCP;
-        const int k0 = 2 * kp, k1 = 2 * kp + 1;
-        W2[F::OFFC + n * F::RSC + kp] = make_float2((k0 < N::IN_COL) ? sc.w_col0[n * N::IN_COL + k0] : 0.0f,
-                                                    (k1 < N::IN_COL) ? sc.w_col0[n * N::IN_COL + k1] : 0.0f);
-    }
-    for (int i = tid; i < 8 * N::K2P; i += nthreads) {
-        const int n = i / N::K2P, kp = i % N::K2P;
-        W2[F::OFFO + n * F::RS2 + kp] = (n < 3) ? make_float2(sc.w_col1[n * 32 + 2 * kp], sc.w_col1[n * 32 + 2 * kp + 1])
-                                                : make_float2(0.f, 0.f);
-    }
-}
-
-__device__ __forceinline__ void mma_f(float (&d)[4], float a0, float a1, float a2, float a3, const float2& b) {
-    const uint32_t a[4] = {__float_as_uint(a0), __float_as_uint(a1), __float_as_uint(a2), __float_as_uint(a3)};
-    mma_tf32(d, a, __float_as_uint(b.x), __float_as_uint(b.y));
-}
-
-template <bool TWO>
-__device__ __forceinline__ void decoder_forward_mma_1x(const float2* __restrict__ W2, const float* __restrict__ X,
-                                                       const float* __restrict__ CFt, int lane, float (&h1)[4][4],
-                                                       float (&o16)[2][4], float (&hc)[4][4]) {
-    using N = NetV2<TWO>;
-    using F = NetF<TWO>;
-    const int g = lane >> 2, t = lane & 3;
-#pragma unroll
-    for (int n = 0; n < 4; ++n)
-#pragma unroll
-        for (int i = 0; i < 4; ++i) { h1[n][i] = 0.f; hc[n][i] = 0.f; }
-#pragma unroll 2
-    for (int ks = 0; ks < N::K1 / 8; ++ks) {
-        const float2 lo = *reinterpret_cast<const float2*>(X + g * kXStride + ks * 8 + 2 * t);
-        const float2 hi = *reinterpret_cast<const float2*>(X + (g + 8) * kXStride + ks * 8 + 2 * t);
-#pragma unroll
-        for (int n = 0; n < 4; ++n) mma_f(h1[n], lo.x, hi.x, lo.y, hi.y, W2[F::OFF1 + (n * 8 + g) * F::RS1 + ks * 4 + t]);
-    }
-#pragma unroll
-    for (int n = 0; n < 4; ++n)
-#pragma unroll
-        for (int i = 0; i < 4; ++i) h1[n][i] = fmaxf(h1[n][i], 0.f);
-#pragma unroll
-    for (int n = 0; n < 2; ++n)
-#pragma unroll
-        for (int i = 0; i < 4; ++i) o16[n][i] = 0.f;
-#pragma unroll
-    for (int ks = 0; ks < 4; ++ks)
-#pragma unroll
-        for (int n = 0; n < 2; ++n)
-            mma_f(o16[n], h1[ks][0], h1[ks][2], h1[ks][1], h1[ks][3], W2[F::OFF2 + (n * 8 + g) * F::RS2 + ks * 4 + t]);
-    int kp0 = 0;
-#pragma unroll 2
-    for (int ks = 0; ks < kBlob / 8; ++ks) {
-        const float2 lo = *reinterpret_cast<const float2*>(X + g * kXStride + kBlobCol + ks * 8 + 2 * t);
-        const float2 hi = *reinterpret_cast<const float2*>(X + (g + 8) * kXStride + kBlobCol + ks * 8 + 2 * t);
-#pragma unroll
-        for (int n = 0; n < 4; ++n) mma_f(hc[n], lo.x, hi.x, lo.y, hi.y, W2[F::OFFC + (n * 8 + g) * F::RSC + kp0 + ks * 4 + t]);
-    }
-    kp0 += kBlob / 2;
-    if (TWO) {
-#pragma unroll 2
-        for (int ks = 0; ks < 8; ++ks) {
-            const float2 lo = *reinterpret_cast<const float2*>(CFt + g * kCStride + ks * 8 + 2 * t);
-            const float2 hi = *reinterpret_cast<const float2*>(CFt + (g + 8) * kCStride + ks * 8 + 2 * t);
-#pragma unroll
-            for (int n = 0; n < 4; ++n) mma_f(hc[n], lo.x, hi.x, lo.y, hi.y, W2[F::OFFC + (n * 8 + g) * F::RSC + kp0 + ks * 4 + t]);
-        }
-        kp0 += 32;
-    }
-#pragma unroll
-    for (int ks = 0; ks < 2; ++ks)
-#pragma unroll
-        for (int n = 0; n < 4; ++n)
-            mma_f(hc[n], o16[ks][0], o16[ks][2], o16[ks][1], o16[ks][3], W2[F::OFFC + (n * 8 + g) * F::RSC + kp0 + ks * 4 + t]);
-#pragma unroll
-    for (int n = 0; n < 4; ++n)
-#pragma unroll
-        for (int i = 0; i < 4; ++i) hc[n][i] = fmaxf(hc[n][i], 0.f);
-}
-
 }  // namespace mne

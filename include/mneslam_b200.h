@@ -230,6 +230,21 @@ int mne_adam_step_segments(float* param, float* grad, float* exp_avg, float* exp
                            float beta1, float beta2, const int64_t* step_dev, int64_t step_host, int32_t zero_grad,
                            uint8_t* touched, mne_stream_t stream);
 
+/* ---- data-parallel optimiser step over NVLink peer memory: ONE kernel instead of NCCL reduce-scatter + Adam +
+ * all-gather (the reference has no multi-GPU training at all; this serves the ray-sharded mapping of BASELINE.json
+ * configs[3]).  param_ptrs / grad_ptrs: HOST arrays of world_size device pointers to every rank's full flat
+ * parameter / gradient buffer, all mapped into this process (e.g. torch symmetric memory).  This rank owns the
+ * elements [slice_begin, slice_begin + segment_ends[last]) and holds exp_avg / exp_avg_sq / touched for that slice
+ * only.  The kernel sums the slice's gradient over all ranks (peer loads), clears what it read, applies Adam and
+ * stores the new parameters into every rank's buffer (peer stores).  The caller must place a cross-rank barrier
+ * before the call (all gradients complete) and after it (all parameters written). */
+#define MNE_MAX_PEERS 16
+int mne_adam_step_peers(int32_t world_size, int32_t rank, float* const* param_ptrs, float* const* grad_ptrs,
+                        int64_t slice_begin, float* exp_avg, float* exp_avg_sq, int32_t n_segments,
+                        const int64_t* segment_ends, const float* lr, const float* eps, const float* weight_decay,
+                        float beta1, float beta2, const int64_t* step_dev, int64_t step_host, uint8_t* touched,
+                        mne_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -177,3 +177,115 @@ extern "C" int mne_adam_step_segments(float* param, float* grad, float* exp_avg,
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Data-parallel optimiser step as ONE kernel over NVLink peer memory (replaces reduce-scatter + Adam + all-gather).
+//
+// Every rank holds the whole flat gradient and parameter buffers in peer-mapped memory.  Rank r owns the slice
+// [begin, begin + len) of the parameters (and keeps the Adam moments of that slice only).  For each 16-byte group
+// of its slice the kernel
+//   - loads the gradient group from EVERY rank's buffer (local load + P2P loads) and sums them,
+//   - clears the groups it read that were non-zero (so nobody needs a separate 129 MB memset pass),
+//   - applies Adam (same arithmetic and the same never-touched skip as adam_segments_kernel),
+//   - stores the updated parameters into EVERY rank's parameter buffer (local store + P2P stores).
+// NVLink traffic per rank: (G-1)/G of the gradient in, (G-1)/G of the parameters out -- what reduce-scatter +
+// all-gather move, but overlapped with the HBM work of the update and without staging buffers.
+// The caller brackets the launch with cross-rank barriers (gradients complete before, parameters visible after).
+// ---------------------------------------------------------------------------------------------------------
+namespace mne {
+
+struct AdamPeers {
+    float* param[MNE_MAX_PEERS];
+    float* grad[MNE_MAX_PEERS];
+    int world, rank;
+    int64_t begin4;            // first float4 group of this rank's slice
+    float* m;                  // moments of the slice
+    float* v;
+    int n_seg;
+    int64_t end4[MNE_ADAM_MAX_SEGMENTS];      // slice-relative exclusive ends, float4 units
+    float lr[MNE_ADAM_MAX_SEGMENTS], eps[MNE_ADAM_MAX_SEGMENTS], wd[MNE_ADAM_MAX_SEGMENTS];
+    float beta1, beta2;
+    const int64_t* step_dev;
+    int64_t step_host;
+    uint8_t* touched;
+};
+
+__global__ void __launch_bounds__(256) adam_peers_kernel(const __grid_constant__ AdamPeers s) {
+    const double t = (double)(s.step_dev ? *s.step_dev : s.step_host);
+    const float bc1 = (float)(1.0 - pow((double)s.beta1, t));
+    const float bc2_sqrt = (float)sqrt(1.0 - pow((double)s.beta2, t));
+    const int64_t n4 = s.end4[s.n_seg - 1];
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    float4* m4 = reinterpret_cast<float4*>(s.m);
+    float4* v4 = reinterpret_cast<float4*>(s.v);
+    int seg = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        while (i >= s.end4[seg]) ++seg;
+        const int64_t gi = s.begin4 + i;
+        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int r = 0; r < s.world; ++r) {
+            float4* gp = reinterpret_cast<float4*>(s.grad[r]) + gi;
+            const float4 x = *gp;
+            if (x.x != 0.0f || x.y != 0.0f || x.z != 0.0f || x.w != 0.0f) {
+                g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
+                *gp = zero;
+            }
+        }
+        AdamArgs a{};
+        a.beta1 = s.beta1; a.beta2 = s.beta2; a.eps = s.eps[seg]; a.weight_decay = s.wd[seg]; a.zero_grad = 0;
+        if (s.touched && a.weight_decay == 0.0f) {
+            const bool nz = g.x != 0.0f || g.y != 0.0f || g.z != 0.0f || g.w != 0.0f;
+            const uint8_t f = s.touched[i];
+            if (!nz && !f) continue;                 // identity update: every replica already holds this value
+            if (!f) s.touched[i] = 1;
+        }
+        const float step_size = (float)((double)s.lr[seg] / (double)bc1);
+        float4 p = reinterpret_cast<float4*>(s.param[s.rank])[gi], m = m4[i], v = v4[i];
+        adam_one(p.x, g.x, m.x, v.x, a, step_size, bc2_sqrt);
+        adam_one(p.y, g.y, m.y, v.y, a, step_size, bc2_sqrt);
+        adam_one(p.z, g.z, m.z, v.z, a, step_size, bc2_sqrt);
+        adam_one(p.w, g.w, m.w, v.w, a, step_size, bc2_sqrt);
+        m4[i] = m; v4[i] = v;
+        for (int r = 0; r < s.world; ++r) reinterpret_cast<float4*>(s.param[r])[gi] = p;
+    }
+}
+
+}  // namespace mne
+
+extern "C" int mne_adam_step_peers(int32_t world_size, int32_t rank, float* const* param_ptrs, float* const* grad_ptrs,
+                                   int64_t slice_begin, float* exp_avg, float* exp_avg_sq, int32_t n_segments,
+                                   const int64_t* segment_ends, const float* lr, const float* eps, const float* weight_decay,
+                                   float beta1, float beta2, const int64_t* step_dev, int64_t step_host, uint8_t* touched,
+                                   mne_stream_t stream) {
+    using namespace mne;
+    MNE_CHECK_ARG(param_ptrs && grad_ptrs && exp_avg && exp_avg_sq && segment_ends && lr && eps && weight_decay,
+                  "mne_adam_step_peers: null argument");
+    MNE_CHECK_ARG(world_size >= 1 && world_size <= MNE_MAX_PEERS && rank >= 0 && rank < world_size,
+                  "mne_adam_step_peers: world size %d / rank %d out of range (at most %d peers)", world_size, rank, MNE_MAX_PEERS);
+    MNE_CHECK_ARG(n_segments >= 1 && n_segments <= MNE_ADAM_MAX_SEGMENTS, "mne_adam_step_peers: 1..%d segments supported", MNE_ADAM_MAX_SEGMENTS);
+    MNE_CHECK_ARG(slice_begin >= 0 && (slice_begin & 3) == 0, "mne_adam_step_peers: slice_begin must be a multiple of 4 elements");
+    MNE_CHECK_ARG(step_dev || step_host >= 1, "mne_adam_step_peers: step must be >= 1");
+    AdamPeers s{};
+    for (int r = 0; r < world_size; ++r) {
+        MNE_CHECK_ARG(param_ptrs[r] && grad_ptrs[r] && ((((uintptr_t)param_ptrs[r]) | ((uintptr_t)grad_ptrs[r])) & 15) == 0,
+                      "mne_adam_step_peers: peer buffers must be non-null and 16-byte aligned");
+        s.param[r] = param_ptrs[r]; s.grad[r] = grad_ptrs[r];
+    }
+    s.world = world_size; s.rank = rank; s.begin4 = slice_begin >> 2; s.m = exp_avg; s.v = exp_avg_sq; s.n_seg = n_segments;
+    int64_t prev = 0;
+    for (int i = 0; i < n_segments; ++i) {
+        MNE_CHECK_ARG(segment_ends[i] >= prev && (segment_ends[i] & 3) == 0,
+                      "mne_adam_step_peers: segment ends must be ascending multiples of 4 elements");
+        s.end4[i] = segment_ends[i] >> 2; s.lr[i] = lr[i]; s.eps[i] = eps[i]; s.wd[i] = weight_decay[i];
+        prev = segment_ends[i];
+    }
+    if (prev == 0) return 0;
+    s.beta1 = beta1; s.beta2 = beta2; s.step_dev = step_dev; s.step_host = step_host; s.touched = touched;
+    int64_t blocks = ((prev >> 2) + 255) / 256;
+    const int64_t cap = (int64_t)sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    adam_peers_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
+    MNE_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}

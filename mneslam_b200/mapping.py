@@ -35,7 +35,8 @@ def loss_weight_vector(cfg, is_co_sdf=None):
 
 
 class FusedMapper:
-    def __init__(self, model, is_co_sdf=None, process_group=None, world_size=1, adopt_parameters=True, skip_untouched=True):
+    def __init__(self, model, is_co_sdf=None, process_group=None, world_size=1, adopt_parameters=True, skip_untouched=True,
+                 peer_memory=True):
         """``adopt_parameters``: move the planes and decoder weights into ONE flat buffer (each tensor keeps its
         Python identity, shape and strides; only its storage changes), with gradients and Adam moments laid out
         the same way, so that the optimiser is a single streaming launch and the multi-GPU gradient exchange a
@@ -67,12 +68,36 @@ class FusedMapper:
         else:
             padded = total
         self.total = total
-        self.flat_grad = torch.zeros(padded, dtype=torch.float32, device=self.dev)
+        # several GPUs: gradient and parameter buffers in NVLink peer-mapped (symmetric) memory, so that the optimiser
+        # can be ONE kernel that reduces over the peers and writes the result back to them (mne_adam_step_peers);
+        # if that memory cannot be set up, the NCCL reduce-scatter / all-gather path is used instead
+        self.peers = None
+        if world_size > 1 and peer_memory:
+            try:
+                import torch.distributed._symmetric_memory as symm
+                group = process_group if process_group is not None else torch.distributed.group.WORLD
+                g_buf = symm.empty(padded, dtype=torch.float32, device=self.dev)
+                p_buf = symm.empty(padded, dtype=torch.float32, device=self.dev)
+                hg, hp = symm.rendezvous(g_buf, group.group_name), symm.rendezvous(p_buf, group.group_name)
+                self.peers = {'grad': g_buf, 'param': p_buf, 'hg': hg, 'hp': hp,
+                              'grad_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hg.buffer_ptrs]),
+                              'param_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hp.buffer_ptrs])}
+            except Exception as e:      # no peer access / no symmetric-memory support: NCCL collectives instead
+                import warnings
+                warnings.warn('mneslam_b200: peer-memory optimiser unavailable (%r); using NCCL collectives' % (e,))
+                self.peers = None
+        if self.peers is not None:
+            self.flat_grad = self.peers['grad'].zero_()
+        else:
+            self.flat_grad = torch.zeros(padded, dtype=torch.float32, device=self.dev)
         # single GPU: full-length Adam moments; multi GPU: each rank keeps the moments of its own slice only
         mv_len = padded // world_size
         self.flat_m = torch.zeros(mv_len, dtype=torch.float32, device=self.dev)
         self.flat_v = torch.zeros(mv_len, dtype=torch.float32, device=self.dev)
-        self.flat_param = torch.zeros(padded, dtype=torch.float32, device=self.dev) if adopt_parameters else None
+        if self.peers is not None:
+            self.flat_param = self.peers['param'].zero_()
+        else:
+            self.flat_param = torch.zeros(padded, dtype=torch.float32, device=self.dev) if adopt_parameters else None
         # one byte per 4 parameters of this rank's slice: groups never hit by a gradient are skipped by Adam (exact)
         self.touched = torch.zeros(mv_len // 4, dtype=torch.uint8, device=self.dev) if (adopt_parameters and skip_untouched) else None
         self.grads, self.exp_avg, self.exp_avg_sq = [], [], []
@@ -168,6 +193,16 @@ class FusedMapper:
         lib = _lib.lib()
         st = ops._stream()
         _lib.check(lib.mne_adam_tick(self.step_dev.data_ptr(), st), 'mne_adam_tick')
+        if self.world_size > 1 and self.peers is not None:
+            n_seg, ends, lr, eps, wd = self._local_segments
+            pr = self.peers
+            pr['hg'].barrier(channel=0)               # every rank's backward has finished writing its gradient
+            _lib.check(lib.mne_adam_step_peers(self.world_size, self.shards.rank, pr['param_ptrs'], pr['grad_ptrs'],
+                                               self.shards.lo, self.flat_m.data_ptr(), self.flat_v.data_ptr(), n_seg, ends, lr,
+                                               eps, wd, self.betas[0], self.betas[1], self.step_dev.data_ptr(), 0,
+                                               ops._ptr(self.touched), st), 'mne_adam_step_peers')
+            pr['hp'].barrier(channel=1)               # every rank's slice has landed in every parameter buffer
+            return
         if self.world_size > 1:
             from .distributed import sharded_optimizer_step
 

@@ -233,17 +233,28 @@ int mne_adam_step_segments(float* param, float* grad, float* exp_avg, float* exp
 /* ---- data-parallel optimiser step over NVLink peer memory: ONE kernel instead of NCCL reduce-scatter + Adam +
  * all-gather (the reference has no multi-GPU training at all; this serves the ray-sharded mapping of BASELINE.json
  * configs[3]).  param_ptrs / grad_ptrs: HOST arrays of world_size device pointers to every rank's full flat
- * parameter / gradient buffer, all mapped into this process (e.g. torch symmetric memory).  This rank owns the
- * elements [slice_begin, slice_begin + segment_ends[last]) and holds exp_avg / exp_avg_sq / touched for that slice
- * only.  The kernel sums the slice's gradient over all ranks (peer loads), clears what it read, applies Adam and
- * stores the new parameters into every rank's buffer (peer stores).  The caller must place a cross-rank barrier
- * before the call (all gradients complete) and after it (all parameters written). */
+ * parameter / gradient buffer (n_total floats each, padding included), all mapped into this process (e.g. torch
+ * symmetric memory).  Ownership is block-cyclic: chunk c (`chunk` floats, a multiple of 32) belongs to rank
+ * c % world_size -- contiguous slices would hand one rank the densely observed planes and another the barely
+ * touched ones.  exp_avg / exp_avg_sq / touched hold this rank's n_total / world_size elements packed in ownership
+ * order; segment_ends are GLOBAL offsets.  The kernel sums the slice's gradient over all ranks (peer loads), clears what it read, applies Adam and
+ * stores the new parameters into every rank's buffer (peer stores).  When multicast_param / multicast_grad (the
+ * NVLink-switch multicast addresses of the same two buffers) are given, the reduction and the broadcast happen in the
+ * switch: multimem.ld_reduce for the gradient, multimem.st for the parameters and for clearing the gradient.
+ * dirty_ptrs (HOST array of world_size device pointers, or NULL): every rank's "non-zero this step" map of its own
+ * gradient buffer, one byte per 32 floats, written by mne_grad_dirty_map before the barrier.  With it the owner
+ * fetches a peer's 16-byte group only where that peer flagged the texel -- a mapping iteration touches about a fifth
+ * of the map, so most of the NVLink traffic of a dense reduction disappears.  The caller must place a cross-rank barrier before the call (all gradients and dirty maps complete) and
+ * after it (all parameters written). */
 #define MNE_MAX_PEERS 16
 int mne_adam_step_peers(int32_t world_size, int32_t rank, float* const* param_ptrs, float* const* grad_ptrs,
-                        int64_t slice_begin, float* exp_avg, float* exp_avg_sq, int32_t n_segments,
+                        int64_t n_total, int32_t chunk, float* exp_avg, float* exp_avg_sq, int32_t n_segments,
                         const int64_t* segment_ends, const float* lr, const float* eps, const float* weight_decay,
                         float beta1, float beta2, const int64_t* step_dev, int64_t step_host, uint8_t* touched,
+                        float* multicast_param, float* multicast_grad, const uint8_t* const* dirty_ptrs,
                         mne_stream_t stream);
+/* dirty[i] = 1 iff grad[32 i .. 32 i + 31] holds a non-zero value (n a multiple of 32). */
+int mne_grad_dirty_map(const float* grad, int64_t n, uint8_t* dirty, mne_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -34,9 +34,12 @@ def loss_weight_vector(cfg, is_co_sdf=None):
     return w
 
 
+PEER_CHUNK = 1024      # floats per ownership chunk (4 KB) of the peer-memory optimiser
+
+
 class FusedMapper:
     def __init__(self, model, is_co_sdf=None, process_group=None, world_size=1, adopt_parameters=True, skip_untouched=True,
-                 peer_memory=True):
+                 peer_memory=True, use_multicast=True):
         """``adopt_parameters``: move the planes and decoder weights into ONE flat buffer (each tensor keeps its
         Python identity, shape and strides; only its storage changes), with gradients and Adam moments laid out
         the same way, so that the optimiser is a single streaming launch and the multi-GPU gradient exchange a
@@ -63,7 +66,7 @@ class FusedMapper:
         if world_size > 1:
             if not adopt_parameters:
                 raise ValueError('multi-GPU mapping needs adopt_parameters=True (flat buffers for the collectives)')
-            q = world_size * 4
+            q = world_size * PEER_CHUNK  # whole ownership chunks per rank (block-cyclic ownership of the peer optimiser)
             padded = (total + q - 1) // q * q
         else:
             padded = total
@@ -78,10 +81,21 @@ class FusedMapper:
                 group = process_group if process_group is not None else torch.distributed.group.WORLD
                 g_buf = symm.empty(padded, dtype=torch.float32, device=self.dev)
                 p_buf = symm.empty(padded, dtype=torch.float32, device=self.dev)
+                d_buf = symm.empty(padded // 32, dtype=torch.uint8, device=self.dev)     # "non-zero this step" flags
                 hg, hp = symm.rendezvous(g_buf, group.group_name), symm.rendezvous(p_buf, group.group_name)
-                self.peers = {'grad': g_buf, 'param': p_buf, 'hg': hg, 'hp': hp,
+                hd = symm.rendezvous(d_buf, group.group_name)
+                d_buf.zero_()
+                self.peers = {'grad': g_buf, 'param': p_buf, 'dirty': d_buf, 'hg': hg, 'hp': hp, 'hd': hd,
+                              'dirty_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hd.buffer_ptrs]),
                               'grad_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hg.buffer_ptrs]),
-                              'param_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hp.buffer_ptrs])}
+                              'param_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hp.buffer_ptrs]),
+                              # NVLink-switch multicast addresses (0 when the fabric has no multicast support)
+                              'mc_grad': int(getattr(hg, 'multicast_ptr', 0) or 0) if use_multicast else 0,
+                              'mc_param': int(getattr(hp, 'multicast_ptr', 0) or 0) if use_multicast else 0}
+                # measured (r01): multicast stores pay off from 4 ranks up; with 2 ranks plain peer stores are faster
+                if world_size < 4:
+                    self.peers['mc_param'] = 0
+                self.peers['mc_grad'] = 0             # the gradient side uses the sparse (dirty-map) peer reduction
             except Exception as e:      # no peer access / no symmetric-memory support: NCCL collectives instead
                 import warnings
                 warnings.warn('mneslam_b200: peer-memory optimiser unavailable (%r); using NCCL collectives' % (e,))
@@ -124,7 +138,7 @@ class FusedMapper:
         if world_size > 1:
             from .distributed import FlatShards
             rank = torch.distributed.get_rank(process_group)
-            self.shards = FlatShards(total, world_size, rank, seg_ends, list(zip(seg_lr, seg_eps, seg_wd)))
+            self.shards = FlatShards(total, world_size, rank, seg_ends, list(zip(seg_lr, seg_eps, seg_wd)), align=PEER_CHUNK)
             self.grad_shard = torch.zeros(self.shards.shard_len, dtype=torch.float32, device=self.dev)
             self._local_segments = self._pack_segments(self.shards.local_ends, self.shards.local_hparams)
         n_planes = len(planes)
@@ -194,13 +208,16 @@ class FusedMapper:
         st = ops._stream()
         _lib.check(lib.mne_adam_tick(self.step_dev.data_ptr(), st), 'mne_adam_tick')
         if self.world_size > 1 and self.peers is not None:
-            n_seg, ends, lr, eps, wd = self._local_segments
+            n_seg, ends, lr, eps, wd = self._segments          # global segment ends; ownership is block-cyclic
             pr = self.peers
-            pr['hg'].barrier(channel=0)               # every rank's backward has finished writing its gradient
+            _lib.check(lib.mne_grad_dirty_map(self.flat_grad.data_ptr(), self.flat_grad.numel(), pr['dirty'].data_ptr(), st),
+                       'mne_grad_dirty_map')
+            pr['hg'].barrier(channel=0)               # every rank's gradient and dirty map are complete
             _lib.check(lib.mne_adam_step_peers(self.world_size, self.shards.rank, pr['param_ptrs'], pr['grad_ptrs'],
-                                               self.shards.lo, self.flat_m.data_ptr(), self.flat_v.data_ptr(), n_seg, ends, lr,
+                                               self.flat_grad.numel(), PEER_CHUNK, self.flat_m.data_ptr(), self.flat_v.data_ptr(), n_seg, ends, lr,
                                                eps, wd, self.betas[0], self.betas[1], self.step_dev.data_ptr(), 0,
-                                               ops._ptr(self.touched), st), 'mne_adam_step_peers')
+                                               ops._ptr(self.touched), pr['mc_param'] or None, pr['mc_grad'] or None, pr['dirty_ptrs'], st),
+                       'mne_adam_step_peers')
             pr['hp'].barrier(channel=1)               # every rank's slice has landed in every parameter buffer
             return
         if self.world_size > 1:

@@ -241,20 +241,25 @@ int mne_adam_step_segments(float* param, float* grad, float* exp_avg, float* exp
  * stores the new parameters into every rank's buffer (peer stores).  When multicast_param / multicast_grad (the
  * NVLink-switch multicast addresses of the same two buffers) are given, the reduction and the broadcast happen in the
  * switch: multimem.ld_reduce for the gradient, multimem.st for the parameters and for clearing the gradient.
- * dirty_ptrs (HOST array of world_size device pointers, or NULL): every rank's "non-zero this step" map of its own
- * gradient buffer, one byte per 32 floats, written by mne_grad_dirty_map before the barrier.  With it the owner
- * fetches a peer's 16-byte group only where that peer flagged the texel -- a mapping iteration touches about a fifth
- * of the map, so most of the NVLink traffic of a dense reduction disappears.  The caller must place a cross-rank barrier before the call (all gradients and dirty maps complete) and
+ * dirty (device pointer on THIS rank, or NULL): [world_size][n_total / 32 / world_size] flag bytes, slot r holding
+ * rank r's "non-zero this step" flags of the 32-float texels this rank owns (packed in ownership order), pushed
+ * there by every rank's mne_grad_dirty_map before the barrier.  With it the owner fetches a peer's 16-byte group only
+ * where that peer flagged the texel -- a mapping iteration touches about a fifth of the map, so most of the NVLink
+ * traffic of a dense reduction disappears.  chunk must be a power of two >= 32.  The caller must place a cross-rank
+ * barrier before the call (all gradients and flags complete) and
  * after it (all parameters written). */
 #define MNE_MAX_PEERS 16
 int mne_adam_step_peers(int32_t world_size, int32_t rank, float* const* param_ptrs, float* const* grad_ptrs,
                         int64_t n_total, int32_t chunk, float* exp_avg, float* exp_avg_sq, int32_t n_segments,
                         const int64_t* segment_ends, const float* lr, const float* eps, const float* weight_decay,
                         float beta1, float beta2, const int64_t* step_dev, int64_t step_host, uint8_t* touched,
-                        float* multicast_param, float* multicast_grad, const uint8_t* const* dirty_ptrs,
+                        float* multicast_param, float* multicast_grad, const uint8_t* dirty,
                         mne_stream_t stream);
-/* dirty[i] = 1 iff grad[32 i .. 32 i + 31] holds a non-zero value (n a multiple of 32). */
-int mne_grad_dirty_map(const float* grad, int64_t n, uint8_t* dirty, mne_stream_t stream);
+/* For every 32-float texel of this rank's gradient buffer: flag = 1 iff it holds a non-zero value; the flag is
+ * stored into the texel OWNER's flag array (dirty_ptrs[owner], HOST array of world_size peer-mapped device pointers)
+ * at [rank][owner-local texel index] -- the layout mne_adam_step_peers reads.  world_size = 1: a plain local map. */
+int mne_grad_dirty_map(const float* grad, int64_t n_total, int32_t chunk, int32_t world_size, int32_t rank,
+                       uint8_t* const* dirty_ptrs, mne_stream_t stream);
 
 #ifdef __cplusplus
 }

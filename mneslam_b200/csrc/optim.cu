@@ -200,7 +200,7 @@ struct AdamPeers {
     int world, rank;
     int64_t total4;            // float4 groups in the whole (padded) buffer
     int64_t local4;            // float4 groups this rank owns
-    int chunk4;                // ownership is block-cyclic: chunk c (chunk4 groups) belongs to rank c % world
+    int chunk4_log2;           // ownership is block-cyclic: chunk c (2^chunk4_log2 groups) belongs to rank c % world
     float* m;                  // moments of the owned groups, packed in ownership order
     float* v;
     int n_seg;
@@ -212,22 +212,34 @@ struct AdamPeers {
     uint8_t* touched;
     float* mc_param;           // NVLink-switch multicast addresses of the same buffers, or NULL (plain peer loads / stores)
     float* mc_grad;
-    const uint8_t* dirty[MNE_MAX_PEERS];   // per rank: one byte per 32 floats of its gradient buffer, "non-zero this step"
+    const uint8_t* dirty;      // LOCAL [world][local4 / 8]: rank r's "non-zero this step" flags of the texels this rank owns
     int use_dirty;
 };
 
 // one flag byte per 32 consecutive floats (a 128-byte texel): does this rank's gradient have anything there?
-// A mapping iteration touches ~20 % of the texels, so the owners fetch only flagged groups from their peers.
-__global__ void __launch_bounds__(256) grad_dirty_kernel(const float4* __restrict__ g4, int64_t n32, uint8_t* __restrict__ dirty) {
+// A mapping iteration touches ~20 % of the texels, so the owners fetch only flagged groups from their peers.  The flag
+// is PUSHED to the texel's owner (slot `rank` of the owner's flag array, packed in ownership order): peer stores are
+// fire-and-forget, whereas flag loads from the peers cost the optimiser kernel 60 us of NVLink round trips (measured).
+struct DirtyPush {
+    uint8_t* dst[MNE_MAX_PEERS];
+    int world, rank, chunk_tx_log2;
+    int64_t n32, local32;
+};
+__global__ void __launch_bounds__(256) grad_dirty_kernel(const float4* __restrict__ g4, const __grid_constant__ DirtyPush d) {
     const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 3;
     const int sub = threadIdx.x & 7;
-    for (int64_t tx = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3; tx < n32; tx += stride) {
+    for (int64_t tx = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3; tx < d.n32; tx += stride) {
         const float4 v = g4[tx * 8 + sub];
         unsigned nz = (v.x != 0.0f || v.y != 0.0f || v.z != 0.0f || v.w != 0.0f) ? 1u : 0u;
         nz |= __shfl_xor_sync(0xffffffffu, nz, 1);
         nz |= __shfl_xor_sync(0xffffffffu, nz, 2);
         nz |= __shfl_xor_sync(0xffffffffu, nz, 4);
-        if (sub == 0) dirty[tx] = (uint8_t)nz;
+        if (sub == 0) {
+            const uint32_t c = (uint32_t)(tx >> d.chunk_tx_log2);
+            const uint32_t owner = c % (uint32_t)d.world;
+            const int64_t lt = ((int64_t)(c / (uint32_t)d.world) << d.chunk_tx_log2) + (tx & ((1 << d.chunk_tx_log2) - 1));
+            d.dst[owner][(int64_t)d.rank * d.local32 + lt] = (uint8_t)nz;
+        }
     }
 }
 
@@ -243,6 +255,87 @@ __device__ __forceinline__ void multimem_st(float4* p, const float4& v) {
                  :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
+// Sparse variant (dirty maps): the NVLink round trips are what bounds this kernel, so they are batched -- all peers'
+// flags of the NEXT group are fetched while the current one is processed, and the flagged peers' gradients are loaded
+// four at a time before anything depends on them.
+__device__ __forceinline__ int64_t owned_group(const AdamPeers& s, int64_t i) {
+    return ((((i >> s.chunk4_log2) * s.world + s.rank)) << s.chunk4_log2) + (i & ((1 << s.chunk4_log2) - 1));
+}
+__device__ __forceinline__ uint32_t peer_flags(const AdamPeers& s, int64_t i) {
+    const uint8_t* f = s.dirty + (i >> 3);
+    const int64_t local32 = s.local4 >> 3;
+    uint32_t mk = 0;
+#pragma unroll 4
+    for (int r = 0; r < s.world; ++r) mk |= (uint32_t)(f[r * local32] != 0) << r;
+    return mk;
+}
+
+__global__ void __launch_bounds__(256) adam_peers_sparse_kernel(const __grid_constant__ AdamPeers s) {
+    const double t = (double)(s.step_dev ? *s.step_dev : s.step_host);
+    const float bc1 = (float)(1.0 - pow((double)s.beta1, t));
+    const float bc2_sqrt = (float)sqrt(1.0 - pow((double)s.beta2, t));
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t end_all = s.end4[s.n_seg - 1];
+    float4* m4 = reinterpret_cast<float4*>(s.m);
+    float4* v4 = reinterpret_cast<float4*>(s.v);
+    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+    int seg = 0;
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t gi_n = i < s.local4 ? owned_group(s, i) : end_all;
+    uint32_t mk_n = 0;
+    uint8_t tf_n = 1;
+    if (gi_n < end_all) { mk_n = peer_flags(s, i); if (s.touched) tf_n = s.touched[i]; }
+    for (; i < s.local4; i += stride) {
+        const int64_t gi = gi_n;
+        const uint32_t mk = mk_n;
+        const uint8_t tf = tf_n;
+        const int64_t i2 = i + stride;
+        gi_n = i2 < s.local4 ? owned_group(s, i2) : end_all;
+        mk_n = 0; tf_n = 1;
+        if (gi_n < end_all) { mk_n = peer_flags(s, i2); if (s.touched) tf_n = s.touched[i2]; }
+        if (gi >= end_all) continue;                       // padding
+        while (gi >= s.end4[seg]) ++seg;
+        const float wd = s.wd[seg];
+        if (s.touched && wd == 0.0f && !mk && !tf) continue;   // identity update: every replica already holds this value
+        float4 p = reinterpret_cast<float4*>(s.param[s.rank])[gi], m = m4[i], v = v4[i];
+        float4 g = zero;
+        uint32_t rest = mk;
+        while (rest) {
+            float4 x[4];
+            float4* gp[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                gp[k] = nullptr; x[k] = zero;
+                if (rest) {
+                    const int r = __ffs(rest) - 1;
+                    rest &= rest - 1;
+                    gp[k] = reinterpret_cast<float4*>(s.grad[r]) + gi;
+                    x[k] = *gp[k];
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (gp[k]) { g.x += x[k].x; g.y += x[k].y; g.z += x[k].z; g.w += x[k].w; *gp[k] = zero; }
+        }
+        AdamArgs a{};
+        a.beta1 = s.beta1; a.beta2 = s.beta2; a.eps = s.eps[seg]; a.weight_decay = wd; a.zero_grad = 0;
+        if (s.touched && wd == 0.0f) {
+            const bool nz = g.x != 0.0f || g.y != 0.0f || g.z != 0.0f || g.w != 0.0f;
+            if (!nz && !tf) continue;                // flagged texel, but this group of it carried no gradient
+            if (!tf) s.touched[i] = 1;
+        }
+        const float step_size = (float)((double)s.lr[seg] / (double)bc1);
+        adam_one(p.x, g.x, m.x, v.x, a, step_size, bc2_sqrt);
+        adam_one(p.y, g.y, m.y, v.y, a, step_size, bc2_sqrt);
+        adam_one(p.z, g.z, m.z, v.z, a, step_size, bc2_sqrt);
+        adam_one(p.w, g.w, m.w, v.w, a, step_size, bc2_sqrt);
+        m4[i] = m; v4[i] = v;
+        if (s.mc_param) multimem_st(reinterpret_cast<float4*>(s.mc_param) + gi, p);
+        else
+            for (int r = 0; r < s.world; ++r) reinterpret_cast<float4*>(s.param[r])[gi] = p;
+    }
+}
+
 __global__ void __launch_bounds__(256) adam_peers_kernel(const __grid_constant__ AdamPeers s) {
     const double t = (double)(s.step_dev ? *s.step_dev : s.step_host);
     const float bc1 = (float)(1.0 - pow((double)s.beta1, t));
@@ -254,23 +347,12 @@ __global__ void __launch_bounds__(256) adam_peers_kernel(const __grid_constant__
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < s.local4; i += stride) {
         // block-cyclic ownership: contiguous slices would give one rank the densely observed planes and another the
         // barely touched ones (measured: 75 % vs 21 % touched at two ranks); 4 KB chunks dealt round-robin balance it
-        const int64_t gi = ((i / s.chunk4) * s.world + s.rank) * s.chunk4 + (i % s.chunk4);
+        const int64_t gi = owned_group(s, i);
         if (gi >= s.end4[s.n_seg - 1]) continue;          // padding
         while (gi >= s.end4[seg]) ++seg;
         float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
         const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (s.use_dirty) {
-            // sparse reduction: fetch a peer's group only where that peer flagged its texel
-            const int64_t tx = gi >> 3;
-            for (int r = 0; r < s.world; ++r) {
-                if (s.dirty[r][tx]) {
-                    float4* gp = reinterpret_cast<float4*>(s.grad[r]) + gi;
-                    const float4 x = *gp;
-                    g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
-                    *gp = zero;
-                }
-            }
-        } else if (s.mc_grad) {
+        if (s.mc_grad) {
             g = multimem_ld_reduce_add(reinterpret_cast<const float4*>(s.mc_grad) + gi);
             // (a sum of non-zero terms can cancel to zero; clear whenever any rank may have written: cheap test on the
             //  local copy plus the sum covers every case but exact cancellation with a zero local part, so clear on
@@ -315,7 +397,7 @@ extern "C" int mne_adam_step_peers(int32_t world_size, int32_t rank, float* cons
                                    int64_t n_total, int32_t chunk, float* exp_avg, float* exp_avg_sq, int32_t n_segments,
                                    const int64_t* segment_ends, const float* lr, const float* eps, const float* weight_decay,
                                    float beta1, float beta2, const int64_t* step_dev, int64_t step_host, uint8_t* touched,
-                                   float* multicast_param, float* multicast_grad, const uint8_t* const* dirty_ptrs,
+                                   float* multicast_param, float* multicast_grad, const uint8_t* dirty,
                                    mne_stream_t stream) {
     using namespace mne;
     MNE_CHECK_ARG(param_ptrs && grad_ptrs && exp_avg && exp_avg_sq && segment_ends && lr && eps && weight_decay,
@@ -323,8 +405,8 @@ extern "C" int mne_adam_step_peers(int32_t world_size, int32_t rank, float* cons
     MNE_CHECK_ARG(world_size >= 1 && world_size <= MNE_MAX_PEERS && rank >= 0 && rank < world_size,
                   "mne_adam_step_peers: world size %d / rank %d out of range (at most %d peers)", world_size, rank, MNE_MAX_PEERS);
     MNE_CHECK_ARG(n_segments >= 1 && n_segments <= MNE_ADAM_MAX_SEGMENTS, "mne_adam_step_peers: 1..%d segments supported", MNE_ADAM_MAX_SEGMENTS);
-    MNE_CHECK_ARG(chunk >= 32 && (chunk & 31) == 0 && n_total > 0 && n_total % ((int64_t)chunk * world_size) == 0,
-                  "mne_adam_step_peers: chunk must be a multiple of 32 and n_total a multiple of chunk * world_size");
+    MNE_CHECK_ARG(chunk >= 32 && (chunk & (chunk - 1)) == 0 && n_total > 0 && n_total % ((int64_t)chunk * world_size) == 0,
+                  "mne_adam_step_peers: chunk must be a power of two >= 32 and n_total a multiple of chunk * world_size");
     MNE_CHECK_ARG(step_dev || step_host >= 1, "mne_adam_step_peers: step must be >= 1");
     AdamPeers s{};
     for (int r = 0; r < world_size; ++r) {
@@ -332,7 +414,7 @@ extern "C" int mne_adam_step_peers(int32_t world_size, int32_t rank, float* cons
                       "mne_adam_step_peers: peer buffers must be non-null and 16-byte aligned");
         s.param[r] = param_ptrs[r]; s.grad[r] = grad_ptrs[r];
     }
-    s.world = world_size; s.rank = rank; s.total4 = n_total >> 2; s.local4 = (n_total / world_size) >> 2; s.chunk4 = chunk >> 2;
+    s.world = world_size; s.rank = rank; s.total4 = n_total >> 2; s.local4 = (n_total / world_size) >> 2; s.chunk4_log2 = 31 - __builtin_clz((unsigned)chunk) - 2;
     s.m = exp_avg; s.v = exp_avg_sq; s.n_seg = n_segments;
     int64_t prev = 0;
     for (int i = 0; i < n_segments; ++i) {
@@ -345,31 +427,37 @@ extern "C" int mne_adam_step_peers(int32_t world_size, int32_t rank, float* cons
     if (prev == 0) return 0;
     s.beta1 = beta1; s.beta2 = beta2; s.step_dev = step_dev; s.step_host = step_host; s.touched = touched;
     s.mc_param = multicast_param; s.mc_grad = multicast_grad;
-    s.use_dirty = dirty_ptrs != nullptr;
-    if (dirty_ptrs) {
-        for (int r = 0; r < world_size; ++r) {
-            MNE_CHECK_ARG(dirty_ptrs[r], "mne_adam_step_peers: null dirty map");
-            s.dirty[r] = dirty_ptrs[r];
-        }
-    }
+    s.use_dirty = dirty != nullptr;
+    s.dirty = dirty;
     int64_t blocks = (s.local4 + 255) / 256;
     const int64_t cap = (int64_t)sm_count() * 8;
     if (blocks > cap) blocks = cap;
-    adam_peers_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
+    if (s.use_dirty) adam_peers_sparse_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
+    else adam_peers_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
 
-extern "C" int mne_grad_dirty_map(const float* grad, int64_t n, uint8_t* dirty, mne_stream_t stream) {
+extern "C" int mne_grad_dirty_map(const float* grad, int64_t n_total, int32_t chunk, int32_t world_size, int32_t rank,
+                                  uint8_t* const* dirty_ptrs, mne_stream_t stream) {
     using namespace mne;
-    MNE_CHECK_ARG(grad && dirty, "mne_grad_dirty_map: null argument");
-    MNE_CHECK_ARG(n >= 0 && (n & 31) == 0 && (((uintptr_t)grad) & 15) == 0, "mne_grad_dirty_map: n must be a multiple of 32 and grad 16-byte aligned");
-    if (n == 0) return 0;
-    const int64_t n32 = n >> 5;
-    int64_t blocks = (n32 * 8 + 255) / 256;
+    MNE_CHECK_ARG(grad && dirty_ptrs, "mne_grad_dirty_map: null argument");
+    MNE_CHECK_ARG(world_size >= 1 && world_size <= MNE_MAX_PEERS && rank >= 0 && rank < world_size, "mne_grad_dirty_map: bad world_size / rank");
+    MNE_CHECK_ARG(chunk >= 32 && (chunk & (chunk - 1)) == 0 && n_total >= 0 && n_total % ((int64_t)chunk * world_size) == 0 &&
+                  (((uintptr_t)grad) & 15) == 0 && (n_total >> 5) / chunk < (int64_t)1 << 31,
+                  "mne_grad_dirty_map: chunk must be a power of two >= 32, n_total a multiple of chunk * world_size, grad 16-byte aligned");
+    if (n_total == 0) return 0;
+    DirtyPush d{};
+    for (int r = 0; r < world_size; ++r) {
+        MNE_CHECK_ARG(dirty_ptrs[r], "mne_grad_dirty_map: null flag array");
+        d.dst[r] = dirty_ptrs[r];
+    }
+    d.world = world_size; d.rank = rank; d.chunk_tx_log2 = 31 - __builtin_clz((unsigned)chunk) - 5;
+    d.n32 = n_total >> 5; d.local32 = d.n32 / world_size;
+    int64_t blocks = (d.n32 * 8 + 255) / 256;
     const int64_t cap = (int64_t)sm_count() * 8;
     if (blocks > cap) blocks = cap;
-    grad_dirty_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float4*>(grad), n32, dirty);
+    grad_dirty_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float4*>(grad), d);
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

@@ -81,7 +81,7 @@ class FusedMapper:
                 group = process_group if process_group is not None else torch.distributed.group.WORLD
                 g_buf = symm.empty(padded, dtype=torch.float32, device=self.dev)
                 p_buf = symm.empty(padded, dtype=torch.float32, device=self.dev)
-                d_buf = symm.empty(padded // 32, dtype=torch.uint8, device=self.dev)     # "non-zero this step" flags
+                d_buf = symm.empty(padded // 32, dtype=torch.uint8, device=self.dev)     # [rank][owned texel] "non-zero this step" flags, pushed by the peers
                 hg, hp = symm.rendezvous(g_buf, group.group_name), symm.rendezvous(p_buf, group.group_name)
                 hd = symm.rendezvous(d_buf, group.group_name)
                 d_buf.zero_()
@@ -210,13 +210,14 @@ class FusedMapper:
         if self.world_size > 1 and self.peers is not None:
             n_seg, ends, lr, eps, wd = self._segments          # global segment ends; ownership is block-cyclic
             pr = self.peers
-            _lib.check(lib.mne_grad_dirty_map(self.flat_grad.data_ptr(), self.flat_grad.numel(), pr['dirty'].data_ptr(), st),
+            _lib.check(lib.mne_grad_dirty_map(self.flat_grad.data_ptr(), self.flat_grad.numel(), PEER_CHUNK, self.world_size,
+                                              self.shards.rank, pr['dirty_ptrs'], st),
                        'mne_grad_dirty_map')
             pr['hg'].barrier(channel=0)               # every rank's gradient and dirty map are complete
             _lib.check(lib.mne_adam_step_peers(self.world_size, self.shards.rank, pr['param_ptrs'], pr['grad_ptrs'],
                                                self.flat_grad.numel(), PEER_CHUNK, self.flat_m.data_ptr(), self.flat_v.data_ptr(), n_seg, ends, lr,
                                                eps, wd, self.betas[0], self.betas[1], self.step_dev.data_ptr(), 0,
-                                               ops._ptr(self.touched), pr['mc_param'] or None, pr['mc_grad'] or None, pr['dirty_ptrs'], st),
+                                               ops._ptr(self.touched), pr['mc_param'] or None, pr['mc_grad'] or None, pr['dirty'].data_ptr(), st),
                        'mne_adam_step_peers')
             pr['hp'].barrier(channel=1)               # every rank's slice has landed in every parameter buffer
             return

@@ -29,14 +29,14 @@ for it in range(K):
     ev[0].record()
     mapper.forward_backward(*batch)
     ev[1].record()
-    lib.mne_grad_dirty_map(mapper.flat_grad.data_ptr(), mapper.flat_grad.numel(), pr['dirty'].data_ptr(), st)
+    lib.mne_grad_dirty_map(mapper.flat_grad.data_ptr(), mapper.flat_grad.numel(), 1024, world, rank, pr['dirty_ptrs'], st)
     ev[2].record()
     pr['hg'].barrier(channel=0)
     ev[3].record()
     lib.mne_adam_tick(mapper.step_dev.data_ptr(), st)
     lib.mne_adam_step_peers(world, mapper.shards.rank, pr['param_ptrs'], pr['grad_ptrs'], mapper.flat_grad.numel(), 1024, mapper.flat_m.data_ptr(),
                             mapper.flat_v.data_ptr(), n_seg, ends, lr, eps, wd, 0.9, 0.99, mapper.step_dev.data_ptr(), 0,
-                            ops._ptr(mapper.touched), pr['mc_param'] or None, None, pr['dirty_ptrs'], st)
+                            ops._ptr(mapper.touched), pr['mc_param'] or None, None, pr['dirty'].data_ptr(), st)
     ev[4].record()
     pr['hp'].barrier(channel=1)
     ev[5].record()
@@ -46,5 +46,28 @@ for it in range(K):
 dirty_frac = pr['dirty'].float().mean().item()
 print('rank %d  us: %s  dirty texels this step: %.3f  touched groups: %.3f' % (rank, {k: round(v, 1) for k, v in tot.items()}, dirty_frac,
       mapper.touched.float().mean().item()), flush=True)
+# where does the peer kernel's time go?  Re-run it with some of the peer pointers replaced by local ones (the values
+# are garbage afterwards -- this is the last thing the script does)
+import ctypes as C
+def ptrs(kind, local_only):
+    own = [int(x) for x in pr[kind]]
+    return (C.c_void_p * world)(*([own[rank]] * world if local_only else own))
+def timed(param_local, grad_local):
+    pp, gp, dp = ptrs('param_ptrs', param_local), ptrs('grad_ptrs', grad_local), pr['dirty'].data_ptr()
+    ts = []
+    for it in range(6):
+        mapper.forward_backward(*db.sample(2048))
+        lib.mne_grad_dirty_map(mapper.flat_grad.data_ptr(), mapper.flat_grad.numel(), 1024, world, rank, pr['dirty_ptrs'], st)
+        torch.cuda.synchronize(); dist.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        lib.mne_adam_step_peers(world, rank, pp, gp, mapper.flat_grad.numel(), 1024, mapper.flat_m.data_ptr(),
+                                mapper.flat_v.data_ptr(), n_seg, ends, lr, eps, wd, 0.9, 0.99, mapper.step_dev.data_ptr(), 0,
+                                ops._ptr(mapper.touched), None, None, dp, st)
+        b.record(); torch.cuda.synchronize(); dist.barrier()
+        ts.append(a.elapsed_time(b) * 1e3)
+    return round(sorted(ts)[len(ts) // 2], 1)
+res = {'all_peer': timed(False, False), 'param_local': timed(True, False), 'all_local': timed(True, True)}
+print('rank %d  adam_peers variants us: %s' % (rank, res), flush=True)
 dist.barrier()
 os._exit(0)

@@ -172,3 +172,71 @@ def test_touched_map_adam_is_bit_identical_to_dense():
     assert torch.equal(pd, ps) and torch.equal(md, ms) and torch.equal(vd, vs)
     frac = touched[: (n - 4096) // 4].float().mean().item()
     assert 0.2 < frac < 0.95, frac
+
+
+def test_peer_optimiser_on_one_gpu_matches_dense_adam():
+    """mne_grad_dirty_map + mne_adam_step_peers with two emulated ranks on ONE device (both "peers'" buffers live on
+    the same GPU, the two ranks' kernels run one after the other): block-cyclic ownership, pushed dirty flags, sparse
+    gradient reduction, parameter write-back into both replicas, exact skip of never-touched groups."""
+    import ctypes as C
+    from mneslam_b200 import _lib, ops
+    lib, st = _lib.lib(), ops._stream()
+    torch.manual_seed(1)
+    world, chunk = 2, 64
+    n_used, n_total = 5 * 128 - 32, 5 * 128 + 128           # padding: one and a bit chunk pairs
+    seg_ends = (C.c_int64 * 2)(256, n_used)
+    lr, eps, wd = (C.c_float * 2)(5e-3, 1e-2), (C.c_float * 2)(1e-15, 1e-8), (C.c_float * 2)(0.0, 1e-6)
+    p0 = torch.randn(n_total, device='cuda'); p0[n_used:] = 0
+    params = [p0.clone(), p0.clone()]
+    grads = [torch.zeros(n_total, device='cuda') for _ in range(world)]
+    dirty = [torch.zeros(n_total // 32, dtype=torch.uint8, device='cuda') for _ in range(world)]
+    local = n_total // world
+    m = [torch.zeros(local, device='cuda') for _ in range(world)]
+    v = [torch.zeros(local, device='cuda') for _ in range(world)]
+    touched = [torch.zeros(local // 4, dtype=torch.uint8, device='cuda') for _ in range(world)]
+    pp = (C.c_void_p * world)(*[x.data_ptr() for x in params])
+    gp = (C.c_void_p * world)(*[x.data_ptr() for x in grads])
+    dp = (C.c_void_p * world)(*[x.data_ptr() for x in dirty])
+    ref = torch.nn.Parameter(p0.clone())
+    opts = [torch.optim.Adam([ref], lr=5e-3, betas=(0.9, 0.99), eps=1e-15, foreach=False),
+            torch.optim.Adam([ref], lr=1e-2, betas=(0.9, 0.99), eps=1e-8, weight_decay=1e-6, foreach=False)]
+    ever = torch.zeros(n_used, dtype=torch.bool, device='cuda')
+    for t in range(1, 5):
+        total = torch.zeros(n_total, device='cuda')
+        for r in range(world):
+            mask = torch.rand(n_total // 32, device='cuda') < 0.3            # sparse, texel-granular like a map step
+            g = torch.randn(n_total, device='cuda') * mask.repeat_interleave(32)
+            g[::3] = 0; g[n_used:] = 0
+            grads[r].copy_(g); total += g
+        ever |= (total[:n_used] != 0)
+        # reference: the two parameter groups with their own hyper-parameters; plane groups never touched stay put
+        full = total.clone()
+        for o, (a, b) in zip(opts, ((0, 256), (256, n_used))):
+            gsel = torch.zeros_like(full); gsel[a:b] = full[a:b]
+            before = ref.detach().clone()
+            ref.grad = gsel
+            o.step()
+            with torch.no_grad():
+                keep = torch.ones(n_total, dtype=torch.bool, device='cuda'); keep[a:b] = False
+                ref[keep] = before[keep]
+        for r in range(world):
+            _lib.check(lib.mne_grad_dirty_map(grads[r].data_ptr(), n_total, chunk, world, r, dp, st), 'dirty')
+        for r in range(world):
+            _lib.check(lib.mne_adam_step_peers(world, r, pp, gp, n_total, chunk, m[r].data_ptr(), v[r].data_ptr(), 2, seg_ends,
+                                               lr, eps, wd, 0.9, 0.99, None, t, touched[r].data_ptr(), None, None,
+                                               dirty[r].data_ptr(), st), 'peers')
+        torch.cuda.synchronize()
+        assert all(float(g.abs().max()) == 0.0 for g in grads)               # every gradient was consumed and cleared
+        assert torch.equal(params[0], params[1])                             # both replicas hold the same parameters
+    # the reference above ran Adam on never-touched plane groups too (zero gradient, zero moments: identity), so the
+    # results must agree everywhere to fp32 rounding
+    assert rel(params[0].cpu().numpy(), ref.detach().cpu().numpy()) < 5e-6
+    assert float(params[0][n_used:].abs().max()) == 0.0
+    # touched flags: set exactly where a gradient ever arrived (plane segment), in ownership order
+    gi = torch.arange(n_total // 4, device='cuda')
+    owner, li = (gi // (chunk // 4)) % world, (gi // (chunk // 4)) // world * (chunk // 4) + gi % (chunk // 4)
+    ever4 = torch.zeros(n_total // 4, dtype=torch.bool, device='cuda')
+    ever4[:n_used // 4] = ever.view(-1, 4).any(1)
+    for r in range(world):
+        sel = (owner == r) & (gi < 256 // 4)
+        assert torch.equal(touched[r][li[sel]].bool(), ever4[sel])

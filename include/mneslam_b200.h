@@ -83,6 +83,13 @@ typedef struct MneSceneDesc {
     float* g_sdf1;
     float* g_col0;
     float* g_col1;
+    /* optional (multi-GPU optimiser, no counterpart in the reference): when dirty is non-NULL, mne_render_backward
+     * also sets dirty[(g - dirty_base) / 32] = 1 for every 32-float texel of the plane / hash-table gradient it adds
+     * into (g = the address it adds at; all plane / table gradients must then live in the one buffer dirty_base points
+     * into).  Decoder-weight gradients are NOT flagged (they are dense; mne_dirty_push flags them wholesale).
+     * Supported by the vectorised-plane and hash paths of impl 2; any other path rejects a non-NULL dirty. */
+    uint8_t* dirty;
+    const float* dirty_base;
 } MneSceneDesc;
 
 /* Constants of the sampling stage (reference model/scene_rep.py:361-381).  The linspace tables are built
@@ -177,7 +184,7 @@ int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int
  * for callers that must not allocate device memory (a host that forbids cudaMalloc around the call, a real-time
  * loop that cannot take the allocator's lock, a plugin that is only handed input and output buffers).  It is
  * mne_render_backward with the 16-byte-per-sample workspace taken from an array built into the library image
- * (MNE_STATIC_SCRATCH_SAMPLES * 16 bytes = 2 MiB, held on every GPU that loads the library until the process
+ * (MNE_STATIC_SCRATCH_SAMPLES * 20 bytes = 2.5 MiB, held on every GPU that loads the library until the process
  * exits) instead of the `scratch` argument; inputs and outputs are still the caller's.  It calls no cudaMalloc /
  * cudaFree or other allocating routine.
  *   - n_rays * n_samples must not exceed MNE_STATIC_SCRATCH_SAMPLES; larger batches are rejected with an error.
@@ -260,6 +267,11 @@ int mne_adam_step_peers(int32_t world_size, int32_t rank, float* const* param_pt
  * at [rank][owner-local texel index] -- the layout mne_adam_step_peers reads.  world_size = 1: a plain local map. */
 int mne_grad_dirty_map(const float* grad, int64_t n_total, int32_t chunk, int32_t world_size, int32_t rank,
                        uint8_t* const* dirty_ptrs, mne_stream_t stream);
+/* Same hand-over without reading the gradient buffer: local_map (n_total / 32 bytes) holds the flags the backward pass
+ * set through MneSceneDesc.dirty; they are pushed to the owners in the same layout and local_map is cleared.  Texels
+ * at or beyond element dense_from (the decoder weights at the tail of the flat buffer) are always flagged. */
+int mne_dirty_push(uint8_t* local_map, int64_t n_total, int64_t dense_from, int32_t chunk, int32_t world_size, int32_t rank,
+                   uint8_t* const* dirty_ptrs, mne_stream_t stream);
 
 #ifdef __cplusplus
 }

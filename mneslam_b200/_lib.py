@@ -38,7 +38,8 @@ class SceneDesc(C.Structure):
                 ('bound_lo', C.c_float * 3), ('bound_ext', C.c_float * 3),
                 ('bbox_lo', C.c_double * 3), ('bbox_ext', C.c_double * 3),
                 ('w_sdf0', C.c_void_p), ('w_sdf1', C.c_void_p), ('w_col0', C.c_void_p), ('w_col1', C.c_void_p),
-                ('g_sdf0', C.c_void_p), ('g_sdf1', C.c_void_p), ('g_col0', C.c_void_p), ('g_col1', C.c_void_p)]
+                ('g_sdf0', C.c_void_p), ('g_sdf1', C.c_void_p), ('g_col0', C.c_void_p), ('g_col1', C.c_void_p),
+                ('dirty', C.c_void_p), ('dirty_base', C.c_void_p)]
 
 
 class SampleCfg(C.Structure):
@@ -79,6 +80,7 @@ _SIGNATURES = {
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_int64,
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'mne_grad_dirty_map': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
+    'mne_dirty_push': (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     'mne_query_points': (C.c_int, [C.POINTER(SceneDesc), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                    C.c_void_p]),
 }

@@ -243,6 +243,20 @@ __global__ void __launch_bounds__(256) grad_dirty_kernel(const float4* __restric
     }
 }
 
+// the same hand-over when the backward pass already flagged the texels it touched (MneSceneDesc.dirty): no pass over the
+// 129 MB gradient buffer, only over the 1 MB flag map, which is cleared for the next iteration on the way
+__global__ void __launch_bounds__(256) dirty_push_kernel(uint8_t* __restrict__ local_map, int64_t dense_from32,
+                                                         const __grid_constant__ DirtyPush d) {
+    const int64_t tx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (tx >= d.n32) return;
+    uint8_t f = 1;
+    if (tx < dense_from32) { f = local_map[tx]; if (f) local_map[tx] = 0; }
+    const uint32_t c = (uint32_t)(tx >> d.chunk_tx_log2);
+    const uint32_t owner = c % (uint32_t)d.world;
+    const int64_t lt = ((int64_t)(c / (uint32_t)d.world) << d.chunk_tx_log2) + (tx & ((1 << d.chunk_tx_log2) - 1));
+    d.dst[owner][(int64_t)d.rank * d.local32 + lt] = f;
+}
+
 // in-switch reduction / broadcast (NVLS): one load returns the sum over all ranks, one store reaches all ranks
 __device__ __forceinline__ float4 multimem_ld_reduce_add(const float4* p) {
     float4 v;
@@ -458,6 +472,28 @@ extern "C" int mne_grad_dirty_map(const float* grad, int64_t n_total, int32_t ch
     const int64_t cap = (int64_t)sm_count() * 8;
     if (blocks > cap) blocks = cap;
     grad_dirty_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float4*>(grad), d);
+    MNE_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int mne_dirty_push(uint8_t* local_map, int64_t n_total, int64_t dense_from, int32_t chunk, int32_t world_size,
+                              int32_t rank, uint8_t* const* dirty_ptrs, mne_stream_t stream) {
+    using namespace mne;
+    MNE_CHECK_ARG(local_map && dirty_ptrs, "mne_dirty_push: null argument");
+    MNE_CHECK_ARG(world_size >= 1 && world_size <= MNE_MAX_PEERS && rank >= 0 && rank < world_size, "mne_dirty_push: bad world_size / rank");
+    MNE_CHECK_ARG(chunk >= 32 && (chunk & (chunk - 1)) == 0 && n_total >= 0 && n_total % ((int64_t)chunk * world_size) == 0 &&
+                  (n_total >> 5) / chunk < (int64_t)1 << 31 && dense_from >= 0,
+                  "mne_dirty_push: chunk must be a power of two >= 32 and n_total a multiple of chunk * world_size");
+    if (n_total == 0) return 0;
+    DirtyPush d{};
+    for (int r = 0; r < world_size; ++r) {
+        MNE_CHECK_ARG(dirty_ptrs[r], "mne_dirty_push: null flag array");
+        d.dst[r] = dirty_ptrs[r];
+    }
+    d.world = world_size; d.rank = rank; d.chunk_tx_log2 = 31 - __builtin_clz((unsigned)chunk) - 5;
+    d.n32 = n_total >> 5; d.local32 = d.n32 / world_size;
+    const int64_t blocks = (d.n32 + 255) / 256;
+    dirty_push_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(local_map, dense_from >> 5, d);   // floor: a texel straddling dense_from is flagged
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

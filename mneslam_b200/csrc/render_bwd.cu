@@ -469,7 +469,9 @@ static int dispatch_bwd(const BwdParams& P, bool ray_grad, bool param_grad, cuda
 
 extern "C" size_t mne_backward_scratch_bytes(int32_t n_rays, int32_t n_samples) {
     if (n_rays <= 0 || n_samples <= 0) return 0;
-    return (size_t)n_rays * (size_t)n_samples * sizeof(float4);
+    // d loss / d raw per sample, the list of samples where it is non-zero, and the length of that list
+    const size_t n = (size_t)n_rays * (size_t)n_samples;
+    return n * sizeof(float4) + ((n + 3) & ~(size_t)3) * sizeof(int) + 16;
 }
 
 extern "C" int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples,
@@ -498,9 +500,11 @@ extern "C" int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg
         MNE_CHECK_CUDA(cudaMemsetAsync(g_rays_o, 0, sizeof(float) * 3 * (size_t)n_rays, st));
         MNE_CHECK_CUDA(cudaMemsetAsync(g_rays_d, 0, sizeof(float) * 3 * (size_t)n_rays, st));
     }
+    MNE_CHECK_ARG(!scene->dirty || scene->dirty_base, "mne_render_backward: dirty without dirty_base");
     if (impl_version() == 2 && !(scene->two_grid && ray_grad && param_grad))
         return render_backward_v2(scene, rcfg, n_rays, n_samples, rays_o, rays_d, z_vals, raw, target_rgb, target_d, acc,
                                   loss_grads, g_rgb, g_depth, g_raw, scratch, g_rays_o, g_rays_d, param_grad, st);
+    MNE_CHECK_ARG(!scene->dirty, "mne_render_backward: MneSceneDesc.dirty is supported by impl 2 without combined two-grid ray + parameter gradients only");
     BwdParams P{};
     P.sc = *scene; P.rc = *rcfg; P.n_rays = n_rays; P.n_samples = n_samples;
     P.rays_per_group = choose_rays_per_group(n_rays, n_samples, sm_count() * (scene->two_grid ? bwd_warps<true>() : bwd_warps<false>()));
@@ -517,7 +521,7 @@ extern "C" int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg
 // one: code that runs where cudaMalloc is off limits (inside a region the host application has fenced off
 // from the allocator, in a real-time loop that must not take the driver's allocation lock, or in a plugin
 // whose host only hands it input and output buffers).  For them the workspace below lives in the library
-// image itself: every GPU that loads the library reserves MNE_STATIC_SCRATCH_SAMPLES * 16 bytes (2 MiB)
+// image itself: every GPU that loads the library reserves MNE_STATIC_SCRATCH_SAMPLES * 20 bytes (2.5 MiB)
 // until the process exits, and nothing is allocated at call time.
 //
 // In host code the name `g_static_draw` is only a handle for the symbol, not a device address, so the device
@@ -526,7 +530,7 @@ extern "C" int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg
 namespace mne {
 
 constexpr int kStaticScratchSamples = MNE_STATIC_SCRATCH_SAMPLES;
-static __device__ __align__(256) float4 g_static_draw[kStaticScratchSamples];
+static __device__ __align__(256) float4 g_static_draw[kStaticScratchSamples + kStaticScratchSamples / 4 + 1];   // = mne_backward_scratch_bytes
 
 static int static_scratch_for_current_device(float4** out) {
     constexpr int kMaxDevices = 64;
@@ -562,9 +566,9 @@ extern "C" int mne_render_backward_static(const MneSceneDesc* scene, const MneRe
                   (long long)n_rays * n_samples, kStaticScratchSamples);
     float4* scratch = nullptr;
     if (int e = static_scratch_for_current_device(&scratch)) return e;
-    // Every sample slot of the workspace that the kernel reads is written earlier in the same launch (the
-    // compositing-backward phase fills d_raw for all n_rays * n_samples entries), so leftovers of a previous call
-    // are never read and nothing has to be cleared here.
+    // Every sample slot of the workspace that the kernels read is written earlier in the same call (the compositing-
+    // backward kernel fills d_raw for all n_rays * n_samples entries and the list of non-zero ones; the list length is
+    // reset by a memset node on the stream), so leftovers of a previous call are never read.
     return mne_render_backward(scene, rcfg, n_rays, n_samples, rays_o, rays_d, z_vals, raw, target_rgb, target_d, acc,
                                loss_grads, g_rgb, g_depth, g_raw, scratch, g_rays_o, g_rays_d, stream);
 }

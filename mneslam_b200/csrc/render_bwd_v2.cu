@@ -84,6 +84,8 @@ struct PtsBwdParams {
     const float4* draw;      // [n_pts] d loss / d raw
     float* g_rays_o;         // [N,3] accumulated into (zeroed by the entry point), or NULL
     float* g_rays_d;
+    const int* list;         // samples with a non-zero draw (compacted by rays_bwd_kernel)
+    const int* n_active;     // how many
 };
 
 __device__ __forceinline__ void mma_1x(float (&d)[4], float a0, float a1, float a2, float a3, float b0, float b1) {
@@ -140,7 +142,10 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
     load_weights_t<TWO, RAY>(P.sc, WT, threadIdx.x, blockDim.x);
     __syncthreads();
 
-    const int64_t n_tiles = (P.n_pts + kTilePts - 1) / kTilePts;
+    // only samples with a non-zero d loss / d raw are processed (list written by rays_bwd_kernel): everything behind
+    // the truncation band of a ray -- about a third of a mapping batch -- would only add exact zeros
+    const int64_t n_pts = *P.n_active;
+    const int64_t n_tiles = (n_pts + kTilePts - 1) / kTilePts;
     const int64_t tiles_per_round = (int64_t)gridDim.x * NW;
     const int64_t n_rounds = (n_tiles + tiles_per_round - 1) / tiles_per_round;
     const int p_loc = lane & 15, half = lane >> 4;
@@ -171,13 +176,14 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
         const int64_t tile = round * tiles_per_round + (int64_t)warp * gridDim.x + blockIdx.x;
         const bool have = tile < n_tiles;
         const int64_t pt0 = tile * kTilePts;
-        const int np = have ? (int)min((int64_t)kTilePts, P.n_pts - pt0) : 0;
+        const int np = have ? (int)min((int64_t)kTilePts, n_pts - pt0) : 0;
 
         // ---- 1. position, taps, gather, OneBlob
         float px = 0.f, py = 0.f, pz = 0.f;
+        int q = 0;                                               // sample index of this lane's row
         if (p_loc < np) {
-            const int64_t q = pt0 + p_loc;
-            const int64_t ray = q / P.n_samples;
+            q = P.list[pt0 + p_loc];
+            const int ray = q / P.n_samples;
             const float z = P.z_vals[q];
             px = __fadd_rn(P.rays_o[ray * 3 + 0], __fmul_rn(P.rays_d[ray * 3 + 0], z));
             py = __fadd_rn(P.rays_o[ray * 3 + 1], __fmul_rn(P.rays_d[ray * 3 + 1], z));
@@ -229,8 +235,9 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
             decoder_forward_mma<TWO>(W4, X, CFt, lane, h1, o16, hc, rgb_unused);
         }
         float4 dr_lo = make_float4(0.f, 0.f, 0.f, 0.f), dr_hi = dr_lo;
-        if (g < np) dr_lo = __ldg(P.draw + pt0 + g);
-        if (g + 8 < np) dr_hi = __ldg(P.draw + pt0 + g + 8);
+        const int q_lo = __shfl_sync(0xffffffffu, q, g), q_hi = __shfl_sync(0xffffffffu, q, g + 8);
+        if (g < np) dr_lo = __ldg(P.draw + q_lo);
+        if (g + 8 < np) dr_hi = __ldg(P.draw + q_hi);
 
         // ---- 3. colour branch backward
         // A fragment of d_rgb: columns (2t, 2t+1) of (r, g, b, 0, ...)
@@ -401,7 +408,7 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
         if (MODE == 2) {
             if (half == 0) { row[kBlobCol] = bx0; row[kBlobCol + 1] = by0; row[kBlobCol + 2] = bz0; }
             __syncwarp();
-            if (PARAM && P.sc.hash[0].grad) scatter16_hash(P.sc.hash[0], X + kBlobCol, kXStride, X, kXStride, np, lane);
+            if (PARAM && P.sc.hash[0].grad) scatter16_hash(P.sc.hash[0], X + kBlobCol, kXStride, X, kXStride, np, lane, P.sc.dirty, P.sc.dirty_base);
         } else if (half == 1) {
             write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 0);
         }
@@ -432,8 +439,10 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
                             const float4 gv = *reinterpret_cast<const float4*>(gsrc + p * gstride + l * 32 + q * 4);
                             const unsigned off = __float_as_uint(seg[8 * tp + c]);
                             const float w = seg[8 * tp + 4 + c];
-                            if (gp && w != 0.f)
+                            if (gp && w != 0.f) {
                                 atomicAdd(reinterpret_cast<float4*>(gp + off) + q, make_float4(gv.x * w, gv.y * w, gv.z * w, gv.w * w));
+                                if (q == 0 && P.sc.dirty) mark_dirty(P.sc.dirty, ((gp + off) - P.sc.dirty_base) >> 5);
+                            }
                             const unsigned fl = (pflags >> (2 * (grp * 6 + tp))) & 3u;
                             if (RAY && fl) {
                                 // D_c = <d feat, texel c>, reduced over this corner's 8 lanes, then shared with everyone
@@ -487,9 +496,8 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
             }
         }
         if (RAY && half == 0 && p_loc < np) {
-            const int64_t q2 = pt0 + p_loc;
-            const int64_t ray = q2 / P.n_samples;
-            const float z = P.z_vals[q2];
+            const int ray = q / P.n_samples;
+            const float z = P.z_vals[q];
 #pragma unroll
             for (int a = 0; a < 3; ++a) {
                 const float gpnt = dn_keep[a] * (2.0f / P.sc.bound_ext[a]) + dpt[a];
@@ -565,6 +573,8 @@ struct RayBwdParams {
     const float* g_depth;
     const float* g_raw;
     float4* draw;
+    int* list;                 // indices of the samples with a non-zero draw, [*n_active]
+    int* n_active;             // zeroed before the launch
 };
 
 __global__ void __launch_bounds__(256) rays_bwd_kernel(const RayBwdParams P) {
@@ -601,7 +611,10 @@ __global__ void __launch_bounds__(256) rays_bwd_kernel(const RayBwdParams P) {
         }
         if (P.g_rgb) { G[0] += P.g_rgb[ray * 3 + 0]; G[1] += P.g_rgb[ray * 3 + 1]; G[2] += P.g_rgb[ray * 3 + 2]; }
         if (P.g_depth) Gd += P.g_depth[ray];
-        for (int s = lane; s < S; s += 32) {
+        for (int s0 = 0; s0 < S; s0 += 32) {
+            const int s = s0 + lane;
+            bool active = false;
+            if (s < S) {
             const float z = __ldg(P.z_vals + rb + s);
             const float4 v = __ldg(reinterpret_cast<const float4*>(P.raw) + rb + s);
             float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -630,6 +643,15 @@ __global__ void __launch_bounds__(256) rays_bwd_kernel(const RayBwdParams P) {
                 o.x += e.x; o.y += e.y; o.z += e.z; o.w += e.w;
             }
             P.draw[rb + s] = o;
+            active = o.x != 0.0f || o.y != 0.0f || o.z != 0.0f || o.w != 0.0f;
+            }
+            const unsigned b = __ballot_sync(0xffffffffu, active);
+            if (b) {
+                int base = 0;
+                if (lane == 0) base = atomicAdd(P.n_active, __popc(b));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (active) P.list[base + __popc(b & ((1u << lane) - 1u))] = (int)(rb + s);
+            }
         }
     }
 }
@@ -677,19 +699,26 @@ int render_backward_v2(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int3
     R.rc = *rcfg; R.n_rays = n_rays; R.n_samples = n_samples; R.z_vals = z_vals; R.raw = raw; R.target_rgb = target_rgb;
     R.target_d = target_d; R.acc = acc; R.loss_grads = loss_grads; R.g_rgb = g_rgb; R.g_depth = g_depth; R.g_raw = g_raw;
     R.draw = reinterpret_cast<float4*>(scratch);
+    const int64_t n_pts = (int64_t)n_rays * n_samples;
+    MNE_CHECK_ARG(n_pts < ((int64_t)1 << 31), "mne_render_backward: more than 2^31 samples in one call");
+    R.list = reinterpret_cast<int*>(R.draw + n_pts);
+    R.n_active = R.list + ((n_pts + 3) & ~(int64_t)3);
+    MNE_CHECK_CUDA(cudaMemsetAsync(R.n_active, 0, sizeof(int), st));
     const int blocks = max(1, min((n_rays + 7) / 8, sm_count() * 4));
     rays_bwd_kernel<<<blocks, 256, 0, st>>>(R);
     MNE_CHECK_CUDA(cudaGetLastError());
     PtsBwdParams P{};
     P.sc = *scene; P.n_pts = (int64_t)n_rays * n_samples; P.n_samples = n_samples;
     P.rays_o = rays_o; P.rays_d = rays_d; P.z_vals = z_vals; P.draw = reinterpret_cast<const float4*>(scratch);
-    P.g_rays_o = g_rays_o; P.g_rays_d = g_rays_d;
+    P.g_rays_o = g_rays_o; P.g_rays_d = g_rays_d; P.list = R.list; P.n_active = R.n_active;
     const bool ray = g_rays_o != nullptr;
     if (scene->encoder == 1) {
         MNE_CHECK_ARG(!ray, "mne_render_backward: ray gradients through the hash grid are not built yet");
         return launch_points_bwd<false, 2, false, true>(P, st);
     }
-    return planes_vectorizable(*scene) ? dispatch_points_bwd<1>(P, ray, param_grad, st) : dispatch_points_bwd<0>(P, ray, param_grad, st);
+    if (planes_vectorizable(*scene)) return dispatch_points_bwd<1>(P, ray, param_grad, st);
+    MNE_CHECK_ARG(!scene->dirty, "mne_render_backward: MneSceneDesc.dirty needs channels-last planes or the hash grid");
+    return dispatch_points_bwd<0>(P, ray, param_grad, st);
 }
 
 }  // namespace mne

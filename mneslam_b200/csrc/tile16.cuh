@@ -281,9 +281,16 @@ __device__ __forceinline__ void gather16_hash(const MneHashDesc& h, const float*
     for (int p = 0; p < kTilePts; ++p) dst[p * dst_stride + 32 + lane] = 0.0f;      // padding columns 32..63
 }
 
+// flag store of the multi-GPU dirty map.  Through inline PTX on purpose: a plain store through a uint8_t pointer may alias
+// anything, which made the compiler reload the tile from shared memory after every flag (+120 us on the backward pass).
+__device__ __forceinline__ void mark_dirty(uint8_t* map, int64_t texel) {
+    asm volatile("st.global.u8 [%0], %1;" :: "l"(map + texel), "r"(1));
+}
+
 // gradient of the table: grad[corner] += w * d feat (one 64-bit vector reduction per corner)
 __device__ __forceinline__ void scatter16_hash(const MneHashDesc& h, const float* __restrict__ xn, int xn_stride,
-                                               const float* __restrict__ src, int src_stride, int np, int lane) {
+                                               const float* __restrict__ src, int src_stride, int np, int lane,
+                                               uint8_t* dirty = nullptr, const float* dirty_base = nullptr) {
     const int l = lane & 15, pp = lane >> 4;
     const HashLevel L = hash_level(h, l);
     float2* grad = reinterpret_cast<float2*>(h.grad) + L.offset;
@@ -297,6 +304,7 @@ __device__ __forceinline__ void scatter16_hash(const MneHashDesc& h, const float
                 const uint32_t idx = hash_index(L, c.g[0] + (k & 1), c.g[1] + ((k >> 1) & 1), c.g[2] + ((k >> 2) & 1));
                 const float w = corner_weight(c, k);
                 atomicAdd(grad + idx, make_float2(w * g2.x, w * g2.y));
+                if (dirty) mark_dirty(dirty, (reinterpret_cast<const float*>(grad + idx) - dirty_base) >> 5);
             }
         }
     }

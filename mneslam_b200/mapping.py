@@ -142,6 +142,13 @@ class FusedMapper:
             self.grad_shard = torch.zeros(self.shards.shard_len, dtype=torch.float32, device=self.dev)
             self._local_segments = self._pack_segments(self.shards.local_ends, self.shards.local_hparams)
         n_planes = len(planes)
+        # several GPUs: the backward pass flags the 128-byte texels of the plane / table gradient it adds into, so that
+        # the owners fetch only those over NVLink (needs the vector or hash kernels: channels-last planes)
+        self.dirty_local = None
+        self.dense_from = sum(p.numel() for p in planes)
+        if self.peers is not None and (model.hash_meta is not None or
+                                       all(p.stride(1) == 1 and p.shape[1] == 32 for p in planes)):
+            self.dirty_local = torch.zeros(padded // 32, dtype=torch.uint8, device=self.dev)
         self.plane_grads = self.grads[:n_planes]
         self.weight_grads = self.grads[n_planes:]
         self.step_dev = torch.zeros(1, dtype=torch.int64, device=self.dev)
@@ -171,7 +178,9 @@ class FusedMapper:
         return ops.make_scene(m._flat_planes(), m.decoder.weight_list(), m.bound, m.bounding_box,
                               self.cfg['pos']['n_bins'],
                               plane_grads=self.plane_grads if with_grads else None,
-                              weight_grads=self.weight_grads if with_grads else None, hash_meta=m.hash_meta)
+                              weight_grads=self.weight_grads if with_grads else None, hash_meta=m.hash_meta,
+                              dirty=self.dirty_local if with_grads else None,
+                              dirty_base=self.flat_grad if (with_grads and self.dirty_local is not None) else None)
 
     def forward_backward(self, rays_o, rays_d, target_rgb, target_d, noise=None):
         """sample -> forward -> finalize -> backward; gradients are ADDED to the flat buffer.  Returns losses[8]."""
@@ -193,8 +202,8 @@ class FusedMapper:
         if self.world_size > 1:
             torch.distributed.all_reduce(acc, group=self.group)
         losses = ops.loss_finalize(rcfg, s, acc)
-        if self._scratch is None or self._scratch.numel() * 4 < n * s * 16:
-            self._scratch = ops.backward_scratch(n, s, dev)
+        if self._scratch is None or self._scratch_for != (n, s):
+            self._scratch, self._scratch_for = ops.backward_scratch(n, s, dev), (n, s)
         ops.render_backward(self._scene(True), rcfg, rays_o, rays_d, z_vals, out['raw'], target_rgb, td, acc,
                             loss_grads=self.loss_grads, scratch=self._scratch)
         self.last_render = out
@@ -210,9 +219,12 @@ class FusedMapper:
         if self.world_size > 1 and self.peers is not None:
             n_seg, ends, lr, eps, wd = self._segments          # global segment ends; ownership is block-cyclic
             pr = self.peers
-            _lib.check(lib.mne_grad_dirty_map(self.flat_grad.data_ptr(), self.flat_grad.numel(), PEER_CHUNK, self.world_size,
-                                              self.shards.rank, pr['dirty_ptrs'], st),
-                       'mne_grad_dirty_map')
+            if self.dirty_local is not None:          # flags set by the backward kernels: hand them to the owners
+                _lib.check(lib.mne_dirty_push(self.dirty_local.data_ptr(), self.flat_grad.numel(), self.dense_from, PEER_CHUNK,
+                                              self.world_size, self.shards.rank, pr['dirty_ptrs'], st), 'mne_dirty_push')
+            else:                                     # strided planes: derive the flags from the gradient buffer
+                _lib.check(lib.mne_grad_dirty_map(self.flat_grad.data_ptr(), self.flat_grad.numel(), PEER_CHUNK, self.world_size,
+                                                  self.shards.rank, pr['dirty_ptrs'], st), 'mne_grad_dirty_map')
             pr['hg'].barrier(channel=0)               # every rank's gradient and dirty map are complete
             _lib.check(lib.mne_adam_step_peers(self.world_size, self.shards.rank, pr['param_ptrs'], pr['grad_ptrs'],
                                                self.flat_grad.numel(), PEER_CHUNK, self.flat_m.data_ptr(), self.flat_v.data_ptr(), n_seg, ends, lr,

@@ -107,10 +107,12 @@ def bounds_to_host(bound, bounding_box):
     return hit[:4]
 
 
-def make_scene(planes, weights, bound, bounding_box, n_bins=16, plane_grads=None, weight_grads=None, hash_meta=None):
+def make_scene(planes, weights, bound, bounding_box, n_bins=16, plane_grads=None, weight_grads=None, hash_meta=None,
+               dirty=None, dirty_base=None):
     """planes: flat list of 6 or 12 ``[1,32,H,W]`` tensors in ``all_planes`` order (group, axis, level) -- or, with
     ``hash_meta`` (a ``hashgrid.HashGridMeta``), the one-element list ``[table]`` of the hash grid encoder.
-    weights: [sdf0, sdf1, col0, col1].  bound: float32 [3,2] (CPU ok).  bounding_box: float64 [3,2]."""
+    weights: [sdf0, sdf1, col0, col1].  bound: float32 [3,2] (CPU ok).  bounding_box: float64 [3,2].
+    dirty / dirty_base: uint8 flag map and the flat gradient buffer it indexes (``MneSceneDesc.dirty``)."""
     sc = SceneDesc()
     sc.n_bins = n_bins
     keep = []
@@ -160,6 +162,11 @@ def make_scene(planes, weights, bound, bounding_box, n_bins=16, plane_grads=None
             if g is not None and (g.shape != w.shape or not g.is_contiguous()):
                 raise TypeError('decoder gradient buffers must be contiguous and match the weights')
         sc.g_sdf0, sc.g_sdf1, sc.g_col0, sc.g_col1 = [_ptr(g) for g in weight_grads]
+    if dirty is not None:
+        if dirty.dtype != torch.uint8 or dirty_base is None or dirty.numel() * 32 < dirty_base.numel():
+            raise TypeError('dirty must be a uint8 map with one byte per 32 floats of dirty_base')
+        sc.dirty, sc.dirty_base = dirty.data_ptr(), dirty_base.data_ptr()
+        keep.extend([dirty, dirty_base])
     sc._keep = keep
     return sc
 

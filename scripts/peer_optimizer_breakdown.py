@@ -20,6 +20,11 @@ for _ in range(30):
 torch.cuda.synchronize(); dist.barrier()
 lib, st, pr = _lib.lib(), ops._stream(), mapper.peers
 n_seg, ends, lr, eps, wd = mapper._segments
+def hand_over():
+    if mapper.dirty_local is not None:
+        lib.mne_dirty_push(mapper.dirty_local.data_ptr(), mapper.flat_grad.numel(), mapper.dense_from, 1024, world, rank, pr['dirty_ptrs'], st)
+    else:
+        lib.mne_grad_dirty_map(mapper.flat_grad.data_ptr(), mapper.flat_grad.numel(), 1024, world, rank, pr['dirty_ptrs'], st)
 names = ['fwd_bwd', 'dirty', 'barrier0', 'adam_peers', 'barrier1']
 tot = {k: 0.0 for k in names}
 K = 20
@@ -29,7 +34,7 @@ for it in range(K):
     ev[0].record()
     mapper.forward_backward(*batch)
     ev[1].record()
-    lib.mne_grad_dirty_map(mapper.flat_grad.data_ptr(), mapper.flat_grad.numel(), 1024, world, rank, pr['dirty_ptrs'], st)
+    hand_over()
     ev[2].record()
     pr['hg'].barrier(channel=0)
     ev[3].record()
@@ -57,7 +62,7 @@ def timed(param_local, grad_local):
     ts = []
     for it in range(6):
         mapper.forward_backward(*db.sample(2048))
-        lib.mne_grad_dirty_map(mapper.flat_grad.data_ptr(), mapper.flat_grad.numel(), 1024, world, rank, pr['dirty_ptrs'], st)
+        hand_over()
         torch.cuda.synchronize(); dist.barrier()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()

@@ -240,3 +240,52 @@ def test_peer_optimiser_on_one_gpu_matches_dense_adam():
     for r in range(world):
         sel = (owner == r) & (gi < 256 // 4)
         assert torch.equal(touched[r][li[sel]].bool(), ever4[sel])
+
+
+@pytest.mark.parametrize('use_hash', [False, True])
+def test_backward_flags_exactly_the_texels_it_adds_into(use_hash):
+    """MneSceneDesc.dirty: after a backward pass every 32-float texel of the plane / table gradient that holds a
+    non-zero value is flagged, (almost) nothing else is, and mne_dirty_push hands the flags over in the owner layout
+    mne_grad_dirty_map derives from the gradient buffer itself."""
+    import ctypes as C
+    from mneslam_b200 import JointEncoding, _lib, ops
+    from mneslam_b200.mapping import FusedMapper
+    cfg = configs.small_test_config()
+    if use_hash:
+        cfg['grid']['use_hash'] = True
+        cfg['grid']['oneGrid'] = True
+    torch.manual_seed(0)
+    model = JointEncoding(cfg, torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)).cuda()
+    mapper = FusedMapper(model)
+    n = mapper.flat_grad.numel()
+    mapper.dirty_local = torch.zeros((n + 31) // 32, dtype=torch.uint8, device='cuda')
+    b = synthetic.make_ray_batch(cfg, 256, seed=4)
+    mapper.forward_backward(b['rays_o'].cuda(), b['rays_d'].cuda(), b['target_rgb'].cuda(), b['target_d'].cuda())
+    torch.cuda.synchronize()
+    g = mapper.flat_grad
+    n_tab = mapper.dense_from
+    full = n_tab // 32
+    nz = (g[:full * 32].view(-1, 32) != 0).any(1)
+    fl = mapper.dirty_local[:full].bool()
+    assert int(nz.sum()) > 0
+    assert bool((fl | ~nz).all())                                   # non-zero => flagged
+    # flagged => (almost always) non-zero; the hash scatter also flags corners it adds an exact zero to (points whose
+    # sdf gradient vanished), which costs a little NVLink traffic and nothing else
+    slack = 1.2 if use_hash else 1.02
+    assert int(fl.sum()) <= int(nz.sum()) * slack + 2
+    assert int(mapper.dirty_local[(n_tab + 31) // 32:].sum()) == 0  # the decoder weights are not flagged by the kernels
+    if n % 128 == 0:
+        # push (flags from the kernels) and scan (flags from the buffer) produce the same owner-side arrays where the
+        # gradient is non-zero; two emulated ranks on one device
+        world, chunk = 2, 64
+        lib, st = _lib.lib(), ops._stream()
+        a = [torch.zeros(n // 32, dtype=torch.uint8, device='cuda') for _ in range(world)]
+        b = [torch.zeros(n // 32, dtype=torch.uint8, device='cuda') for _ in range(world)]
+        pa, pb = (C.c_void_p * world)(*[x.data_ptr() for x in a]), (C.c_void_p * world)(*[x.data_ptr() for x in b])
+        _lib.check(lib.mne_grad_dirty_map(g.data_ptr(), n, chunk, world, 1, pa, st), 'scan')
+        _lib.check(lib.mne_dirty_push(mapper.dirty_local.data_ptr(), n, n_tab, chunk, world, 1, pb, st), 'push')
+        torch.cuda.synchronize()
+        for x, y in zip(a, b):
+            assert bool((y.bool() | ~x.bool()).all())
+            assert int(y.sum()) <= int(x.sum()) * slack + 2 + (n - n_tab + 31) // 32
+        assert int(mapper.dirty_local.sum()) == 0                   # cleared for the next iteration

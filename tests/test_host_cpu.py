@@ -31,7 +31,7 @@ def test_library_exports_every_declared_symbol():
 def test_struct_layout_matches_header():
     assert ctypes.sizeof(_lib.PlaneDesc) == 48
     assert ctypes.sizeof(_lib.HashDesc) == 424
-    assert ctypes.sizeof(_lib.SceneDesc) == 1576
+    assert ctypes.sizeof(_lib.SceneDesc) == 1592
     assert _lib.SceneDesc.bound_lo.offset == 1440 and _lib.SceneDesc.bbox_lo.offset == 1464
     assert _lib.SceneDesc.w_sdf0.offset == 1512
     assert ctypes.sizeof(_lib.RenderCfg) == 40 and _lib.RenderCfg.norm_rays.offset == 32
@@ -48,7 +48,7 @@ def test_argument_errors_are_reported_without_a_gpu():
     scene.n_bins, scene.c_dim = 8, 32
     assert handle.mne_query_points(ctypes.byref(scene), 4, None, None, None, None, None) != 0
     assert b'n_bins' in handle.mne_last_error()
-    assert handle.mne_backward_scratch_bytes(2048, 43) == 2048 * 43 * 16
+    assert handle.mne_backward_scratch_bytes(2048, 43) == 2048 * 43 * 20 + 16   # d_raw, active-sample list, its length
 
 
 def test_render_cfg_uses_float32_roundings():

@@ -39,11 +39,16 @@ PEER_CHUNK = 1024      # floats per ownership chunk (4 KB) of the peer-memory op
 
 class FusedMapper:
     def __init__(self, model, is_co_sdf=None, process_group=None, world_size=1, adopt_parameters=True, skip_untouched=True,
-                 peer_memory=True, use_multicast=True):
+                 peer_memory=True, use_multicast=True, mark_dirty=True):
         """``adopt_parameters``: move the planes and decoder weights into ONE flat buffer (each tensor keeps its
         Python identity, shape and strides; only its storage changes), with gradients and Adam moments laid out
-        the same way, so that the optimiser is a single streaming launch and the multi-GPU gradient exchange a
-        single all-reduce."""
+        the same way, so that the optimiser is a single streaming launch.  ``skip_untouched``: exact skip of parameter
+        groups that never received a gradient.  Several GPUs (``world_size`` > 1, rays sharded over ranks):
+        ``peer_memory`` puts the flat buffers into NVLink peer-mapped memory and runs the optimiser as ONE kernel that
+        reduces the gradient over the peers and writes the parameters back (else NCCL reduce-scatter / all-gather);
+        ``use_multicast`` lets that kernel store through the NVLink switch from 4 ranks up; ``mark_dirty`` has the
+        backward kernels flag the texels they add into, so that owners fetch only those from their peers (else the
+        flags are derived by a pass over the gradient buffer)."""
         ops.require_cuda()
         self.model, self.cfg = model, model.config
         self.world_size, self.group = world_size, process_group
@@ -146,7 +151,7 @@ class FusedMapper:
         # the owners fetch only those over NVLink (needs the vector or hash kernels: channels-last planes)
         self.dirty_local = None
         self.dense_from = sum(p.numel() for p in planes)
-        if self.peers is not None and (model.hash_meta is not None or
+        if self.peers is not None and mark_dirty and (model.hash_meta is not None or
                                        all(p.stride(1) == 1 and p.shape[1] == 32 for p in planes)):
             self.dirty_local = torch.zeros(padded // 32, dtype=torch.uint8, device=self.dev)
         self.plane_grads = self.grads[:n_planes]

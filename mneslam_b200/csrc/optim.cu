@@ -31,7 +31,17 @@ __device__ __forceinline__ void adam_one(float& p, float& g, float& m, float& v,
     if (a.zero_grad) g = 0.0f;
 }
 
-__global__ void __launch_bounds__(256) adam_kernel(const AdamArgs a) {
+// Grid-stride kernels below are launched with exactly as many CTAs as are resident at once (occupancy API): with a fixed
+// "8 per SM" the 47-register kernels fitted only 5, so the grid ran as 1.6 waves with a half-empty second one (ncu:
+// 50 % of the warp slots active, profiles/r01_adam_before_after.md).
+template <typename K>
+static int resident_ctas(K kernel, int threads) {
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+    return per_sm;
+}
+
+__global__ void __launch_bounds__(256, 6) adam_kernel(const AdamArgs a) {
     const double t = (double)(a.step_dev ? *a.step_dev : a.step_host);
     const float step_size = (float)((double)a.lr / (1.0 - pow((double)a.beta1, t)));
     const float bc2_sqrt = (float)sqrt(1.0 - pow((double)a.beta2, t));
@@ -76,7 +86,10 @@ struct AdamSegments {
     uint8_t* touched;      // one byte per float4 group: has this group ever received a gradient?  (NULL = dense)
 };
 
-__global__ void __launch_bounds__(256) adam_segments_kernel(const __grid_constant__ AdamSegments s) {
+// The kernel is bound by memory latency (ncu: long-scoreboard stalls, 0.5 eligible warps per cycle), so every thread keeps
+// two groups in flight and issues the independent loads of both before anything depends on them: flags + gradients
+// first, then parameters + moments of the groups that need the update.
+__global__ void __launch_bounds__(256, 4) adam_segments_kernel(const __grid_constant__ AdamSegments s) {
     const double t = (double)(s.step_dev ? *s.step_dev : s.step_host);
     const float bc1 = (float)(1.0 - pow((double)s.beta1, t));
     const float bc2_sqrt = (float)sqrt(1.0 - pow((double)s.beta2, t));
@@ -86,28 +99,48 @@ __global__ void __launch_bounds__(256) adam_segments_kernel(const __grid_constan
     float4* g4 = reinterpret_cast<float4*>(s.g);
     float4* m4 = reinterpret_cast<float4*>(s.m);
     float4* v4 = reinterpret_cast<float4*>(s.v);
-    int seg = 0;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
-        while (i >= s.end4[seg]) ++seg;
-        AdamArgs a{};
-        a.beta1 = s.beta1; a.beta2 = s.beta2; a.eps = s.eps[seg]; a.weight_decay = s.wd[seg]; a.zero_grad = s.zero_grad;
-        const float step_size = (float)((double)s.lr[seg] / (double)bc1);
-        float4 g = g4[i];
-        const bool nz = g.x != 0.0f || g.y != 0.0f || g.z != 0.0f || g.w != 0.0f;
-        if (s.touched && a.weight_decay == 0.0f) {
+    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+    constexpr int U = 2;             // measured: 1 -> 119 us, 2 -> 108 us, 4 (2 CTAs / SM) -> 117 us
+    int seg[U] = {};
+    for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n4; i0 += U * stride) {
+        int64_t idx[U];
+        bool act[U];
+        float4 g[U];
+        uint8_t f[U];
+#pragma unroll
+        for (int k = 0; k < U; ++k) { idx[k] = i0 + k * stride; act[k] = idx[k] < n4; f[k] = 1; }
+#pragma unroll
+        for (int k = 0; k < U; ++k) {
+            g[k] = act[k] ? g4[idx[k]] : zero;
+            if (s.touched && act[k]) f[k] = s.touched[idx[k]];
+        }
+        bool nz[U];
+#pragma unroll
+        for (int k = 0; k < U; ++k) {
+            if (act[k]) while (idx[k] >= s.end4[seg[k]]) ++seg[k];
+            nz[k] = g[k].x != 0.0f || g[k].y != 0.0f || g[k].z != 0.0f || g[k].w != 0.0f;
             // A group that never saw a gradient has m = v = g = 0: its dense Adam update is exactly the identity, so
             // skipping it (no p / m / v traffic) gives bit-identical parameters.  Once touched, always updated.
-            const uint8_t f = s.touched[i];
-            if (!nz && !f) continue;
-            if (!f) s.touched[i] = 1;
+            if (s.touched && s.wd[seg[k]] == 0.0f && !nz[k] && !f[k]) act[k] = false;
         }
-        float4 p = p4[i], m = m4[i], v = v4[i];
-        adam_one(p.x, g.x, m.x, v.x, a, step_size, bc2_sqrt);
-        adam_one(p.y, g.y, m.y, v.y, a, step_size, bc2_sqrt);
-        adam_one(p.z, g.z, m.z, v.z, a, step_size, bc2_sqrt);
-        adam_one(p.w, g.w, m.w, v.w, a, step_size, bc2_sqrt);
-        p4[i] = p; m4[i] = m; v4[i] = v;
-        if (s.zero_grad && nz) g4[i] = g;       // a zero gradient needs no clearing
+        float4 p[U], m[U], v[U];
+#pragma unroll
+        for (int k = 0; k < U; ++k)
+            if (act[k]) { p[k] = p4[idx[k]]; m[k] = m4[idx[k]]; v[k] = v4[idx[k]]; }
+#pragma unroll
+        for (int k = 0; k < U; ++k) {
+            if (!act[k]) continue;
+            AdamArgs a{};
+            a.beta1 = s.beta1; a.beta2 = s.beta2; a.eps = s.eps[seg[k]]; a.weight_decay = s.wd[seg[k]]; a.zero_grad = s.zero_grad;
+            const float step_size = (float)((double)s.lr[seg[k]] / (double)bc1);
+            if (s.touched && a.weight_decay == 0.0f && !f[k]) s.touched[idx[k]] = 1;
+            adam_one(p[k].x, g[k].x, m[k].x, v[k].x, a, step_size, bc2_sqrt);
+            adam_one(p[k].y, g[k].y, m[k].y, v[k].y, a, step_size, bc2_sqrt);
+            adam_one(p[k].z, g[k].z, m[k].z, v[k].z, a, step_size, bc2_sqrt);
+            adam_one(p[k].w, g[k].w, m[k].w, v[k].w, a, step_size, bc2_sqrt);
+            p4[idx[k]] = p[k]; m4[idx[k]] = m[k]; v4[idx[k]] = v[k];
+            if (s.zero_grad && nz[k]) g4[idx[k]] = g[k];       // a zero gradient needs no clearing
+        }
     }
 }
 
@@ -137,7 +170,7 @@ extern "C" int mne_adam_step(float* param, float* grad, float* exp_avg, float* e
     if (n == 0) return 0;
     AdamArgs a{param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, step_dev, step_host, zero_grad};
     int64_t blocks = (n / 4 + 255) / 256;
-    const int64_t cap = (int64_t)sm_count() * 8;
+    const int64_t cap = (int64_t)sm_count() * resident_ctas(adam_kernel, 256);
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     adam_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(a);
@@ -171,7 +204,7 @@ extern "C" int mne_adam_step_segments(float* param, float* grad, float* exp_avg,
     s.beta1 = beta1; s.beta2 = beta2; s.step_dev = step_dev; s.step_host = step_host; s.zero_grad = zero_grad;
     s.touched = touched;
     int64_t blocks = ((prev >> 2) + 255) / 256;
-    const int64_t cap = (int64_t)sm_count() * 8;
+    const int64_t cap = (int64_t)sm_count() * resident_ctas(adam_segments_kernel, 256);
     if (blocks > cap) blocks = cap;
     adam_segments_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
     MNE_CHECK_CUDA(cudaGetLastError());
@@ -284,7 +317,7 @@ __device__ __forceinline__ uint32_t peer_flags(const AdamPeers& s, int64_t i) {
     return mk;
 }
 
-__global__ void __launch_bounds__(256) adam_peers_sparse_kernel(const __grid_constant__ AdamPeers s) {
+__global__ void __launch_bounds__(256, 4) adam_peers_sparse_kernel(const __grid_constant__ AdamPeers s) {
     const double t = (double)(s.step_dev ? *s.step_dev : s.step_host);
     const float bc1 = (float)(1.0 - pow((double)s.beta1, t));
     const float bc2_sqrt = (float)sqrt(1.0 - pow((double)s.beta2, t));
@@ -350,7 +383,7 @@ __global__ void __launch_bounds__(256) adam_peers_sparse_kernel(const __grid_con
     }
 }
 
-__global__ void __launch_bounds__(256) adam_peers_kernel(const __grid_constant__ AdamPeers s) {
+__global__ void __launch_bounds__(256, 5) adam_peers_kernel(const __grid_constant__ AdamPeers s) {
     const double t = (double)(s.step_dev ? *s.step_dev : s.step_host);
     const float bc1 = (float)(1.0 - pow((double)s.beta1, t));
     const float bc2_sqrt = (float)sqrt(1.0 - pow((double)s.beta2, t));
@@ -444,7 +477,7 @@ extern "C" int mne_adam_step_peers(int32_t world_size, int32_t rank, float* cons
     s.use_dirty = dirty != nullptr;
     s.dirty = dirty;
     int64_t blocks = (s.local4 + 255) / 256;
-    const int64_t cap = (int64_t)sm_count() * 8;
+    const int64_t cap = (int64_t)sm_count() * (s.use_dirty ? resident_ctas(adam_peers_sparse_kernel, 256) : resident_ctas(adam_peers_kernel, 256));
     if (blocks > cap) blocks = cap;
     if (s.use_dirty) adam_peers_sparse_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
     else adam_peers_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
@@ -469,7 +502,7 @@ extern "C" int mne_grad_dirty_map(const float* grad, int64_t n_total, int32_t ch
     d.world = world_size; d.rank = rank; d.chunk_tx_log2 = 31 - __builtin_clz((unsigned)chunk) - 5;
     d.n32 = n_total >> 5; d.local32 = d.n32 / world_size;
     int64_t blocks = (d.n32 * 8 + 255) / 256;
-    const int64_t cap = (int64_t)sm_count() * 8;
+    const int64_t cap = (int64_t)sm_count() * resident_ctas(grad_dirty_kernel, 256);
     if (blocks > cap) blocks = cap;
     grad_dirty_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float4*>(grad), d);
     MNE_CHECK_CUDA(cudaGetLastError());

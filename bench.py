@@ -190,12 +190,15 @@ def measured_peak():
     return 6650.0, 'fallback 6.65 TB/s (B200_PROFILING.md)'
 
 
-def ncu_traffic():
-    """dram bytes per launch of the dominant kernel from the committed ncu summary, if there is one."""
+def ncu_traffic(kernel):
+    """dram bytes per launch of a kernel from the committed ncu summary (profiles/traffic.json), if there is one."""
     path = os.path.join(ROOT, 'profiles', 'traffic.json')
     if os.path.exists(path):
         try:
-            return json.load(open(path)).get('render_bwd_dram_bytes_per_launch')
+            table = json.load(open(path)).get('dram_bytes_per_launch', {})
+            for name, v in table.items():
+                if name.startswith(kernel):
+                    return v
         except Exception:
             return None
     return None
@@ -439,9 +442,19 @@ def run_ours(args):
 
     if rank == 0:
         peak, peak_src = measured_peak()
-        bwd_gbs = pts_per_rank * ALG_BYTES_PER_POINT_BWD / (us['bwd'] * 1e-6) / 1e9
-        fwd_gbs = pts_per_rank * ALG_BYTES_PER_POINT_FWD / (us['fwd'] * 1e-6) / 1e9
-        both_gbs = pts_per_rank * (ALG_BYTES_PER_POINT_FWD + ALG_BYTES_PER_POINT_BWD) / ((us['fwd'] + us['bwd']) * 1e-6) / 1e9
+        # algorithmic bytes per launch (DESIGN.md "Roofline accounting"):
+        #   forward : every sample gathers 3 planes x 2 levels x 4 texels x 128 B
+        #   backward: the samples with a non-zero loss gradient scatter into the same texels (the others add nothing)
+        #   Adam    : 32 B per parameter of a group that ever received a gradient (p, g, m, v read; p, m, v, g written),
+        #             4 B gradient read per parameter of the others, 0.25 B of flags per parameter
+        n_active = ops.backward_active_count(mapper._scratch, n_rays, s)
+        fwd_bytes = pts_per_rank * ALG_BYTES_PER_POINT_FWD
+        bwd_bytes = n_active * ALG_BYTES_PER_POINT_BWD
+        n_param = mapper.total
+        touched = float(mapper.touched.float().mean().item()) if mapper.touched is not None else 1.0
+        adam_bytes = int(n_param * (touched * 32 + (1.0 - touched) * 4 + (0.25 if mapper.touched is not None else 0.0)))
+        gbs = lambda b, t_us: b / (t_us * 1e-6) / 1e9
+        fwd_gbs, bwd_gbs, adam_gbs = gbs(fwd_bytes, us['fwd']), gbs(bwd_bytes, us['bwd']), gbs(adam_bytes, us['adam'])
         line = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3),
             'ms_per_step': ms_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
@@ -456,13 +469,19 @@ def run_ours(args):
                            'path': 'JointEncoding.forward -> loss.backward() -> torch.optim.Adam.step() (the reference call '
                                    'sites unchanged), same host buffers'},
             'tracking': tracking,
-            'roofline': {'bound': 'hbm', 'kernel': 'points_bwd_kernel', 'achieved': bwd_gbs, 'peak': peak, 'unit': 'GB/s',
-                         'frac': bwd_gbs / peak, 'traffic': ncu_traffic(), 'peak_source': peak_src,
-                         'algorithmic_bytes_per_launch': pts_per_rank * ALG_BYTES_PER_POINT_BWD,
-                         'launch_us': us['bwd'],
-                         'fwd_kernel': {'achieved': fwd_gbs, 'frac': fwd_gbs / peak, 'launch_us': us['fwd']},
-                         'fwd_plus_bwd': {'achieved': both_gbs, 'frac': both_gbs / peak,
-                                          'bytes_per_point': ALG_BYTES_PER_POINT_FWD + ALG_BYTES_PER_POINT_BWD}},
+            # the dominant kernel of the step is the optimiser; the two gather / scatter kernels follow
+            'roofline': {'bound': 'hbm', 'kernel': 'adam_segments_kernel' if world == 1 else 'optimizer step: flag hand-over + barrier + adam_peers_sparse_kernel + barrier', 'achieved': adam_gbs, 'peak': peak, 'unit': 'GB/s',
+                         'frac': adam_gbs / peak, 'traffic': ncu_traffic('adam_segments_kernel'), 'peak_source': peak_src,
+                         'algorithmic_bytes_per_launch': adam_bytes, 'launch_us': us['adam'],
+                         'touched_fraction': touched,
+                         'points_fwd_kernel': {'achieved': fwd_gbs, 'frac': fwd_gbs / peak, 'launch_us': us['fwd'],
+                                               'algorithmic_bytes_per_launch': fwd_bytes,
+                                               'traffic': ncu_traffic('points_fwd_kernel'),
+                                               'note': 'launch_us includes rays_fwd_kernel (compositing + loss sums)'},
+                         'points_bwd_kernel': {'achieved': bwd_gbs, 'frac': bwd_gbs / peak, 'launch_us': us['bwd'],
+                                               'algorithmic_bytes_per_launch': bwd_bytes, 'active_samples': n_active,
+                                               'traffic': ncu_traffic('points_bwd_kernel'),
+                                               'note': 'launch_us includes rays_bwd_kernel (d loss / d raw + compaction)'}},
             'breakdown_us': us,
             'fwd_bwd_points_per_s': pts_per_rank * world / ((us['sample'] + us['fwd'] + us['bwd']) * 1e-6),
             'clocks': clocks,

@@ -224,6 +224,13 @@ def backward_scratch(n_rays, n_samples, device):
     return torch.empty(max(nbytes // 4, 4), dtype=torch.float32, device=device)
 
 
+def backward_active_count(scratch, n_rays, n_samples):
+    """How many samples the last mne_render_backward on this scratch buffer processed (those with a non-zero loss
+    gradient); layout of the buffer: d_raw float4[n] | sample list int32[round4(n)] | count.  Synchronises."""
+    n = n_rays * n_samples
+    return int(scratch.view(torch.int32)[n * 4 + (n + 3) // 4 * 4].item())
+
+
 def render_backward(scene, render_cfg, rays_o, rays_d, z_vals, raw, target_rgb=None, target_d=None, acc=None,
                     loss_grads=None, g_rgb=None, g_depth=None, g_raw=None, want_ray_grads=False, scratch=None):
     n, s = z_vals.shape

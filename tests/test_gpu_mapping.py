@@ -18,11 +18,9 @@ def _small_model(seed=3, one_grid=True):
     return cfg, bb, planes, weights
 
 
-@pytest.mark.parametrize('one_grid', [True, False])
-def test_fused_iterations_match_autograd_plus_torch_adam(one_grid):
-    """Five mapping iterations: FusedMapper (sample/fwd/bwd/Adam kernels) against the drop-in class driven the
-    way the reference drives it (forward -> get_loss_from_ret -> backward -> torch.optim.Adam, create_optimizer's
-    parameter groups)."""
+def _five_iterations(one_grid):
+    """Bulk relative parameter differences (planes, decoder weights) between FusedMapper and the drop-in class driven
+    the way the reference drives it, after five mapping iterations from the same start."""
     from mneslam_b200.mapping import FusedMapper
     cfg, bb, planes, weights = _small_model(one_grid=one_grid)
     a = build_model(cfg, bb, planes, weights)
@@ -45,16 +43,35 @@ def test_fused_iterations_match_autograd_plus_torch_adam(one_grid):
         opt.zero_grad()
         losses = mapper.step(batch['rays_o'], batch['rays_d'], batch['target_rgb'], batch['target_d'], noise=noise)
         assert mapper.total_loss(losses).item() == pytest.approx(loss.item(), rel=2e-4)
-    # Adam's early steps are sign-like (m / sqrt(v) ~ g / |g|), so the ordering noise of the float atomics in the
-    # backward is amplified on parameters whose gradient is almost zero: compare the bulk, not the worst element
-    def bulk_close(x, y):
-        x, y = x.detach().double().reshape(-1), y.detach().double().reshape(-1)
-        return float((x - y).norm() / (y.norm() + 1e-30)) < 2e-3
-    for pa, pb in zip(flat_planes(a), flat_planes(b)):
-        assert bulk_close(pb, pa)
-    for wa, wb in zip(a.decoder.weight_list(), b.decoder.weight_list()):
-        assert bulk_close(wb, wa)
     assert float(mapper.flat_grad.abs().max()) == 0.0, 'the Adam kernel leaves the gradients zeroed'
+
+    def bulk(x, y):
+        x, y = x.detach().double().reshape(-1), y.detach().double().reshape(-1)
+        return float((x - y).norm() / (y.norm() + 1e-30))
+    return (max(bulk(pb, pa) for pa, pb in zip(flat_planes(a), flat_planes(b))),
+            max(bulk(wb, wa) for wa, wb in zip(a.decoder.weight_list(), b.decoder.weight_list())))
+
+
+@pytest.mark.parametrize('one_grid', [True, False])
+def test_fused_iterations_match_autograd_plus_torch_adam(one_grid):
+    """Five mapping iterations: FusedMapper (sample/fwd/bwd/Adam kernels) against the drop-in class driven the
+    way the reference drives it (forward -> get_loss_from_ret -> backward -> torch.optim.Adam, create_optimizer's
+    parameter groups).
+
+    Both arms sum their gradients with float atomics, so two runs never see bit-identical gradients, and a trajectory
+    is not a smooth function of them: Adam's early steps are sign-like (m / sqrt(v) ~ g / |g|) and the compositing
+    has discrete decisions (first sign change of the sdf, truncation masks).  Measured over repeated runs
+    (scripts/traj_noise.py): the bulk difference is ~1e-6, with an occasional run at ~2e-3 when one of those decisions
+    falls the other way.  So: up to three attempts, the best one must be within 2e-5 (any systematic error -- moments,
+    bias correction, parameter groups, zeroing -- shows in every attempt), and none may be off by more than 5e-2."""
+    best = (1.0, 1.0)
+    for attempt in range(3):
+        pe, we = _five_iterations(one_grid)
+        assert pe < 5e-2 and we < 5e-2, (pe, we)
+        best = min(best, (pe, we), key=max)
+        if max(best) < 2e-5:
+            break
+    assert max(best) < 2e-5, best
 
 
 def test_adam_kernel_matches_torch_single_tensor():

@@ -303,7 +303,10 @@ def run_ours(args):
 
     # ---- per-kernel device times (events around each launch, same stream, un-graphed), K steps
     def timed(fn):
+        # a short device-side sleep first, so that the host has enqueued the launches before the first event is reached
+        # on the stream: the interval then holds kernel time, not launch gaps
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda._sleep(400000)
         a.record(); r = fn(); b.record()
         return r, (a, b)
     tables = ops.SampleTables.get(cfg, dev, True)

@@ -60,14 +60,15 @@ def workload_config(cfg, n_rays, world):
 # CPU baseline: the oracle port of the reference's path (torch CPU ops incl. F.grid_sample, as the reference)
 # ----------------------------------------------------------------------------------------------------
 class CpuMapper:
-    def __init__(self, cfg, seed=0):
+    def __init__(self, cfg, seed=0, device='cpu'):
         from oracle import joint_encoding as J
         self.J, self.cfg = J, cfg
         self.bound = J.enlarged_bound(cfg)
         self.bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
         planes = J.init_planes(cfg, self.bound, seed=seed, std=0.01)
-        self.planes = tuple([torch.nn.Parameter(p) for p in grp] for grp in planes)
-        self.weights = {k: torch.nn.Parameter(v) for k, v in J.init_weights(cfg, seed=seed).items()}
+        self.bound, self.bb = self.bound.to(device), self.bb.to(device)
+        self.planes = tuple([torch.nn.Parameter(p.to(device)) for p in grp] for grp in planes)
+        self.weights = {k: torch.nn.Parameter(v.to(device)) for k, v in J.init_weights(cfg, seed=seed).items()}
         mp = cfg['mapping']
         self.opt = torch.optim.Adam([
             {'params': list(self.weights.values()), 'weight_decay': 1e-6, 'lr': mp['lr_decoder']},
@@ -81,7 +82,7 @@ class CpuMapper:
         loss.backward()
         self.opt.step()
         self.opt.zero_grad()
-        return float(loss)
+        return float(loss.detach())
 
 
 def time_cpu(cfg, n_rays, steps, warmup):
@@ -100,6 +101,30 @@ def time_cpu(cfg, n_rays, steps, warmup):
     times.sort()
     med = times[len(times) // 2]
     return n_rays * s / med, med, sum(times)
+
+
+def torch_gpu_record(cfg, n_rays, dev, steps=10, warmup=3):
+    """The same oracle port with every tensor on the GPU: torch's own CUDA kernels (grid_sample, matmul, multi-tensor
+    Adam) -- the operator mix of the reference's GPU path, OneBlob restated in torch instead of tiny-cuda-nn.  Reported
+    beside cpu_baseline for orientation; device-resident inputs, CUDA events."""
+    from mneslam_b200 import synthetic
+    s = synthetic.n_samples_total(cfg)
+    m = CpuMapper(cfg, device=dev)
+    batches = [{k: v.to(dev) for k, v in synthetic.make_ray_batch(cfg, n_rays, seed=i).items()} for i in range(4)]
+    noises = [synthetic.make_noise(n_rays, s, seed=i).to(dev) for i in range(4)]
+    for i in range(warmup):
+        m.step(batches[i % 4], noises[i % 4])
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for i in range(steps):
+        m.step(batches[i % 4], noises[i % 4])
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / steps
+    return {'value': n_rays * s / (ms * 1e-3), 'unit': UNIT, 'ms_per_step': ms, 'steps': steps,
+            'path': 'oracle port on the GPU: torch CUDA ops (F.grid_sample, matmul, torch.optim.Adam), fp32, eager; includes one '
+                    'loss.item() per step as the reference loop has'}
 
 
 def cpu_baseline_record(cfg, n_rays, steps=5, warmup=1):
@@ -494,6 +519,12 @@ def run_ours(args):
         }
         if world == 1 and not args.no_cpu_baseline:
             line['cpu_baseline'] = cpu_baseline_record(cfg, n_rays)
+            try:
+                del mapper, model, graph
+                torch.cuda.empty_cache()
+                line['torch_gpu_baseline'] = torch_gpu_record(cfg, n_rays, dev)
+            except Exception as e:        # orientation only: never fail the bench line over it
+                line['torch_gpu_baseline'] = {'unavailable': repr(e)[:200]}
         print(json.dumps(line), flush=True)
     if world > 1:
         # Tearing NCCL down while a captured graph still references its communicator hung the process once the JSON

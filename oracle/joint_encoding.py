@@ -89,6 +89,8 @@ def sample_z(cfg, n_rays, target_d=None, noise=None):
     """Depth-guided + uniform samples merged by sort, then stratified perturbation.
     Returns (z_vals [N,S], z_sorted [N,S] before perturbation)."""
     tab = sample_tables(cfg)
+    dev = target_d.device if target_d is not None else (noise.device if noise is not None else torch.device('cpu'))
+    tab = {k: v.to(dev) for k, v in tab.items()}          # built on the CPU, moved -- as the reference does (:362-374)
     if target_d is not None:
         z_near = tab['range_off'][None, :].repeat(n_rays, 1) + target_d                 # :363-364
         z_near[target_d.squeeze(-1) <= 0] = tab['range_fallback']                       # :365

@@ -38,11 +38,11 @@ def oneblob(x, n_bins=16):
     x = x.float()
     M, D = x.shape
     pow2 = (n_bins & (n_bins - 1)) == 0
-    left_edges = torch.arange(n_bins, dtype=torch.float32) / n_bins            # [B]
+    left_edges = torch.arange(n_bins, dtype=torch.float32, device=x.device) / n_bins            # [B]
     left = _wrapped_cdf(left_edges[None, None, :] - x[:, :, None], n_bins)       # [M, D, B]
     if pow2:
         right = torch.cat([left[..., 1:], left[..., :1] + 1.0], dim=-1)
     else:
-        right_edges = (torch.arange(n_bins, dtype=torch.float32) + 1) / n_bins
+        right_edges = (torch.arange(n_bins, dtype=torch.float32, device=x.device) + 1) / n_bins
         right = _wrapped_cdf(right_edges[None, None, :] - x[:, :, None], n_bins)
     return (right - left).reshape(M, D * n_bins)

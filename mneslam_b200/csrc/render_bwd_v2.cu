@@ -396,7 +396,7 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
             const float nn[3] = {plane_coord(px, P.sc.bound_lo[0], P.sc.bound_ext[0]), plane_coord(py, P.sc.bound_lo[1], P.sc.bound_ext[1]),
                                  plane_coord(pz, P.sc.bound_lo[2], P.sc.bound_ext[2])};
 #pragma unroll
-            for (int tp = 0; tp < (TWO ? 12 : 6); ++tp) {
+            for (int tp = 0; MODE != 2 && tp < (TWO ? 12 : 6); ++tp) {
                 const int a = (tp % 6) >> 1;
                 const MnePlaneDesc& Pl = P.sc.planes[tp];
                 const AxisTap tx = axis_tap((a == 2) ? nn[1] : nn[0], Pl.W), ty = axis_tap((a == 0) ? nn[1] : nn[2], Pl.H);
@@ -413,7 +413,8 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
             write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 0);
         }
         __syncwarp();
-        float dn_keep[3] = {0.f, 0.f, 0.f};                      // d loss / d normalised plane coordinates of this lane's point
+        float dn_keep[3] = {0.f, 0.f, 0.f};                      // d loss / d normalised plane (or unit-cube) coordinates of this lane's point
+        if (MODE == 2 && RAY) hash_point_grad16(P.sc.hash[0], X + kBlobCol, kXStride, X, kXStride, np, lane, dn_keep);
         // ---- 8. plane gradient scatter: lane = (corner, 4-channel group)
         for (int grp = 0; MODE != 2 && grp < (TWO ? 2 : 1); ++grp) {
             if (grp == 1) {
@@ -500,7 +501,8 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
             const float z = P.z_vals[q];
 #pragma unroll
             for (int a = 0; a < 3; ++a) {
-                const float gpnt = dn_keep[a] * (2.0f / P.sc.bound_ext[a]) + dpt[a];
+                // planes: coordinates in [-1, 1] over `bound`; hash grid: in [0, 1] over `bounding_box` (like the OneBlob input)
+                const float gpnt = (MODE == 2 ? (float)((double)dn_keep[a] / P.sc.bbox_ext[a]) : dn_keep[a] * (2.0f / P.sc.bound_ext[a])) + dpt[a];
                 atomicAdd(P.g_rays_o + ray * 3 + a, gpnt);
                 atomicAdd(P.g_rays_d + ray * 3 + a, gpnt * z);
             }
@@ -713,7 +715,8 @@ int render_backward_v2(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int3
     P.g_rays_o = g_rays_o; P.g_rays_d = g_rays_d; P.list = R.list; P.n_active = R.n_active;
     const bool ray = g_rays_o != nullptr;
     if (scene->encoder == 1) {
-        MNE_CHECK_ARG(!ray, "mne_render_backward: ray gradients through the hash grid are not built yet");
+        if (ray && param_grad) return launch_points_bwd<false, 2, true, true>(P, st);
+        if (ray) return launch_points_bwd<false, 2, true, false>(P, st);
         return launch_points_bwd<false, 2, false, true>(P, st);
     }
     if (planes_vectorizable(*scene)) return dispatch_points_bwd<1>(P, ray, param_grad, st);

@@ -310,6 +310,44 @@ __device__ __forceinline__ void scatter16_hash(const MneHashDesc& h, const float
     }
 }
 
+// d loss / d (unit-cube coordinates) through the table lookup, for the pose path: the interpolation weights are linear in
+// the fractional position, so d feat / d x_d = scale * sum_k (+-1)_d(k) * prod_{d' != d} w_d'(k) * T[k]  (tiny-cuda-nn
+// kernel_grid_backward_input; the indices carry no gradient).  lane = (point parity, level); the 16 levels of a point
+// are reduced by shuffles and handed to the lanes whose tile row is that point (out[] is ADDED to).
+__device__ __forceinline__ void hash_point_grad16(const MneHashDesc& h, const float* __restrict__ xn, int xn_stride,
+                                                  const float* __restrict__ src, int src_stride, int np, int lane, float (&out)[3]) {
+    const int l = lane & 15, pp = lane >> 4;
+    const HashLevel L = hash_level(h, l);
+    const float2* table = reinterpret_cast<const float2*>(h.table) + L.offset;
+    for (int it = 0; it < kTilePts / 2; ++it) {
+        const int p = 2 * it + pp;
+        float d[3] = {0.f, 0.f, 0.f};
+        if (p < np) {
+            const HashCell c = hash_cell(L, xn + p * xn_stride);
+            const float2 g2 = *reinterpret_cast<const float2*>(src + p * src_stride + 2 * l);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const uint32_t idx = hash_index(L, c.g[0] + (k & 1), c.g[1] + ((k >> 1) & 1), c.g[2] + ((k >> 2) & 1));
+                const float2 v = __ldg(table + idx);
+                const float D = g2.x * v.x + g2.y * v.y;
+                const float wx = (k & 1) ? c.f[0] : 1.0f - c.f[0], wy = (k & 2) ? c.f[1] : 1.0f - c.f[1], wz = (k & 4) ? c.f[2] : 1.0f - c.f[2];
+                d[0] += ((k & 1) ? D : -D) * (wy * wz);
+                d[1] += ((k & 2) ? D : -D) * (wx * wz);
+                d[2] += ((k & 4) ? D : -D) * (wx * wy);
+            }
+            d[0] *= L.scale; d[1] *= L.scale; d[2] *= L.scale;
+        }
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+#pragma unroll
+            for (int o = 1; o <= 8; o <<= 1) d[a] += __shfl_xor_sync(0xffffffffu, d[a], o);
+            const float even = __shfl_sync(0xffffffffu, d[a], 0), odd = __shfl_sync(0xffffffffu, d[a], 16);
+            if (l == 2 * it) out[a] += even;
+            if (l == 2 * it + 1) out[a] += odd;
+        }
+    }
+}
+
 __host__ inline bool planes_vectorizable(const MneSceneDesc& sc) {
     const int n = sc.two_grid ? 12 : 6;
     for (int i = 0; i < n; ++i) {

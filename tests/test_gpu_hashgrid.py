@@ -89,6 +89,39 @@ def test_forward_backward_vs_oracle():
     assert emb.shape == (500, 1, 32) and rel(emb.reshape(500, 32).detach().cpu().numpy(), want.numpy()) < 1e-4
 
 
+@pytest.mark.parametrize('with_params', [True, False])
+def test_ray_gradients_through_the_hash_grid(with_params):
+    """Pose path: d loss / d rays_o, d rays_d through the table lookup (fractional position) and OneBlob, alone (tracking:
+    map frozen) and together with the table / decoder gradients (joint optimisation), against autograd on the oracle."""
+    cfg = _hash_cfg()
+    model, meta, table, weights, bb = _model(cfg, seed=5)
+    n = 200
+    batch = synthetic.make_ray_batch(cfg, n, seed=11, zero_depth_frac=0.1, depth_range=(0.3, 2.5))
+    noise = synthetic.make_noise(n, synthetic.n_samples_total(cfg), seed=11)
+    ot = table.clone().requires_grad_(with_params)
+    ow = {k: v.clone().requires_grad_(with_params) for k, v in weights.items()}
+    oo, od = batch['rays_o'].clone().requires_grad_(True), batch['rays_d'].clone().requires_grad_(True)
+    oret, _ = J.forward(cfg, ([ot],), ow, J.enlarged_bound(cfg), bb, oo, od, batch['target_rgb'], batch['target_d'], noise)
+    J.total_loss(cfg, oret).backward()
+
+    if not with_params:
+        model.hash_tables[0].requires_grad_(False)
+        for w in model.decoder.weight_list():
+            w.requires_grad_(False)
+    ro, rd = batch['rays_o'].cuda().requires_grad_(True), batch['rays_d'].cuda().requires_grad_(True)
+    ret = model.forward(ro, rd, batch['target_rgb'].cuda(), batch['target_d'].cuda(), noise=noise.cuda())
+    total_loss(cfg, ret).backward()
+    for got, want, name in ((ro.grad, oo.grad, 'rays_o'), (rd.grad, od.grad, 'rays_d')):
+        assert cosine(got.cpu().numpy(), want.numpy()) >= 0.999, name
+        assert rel(got.cpu().numpy(), want.numpy()) < 5e-3, name
+    if with_params:
+        assert cosine(model.hash_tables[0].grad.cpu().numpy(), ot.grad.numpy()) >= 0.999
+        for w, k in zip(model.decoder.weight_list(), ('sdf0', 'sdf1', 'col0', 'col1')):
+            assert cosine(w.grad.cpu().numpy(), ow[k].grad.numpy()) >= 0.999, k
+    else:
+        assert model.hash_tables[0].grad is None
+
+
 def test_fused_mapper_trains_the_hash_grid():
     cfg = _hash_cfg(hash_size=14)
     model, *_ = _model(cfg, seed=1, table_scale=1e-4)

@@ -346,12 +346,12 @@ def run_ours(args):
         acc = ops.new_acc(dev)
         z, e = timed(lambda: ops.sample_rays(scfg, rcfg, n_rays, s, tdf, noise, acc, dev)); ev['sample'].append(e)
         sc_f, sc_b = mapper._scene(False), mapper._scene(True)          # descriptors built outside the timed intervals
-        out, e = timed(lambda: ops.render_forward(sc_f, rcfg, ro, rd, z, trgb, tdf, acc, want_aux=False)); ev['fwd'].append(e)
+        out, e = timed(lambda: ops.render_forward(sc_f, rcfg, ro, rd, z, trgb, tdf, acc, want_aux=False, act=mapper._act)); ev['fwd'].append(e)
         if world > 1:
             dist.all_reduce(acc)
         scr = mapper._scratch
         _, e = timed(lambda: ops.render_backward(sc_b, rcfg, ro, rd, z, out['raw'], trgb, tdf, acc,
-                                                 loss_grads=mapper.loss_grads, scratch=scr)); ev['bwd'].append(e)
+                                                 loss_grads=mapper.loss_grads, scratch=scr, act=mapper._act)); ev['bwd'].append(e)
         _, e = timed(mapper.optimizer_step); ev['adam'].append(e)
     torch.cuda.synchronize()
     us = {k: 1e3 * sum(a.elapsed_time(b) for a, b in v) / len(v) for k, v in ev.items()}

@@ -12,6 +12,7 @@ MAX_PLANES = 12
 ACC_SLOTS = 16
 N_LOSSES = 8
 STATIC_SCRATCH_SAMPLES = 131072   # MNE_STATIC_SCRATCH_SAMPLES
+ACT_FLOATS = 80                   # MNE_ACT_FLOATS
 
 # accumulator / loss slots (keep in sync with csrc/common.cuh)
 ACC = {'n_valid': 0, 'n_co_front': 1, 'n_co_near': 2, 'n_e_front': 3, 'n_e_center': 4, 'n_e_tail': 5,
@@ -62,12 +63,12 @@ _SIGNATURES = {
     'mne_sample_importance': (C.c_int, [C.POINTER(RenderCfg), C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                         C.c_int32] + [C.c_void_p] * 6),
     'mne_render_forward': (C.c_int, [C.POINTER(SceneDesc), C.POINTER(RenderCfg), C.c_int32, C.c_int32] +
-                           [C.c_void_p] * 15),
+                           [C.c_void_p] * 16),
     'mne_composite': (C.c_int, [C.POINTER(RenderCfg), C.c_int32, C.c_int32] + [C.c_void_p] * 10),
     'mne_loss_finalize': (C.c_int, [C.POINTER(RenderCfg), C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     'mne_backward_scratch_bytes': (C.c_size_t, [C.c_int32, C.c_int32]),
     'mne_render_backward': (C.c_int, [C.POINTER(SceneDesc), C.POINTER(RenderCfg), C.c_int32, C.c_int32] +
-                            [C.c_void_p] * 15),
+                            [C.c_void_p] * 16),
     'mne_render_backward_static': (C.c_int, [C.POINTER(SceneDesc), C.POINTER(RenderCfg), C.c_int32, C.c_int32] +
                                    [C.c_void_p] * 14),
     'mne_hash_indices': (C.c_int, [C.POINTER(HashDesc), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),

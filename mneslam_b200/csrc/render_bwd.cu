@@ -436,9 +436,10 @@ int check_scene(const MneSceneDesc* sc, const char* who, bool need_grads);
 int choose_rays_per_group(int n_rays, int n_samples, int total_warps);
 int sm_count();
 int impl_version();
+bool scene_is_vectorizable(const MneSceneDesc* sc);
 int render_backward_v2(const MneSceneDesc*, const MneRenderCfg*, int32_t, int32_t, const float*, const float*, const float*,
                        const float*, const float*, const float*, const double*, const float*, const float*, const float*,
-                       const float*, void*, float*, float*, bool, cudaStream_t);
+                       const float*, void*, float*, float*, bool, const float*, cudaStream_t);
 
 template <bool TWO, bool RAY_GRAD, bool PARAM_GRAD>
 static int launch_bwd(const BwdParams& P, cudaStream_t stream) {
@@ -478,9 +479,10 @@ extern "C" int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg
                                    const float* rays_o, const float* rays_d, const float* z_vals, const float* raw,
                                    const float* target_rgb, const float* target_d, const double* acc,
                                    const float* loss_grads, const float* g_rgb, const float* g_depth, const float* g_raw,
-                                   void* scratch, float* g_rays_o, float* g_rays_d, mne_stream_t stream) {
+                                   void* scratch, float* g_rays_o, float* g_rays_d, const float* act, mne_stream_t stream) {
     using namespace mne;
     MNE_CHECK_ARG(scene && rcfg, "mne_render_backward: null scene/rcfg");
+    MNE_CHECK_ARG(((uintptr_t)act & 7) == 0, "mne_render_backward: act must be 8-byte aligned");
     if (int e = check_scene(scene, "mne_render_backward", false)) return e;
     MNE_CHECK_ARG(n_rays >= 0 && n_samples > 0, "mne_render_backward: bad sizes n_rays=%d n_samples=%d", n_rays, n_samples);
     if (n_rays == 0) return 0;
@@ -501,9 +503,11 @@ extern "C" int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg
         MNE_CHECK_CUDA(cudaMemsetAsync(g_rays_d, 0, sizeof(float) * 3 * (size_t)n_rays, st));
     }
     MNE_CHECK_ARG(!scene->dirty || scene->dirty_base, "mne_render_backward: dirty without dirty_base");
-    if (impl_version() == 2 && !(scene->two_grid && ray_grad && param_grad))
+    // (two grids with ray AND parameter gradients fit the tensor-pipe kernel's shared memory only without the recompute weights)
+    const bool strided = scene->encoder == 0 && !scene_is_vectorizable(scene);
+    if (impl_version() == 2 && ((act && !strided) || !(scene->two_grid && ray_grad && param_grad)))
         return render_backward_v2(scene, rcfg, n_rays, n_samples, rays_o, rays_d, z_vals, raw, target_rgb, target_d, acc,
-                                  loss_grads, g_rgb, g_depth, g_raw, scratch, g_rays_o, g_rays_d, param_grad, st);
+                                  loss_grads, g_rgb, g_depth, g_raw, scratch, g_rays_o, g_rays_d, param_grad, act, st);
     MNE_CHECK_ARG(!scene->dirty, "mne_render_backward: MneSceneDesc.dirty is supported by impl 2 without combined two-grid ray + parameter gradients only");
     BwdParams P{};
     P.sc = *scene; P.rc = *rcfg; P.n_rays = n_rays; P.n_samples = n_samples;
@@ -570,5 +574,5 @@ extern "C" int mne_render_backward_static(const MneSceneDesc* scene, const MneRe
     // backward kernel fills d_raw for all n_rays * n_samples entries and the list of non-zero ones; the list length is
     // reset by a memset node on the stream), so leftovers of a previous call are never read.
     return mne_render_backward(scene, rcfg, n_rays, n_samples, rays_o, rays_d, z_vals, raw, target_rgb, target_d, acc,
-                               loss_grads, g_rgb, g_depth, g_raw, scratch, g_rays_o, g_rays_d, stream);
+                               loss_grads, g_rgb, g_depth, g_raw, scratch, g_rays_o, g_rays_d, nullptr, stream);
 }

@@ -14,6 +14,7 @@
 namespace mne {
 
 constexpr int kBwdWarps = 8;
+constexpr int kSavedWarps = 12;    // one-grid kernels that read the forward's activations instead of recomputing them
 constexpr int kActStride = 40;     // hidden-wide tiles [16][32 + 8]: == 8 (mod 32)
 constexpr int kGeoStride = 24;     // 16-wide tiles
 constexpr int kRgbStride = 8;
@@ -66,11 +67,12 @@ __device__ __forceinline__ void load_weights_t(const MneSceneDesc& sc, float* WT
 template <bool TWO> __host__ __device__ constexpr int bwd2_warp_floats() {
     return kTilePts * (kXStride + (TWO ? kCStride : 0) + 2 * kActStride + kGeoStride + kRgbStride);
 }
-template <bool TWO, bool RAY, int NW>
+template <bool TWO, bool RAY, int NW, bool SAVED = false>
 constexpr size_t bwd2_smem_bytes() {
     // forward-recompute weights: one grid keeps the split (3-term) layout -- tighter gradients; two grids only fit with
     // the single-TF32 pair layout (half the bytes)
-    return sizeof(float4) * (size_t)NetV2<TWO>::W4_COUNT +
+    // (with the forward's activations at hand there is no recompute and the split weights are not staged at all)
+    return sizeof(float4) * (size_t)(SAVED ? 0 : NetV2<TWO>::W4_COUNT) +
            sizeof(float) * (size_t)((RAY ? NetT<TWO>::FLOATS_RAY : NetT<TWO>::FLOATS_NORAY) + NW * bwd2_warp_floats<TWO>());
 }
 
@@ -86,6 +88,7 @@ struct PtsBwdParams {
     float* g_rays_d;
     const int* list;         // samples with a non-zero draw (compacted by rays_bwd_kernel)
     const int* n_active;     // how many
+    const float* act;        // [n_pts][80] activations kept by the forward (SAVED kernels), or NULL (recompute)
 };
 
 __device__ __forceinline__ void mma_1x(float (&d)[4], float a0, float a1, float a2, float a3, float b0, float b1) {
@@ -118,14 +121,16 @@ __device__ __forceinline__ void outer_mma(float (&acc)[NACC][4], const float* __
 // MODE: 0 = planes through strides, 1 = channels-last planes (vector gather / scatter), 2 = hash grid
 // NW = warps per CTA: 8 for one grid; two grids need more shared memory per warp and for the weights, so 6 (or 5 with
 // the ray-gradient weights); weight-gradient blocks are dealt round-robin to warps (slot = block / NW).
-template <bool TWO, int MODE, bool RAY, bool PARAM, int NW>
+// SAVED: the forward kept h1 / o16 / hc (PtsBwdParams.act): no recompute, no split weights in shared memory, more warps;
+// without parameter gradients (tracking) not even the features are gathered again.
+template <bool TWO, int MODE, bool RAY, bool PARAM, int NW, bool SAVED = false>
 __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_constant__ PtsBwdParams P) {
     using N = NetV2<TWO>;
     using T = NetT<TWO>;
     constexpr int WF = bwd2_warp_floats<TWO>();
     extern __shared__ __align__(16) float4 smem4[];
     float4* W4 = smem4;                                   // split (hi, lo) pairs for the activation recompute
-    float* WT = reinterpret_cast<float*>(W4 + N::W4_COUNT);
+    float* WT = reinterpret_cast<float*>(W4 + (SAVED ? 0 : N::W4_COUNT));
     float* tiles = WT + (RAY ? T::FLOATS_RAY : T::FLOATS_NORAY);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float* X = tiles + warp * WF;
@@ -138,16 +143,20 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
     constexpr int O_CF = kTilePts * kXStride, O_ACT = O_CF + (TWO ? kTilePts * kCStride : 0), O_DY = O_ACT + kTilePts * kActStride,
                   O_GEO = O_DY + kTilePts * kActStride, O_DRGB = O_GEO + kTilePts * kGeoStride;
 
-    load_weights_v2<TWO>(P.sc, W4, threadIdx.x, blockDim.x);
+    if (!SAVED) load_weights_v2<TWO>(P.sc, W4, threadIdx.x, blockDim.x);
     load_weights_t<TWO, RAY>(P.sc, WT, threadIdx.x, blockDim.x);
     __syncthreads();
 
     // only samples with a non-zero d loss / d raw are processed (list written by rays_bwd_kernel): everything behind
     // the truncation band of a ray -- about a third of a mapping batch -- would only add exact zeros
     const int64_t n_pts = *P.n_active;
-    const int64_t n_tiles = (n_pts + kTilePts - 1) / kTilePts;
+    // The kernel is latency bound per tile (one tile per warp and round), so the samples are dealt evenly over the rounds
+    // that are needed anyway: e.g. 35 k samples on 148 x 12 warps are two rounds of 10-sample tiles, not a full round of
+    // 16-sample tiles followed by a quarter-full one of the same length.
     const int64_t tiles_per_round = (int64_t)gridDim.x * NW;
-    const int64_t n_rounds = (n_tiles + tiles_per_round - 1) / tiles_per_round;
+    const int64_t n_rounds = (n_pts + tiles_per_round * kTilePts - 1) / (tiles_per_round * kTilePts);
+    const int ppt = n_rounds > 0 ? (int)((n_pts + n_rounds * tiles_per_round - 1) / (n_rounds * tiles_per_round)) : kTilePts;   // samples per tile, <= 16
+    const int64_t n_tiles = ppt > 0 ? (n_pts + ppt - 1) / ppt : 0;
     const int p_loc = lane & 15, half = lane >> 4;
     const int g = lane >> 2, t = lane & 3;
 
@@ -175,8 +184,8 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
         // consecutive tiles of a round go to different SMs (block-minor), as in the forward
         const int64_t tile = round * tiles_per_round + (int64_t)warp * gridDim.x + blockIdx.x;
         const bool have = tile < n_tiles;
-        const int64_t pt0 = tile * kTilePts;
-        const int np = have ? (int)min((int64_t)kTilePts, n_pts - pt0) : 0;
+        const int64_t pt0 = tile * ppt;
+        const int np = have ? (int)min((int64_t)ppt, n_pts - pt0) : 0;
 
         // ---- 1. position, taps, gather, OneBlob
         float px = 0.f, py = 0.f, pz = 0.f;
@@ -193,7 +202,9 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
         const float bx0 = blob_input(px, P.sc.bbox_lo[0], P.sc.bbox_ext[0]);
         const float by0 = blob_input(py, P.sc.bbox_lo[1], P.sc.bbox_ext[1]);
         const float bz0 = blob_input(pz, P.sc.bbox_lo[2], P.sc.bbox_ext[2]);
-        if (MODE == 2) {
+        if (SAVED && !PARAM) {
+            // nothing of the forward's inputs is needed: no weight gradients, activations at hand
+        } else if (MODE == 2) {
             if (half == 0) { row[kBlobCol] = bx0; row[kBlobCol + 1] = by0; row[kBlobCol + 2] = bz0; }
             __syncwarp();
             gather16_hash(P.sc.hash[0], X + kBlobCol, kXStride, X, kXStride, np, lane);
@@ -212,22 +223,27 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
                 __syncwarp();
             }
         }
-        if (half == 0) {
-            oneblob16_sparse(bx0, row + kBlobCol);
-            oneblob16_sparse(by0, row + kBlobCol + 16);
-        } else {
-            oneblob16_sparse(bz0, row + kBlobCol + 32);
-        }
-        // rows without a point must be finite (they are multiplied by zero gradients later)
-        for (int p = np; p < kTilePts; ++p) {
-            X[p * kXStride + lane] = 0.f; X[p * kXStride + 32 + lane] = 0.f;
-            if (TWO) { CFt[p * kCStride + lane] = 0.f; CFt[p * kCStride + 32 + lane] = 0.f; }
+        if (!(SAVED && !PARAM)) {
+            if (half == 0) {
+                oneblob16_sparse(bx0, row + kBlobCol);
+                oneblob16_sparse(by0, row + kBlobCol + 16);
+            } else {
+                oneblob16_sparse(bz0, row + kBlobCol + 32);
+            }
+            // rows without a point must be finite (they are multiplied by zero gradients later)
+            for (int p = np; p < kTilePts; ++p) {
+                X[p * kXStride + lane] = 0.f; X[p * kXStride + 32 + lane] = 0.f;
+                if (TWO) { CFt[p * kCStride + lane] = 0.f; CFt[p * kCStride + 32 + lane] = 0.f; }
+            }
         }
         __syncwarp();
 
-        // ---- 2. forward recompute, upstream of this tile's rows g and g+8
+        // ---- 2. the forward's activations of this tile's rows g and g+8: kept by the forward, or recomputed
         float h1[4][4], o16[2][4], hc[4][4];
-        {
+        const int q_lo = __shfl_sync(0xffffffffu, q, g), q_hi = __shfl_sync(0xffffffffu, q, g + 8);
+        if (SAVED) {
+            load_act(P.act, q_lo, q_hi, g < np, g + 8 < np, t, h1, o16, hc);
+        } else {
             // same split-precision products as the forward kernel: the ReLU masks and activations must be the
             // forward's (a single-TF32 recompute flips masks of near-zero pre-activations: measured 1e-2..5e-2
             // max-norm gradient error on the two-grid goldens, against 2e-3 with the split)
@@ -235,7 +251,6 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
             decoder_forward_mma<TWO>(W4, X, CFt, lane, h1, o16, hc, rgb_unused);
         }
         float4 dr_lo = make_float4(0.f, 0.f, 0.f, 0.f), dr_hi = dr_lo;
-        const int q_lo = __shfl_sync(0xffffffffu, q, g), q_hi = __shfl_sync(0xffffffffu, q, g + 8);
         if (g < np) dr_lo = __ldg(P.draw + q_lo);
         if (g + 8 < np) dr_hi = __ldg(P.draw + q_hi);
 
@@ -661,21 +676,37 @@ __global__ void __launch_bounds__(256) rays_bwd_kernel(const RayBwdParams P) {
 int check_scene(const MneSceneDesc* sc, const char* who, bool need_grads);
 int sm_count();
 
-template <bool TWO, int MODE, bool RAY, bool PARAM, int NW = kBwdWarps>
+template <bool TWO, int MODE, bool RAY, bool PARAM, int NW = kBwdWarps, bool SAVED = false>
 static int launch_points_bwd(const PtsBwdParams& P, cudaStream_t stream) {
-    const size_t smem = bwd2_smem_bytes<TWO, RAY, NW>();
+    const size_t smem = bwd2_smem_bytes<TWO, RAY, NW, SAVED>();
     static bool configured[64] = {};
     int dev = 0;
     MNE_CHECK_CUDA(cudaGetDevice(&dev));
     if (dev >= 64 || !configured[dev]) {
-        MNE_CHECK_CUDA(cudaFuncSetAttribute(points_bwd_kernel<TWO, MODE, RAY, PARAM, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        MNE_CHECK_CUDA(cudaFuncSetAttribute(points_bwd_kernel<TWO, MODE, RAY, PARAM, NW, SAVED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (dev < 64) configured[dev] = true;
     }
     const int64_t n_tiles = (P.n_pts + kTilePts - 1) / kTilePts;
     const int blocks = (int)max((int64_t)1, min((n_tiles + NW - 1) / NW, (int64_t)sm_count()));
-    points_bwd_kernel<TWO, MODE, RAY, PARAM, NW><<<blocks, NW * 32, smem, stream>>>(P);
+    points_bwd_kernel<TWO, MODE, RAY, PARAM, NW, SAVED><<<blocks, NW * 32, smem, stream>>>(P);
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
+}
+
+// with the forward's activations: no split weights in shared memory, so more warps fit (one grid: 12; two grids: 8..10,
+// and ray AND parameter gradients together fit too)
+template <int MODE>
+static int dispatch_points_bwd_saved(const PtsBwdParams& P, bool ray, bool param, cudaStream_t st) {
+    if constexpr (MODE != 2) {                                // (the hash grid has one table)
+        if (P.sc.two_grid) {
+            if (ray && param) return launch_points_bwd<true, MODE, true, true, 8, true>(P, st);
+            if (ray) return launch_points_bwd<true, MODE, true, false, 9, true>(P, st);
+            return launch_points_bwd<true, MODE, false, true, 10, true>(P, st);
+        }
+    }
+    if (ray && param) return launch_points_bwd<false, MODE, true, true, kSavedWarps, true>(P, st);
+    if (ray) return launch_points_bwd<false, MODE, true, false, kSavedWarps, true>(P, st);
+    return launch_points_bwd<false, MODE, false, true, kSavedWarps, true>(P, st);
 }
 
 template <int MODE>
@@ -691,12 +722,14 @@ static int dispatch_points_bwd(const PtsBwdParams& P, bool ray, bool param, cuda
     return launch_points_bwd<false, MODE, false, true>(P, st);
 }
 
+bool scene_is_vectorizable(const MneSceneDesc* sc) { return planes_vectorizable(*sc); }
+
 // v2 backward
 int render_backward_v2(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples,
                        const float* rays_o, const float* rays_d, const float* z_vals, const float* raw,
                        const float* target_rgb, const float* target_d, const double* acc, const float* loss_grads,
                        const float* g_rgb, const float* g_depth, const float* g_raw, void* scratch, float* g_rays_o,
-                       float* g_rays_d, bool param_grad, cudaStream_t st) {
+                       float* g_rays_d, bool param_grad, const float* act, cudaStream_t st) {
     RayBwdParams R{};
     R.rc = *rcfg; R.n_rays = n_rays; R.n_samples = n_samples; R.z_vals = z_vals; R.raw = raw; R.target_rgb = target_rgb;
     R.target_d = target_d; R.acc = acc; R.loss_grads = loss_grads; R.g_rgb = g_rgb; R.g_depth = g_depth; R.g_raw = g_raw;
@@ -712,14 +745,15 @@ int render_backward_v2(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int3
     PtsBwdParams P{};
     P.sc = *scene; P.n_pts = (int64_t)n_rays * n_samples; P.n_samples = n_samples;
     P.rays_o = rays_o; P.rays_d = rays_d; P.z_vals = z_vals; P.draw = reinterpret_cast<const float4*>(scratch);
-    P.g_rays_o = g_rays_o; P.g_rays_d = g_rays_d; P.list = R.list; P.n_active = R.n_active;
+    P.g_rays_o = g_rays_o; P.g_rays_d = g_rays_d; P.list = R.list; P.n_active = R.n_active; P.act = act;
     const bool ray = g_rays_o != nullptr;
     if (scene->encoder == 1) {
+        if (act) return dispatch_points_bwd_saved<2>(P, ray, param_grad, st);
         if (ray && param_grad) return launch_points_bwd<false, 2, true, true>(P, st);
         if (ray) return launch_points_bwd<false, 2, true, false>(P, st);
         return launch_points_bwd<false, 2, false, true>(P, st);
     }
-    if (planes_vectorizable(*scene)) return dispatch_points_bwd<1>(P, ray, param_grad, st);
+    if (planes_vectorizable(*scene)) return act ? dispatch_points_bwd_saved<1>(P, ray, param_grad, st) : dispatch_points_bwd<1>(P, ray, param_grad, st);
     MNE_CHECK_ARG(!scene->dirty, "mne_render_backward: MneSceneDesc.dirty needs channels-last planes or the hash grid");
     return dispatch_points_bwd<0>(P, ray, param_grad, st);
 }

@@ -23,6 +23,7 @@ struct PtsFwdParams {
     float* raw;               // [M,4]
     float* geo;               // [M,15] or NULL
     float* feat;              // [M,64] or NULL
+    float* act;               // [M,80] hidden activations kept for the backward (tile16.cuh: store_act), or NULL
 };
 
 // MODE: 0 = planes through strides, 1 = channels-last planes (vector gather), 2 = hash grid
@@ -108,6 +109,7 @@ __global__ void __launch_bounds__(pts_warps<TWO>() * 32, 1) points_fwd_kernel(co
         // ---- decoder
         float h1[4][4], o16[2][4], hc[4][4], rgb[4];
         decoder_forward_mma<TWO>(W4, X, CFt, lane, h1, o16, hc, rgb);
+        if (P.act) store_act(P.act, pt0 + g, pt0 + g + 8, g < np, g + 8 < np, t, h1, o16, hc);
         // rows g, g+8: rgb columns 0,1 on t = 0, column 2 on t = 1; sdf = column 15 of o16 = o16[1][1|3] on t = 3
         const int quad = lane & ~3;
         const float b_lo = __shfl_sync(0xffffffffu, rgb[0], quad | 1), b_hi = __shfl_sync(0xffffffffu, rgb[2], quad | 1);
@@ -254,7 +256,8 @@ static int dispatch_points_fwd(const PtsFwdParams& P, cudaStream_t stream) {
 extern "C" int mne_render_forward(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples,
                                   const float* rays_o, const float* rays_d, const float* z_vals, const float* target_rgb,
                                   const float* target_d, float* raw, float* weights, float* rgb, float* depth, float* disp,
-                                  float* acc_map, float* depth_var, int32_t* inds, double* acc, mne_stream_t stream) {
+                                  float* acc_map, float* depth_var, int32_t* inds, double* acc, float* act,
+                                  mne_stream_t stream) {
     using namespace mne;
     if (impl_version() == 1)
         return render_forward_v1(scene, rcfg, n_rays, n_samples, rays_o, rays_d, z_vals, target_rgb, target_d, raw, weights,
@@ -268,7 +271,8 @@ extern "C" int mne_render_forward(const MneSceneDesc* scene, const MneRenderCfg*
     MNE_CHECK_ARG((int64_t)n_rays * n_samples < (int64_t)1 << 31, "mne_render_forward: n_rays * n_samples must be < 2^31");
     PtsFwdParams P{};
     P.sc = *scene; P.n_pts = (int64_t)n_rays * n_samples; P.n_samples = n_samples;
-    P.rays_o = rays_o; P.rays_d = rays_d; P.z_vals = z_vals; P.raw = raw;
+    P.rays_o = rays_o; P.rays_d = rays_d; P.z_vals = z_vals; P.raw = raw; P.act = act;
+    MNE_CHECK_ARG(((uintptr_t)act & 7) == 0, "mne_render_forward: act must be 8-byte aligned");
     if (int e = dispatch_points_fwd(P, (cudaStream_t)stream)) return e;
     RayFwdParams R{};
     R.rc = *rcfg; R.n_rays = n_rays; R.n_samples = n_samples; R.z_vals = z_vals; R.raw = raw;

@@ -409,6 +409,46 @@ __device__ __forceinline__ float oneblob16_sparse_grad(float x, const float* gb)
 }
 
 // ---------------------------------------------------------------------------------------------
+// Activations kept from the forward for the backward (optional): per sample 80 floats = h1[32] | o16[16] | hc[32], in
+// the accumulator-fragment order of the tile (rows g / g+8, columns n*8 + 2t, +1), so both kernels move them as 64-bit
+// words.  With them the backward needs no forward recompute (and no split weights in shared memory).
+// ---------------------------------------------------------------------------------------------
+constexpr int kActFloats = 80;
+__device__ __forceinline__ void store_act(float* __restrict__ act, int64_t s_lo, int64_t s_hi, bool ok_lo, bool ok_hi, int t,
+                                          const float (&h1)[4][4], const float (&o16)[2][4], const float (&hc)[4][4]) {
+    float2* lo = reinterpret_cast<float2*>(act + s_lo * kActFloats) + t;
+    float2* hi = reinterpret_cast<float2*>(act + s_hi * kActFloats) + t;
+#pragma unroll
+    for (int n = 0; n < 4; ++n) {
+        if (ok_lo) { lo[n * 4] = make_float2(h1[n][0], h1[n][1]); lo[24 + n * 4] = make_float2(hc[n][0], hc[n][1]); }
+        if (ok_hi) { hi[n * 4] = make_float2(h1[n][2], h1[n][3]); hi[24 + n * 4] = make_float2(hc[n][2], hc[n][3]); }
+    }
+#pragma unroll
+    for (int n = 0; n < 2; ++n) {
+        if (ok_lo) lo[16 + n * 4] = make_float2(o16[n][0], o16[n][1]);
+        if (ok_hi) hi[16 + n * 4] = make_float2(o16[n][2], o16[n][3]);
+    }
+}
+__device__ __forceinline__ void load_act(const float* __restrict__ act, int64_t s_lo, int64_t s_hi, bool ok_lo, bool ok_hi, int t,
+                                         float (&h1)[4][4], float (&o16)[2][4], float (&hc)[4][4]) {
+    const float2* lo = reinterpret_cast<const float2*>(act + s_lo * kActFloats) + t;
+    const float2* hi = reinterpret_cast<const float2*>(act + s_hi * kActFloats) + t;
+    const float2 z = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int n = 0; n < 4; ++n) {
+        const float2 a = ok_lo ? __ldg(lo + n * 4) : z, b = ok_hi ? __ldg(hi + n * 4) : z;
+        const float2 c = ok_lo ? __ldg(lo + 24 + n * 4) : z, d = ok_hi ? __ldg(hi + 24 + n * 4) : z;
+        h1[n][0] = a.x; h1[n][1] = a.y; h1[n][2] = b.x; h1[n][3] = b.y;
+        hc[n][0] = c.x; hc[n][1] = c.y; hc[n][2] = d.x; hc[n][3] = d.y;
+    }
+#pragma unroll
+    for (int n = 0; n < 2; ++n) {
+        const float2 a = ok_lo ? __ldg(lo + 16 + n * 4) : z, b = ok_hi ? __ldg(hi + 16 + n * 4) : z;
+        o16[n][0] = a.x; o16[n][1] = a.y; o16[n][2] = b.x; o16[n][3] = b.y;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // decoder forward on the tensor pipe for one 16-point tile.
 // X: tile [16][kXStride] (feat | blob); CFt: colour features [16][kCStride] (two grids).
 // Outputs (accumulator fragments, rows g / g+8, columns 2t, 2t+1 of each 8-wide block):

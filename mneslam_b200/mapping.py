@@ -160,6 +160,7 @@ class FusedMapper:
         self.loss_grads = torch.tensor(loss_weight_vector(self.cfg, is_co_sdf), dtype=torch.float32, device=self.dev)
         self.loss_weights = self.loss_grads.clone()
         self._scratch = None
+        self._act = None              # the decoders' hidden activations, forward -> backward (80 floats per sample)
         self.last_losses = None
         self.global_rays_override = None
 
@@ -202,15 +203,17 @@ class FusedMapper:
         td = target_d.reshape(-1)
         acc = ops.new_acc(dev)
         z_vals = ops.sample_rays(scfg, rcfg, n, s, td, noise if perturb else None, acc, dev)
+        if self._act is None or self._act.numel() < n * s * _lib.ACT_FLOATS:
+            self._act = torch.empty(n * s * _lib.ACT_FLOATS, dtype=torch.float32, device=dev)
         out = ops.render_forward(self._scene(False), rcfg, rays_o, rays_d, z_vals, target_rgb, td, acc,
-                                 want_aux=False)
+                                 want_aux=False, act=self._act)
         if self.world_size > 1:
             torch.distributed.all_reduce(acc, group=self.group)
         losses = ops.loss_finalize(rcfg, s, acc)
         if self._scratch is None or self._scratch_for != (n, s):
             self._scratch, self._scratch_for = ops.backward_scratch(n, s, dev), (n, s)
         ops.render_backward(self._scene(True), rcfg, rays_o, rays_d, z_vals, out['raw'], target_rgb, td, acc,
-                            loss_grads=self.loss_grads, scratch=self._scratch)
+                            loss_grads=self.loss_grads, scratch=self._scratch, act=self._act)
         self.last_render = out
         return losses
 

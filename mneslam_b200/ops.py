@@ -190,7 +190,9 @@ def sample_rays(sample_cfg, render_cfg, n_rays, n_samples, target_d, noise, acc,
 
 
 def render_forward(scene, render_cfg, rays_o, rays_d, z_vals, target_rgb=None, target_d=None, acc=None,
-                   want_weights=False, want_aux=True):
+                   want_weights=False, want_aux=True, act=None):
+    """``act``: True = allocate, or a float32 buffer of n * s * ACT_FLOATS elements: the decoders' hidden activations are
+    kept there for ``render_backward`` (returned as ``out['act']``)."""
     n, s = z_vals.shape
     dev = z_vals.device
     ro, rd = _f32(rays_o, 'rays_o'), _f32(rays_d, 'rays_d')
@@ -204,10 +206,16 @@ def render_forward(scene, render_cfg, rays_o, rays_d, z_vals, target_rgb=None, t
         out['inds'] = torch.empty(n, dtype=torch.int32, device=dev)
     if want_weights:
         out['weights'] = torch.empty(n, s, dtype=torch.float32, device=dev)
+    if act is True:
+        act = torch.empty(n * s * _lib.ACT_FLOATS, dtype=torch.float32, device=dev)
+    if act is not None:
+        if act.dtype != torch.float32 or act.numel() < n * s * _lib.ACT_FLOATS or not act.is_contiguous():
+            raise TypeError('act must be a contiguous float32 buffer of at least n_rays * n_samples * %d elements' % _lib.ACT_FLOATS)
+        out['act'] = act
     _lib.check(_lib.lib().mne_render_forward(
         C.byref(scene), C.byref(render_cfg), n, s, _ptr(ro), _ptr(rd), _ptr(z_vals), _ptr(trgb), _ptr(td),
         _ptr(out['raw']), _ptr(out.get('weights')), _ptr(out['rgb']), _ptr(out['depth']), _ptr(out.get('disp_map')),
-        _ptr(out.get('acc_map')), _ptr(out.get('depth_var')), _ptr(out.get('inds')), _ptr(acc), _stream()),
+        _ptr(out.get('acc_map')), _ptr(out.get('depth_var')), _ptr(out.get('inds')), _ptr(acc), _ptr(act), _stream()),
         'mne_render_forward')
     return out
 
@@ -232,7 +240,7 @@ def backward_active_count(scratch, n_rays, n_samples):
 
 
 def render_backward(scene, render_cfg, rays_o, rays_d, z_vals, raw, target_rgb=None, target_d=None, acc=None,
-                    loss_grads=None, g_rgb=None, g_depth=None, g_raw=None, want_ray_grads=False, scratch=None):
+                    loss_grads=None, g_rgb=None, g_depth=None, g_raw=None, want_ray_grads=False, scratch=None, act=None):
     n, s = z_vals.shape
     dev = z_vals.device
     ro, rd = _f32(rays_o, 'rays_o'), _f32(rays_d, 'rays_d')
@@ -247,7 +255,7 @@ def render_backward(scene, render_cfg, rays_o, rays_d, z_vals, raw, target_rgb=N
         g_d = torch.empty(n, 3, dtype=torch.float32, device=dev)
     _lib.check(_lib.lib().mne_render_backward(
         C.byref(scene), C.byref(render_cfg), n, s, _ptr(ro), _ptr(rd), _ptr(z_vals), _ptr(raw), _ptr(trgb), _ptr(td),
-        _ptr(acc), _ptr(lg), _ptr(grgb), _ptr(gdep), _ptr(graw), _ptr(scratch), _ptr(g_o), _ptr(g_d), _stream()),
+        _ptr(acc), _ptr(lg), _ptr(grgb), _ptr(gdep), _ptr(graw), _ptr(scratch), _ptr(g_o), _ptr(g_d), _ptr(act), _stream()),
         'mne_render_backward')
     return g_o, g_d
 

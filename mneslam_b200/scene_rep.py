@@ -59,8 +59,10 @@ class _Render(torch.autograd.Function):
         z_vals = ops.sample_rays(scfg, rcfg, n, n_samples, td, noise if perturb else None, acc, dev)
         scene = ops.make_scene(planes, weights, model.bound, model.bounding_box, cfg['pos']['n_bins'],
                                hash_meta=model.hash_meta)
+        # what autograd would save: the decoders' hidden activations (80 floats per sample), only when a backward can follow
+        want_act = any(ctx.needs_input_grad)
         out = ops.render_forward(scene, rcfg, rays_o, rays_d, z_vals, target_rgb if with_losses else None,
-                                 td if with_losses else None, acc)
+                                 td if with_losses else None, acc, act=True if want_act else None)
         if with_losses:
             if model.acc_allreduce is not None:
                 model.acc_allreduce(acc)
@@ -69,7 +71,7 @@ class _Render(torch.autograd.Function):
             losses = torch.zeros(len(LOSS_KEYS), device=dev)
         ctx.model, ctx.rcfg, ctx.with_losses, ctx.n_planes = model, rcfg, with_losses, n_planes
         ctx.save_for_backward(rays_o, rays_d, z_vals, out['raw'], target_rgb if with_losses else None,
-                              td if with_losses else None, acc, *params)
+                              td if with_losses else None, acc, out.get('act'), *params)
         ctx.set_materialize_grads(False)
         nondiff = (z_vals, out['disp_map'], out['acc_map'], out['depth_var'], out['inds'])
         ctx.mark_non_differentiable(*nondiff)
@@ -77,8 +79,8 @@ class _Render(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g_rgb, g_depth, g_raw, g_losses, *unused):
-        rays_o, rays_d, z_vals, raw, target_rgb, td, acc = ctx.saved_tensors[:7]
-        params = ctx.saved_tensors[7:]
+        rays_o, rays_d, z_vals, raw, target_rgb, td, acc, act = ctx.saved_tensors[:8]
+        params = ctx.saved_tensors[8:]
         model, n_planes = ctx.model, ctx.n_planes
         planes, weights = list(params[:n_planes]), list(params[n_planes:])
         need = ctx.needs_input_grad
@@ -91,7 +93,7 @@ class _Render(torch.autograd.Function):
         lg = g_losses if (ctx.with_losses and g_losses is not None) else None
         g_o, g_d = ops.render_backward(scene, ctx.rcfg, rays_o, rays_d, z_vals, raw, target_rgb, td, acc,
                                        loss_grads=lg, g_rgb=g_rgb, g_depth=g_depth, g_raw=g_raw,
-                                       want_ray_grads=want_rays)
+                                       want_ray_grads=want_rays, act=act)
         return (None, g_o if need[1] else None, g_d if need[2] else None, None, None, None, None,
                 *plane_grads, *weight_grads)
 

@@ -51,7 +51,7 @@ def _backward(model, cfg, batch, fwd, static):
         st = _lib.lib().mne_render_backward_static(*common, g_o.data_ptr(), g_d.data_ptr(), stream)
     else:
         scratch = ops.backward_scratch(n, s, dev)
-        st = _lib.lib().mne_render_backward(*common, scratch.data_ptr(), g_o.data_ptr(), g_d.data_ptr(), stream)
+        st = _lib.lib().mne_render_backward(*common, scratch.data_ptr(), g_o.data_ptr(), g_d.data_ptr(), None, stream)
     _lib.check(st, 'backward')
     torch.cuda.synchronize()
     return pg + wg + [g_o, g_d]

@@ -259,3 +259,48 @@ def test_raw2outputs_and_sdf2weights_entry_points():
         assert rel(got.cpu().numpy(), g[k]) < REL_TOL, k
     w2 = model.sdf2weights(raw[..., 3].contiguous(), z)
     assert torch.allclose(w, w2) and rel(w.sum(-1).cpu().numpy(), g['acc_map']) < REL_TOL
+
+
+@pytest.mark.parametrize('two_grid', [False, True])
+@pytest.mark.parametrize('mode', ['param', 'ray', 'both'])
+def test_backward_with_kept_activations_equals_recompute(two_grid, mode):
+    """mne_render_backward with the forward's activation buffer (no recompute) against the same call without it: same
+    gradients up to summation order, for parameter gradients, ray gradients and both (two grids with both run on the
+    tensor-pipe kernel only with the buffer, on the fp32 v1 kernel without it)."""
+    from mneslam_b200 import ops
+    cfg = configs.small_test_config(one_grid=not two_grid, n_samples_d=13, n_range_d=7)
+    cfg['is_co_sdf'] = two_grid
+    bound = J.enlarged_bound(cfg)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    planes = J.init_planes(cfg, bound, seed=9, std=0.5)
+    weights = J.init_weights(cfg, seed=9)
+    model = build_model(cfg, bb, planes, weights, as_params=False)
+    n, s = 333, synthetic.n_samples_total(cfg)
+    b = {k: v.cuda() for k, v in synthetic.make_ray_batch(cfg, n, seed=21, zero_depth_frac=0.1, depth_range=(0.3, 2.5)).items()}
+    noise = synthetic.make_noise(n, s, 21).cuda()
+    fp, ws = flat_planes(model), model.decoder.weight_list()
+    rcfg = ops.make_render_cfg(cfg, norm_rays=n)
+    tables = ops.SampleTables.get(cfg, 'cuda', True)
+    td = b['target_d'].reshape(-1)
+    acc = ops.new_acc('cuda')
+    z = ops.sample_rays(ops.make_sample_cfg(tables, True), rcfg, n, s, td, noise, acc, 'cuda')
+    sc = ops.make_scene(fp, [w.detach() for w in ws], model.bound, model.bounding_box)
+    out = ops.render_forward(sc, rcfg, b['rays_o'], b['rays_d'], z, b['target_rgb'], td, acc, act=True)
+    assert out['act'].numel() == n * s * 80
+    lg = torch.tensor([1.0, 0.5, 2.0, 3.0, 2.0, 4.0, 1.5, 0.0], device='cuda')
+    want_p, want_r = mode in ('param', 'both'), mode in ('ray', 'both')
+    res = []
+    for act in (out['act'], None):
+        pg = [torch.zeros_like(p) for p in fp] if want_p else None
+        wg = [torch.zeros_like(w) for w in ws] if want_p else None
+        scb = ops.make_scene(fp, [w.detach() for w in ws], model.bound, model.bounding_box, plane_grads=pg, weight_grads=wg)
+        g_o, g_d = ops.render_backward(scb, rcfg, b['rays_o'], b['rays_d'], z, out['raw'], b['target_rgb'], td, acc,
+                                       loss_grads=lg, want_ray_grads=want_r, act=act)
+        res.append(((pg or []) + (wg or []) + ([g_o, g_d] if want_r else [])))
+    torch.cuda.synchronize()
+    for a, c in zip(*res):
+        a, c = a.double(), c.double()
+        assert float(a.abs().max()) > 0
+        # same arithmetic, different accumulation order (and v1's fp32 contraction for two grids with both gradient kinds)
+        tol = 2e-3 if (two_grid and mode == 'both') else 2e-5
+        assert float((a - c).norm() / c.norm()) < tol

@@ -293,3 +293,54 @@ class DeviceKeyframeRays:
         rays_d = torch.sum(rays7[:, None, 0:3] * R, -1)
         rays_o = self.poses[kf_ids, :3, 3]
         return rays_o.contiguous(), rays_d.contiguous(), rays7[:, 3:6].contiguous(), rays7[:, 6:7].contiguous()
+
+
+class HostFedMapper:
+    """Mapping iterations fed from HOST memory as ONE CUDA-graph launch each: the ray batch the caller hands over (the
+    keyframe database lives on the host in the reference, model/keyframe.py:91-103) is copied into a pinned staging buffer,
+    and the graph holds the H2D copies, the on-device ray assembly, the whole iteration (sample, forward, losses,
+    backward, optimiser) and the D2H copy of the loss.  ``step`` returns the loss as a Python float, i.e. it includes the
+    read-back the reference loop does when it logs the loss."""
+
+    def __init__(self, mapper, db, n_rays):
+        self.mapper, self.db, self.n = mapper, db, n_rays
+        dev = mapper.dev
+        self.h_rays = torch.empty(n_rays, 7, dtype=torch.float32).pin_memory()
+        self.h_ids = torch.empty(n_rays, dtype=torch.int64).pin_memory()
+        self.h_loss = torch.zeros(1, dtype=torch.float32).pin_memory()
+        self.d_rays = torch.empty(n_rays, 7, dtype=torch.float32, device=dev)
+        self.d_ids = torch.empty(n_rays, dtype=torch.int64, device=dev)
+        self.h_ids.zero_(); self.h_rays.zero_(); self.h_rays[:, 2] = -1.0
+        self.graph = None
+        self.stream = torch.cuda.Stream(device=dev)
+
+    def _iteration(self):
+        self.d_rays.copy_(self.h_rays, non_blocking=True)
+        self.d_ids.copy_(self.h_ids, non_blocking=True)
+        ro, rd, rgb, d = self.db.assemble(self.d_rays, self.d_ids)
+        losses = self.mapper.step(ro, rd, rgb, d)
+        self.h_loss.copy_(self.mapper.total_loss(losses).reshape(1), non_blocking=True)
+
+    def capture(self, rays7, kf_ids):
+        """Warm up on a real batch (kernel attributes, workspaces; these are real optimiser steps) and capture the graph."""
+        self.h_rays.copy_(rays7); self.h_ids.copy_(kf_ids)
+        self.stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self.stream):
+            for _ in range(2):
+                self._iteration()
+        self.stream.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph, stream=self.stream):
+            self._iteration()
+        return self
+
+    def step(self, rays7, kf_ids):
+        """rays7 [n,7] (camera-frame direction, rgb, depth) and kf_ids [n] int64: HOST tensors (any memory)."""
+        if self.graph is None:
+            self.capture(rays7, kf_ids)
+        self.h_rays.copy_(rays7)
+        self.h_ids.copy_(kf_ids)
+        with torch.cuda.stream(self.stream):        # replay() launches on the CURRENT stream
+            self.graph.replay()
+        self.stream.synchronize()
+        return float(self.h_loss[0])

@@ -46,6 +46,7 @@ def parse():
     ap.add_argument('--workload', default='room0', choices=['room0', 'scannet_hash'],
                     help='room0: BASELINE.json configs[1] (the default, the judged line); scannet_hash: configs[3] -- ScanNet scene0000 bound '
                          'and sampling (117 samples per ray) on the 16-level hash grid; use with --rays = 65536 / GPUs and --value-only')
+    ap.add_argument('--mark-dirty', action='store_true', help='multi-GPU: flag dirty texels in the backward kernel instead of deriving the flags from the gradient buffer')
     ap.add_argument('--value-only', action='store_true', help='print the graph-replayed step time only (side experiments)')
     return ap.parse_args()
 
@@ -265,7 +266,7 @@ def run_ours(args):
     model = JointEncoding(cfg, bb).to(dev)
     model.train()
     # the map is replicated: same seed on every rank gives identical planes and decoder
-    mapper = FusedMapper(model, world_size=world)
+    mapper = FusedMapper(model, world_size=world, mark_dirty=args.mark_dirty)
     rays_cpu, poses_cpu = synthetic.make_keyframe_db(cfg, n_kf=N_KF, seed=0)
     db = DeviceKeyframeRays(rays_cpu.to(dev), poses_cpu.to(dev))
     gen = torch.Generator(device=dev)

@@ -261,17 +261,28 @@ struct DirtyPush {
 __global__ void __launch_bounds__(256) grad_dirty_kernel(const float4* __restrict__ g4, const __grid_constant__ DirtyPush d) {
     const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 3;
     const int sub = threadIdx.x & 7;
-    for (int64_t tx = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3; tx < d.n32; tx += stride) {
-        const float4 v = g4[tx * 8 + sub];
-        unsigned nz = (v.x != 0.0f || v.y != 0.0f || v.z != 0.0f || v.w != 0.0f) ? 1u : 0u;
-        nz |= __shfl_xor_sync(0xffffffffu, nz, 1);
-        nz |= __shfl_xor_sync(0xffffffffu, nz, 2);
-        nz |= __shfl_xor_sync(0xffffffffu, nz, 4);
-        if (sub == 0) {
-            const uint32_t c = (uint32_t)(tx >> d.chunk_tx_log2);
-            const uint32_t owner = c % (uint32_t)d.world;
-            const int64_t lt = ((int64_t)(c / (uint32_t)d.world) << d.chunk_tx_log2) + (tx & ((1 << d.chunk_tx_log2) - 1));
-            d.dst[owner][(int64_t)d.rank * d.local32 + lt] = (uint8_t)nz;
+    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+    // four texels in flight per thread: the pass is a pure read of the gradient buffer, bound by loads in flight
+    for (int64_t tx0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3; tx0 < d.n32; tx0 += 4 * stride) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t tx = tx0 + u * stride;
+            v[u] = tx < d.n32 ? g4[tx * 8 + sub] : zero;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t tx = tx0 + u * stride;
+            unsigned nz = (v[u].x != 0.0f || v[u].y != 0.0f || v[u].z != 0.0f || v[u].w != 0.0f) ? 1u : 0u;
+            nz |= __shfl_xor_sync(0xffffffffu, nz, 1);
+            nz |= __shfl_xor_sync(0xffffffffu, nz, 2);
+            nz |= __shfl_xor_sync(0xffffffffu, nz, 4);
+            if (sub == 0 && tx < d.n32) {
+                const uint32_t c = (uint32_t)(tx >> d.chunk_tx_log2);
+                const uint32_t owner = c % (uint32_t)d.world;
+                const int64_t lt = ((int64_t)(c / (uint32_t)d.world) << d.chunk_tx_log2) + (tx & ((1 << d.chunk_tx_log2) - 1));
+                d.dst[owner][(int64_t)d.rank * d.local32 + lt] = (uint8_t)nz;
+            }
         }
     }
 }

@@ -126,7 +126,9 @@ typedef struct MneRenderCfg {
 int mne_version(void);
 const char* mne_last_error(void);
 /* Process-wide switches.  "impl": 2 (default) = tensor-pipe kernels (16-point tiles, mma TF32 with split
- * operands), 1 = the first-generation fp32 CUDA-core kernels, kept as an on-device cross-check. */
+ * operands), 1 = the first-generation fp32 CUDA-core kernels, kept as an on-device cross-check.
+ * "adam_spare_sms" (default 0, at most 64): SMs the persistent optimiser grids leave free, so that small kernels on
+ * another stream can run under them. */
 int mne_set_option(const char* key, int value);
 
 /* ---- sampling: replaces the z_vals block of JointEncoding.render_rays (model/scene_rep.py:361-381) plus

@@ -83,6 +83,8 @@ int check_scene(const MneSceneDesc* sc, const char* who, bool) {
 
 static int g_impl = 2;
 int impl_version() { return g_impl; }
+static int g_adam_spare_sms = 0;
+int adam_spare_sms() { return g_adam_spare_sms; }
 
 }  // namespace mne
 
@@ -92,6 +94,13 @@ extern "C" int mne_set_option(const char* key, int value) {
     if (strcmp(key, "impl") == 0) {
         MNE_CHECK_ARG(value == 1 || value == 2, "mne_set_option: impl must be 1 (fp32 CUDA-core kernels) or 2 (tensor-pipe kernels)");
         g_impl = value;
+        return 0;
+    }
+    if (strcmp(key, "adam_spare_sms") == 0) {
+        // the optimiser kernels are persistent grids that fill every SM; leaving a few SMs out lets small kernels of another
+        // stream (the next iteration's ray assembly and sampling, mapping.PipelinedMapper) run under them
+        MNE_CHECK_ARG(value >= 0 && value <= 64, "mne_set_option: adam_spare_sms must be in [0, 64]");
+        g_adam_spare_sms = value;
         return 0;
     }
     set_error("mne_set_option: unknown option '%s'", key);

@@ -4,6 +4,7 @@
 //   g += wd * p;  m = lerp(m, g, 1 - b1);  v = b2 * v + (1 - b2) * g * g;
 //   p += -(lr / (1 - b1^t)) * (m / (sqrt(v) / sqrt(1 - b2^t) + eps))
 // Pure streaming: 16 B/param read (p, g, m, v) + 16 B/param written (p, m, v, g = 0).
+#include <algorithm>
 #include "common.cuh"
 
 namespace mne {
@@ -147,6 +148,8 @@ __global__ void __launch_bounds__(256, 4) adam_segments_kernel(const __grid_cons
 __global__ void tick_kernel(int64_t* step) { if (threadIdx.x == 0 && blockIdx.x == 0) *step += 1; }
 
 int sm_count();
+int adam_spare_sms();
+static int adam_sms() { return std::max(1, sm_count() - adam_spare_sms()); }
 
 }  // namespace mne
 
@@ -204,7 +207,7 @@ extern "C" int mne_adam_step_segments(float* param, float* grad, float* exp_avg,
     s.beta1 = beta1; s.beta2 = beta2; s.step_dev = step_dev; s.step_host = step_host; s.zero_grad = zero_grad;
     s.touched = touched;
     int64_t blocks = ((prev >> 2) + 255) / 256;
-    const int64_t cap = (int64_t)sm_count() * resident_ctas(adam_segments_kernel, 256);
+    const int64_t cap = (int64_t)adam_sms() * resident_ctas(adam_segments_kernel, 256);
     if (blocks > cap) blocks = cap;
     adam_segments_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
     MNE_CHECK_CUDA(cudaGetLastError());
@@ -488,7 +491,7 @@ extern "C" int mne_adam_step_peers(int32_t world_size, int32_t rank, float* cons
     s.use_dirty = dirty != nullptr;
     s.dirty = dirty;
     int64_t blocks = (s.local4 + 255) / 256;
-    const int64_t cap = (int64_t)sm_count() * (s.use_dirty ? resident_ctas(adam_peers_sparse_kernel, 256) : resident_ctas(adam_peers_kernel, 256));
+    const int64_t cap = (int64_t)adam_sms() * (s.use_dirty ? resident_ctas(adam_peers_sparse_kernel, 256) : resident_ctas(adam_peers_kernel, 256));
     if (blocks > cap) blocks = cap;
     if (s.use_dirty) adam_peers_sparse_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
     else adam_peers_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);

@@ -191,21 +191,34 @@ class FusedMapper:
                               dirty=self.dirty_local if with_grads else None,
                               dirty_base=self.flat_grad if (with_grads and self.dirty_local is not None) else None)
 
-    def forward_backward(self, rays_o, rays_d, target_rgb, target_d, noise=None):
-        """sample -> forward -> finalize -> backward; gradients are ADDED to the flat buffer.  Returns losses[8]."""
+    def sample_stage(self, target_d, noise=None, z_out=None, acc_out=None):
+        """The part of an iteration that does not read the map: sample positions along the rays and the mask counts
+        (``render_rays``, model/scene_rep.py:361-381).  Returns (z_vals [N,S], acc[16]); with ``z_out`` / ``acc_out`` the
+        results are written into those buffers (``PipelinedMapper`` keeps them across graph replays)."""
         cfg, dev = self.cfg, self.dev
-        n = rays_o.shape[0]
+        n = target_d.shape[0]
         tables = ops.SampleTables.get(cfg, dev, True)
         s = tables[0].numel() + tables[1].numel()
         perturb = cfg['training']['perturb'] > 0.
         if perturb and noise is None:
             noise = torch.rand(n, s, device=dev)
-        # the means of the losses run over the GLOBAL batch; ragged shards set global_rays_override
         rcfg = ops.make_render_cfg(cfg, norm_rays=self.global_rays_override or n * self.world_size)
         scfg = ops.make_sample_cfg(tables, perturb)
+        acc = ops.new_acc(dev) if acc_out is None else acc_out.zero_()
+        z_vals = ops.sample_rays(scfg, rcfg, n, s, target_d.reshape(-1), noise if perturb else None, acc, dev, out=z_out)
+        return z_vals, acc
+
+    def forward_backward(self, rays_o, rays_d, target_rgb, target_d, noise=None, sampled=None):
+        """sample -> forward -> finalize -> backward; gradients are ADDED to the flat buffer.  Returns losses[8].
+        ``sampled``: the (z_vals, acc) of an earlier ``sample_stage`` call on the same ``target_d``."""
+        cfg, dev = self.cfg, self.dev
+        n = rays_o.shape[0]
+        tables = ops.SampleTables.get(cfg, dev, True)
+        s = tables[0].numel() + tables[1].numel()
+        # the means of the losses run over the GLOBAL batch; ragged shards set global_rays_override
+        rcfg = ops.make_render_cfg(cfg, norm_rays=self.global_rays_override or n * self.world_size)
         td = target_d.reshape(-1)
-        acc = ops.new_acc(dev)
-        z_vals = ops.sample_rays(scfg, rcfg, n, s, td, noise if perturb else None, acc, dev)
+        z_vals, acc = sampled if sampled is not None else self.sample_stage(target_d, noise)
         if self._act is None or self._act.numel() < n * s * _lib.ACT_FLOATS:
             self._act = torch.empty(n * s * _lib.ACT_FLOATS, dtype=torch.float32, device=dev)
         out = ops.render_forward(self._scene(False), rcfg, rays_o, rays_d, z_vals, target_rgb, td, acc,
@@ -259,9 +272,9 @@ class FusedMapper:
                                          self.betas[0], self.betas[1], eps, wd, self.step_dev.data_ptr(), 0, 1, st),
                        'mne_adam_step')
 
-    def step(self, rays_o, rays_d, target_rgb, target_d, noise=None):
+    def step(self, rays_o, rays_d, target_rgb, target_d, noise=None, sampled=None):
         """One mapping iteration.  Returns the eight losses (device tensor, order ``LOSS_KEYS``)."""
-        losses = self.forward_backward(rays_o, rays_d, target_rgb, target_d, noise)
+        losses = self.forward_backward(rays_o, rays_d, target_rgb, target_d, noise, sampled)
         self.optimizer_step()
         self.last_losses = losses
         return losses
@@ -345,3 +358,69 @@ class HostFedMapper:
             self.graph.replay()
         self.stream.synchronize()
         return float(self.h_loss[0])
+
+
+class PipelinedMapper:
+    """Mapping iterations on a device-resident keyframe database as ONE CUDA-graph launch each, software-pipelined: the
+    part of iteration t+1 that does not read the map -- drawing the ray batch, assembling the rays, sampling along them --
+    runs on a second stream while the optimiser of iteration t (a pure HBM stream) is in flight.  Every iteration does
+    exactly the work of ``FusedMapper.step(*db.sample(n))``; only the order across iterations changes."""
+
+    def __init__(self, mapper, db, n_rays, spare_sms=8):
+        self.mapper, self.db, self.n = mapper, db, n_rays
+        dev = mapper.dev
+        # the optimiser kernels are persistent grids over every SM: keep a few SMs out of them, or the side stream's
+        # small kernels only start when the optimiser has finished (library-wide option)
+        _lib.check(_lib.lib().mne_set_option(b'adam_spare_sms', int(spare_sms)), 'mne_set_option')
+        tables = ops.SampleTables.get(mapper.cfg, dev, True)
+        s = tables[0].numel() + tables[1].numel()
+        f32 = dict(dtype=torch.float32, device=dev)
+        # the batch in flight: written at the tail of one replay, read at the head of the next
+        self.ro, self.rd, self.rgb = torch.empty(n_rays, 3, **f32), torch.empty(n_rays, 3, **f32), torch.empty(n_rays, 3, **f32)
+        self.d = torch.empty(n_rays, 1, **f32)
+        self.z = torch.empty(n_rays, s, **f32)
+        self.acc = torch.zeros(_lib.ACC_SLOTS, dtype=torch.float64, device=dev)
+        self.losses = torch.zeros(_lib.N_LOSSES, **f32)
+        self.side = torch.cuda.Stream(device=dev)
+        self.graph = None
+
+    def _draw(self):
+        ro, rd, rgb, d = self.db.sample(self.n)
+        self.ro.copy_(ro); self.rd.copy_(rd); self.rgb.copy_(rgb); self.d.copy_(d)
+        self.mapper.sample_stage(self.d, z_out=self.z, acc_out=self.acc)
+
+    def _iteration(self):
+        m = self.mapper
+        main = torch.cuda.current_stream()
+        # acc is consumed (and added to) by the forward of this iteration: work on a private copy so that the side stream
+        # may refill the shared one
+        acc = self.acc.clone()
+        losses = m.forward_backward(self.ro, self.rd, self.rgb, self.d, sampled=(self.z, acc))
+        self.losses.copy_(losses)
+        self.side.wait_stream(main)                 # the batch has been consumed: refill it under the optimiser
+        with torch.cuda.stream(self.side):
+            self._draw()
+        m.optimizer_step()
+        main.wait_stream(self.side)
+        m.last_losses = self.losses
+
+    def capture(self):
+        stream = torch.cuda.Stream(device=self.mapper.dev)
+        stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(stream):
+            self._draw()                             # prologue: the first batch
+            for _ in range(2):
+                self._iteration()
+        stream.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph, stream=stream):
+            self._iteration()
+        self.stream = stream
+        return self
+
+    def step(self):
+        """One iteration; returns the eight losses (device tensor, valid once the launch stream has run)."""
+        if self.graph is None:
+            self.capture()
+        self.graph.replay()
+        return self.losses

@@ -178,8 +178,13 @@ def new_acc(device):
     return torch.zeros(ACC_SLOTS, dtype=torch.float64, device=device)
 
 
-def sample_rays(sample_cfg, render_cfg, n_rays, n_samples, target_d, noise, acc, device):
-    z = torch.empty(n_rays, n_samples, dtype=torch.float32, device=device)
+def sample_rays(sample_cfg, render_cfg, n_rays, n_samples, target_d, noise, acc, device, out=None):
+    if out is not None:
+        if tuple(out.shape) != (n_rays, n_samples) or out.dtype != torch.float32 or not out.is_contiguous():
+            raise TypeError('out must be a contiguous float32 [n_rays, n_samples] tensor')
+        z = out
+    else:
+        z = torch.empty(n_rays, n_samples, dtype=torch.float32, device=device)
     td = _f32(target_d, 'target_d')
     nz = _f32(noise, 'noise')
     if nz is not None and tuple(nz.shape) != (n_rays, n_samples):

@@ -346,3 +346,60 @@ def test_host_fed_graph_iteration_matches_the_eager_driver():
     for x, y in zip(pa, pb):
         assert float((x.double() - y.double()).norm() / (y.double().norm() + 1e-30)) < 5e-2     # see the trajectory test above
     assert min(float((x.double() - y.double()).norm() / (y.double().norm() + 1e-30)) for x, y in zip(pa, pb)) < 2e-5
+
+
+def test_pipelined_iterations_do_the_same_work():
+    """PipelinedMapper draws and samples batch t+1 on a second stream while the optimiser of iteration t runs.  Fed the same
+    batches it must give the same losses and parameters as FusedMapper.step; captured as a graph it must keep training."""
+    from mneslam_b200.mapping import DeviceKeyframeRays, FusedMapper, PipelinedMapper
+    cfg, bb, planes, weights = _small_model(seed=9)
+    cfg['cam'].update({'H': 40, 'W': 60, 'fx': 50.0, 'fy': 50.0, 'cx': 29.5, 'cy': 19.5})
+    cfg['training']['perturb'] = 0
+    rays, poses = synthetic.make_keyframe_db(cfg, n_kf=3, seed=2)
+
+    class FixedDb(DeviceKeyframeRays):
+        """Hands out a fixed sequence of batches."""
+        def __init__(self, rays, poses, n, count):
+            super().__init__(rays, poses)
+            g = torch.Generator().manual_seed(11)
+            self.queue = [torch.randint(0, self.n_kf * self.per_kf, (n,), generator=g).cuda() for _ in range(count)]
+            self.at = 0
+
+        def sample(self, n_rays, generator=None):
+            idx = self.queue[self.at]
+            self.at += 1
+            return self.assemble(self.rays.reshape(-1, 7)[idx], torch.div(idx, self.per_kf, rounding_mode='trunc'))
+
+    results = []
+    for pipelined in (True, False):
+        model = build_model(cfg, bb, planes, weights, as_params=False)
+        mapper = FusedMapper(model)
+        db = FixedDb(rays.cuda(), poses.cuda(), 256, 8)
+        losses = []
+        if pipelined:
+            pipe = PipelinedMapper(mapper, db, 256)
+            pipe._draw()
+            for _ in range(6):
+                pipe._iteration()                     # eager: the same stream choreography as the captured graph
+                torch.cuda.synchronize()
+                losses.append(float(mapper.total_loss(pipe.losses)))
+        else:
+            for _ in range(6):
+                losses.append(float(mapper.total_loss(mapper.step(*db.sample(256)))))
+        torch.cuda.synchronize()
+        results.append((losses, [p.detach().clone() for p in flat_planes(model)]))
+    (la, pa), (lb, pb) = results
+    assert la == pytest.approx(lb, rel=1e-4)
+    assert min(float((x.double() - y.double()).norm() / (y.double().norm() + 1e-30)) for x, y in zip(pa, pb)) < 2e-5
+
+    # graph mode on a random database: the loss keeps going down
+    model = build_model(cfg, bb, planes, weights, as_params=False)
+    mapper = FusedMapper(model)
+    pipe = PipelinedMapper(mapper, DeviceKeyframeRays(rays.cuda(), poses.cuda()), 256).capture()
+    hist = []
+    for i in range(60):
+        pipe.step()
+        if i % 10 == 9:
+            torch.cuda.synchronize()
+            hist.append(float(mapper.total_loss(pipe.losses)))
+    assert all(np.isfinite(hist)) and hist[-1] < hist[0], hist

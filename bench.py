@@ -274,8 +274,8 @@ def run_ours(args):
     gen = torch.Generator(device=dev)
     gen.manual_seed(1234 + rank)
 
-    # sample | points_fwd, rays_fwd | loss_finalize | rays_bwd, points_bwd | adam_tick, adam_segments
-    launches_per_step = 8
+    # assemble_rays | sample | points_fwd, rays_fwd | loss_finalize | rays_bwd, points_bwd | adam_tick, adam_segments
+    launches_per_step = 9
 
     def one_step():
         ro, rd, trgb, td = db.sample(n_rays)

@@ -131,6 +131,15 @@ const char* mne_last_error(void);
  * another stream can run under them. */
 int mne_set_option(const char* key, int value);
 
+/* ---- ray assembly: replaces the gather of KeyFrameDatabase.sample_global_rays (model/keyframe.py:91-103) and the
+ * assembly in mapping_optimize (mp_slam/mapper.py:135-153).  rays7: [*, 7] rows (camera-frame direction, rgb, depth);
+ * idx [n_rays] (or NULL = rows 0..n_rays-1): the rows to take; kf_ids [n_rays] (or NULL = idx / per_kf): the pose
+ * of each ray, -1 = the last one (the current frame); poses [n_kf, 4, 4] camera-to-world, row-major.  Writes
+ * rays_o / rays_d / target_rgb [n_rays, 3] and target_d [n_rays]. */
+int mne_assemble_rays(const float* rays7, const int64_t* idx, int64_t per_kf, const int64_t* kf_ids, const float* poses,
+                      int32_t n_kf, int32_t n_rays, float* rays_o, float* rays_d, float* target_rgb, float* target_d,
+                      mne_stream_t stream);
+
 /* ---- sampling: replaces the z_vals block of JointEncoding.render_rays (model/scene_rep.py:361-381) plus
  * the mask counts of get_masks (model/utils.py:117-145), sdf_losses (model/scene_rep.py:489-499) and
  * valid_depth_mask (:570).  target_d NULL = uniform sampling.  noise NULL = no perturbation.  acc may be

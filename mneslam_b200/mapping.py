@@ -300,13 +300,24 @@ class DeviceKeyframeRays:
         """Uniform sample over all stored rays (with replacement; the reference's ``random.sample`` draws
         without -- for 2048 of ~800k rays the two are statistically indistinguishable)."""
         idx = torch.randint(0, self.n_kf * self.per_kf, (n_rays,), device=self.rays.device, generator=generator)
-        return self.assemble(self.rays.reshape(-1, 7)[idx], torch.div(idx, self.per_kf, rounding_mode='trunc'))
+        return self._assemble(self.rays, idx, None, n_rays)
 
     def assemble(self, rays7, kf_ids):
-        R = self.poses[kf_ids, :3, :3]
-        rays_d = torch.sum(rays7[:, None, 0:3] * R, -1)
-        rays_o = self.poses[kf_ids, :3, 3]
-        return rays_o.contiguous(), rays_d.contiguous(), rays7[:, 3:6].contiguous(), rays7[:, 6:7].contiguous()
+        """rays7 [n,7] and the keyframe of each ray (-1 = the last pose) -> rays_o, rays_d, target_rgb [n,3], target_d [n,1]."""
+        return self._assemble(rays7, None, kf_ids, rays7.shape[0])
+
+    def _assemble(self, rays7, idx, kf_ids, n):
+        dev = self.rays.device
+        if rays7.dtype != torch.float32 or not rays7.is_contiguous() or self.poses.dtype != torch.float32 or not self.poses.is_contiguous():
+            raise TypeError('rays and poses must be contiguous float32 tensors')
+        if kf_ids is not None and (kf_ids.dtype != torch.int64 or not kf_ids.is_contiguous()):
+            kf_ids = kf_ids.to(torch.int64).contiguous()
+        ro, rd, rgb, d = (torch.empty(n, 3, dtype=torch.float32, device=dev), torch.empty(n, 3, dtype=torch.float32, device=dev),
+                          torch.empty(n, 3, dtype=torch.float32, device=dev), torch.empty(n, 1, dtype=torch.float32, device=dev))
+        _lib.check(_lib.lib().mne_assemble_rays(rays7.data_ptr(), ops._ptr(idx), self.per_kf, ops._ptr(kf_ids), self.poses.data_ptr(),
+                                                self.n_kf, n, ro.data_ptr(), rd.data_ptr(), rgb.data_ptr(), d.data_ptr(), ops._stream()),
+                   'mne_assemble_rays')
+        return ro, rd, rgb, d
 
 
 class HostFedMapper:

@@ -235,8 +235,10 @@ class FusedMapper:
 
     def optimizer_step(self):
         """Adam + zero_grad.  One GPU: one launch over the flat buffers (one per tensor when the parameters were not
-        adopted).  Several GPUs: reduce-scatter of the flat gradient, Adam on this rank's slice, all-gather of the
-        parameters (``mneslam_b200.distributed``)."""
+        adopted).  Several GPUs: flags of the non-zero gradient texels handed to their owners, barrier, ONE kernel over
+        NVLink peer memory (reduce the flagged gradients, Adam on the owned groups, parameters written back to every
+        rank), barrier -- or, without peer memory, NCCL reduce-scatter / Adam on the slice / all-gather
+        (``mneslam_b200.distributed``)."""
         lib = _lib.lib()
         st = ops._stream()
         _lib.check(lib.mne_adam_tick(self.step_dev.data_ptr(), st), 'mne_adam_tick')

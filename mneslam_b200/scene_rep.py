@@ -37,7 +37,8 @@ def get_rays(H, W, fx, fy, cx, cy, c2w, device):
 
 
 class _Render(torch.autograd.Function):
-    """sample -> fused forward (+ loss sums) ; backward = fused recompute-backward kernel."""
+    """sample -> fused forward (+ loss sums, hidden activations kept when a backward can follow) ; backward = fused backward
+    kernels over the samples with a non-zero loss gradient."""
 
     @staticmethod
     def forward(ctx, model, rays_o, rays_d, target_rgb, target_d, noise, with_losses, *params):

@@ -49,6 +49,9 @@ def test_argument_errors_are_reported_without_a_gpu():
     assert handle.mne_query_points(ctypes.byref(scene), 4, None, None, None, None, None) != 0
     assert b'n_bins' in handle.mne_last_error()
     assert handle.mne_backward_scratch_bytes(2048, 43) == 2048 * 43 * 20 + 16   # d_raw, active-sample list, its length
+    assert handle.mne_assemble_rays(None, None, 0, None, None, 3, 16, None, None, None, None, None) != 0
+    assert b'mne_assemble_rays' in handle.mne_last_error()
+    assert handle.mne_set_option(b'adam_spare_sms', 1000) != 0 and handle.mne_set_option(b'adam_spare_sms', 0) == 0
 
 
 def test_render_cfg_uses_float32_roundings():

@@ -140,6 +140,20 @@ int mne_assemble_rays(const float* rays7, const int64_t* idx, int64_t per_kf, co
                       int32_t n_kf, int32_t n_rays, float* rays_o, float* rays_d, float* target_rgb, float* target_d,
                       mne_stream_t stream);
 
+/* ---- camera pose: (rotation parameters, translation) -> rays, and ray gradients -> pose update.  rot_rep 0 = axis-angle
+ * [3] (at_to_transform_matrix), 1 = real-first quaternion [4], not assumed unit (qt_to_transform_matrix; reference
+ * optimization/utils.py:161-210).  mne_pose_rays: rays_o = t, rays_d = sum_k dirs_k R[:, k] (mp_slam/mapper.py:392-393).
+ * mne_pose_step replaces the autograd chain ray gradients -> c2w -> pose parameters and the optimizer.step() of
+ * get_pose_param_optim (mneslam_mp.py:577-584): reduces d loss / d rays over the rays, differentiates R analytically
+ * (forward-mode dual numbers on the expression that builds it), applies torch.optim.Adam's update (no weight decay) with
+ * one learning rate for the rotation and one for the translation.  exp_avg / exp_avg_sq [np + 3] (rotation first) and
+ * *step_dev start at zero; grad_out (optional, [np + 3]) receives the pose gradient. */
+int mne_pose_rays(int32_t rot_rep, const float* rot, const float* trans, const float* dirs_cam, int32_t n_rays,
+                  float* rays_o, float* rays_d, mne_stream_t stream);
+int mne_pose_step(int32_t rot_rep, float* rot, float* trans, const float* dirs_cam, const float* g_rays_o,
+                  const float* g_rays_d, int32_t n_rays, float* exp_avg, float* exp_avg_sq, int64_t* step_dev,
+                  float lr_rot, float lr_trans, float beta1, float beta2, float eps, float* grad_out, mne_stream_t stream);
+
 /* ---- sampling: replaces the z_vals block of JointEncoding.render_rays (model/scene_rep.py:361-381) plus
  * the mask counts of get_masks (model/utils.py:117-145), sdf_losses (model/scene_rep.py:489-499) and
  * valid_depth_mask (:570).  target_d NULL = uniform sampling.  noise NULL = no perturbation.  acc may be

@@ -9,6 +9,7 @@ is that loop with the map's gradients switched off, so the fused backward runs i
 """
 import torch
 
+from . import _lib, ops
 from . import pose as pose_lib
 from .mapping import loss_weight_vector
 
@@ -93,6 +94,76 @@ class PoseTracker:
         return loss.detach()
 
 
+class FusedTracker:
+    """``PoseTracker`` without autograd and without torch's optimiser: pose -> rays (``mne_pose_rays``), sample / forward /
+    losses / ray-gradient backward on the frozen map, then ``mne_pose_step`` (ray gradients -> pose gradient through the
+    parameterisation -> Adam on the 6 or 7 pose parameters).  Nine launches per iteration instead of about a hundred
+    element-wise torch kernels; same update (tested against ``PoseTracker``)."""
+
+    def __init__(self, model, c2w_init, rot_rep=None, lr_rot=1e-3, lr_trans=1e-3, is_co_sdf=None,
+                 betas=(0.9, 0.999), eps=1e-8):
+        ops.require_cuda()
+        self.model, self.cfg = model, model.config
+        self.rot_rep = rot_rep or self.cfg['training']['rot_rep']
+        dev = c2w_init.device
+        R = c2w_init[:3, :3]
+        rot = matrix_to_axis_angle(R) if self.rot_rep == 'axis_angle' else matrix_to_quaternion(R)
+        self.rot = rot.detach().to(torch.float32).contiguous().clone()          # [3] or [4]
+        self.trans = c2w_init[:3, 3].detach().to(torch.float32).contiguous().clone()
+        n_par = self.rot.numel() + 3
+        self.exp_avg = torch.zeros(n_par, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(n_par, dtype=torch.float32, device=dev)
+        self.step_dev = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.pose_grad = torch.zeros(n_par, dtype=torch.float32, device=dev)
+        self.lr_rot, self.lr_trans, self.betas, self.eps = lr_rot, lr_trans, betas, eps
+        w = loss_weight_vector(self.cfg, is_co_sdf)
+        self.loss_grads = torch.tensor(w, dtype=torch.float32, device=dev)
+        self.weights = self.loss_grads[:7].clone()
+        self._act = self._scratch = None
+        self._for = None
+
+    def c2w(self):
+        return pose_lib.transform_matrix(self.rot[None], self.trans[None], self.rot_rep)[0]
+
+    def step(self, dirs_cam, target_rgb, target_d, noise=None):
+        """One pose iteration on the frozen map.  Returns the weighted loss (device scalar)."""
+        model, cfg = self.model, self.cfg
+        dev = self.rot.device
+        n = dirs_cam.shape[0]
+        lib, st = _lib.lib(), ops._stream()
+        rep = 0 if self.rot_rep == 'axis_angle' else 1
+        dirs = ops._f32(dirs_cam, 'dirs_cam')
+        rays_o = torch.empty(n, 3, dtype=torch.float32, device=dev)
+        rays_d = torch.empty(n, 3, dtype=torch.float32, device=dev)
+        _lib.check(lib.mne_pose_rays(rep, self.rot.data_ptr(), self.trans.data_ptr(), dirs.data_ptr(), n, rays_o.data_ptr(),
+                                     rays_d.data_ptr(), st), 'mne_pose_rays')
+        tables = ops.SampleTables.get(cfg, dev, True)
+        s = tables[0].numel() + tables[1].numel()
+        perturb = cfg['training']['perturb'] > 0.
+        if perturb and noise is None:
+            noise = torch.rand(n, s, device=dev)
+        rcfg = ops.make_render_cfg(cfg, norm_rays=n)
+        td = target_d.reshape(-1)
+        acc = ops.new_acc(dev)
+        z_vals = ops.sample_rays(ops.make_sample_cfg(tables, perturb), rcfg, n, s, td, noise if perturb else None, acc, dev)
+        if self._for != (n, s):
+            self._act = torch.empty(n * s * _lib.ACT_FLOATS, dtype=torch.float32, device=dev)
+            self._scratch = ops.backward_scratch(n, s, dev)
+            self._for = (n, s)
+        scene = ops.make_scene(model._flat_planes(), [w.detach() for w in model.decoder.weight_list()], model.bound,
+                               model.bounding_box, cfg['pos']['n_bins'], hash_meta=model.hash_meta)
+        out = ops.render_forward(scene, rcfg, rays_o, rays_d, z_vals, target_rgb, td, acc, want_aux=False, act=self._act)
+        losses = ops.loss_finalize(rcfg, s, acc)
+        g_o, g_d = ops.render_backward(scene, rcfg, rays_o, rays_d, z_vals, out['raw'], target_rgb, td, acc,
+                                       loss_grads=self.loss_grads, want_ray_grads=True, scratch=self._scratch, act=self._act)
+        _lib.check(lib.mne_pose_step(rep, self.rot.data_ptr(), self.trans.data_ptr(), dirs.data_ptr(), g_o.data_ptr(),
+                                     g_d.data_ptr(), n, self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(),
+                                     self.step_dev.data_ptr(), self.lr_rot, self.lr_trans, self.betas[0], self.betas[1],
+                                     self.eps, self.pose_grad.data_ptr(), st), 'mne_pose_step')
+        self.last_render = out
+        return (losses[:7] * self.weights).sum()
+
+
 class GraphedPoseTracker:
     """One pose iteration (pose -> rays -> fused forward -> losses -> ray-gradient backward -> Adam) captured in a
     CUDA graph for a fixed frame: the per-frame optimisation is ``iters`` replays with no Python in between."""
@@ -108,7 +179,8 @@ class GraphedPoseTracker:
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
-        tracker.optimizer.zero_grad(set_to_none=True)
+        if hasattr(tracker, 'optimizer'):
+            tracker.optimizer.zero_grad(set_to_none=True)
         with torch.cuda.graph(self.graph):
             self.loss = tracker.step(self.dirs, self.rgb, self.d)
 

@@ -135,3 +135,46 @@ def test_graphed_tracker_matches_eager():
     assert float((graphed.trans.detach().cpu()[0] - init[:3, 3]).norm()) > 1e-3, 'the pose must have moved'
     for a, b in zip(before, flat_planes(model)):
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize('rot_rep', ['quat', 'axis_angle'])
+def test_fused_tracker_matches_autograd_tracker(rot_rep):
+    """FusedTracker (mne_pose_rays + ray-gradient backward + mne_pose_step: dual-number chain rule and Adam in one kernel)
+    against PoseTracker (torch autograd over the same fused render + torch.optim.Adam): same pose gradient on the first
+    iteration, same pose after twelve; also as CUDA-graph replays."""
+    from mneslam_b200.tracking import FusedTracker, GraphedPoseTracker
+    cfg = configs.small_test_config(n_samples_d=13, n_range_d=7)
+    bound = J.enlarged_bound(cfg)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    gen = torch.Generator().manual_seed(5)
+    model = build_model(cfg, bb, J.init_planes(cfg, bound, seed=4, std=0.3), J.init_weights(cfg, seed=4), as_params=False)
+    cfg['training']['perturb'] = 0
+    c2w_gt = _pose(0.4)
+    init = c2w_gt.clone()
+    init[:3, 3] += torch.tensor([0.03, -0.02, 0.025])
+    dirs = _camera_dirs(cfg, 300, gen).cuda()
+    rgb, d = synthetic.render_box_scene(cfg, c2w_gt, dirs.cpu())
+    rgb, d = rgb.cuda(), d.cuda()
+    ref = PoseTracker(model, init.cuda(), rot_rep=rot_rep, lr_rot=2e-3, lr_trans=2e-3)
+    fused = FusedTracker(model, init.cuda(), rot_rep=rot_rep, lr_rot=2e-3, lr_trans=2e-3)
+    assert torch.allclose(fused.c2w(), ref.c2w().detach(), atol=1e-6)
+    l_ref = ref.step(dirs, rgb, d)
+    l_fused = fused.step(dirs, rgb, d)
+    torch.cuda.synchronize()
+    assert l_fused.item() == pytest.approx(l_ref.item(), rel=1e-4)
+    # PoseTracker leaves the gradients of its last backward on the parameters
+    g_ref = torch.cat([ref.rot.grad.reshape(-1), ref.trans.grad.reshape(-1)])
+    assert float((fused.pose_grad - g_ref).norm() / g_ref.norm()) < 2e-3
+    for _ in range(11):
+        ref.step(dirs, rgb, d)
+        fused.step(dirs, rgb, d)
+    torch.cuda.synchronize()
+    assert torch.allclose(fused.trans, ref.trans.detach()[0], atol=2e-4), (fused.trans, ref.trans)
+    assert torch.allclose(fused.rot, ref.rot.detach()[0], atol=2e-4), (fused.rot, ref.rot)
+    assert float((fused.trans.cpu() - init[:3, 3]).norm()) > 1e-3, 'the pose must have moved'
+    # graph replay of the fused iteration
+    again = FusedTracker(model, init.cuda(), rot_rep=rot_rep, lr_rot=2e-3, lr_trans=2e-3)
+    g = GraphedPoseTracker(again, dirs, rgb, d)          # three warm-up steps inside
+    g.run(9)
+    torch.cuda.synchronize()
+    assert torch.allclose(again.trans, fused.trans, atol=2e-4) and torch.allclose(again.rot, fused.rot, atol=2e-4)

@@ -164,6 +164,47 @@ class FusedTracker:
         return (losses[:7] * self.weights).sum()
 
 
+    def step_align(self, dirs_cam, target_rgb, target_depth, noise=None):
+        """One iteration of the loop-closure alignment (mp_slam/mapper.py:388-410): rays from the current pose estimate,
+        ``render_rays(..., target_d=None)`` (uniform samples), ``rgb_weight * mse(rgb) + depth_weight * mse(depth)`` against
+        the teacher's rendering, pose update.  Returns the loss (device scalar)."""
+        model, cfg = self.model, self.cfg
+        dev = self.rot.device
+        n = dirs_cam.shape[0]
+        lib, st = _lib.lib(), ops._stream()
+        rep = 0 if self.rot_rep == 'axis_angle' else 1
+        dirs = ops._f32(dirs_cam, 'dirs_cam')
+        rays_o = torch.empty(n, 3, dtype=torch.float32, device=dev)
+        rays_d = torch.empty(n, 3, dtype=torch.float32, device=dev)
+        _lib.check(lib.mne_pose_rays(rep, self.rot.data_ptr(), self.trans.data_ptr(), dirs.data_ptr(), n, rays_o.data_ptr(),
+                                     rays_d.data_ptr(), st), 'mne_pose_rays')
+        tables = ops.SampleTables.get(cfg, dev, False)
+        s = tables[0].numel() + tables[1].numel()
+        perturb = cfg['training']['perturb'] > 0.
+        if perturb and noise is None:
+            noise = torch.rand(n, s, device=dev)
+        rcfg = ops.make_render_cfg(cfg, norm_rays=n)
+        z_vals = ops.sample_rays(ops.make_sample_cfg(tables, perturb), rcfg, n, s, None, noise if perturb else None, None, dev)
+        if self._for != (n, s):
+            self._act = torch.empty(n * s * _lib.ACT_FLOATS, dtype=torch.float32, device=dev)
+            self._scratch = ops.backward_scratch(n, s, dev)
+            self._for = (n, s)
+        scene = ops.make_scene(model._flat_planes(), [w.detach() for w in model.decoder.weight_list()], model.bound,
+                               model.bounding_box, cfg['pos']['n_bins'], hash_meta=model.hash_meta)
+        out = ops.render_forward(scene, rcfg, rays_o, rays_d, z_vals, want_aux=False, act=self._act)
+        w_c, w_d = cfg['training']['rgb_weight'], cfg['training']['depth_weight']
+        e_c, e_d = out['rgb'] - target_rgb, out['depth'] - target_depth.reshape(-1)
+        g_rgb, g_depth = e_c * (2.0 * w_c / (3 * n)), e_d * (2.0 * w_d / n)          # d loss / d rendered maps (F.mse_loss means)
+        g_o, g_d = ops.render_backward(scene, rcfg, rays_o, rays_d, z_vals, out['raw'], g_rgb=g_rgb, g_depth=g_depth,
+                                       want_ray_grads=True, scratch=self._scratch, act=self._act)
+        _lib.check(lib.mne_pose_step(rep, self.rot.data_ptr(), self.trans.data_ptr(), dirs.data_ptr(), g_o.data_ptr(),
+                                     g_d.data_ptr(), n, self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(),
+                                     self.step_dev.data_ptr(), self.lr_rot, self.lr_trans, self.betas[0], self.betas[1],
+                                     self.eps, self.pose_grad.data_ptr(), st), 'mne_pose_step')
+        self.last_render = out
+        return w_c * (e_c * e_c).mean() + w_d * (e_d * e_d).mean()
+
+
 class GraphedPoseTracker:
     """One pose iteration (pose -> rays -> fused forward -> losses -> ray-gradient backward -> Adam) captured in a
     CUDA graph for a fixed frame: the per-frame optimisation is ``iters`` replays with no Python in between."""

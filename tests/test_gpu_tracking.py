@@ -178,3 +178,47 @@ def test_fused_tracker_matches_autograd_tracker(rot_rep):
     g.run(9)
     torch.cuda.synchronize()
     assert torch.allclose(again.trans, fused.trans, atol=2e-4) and torch.allclose(again.rot, fused.rot, atol=2e-4)
+
+
+def test_fused_loop_alignment_matches_the_reference_loop():
+    """FusedTracker.step_align against the loop of mp_slam/mapper.py:388-410 written with the drop-in class and torch:
+    render_rays(target_d=None) -> rgb_weight * mse(rgb) + depth_weight * mse(depth) against a teacher rendering ->
+    backward -> Adam on (axis-angle, translation)."""
+    import torch.nn.functional as F
+    from mneslam_b200.tracking import FusedTracker, frozen_map, matrix_to_axis_angle
+    cfg = configs.small_test_config(n_samples_d=13, n_range_d=7, n_samples=24)
+    cfg['training']['perturb'] = 0
+    bound = J.enlarged_bound(cfg)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    gen = torch.Generator().manual_seed(6)
+    model = build_model(cfg, bb, J.init_planes(cfg, bound, seed=4, std=0.3), J.init_weights(cfg, seed=4), as_params=False)
+    model.train()
+    base = _pose(0.4)
+    init = base.clone()
+    init[:3, 3] += torch.tensor([0.02, -0.015, 0.01])
+    dirs = _camera_dirs(cfg, 300, gen).cuda()
+    with torch.no_grad():
+        ro, rd = pose.rays_from_c2w(base.cuda(), dirs)
+        teacher = model.render_rays(ro.contiguous(), rd.contiguous(), target_d=None)
+        t_rgb, t_depth = teacher['rgb'].detach(), teacher['depth'].detach()
+    # the reference loop (get_pose_param_optim: axis-angle for Replica-style configs)
+    rot = torch.nn.Parameter(matrix_to_axis_angle(init[:3, :3].cuda())[None].clone())
+    trans = torch.nn.Parameter(init[None, :3, 3].cuda().clone())
+    opt = torch.optim.Adam([{'params': [rot], 'lr': 2e-3}, {'params': [trans], 'lr': 2e-3}])
+    fused = FusedTracker(model, init.cuda(), rot_rep='axis_angle', lr_rot=2e-3, lr_trans=2e-3)
+    w_c, w_d = cfg['training']['rgb_weight'], cfg['training']['depth_weight']
+    for it in range(8):
+        opt.zero_grad()
+        c2w = pose.transform_matrix(rot, trans, 'axis_angle')[0]
+        with frozen_map(model):
+            ro, rd = pose.rays_from_c2w(c2w, dirs)
+            r = model.render_rays(ro.contiguous(), rd.contiguous(), target_d=None)
+            loss = w_c * F.mse_loss(r['rgb'], t_rgb) + w_d * F.mse_loss(r['depth'], t_depth)
+            loss.backward()
+        opt.step()
+        l_fused = fused.step_align(dirs, t_rgb, t_depth)
+        assert l_fused.item() == pytest.approx(loss.item(), rel=2e-3, abs=1e-9)
+    torch.cuda.synchronize()
+    assert torch.allclose(fused.trans, trans.detach()[0], atol=2e-4), (fused.trans, trans)
+    assert torch.allclose(fused.rot, rot.detach()[0], atol=2e-4), (fused.rot, rot)
+    assert float((fused.trans.cpu() - init[:3, 3]).norm()) > 1e-3

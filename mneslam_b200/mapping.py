@@ -281,6 +281,13 @@ class FusedMapper:
         self.last_losses = losses
         return losses
 
+    def distill_step(self, teacher, rays_o, rays_d):
+        """One iteration of the joint distillation of mp_slam/mapper.py:598-642: the teacher (a foreign agent's model)
+        renders the rays without depth guidance, the student takes a mapping iteration on those renderings."""
+        with torch.no_grad():
+            t = teacher.render_rays(rays_o, rays_d, target_d=None)
+        return self.step(rays_o, rays_d, t['rgb'].detach(), t['depth'].detach().unsqueeze(-1))
+
     def total_loss(self, losses):
         return (losses[:7] * self.loss_weights[:7]).sum()
 

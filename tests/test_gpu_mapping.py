@@ -403,3 +403,28 @@ def test_pipelined_iterations_do_the_same_work():
             torch.cuda.synchronize()
             hist.append(float(mapper.total_loss(pipe.losses)))
     assert all(np.isfinite(hist)) and hist[-1] < hist[0], hist
+
+
+def test_distillation_step_pulls_the_student_towards_the_teacher():
+    """FusedMapper.distill_step (mp_slam/mapper.py:598-642): the student's rendering of the shared rays approaches the
+    teacher's."""
+    from mneslam_b200.mapping import FusedMapper
+    cfg, bb, planes, weights = _small_model(seed=9)
+    teacher = build_model(cfg, bb, planes, weights, as_params=False)
+    cfg2, _, planes2, weights2 = _small_model(seed=21)
+    student = build_model(cfg, bb, planes2, weights2, as_params=False)
+    mapper = FusedMapper(student)
+    b = {k: v.cuda() for k, v in synthetic.make_ray_batch(cfg, 400, seed=3).items()}
+
+    def gap():
+        with torch.no_grad():
+            a = teacher.render_rays(b['rays_o'], b['rays_d'], target_d=None)
+            c = student.render_rays(b['rays_o'], b['rays_d'], target_d=None)
+        return float((a['depth'] - c['depth']).abs().mean()), float((a['rgb'] - c['rgb']).abs().mean())
+    d0, c0 = gap()
+    for _ in range(80):
+        losses = mapper.distill_step(teacher, b['rays_o'], b['rays_d'])
+    torch.cuda.synchronize()
+    d1, c1 = gap()
+    assert torch.isfinite(losses[:2]).all()
+    assert d1 < 0.7 * d0 or c1 < 0.7 * c0, (d0, d1, c0, c1)

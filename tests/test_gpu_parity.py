@@ -304,3 +304,51 @@ def test_backward_with_kept_activations_equals_recompute(two_grid, mode):
         # same arithmetic, different accumulation order (and v1's fp32 contraction for two grids with both gradient kinds)
         tol = 2e-3 if (two_grid and mode == 'both') else 2e-5
         assert float((a - c).norm() / c.norm()) < tol
+
+
+@pytest.mark.parametrize('n_rays', [1, 37, 333])
+def test_workspaces_are_not_overrun(n_rays):
+    """Guard words behind every buffer the kernels write (raw, act, the backward workspace with its sample list, ray
+    gradients, z_vals) stay intact for ragged sizes -- compute-sanitizer is not available on the pool, so the bounds are
+    checked this way."""
+    from mneslam_b200 import _lib, ops
+    cfg = configs.small_test_config(one_grid=True, n_samples_d=13, n_range_d=7)
+    bound = J.enlarged_bound(cfg)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    model = build_model(cfg, bb, J.init_planes(cfg, bound, seed=3, std=0.5), J.init_weights(cfg, seed=3), as_params=False)
+    s = synthetic.n_samples_total(cfg)
+    n = n_rays
+    b = {k: v.cuda() for k, v in synthetic.make_ray_batch(cfg, n, seed=5, zero_depth_frac=0.2, depth_range=(0.3, 2.5)).items()}
+    noise = synthetic.make_noise(n, s, 5).cuda()
+    GUARD, MAGIC = 64, 12345.0
+
+    def guarded(numel):
+        t = torch.full((numel + GUARD,), MAGIC, dtype=torch.float32, device='cuda')
+        return t, t[:numel]
+    fp, ws = flat_planes(model), [w.detach() for w in model.decoder.weight_list()]
+    rcfg = ops.make_render_cfg(cfg, norm_rays=n)
+    tables = ops.SampleTables.get(cfg, 'cuda', True)
+    td = b['target_d'].reshape(-1)
+    acc = ops.new_acc('cuda')
+    z_full, z = guarded(n * s)
+    z = z.view(n, s)
+    ops.sample_rays(ops.make_sample_cfg(tables, True), rcfg, n, s, td, noise, acc, 'cuda', out=z)
+    act_full, act = guarded(n * s * _lib.ACT_FLOATS)
+    sc = ops.make_scene(fp, ws, model.bound, model.bounding_box)
+    out = ops.render_forward(sc, rcfg, b['rays_o'], b['rays_d'], z, b['target_rgb'], td, acc, act=act)
+    nbytes = _lib.lib().mne_backward_scratch_bytes(n, s)
+    assert nbytes % 4 == 0
+    scr_full, scr = guarded(nbytes // 4)
+    pg, wg = [torch.zeros_like(p) for p in fp], [torch.zeros_like(w) for w in ws]
+    scb = ops.make_scene(fp, ws, model.bound, model.bounding_box, plane_grads=pg, weight_grads=wg)
+    lg = torch.tensor([1.0, 0.5, 2.0, 3.0, 2.0, 4.0, 1.5, 0.0], device='cuda')
+    g_o, g_d = ops.render_backward(scb, rcfg, b['rays_o'], b['rays_d'], z, out['raw'], b['target_rgb'], td, acc,
+                                   loss_grads=lg, want_ray_grads=True, scratch=scr, act=act)
+    torch.cuda.synchronize()
+    for name, full in (('z_vals', z_full), ('act', act_full), ('scratch', scr_full)):
+        assert bool((full[-GUARD:] == MAGIC).all()), name
+    n_active = ops.backward_active_count(scr, n, s)
+    assert 0 < n_active <= n * s
+    lst = scr.view(torch.int32)[n * s * 4: n * s * 4 + n_active]
+    assert int(lst.min()) >= 0 and int(lst.max()) < n * s and lst.unique().numel() == n_active
+    assert torch.isfinite(g_o).all() and torch.isfinite(g_d).all()

@@ -468,6 +468,16 @@ def run_ours(args):
         return ms, k
 
     ms_dropin, k_e2e = time_e2e(e2e_step)
+    # the same call sites with the optimiser class swapped in create_optimizer (mneslam_b200.optim.Adam: one fused launch per tensor)
+    ms_dropin_optim = None
+    if world == 1:
+        try:
+            from mneslam_b200.optim import Adam as MapAdam
+            opt = MapAdam([{'params': model.decoder.parameters(), 'weight_decay': 1e-6, 'lr': mp['lr_decoder']},
+                           {'params': model._flat_planes(), 'eps': 1e-15, 'lr': mp['lr_embed']}], betas=(0.9, 0.99))
+            ms_dropin_optim, _ = time_e2e(e2e_step)
+        except Exception as e:
+            print('bench.py: drop-in with the fused optimiser class failed (%r)' % (e,), file=sys.stderr)
     # the fused driver shares the planes with the (now Parameter-wrapped) model: rebuild it on the same storage
     mapper2 = FusedMapper(model, world_size=world)
     mapper2.step_dev.copy_(mapper.step_dev)
@@ -583,7 +593,8 @@ def run_ours(args):
                     'ms_per_step': ms_e2e, 'steps': k_e2e, 'path': e2e_path, 'ms_per_step_eager_driver': ms_e2e_eager},
             'e2e_dropin': {'value': pts_per_rank * world / (ms_dropin * 1e-3), 'unit': UNIT, 'ms_per_step': ms_dropin,
                            'path': 'JointEncoding.forward -> loss.backward() -> torch.optim.Adam.step() (the reference call '
-                                   'sites unchanged), same host buffers'},
+                                   'sites unchanged), same host buffers',
+                           'ms_per_step_with_mneslam_b200_optim_Adam': ms_dropin_optim},
             'tracking': tracking,
             # the dominant kernel of the step is the optimiser; the two gather / scatter kernels follow
             'roofline': {'bound': 'hbm', 'kernel': 'adam_segments_kernel' if world == 1 else 'optimizer step: flag hand-over + barrier + adam_peers_sparse_kernel + barrier', 'achieved': adam_gbs, 'peak': peak, 'unit': 'GB/s',

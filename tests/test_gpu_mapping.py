@@ -428,3 +428,38 @@ def test_distillation_step_pulls_the_student_towards_the_teacher():
     d1, c1 = gap()
     assert torch.isfinite(losses[:2]).all()
     assert d1 < 0.7 * d0 or c1 < 0.7 * c0, (d0, d1, c0, c1)
+
+
+def test_optim_adam_is_a_drop_in_for_torch_adam():
+    """mneslam_b200.optim.Adam in place of torch.optim.Adam in create_optimizer's two parameter groups (decoder with
+    weight decay, channels-last planes with eps 1e-15): same parameters after five steps, zero_grad / state_dict work."""
+    from mneslam_b200.optim import Adam
+    torch.manual_seed(3)
+    shapes = [((32, 112), False), ((1, 32, 20, 30), True), ((3, 32), False), ((1, 32, 7, 9), True)]
+
+    def make():
+        torch.manual_seed(3)
+        ps = []
+        for shp, cl in shapes:
+            t = torch.randn(*shp, device='cuda')
+            if cl:
+                t = t.contiguous(memory_format=torch.channels_last)
+            ps.append(torch.nn.Parameter(t))
+        return ps
+    pa, pb = make(), make()
+    groups = lambda ps: [{'params': [ps[0], ps[2]], 'weight_decay': 1e-6, 'lr': 1e-2}, {'params': [ps[1], ps[3]], 'eps': 1e-15, 'lr': 5e-3}]
+    oa = torch.optim.Adam(groups(pa), betas=(0.9, 0.99), foreach=False)
+    ob = Adam(groups(pb), betas=(0.9, 0.99))
+    for t in range(5):
+        torch.manual_seed(100 + t)
+        for x, y in zip(pa, pb):
+            g = torch.randn_like(x) * (0.1 if t % 2 else 5.0)
+            x.grad, y.grad = g.clone(), g.clone()
+        oa.step(); ob.step()
+        oa.zero_grad(); ob.zero_grad()
+    torch.cuda.synchronize()
+    for x, y in zip(pa, pb):
+        assert y.stride() == x.stride()
+        assert rel(y.detach().cpu().numpy(), x.detach().cpu().numpy()) < 5e-6
+    sd = ob.state_dict()
+    assert len(sd['state']) == 4 and sd['state'][0]['step'] == 5

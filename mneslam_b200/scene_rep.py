@@ -234,7 +234,9 @@ class JointEncoding(nn.Module):
             if gt_depth is not None:
                 gt_depth = gt_depth.reshape(-1).unsqueeze(1).to(device)
             depths, colours = [], []
-            bs = self.ray_batch_size
+            # rays are rendered independently, so the chunk size only sets the launch count: at least 64 Ki rays per launch
+            # (the reference's 4096-ray chunks are 200 launches for a 1200 x 680 image)
+            bs = getattr(self, 'render_chunk', None) or max(self.ray_batch_size, 65536)
             for i in range(0, rays_d.shape[0], bs):
                 td = None if gt_depth is None else gt_depth[i:i + bs]
                 ret = self.render_rays(rays_o[i:i + bs], rays_d[i:i + bs], target_d=td)

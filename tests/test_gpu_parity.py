@@ -352,3 +352,32 @@ def test_workspaces_are_not_overrun(n_rays):
     lst = scr.view(torch.int32)[n * s * 4: n * s * 4 + n_active]
     assert int(lst.min()) >= 0 and int(lst.max()) < n * s and lst.unique().numel() == n_active
     assert torch.isfinite(g_o).all() and torch.isfinite(g_d).all()
+
+
+@pytest.mark.parametrize('with_depth', [True, False])
+def test_render_img_matches_render_rays(with_depth):
+    """render_img (reference model/scene_rep.py:422-473): all pixels of the cropped image through render_rays in chunks;
+    (depth [H,W] float64, colour [H,W,3]) must equal one render_rays call over the same rays, whatever the chunking."""
+    from mneslam_b200.scene_rep import get_rays
+    cfg = configs.small_test_config(one_grid=True, n_samples_d=13, n_range_d=7, n_samples=24)
+    cfg['training']['perturb'] = 0
+    cfg['cam'].update({'H': 44, 'W': 64, 'fx': 50.0, 'fy': 50.0, 'cx': 31.5, 'cy': 21.5, 'crop_edge': 2})
+    bound = J.enlarged_bound(cfg)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    model = build_model(cfg, bb, J.init_planes(cfg, bound, seed=3, std=0.5), J.init_weights(cfg, seed=3), as_params=False)
+    model.eval()
+    H, W = 40, 60
+    c2w = torch.eye(4, device='cuda')
+    c2w[:3, 3] = torch.tensor([0.1, 0.0, 0.05])
+    gt = (torch.rand(H, W, device='cuda') * 2.0 + 0.3) if with_depth else None
+    model.render_chunk = 700                                    # ragged chunks (default: at least 64 Ki rays per launch)
+    depth, colour = model.render_img(c2w, 'cuda', gt_depth=gt)
+    model.render_chunk = None
+    depth1, colour1 = model.render_img(c2w, 'cuda', gt_depth=gt)
+    assert torch.equal(depth, depth1) and torch.equal(colour, colour1)
+    assert depth.shape == (H, W) and depth.dtype == torch.float64 and colour.shape == (H, W, 3)
+    ro, rd = get_rays(H, W, 50.0, 50.0, 31.5, 21.5, c2w, 'cuda')
+    with torch.no_grad():
+        ref = model.render_rays(ro.reshape(-1, 3).contiguous(), rd.reshape(-1, 3).contiguous(),
+                                target_d=None if gt is None else gt.reshape(-1, 1))
+    assert torch.equal(depth.float().reshape(-1), ref['depth']) and torch.equal(colour.reshape(-1, 3), ref['rgb'])

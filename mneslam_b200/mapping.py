@@ -419,10 +419,14 @@ class PipelinedMapper:
         self.losses.copy_(losses)
         self.side.wait_stream(main)                 # the batch has been consumed: refill it under the optimiser
         with torch.cuda.stream(self.side):
+            self._after_losses()
             self._draw()
         m.optimizer_step()
         main.wait_stream(self.side)
         m.last_losses = self.losses
+
+    def _after_losses(self):
+        """Hook on the side stream, once the iteration's losses exist (subclasses copy them to the host here)."""
 
     def capture(self):
         stream = torch.cuda.Stream(device=self.mapper.dev)
@@ -444,3 +448,51 @@ class PipelinedMapper:
             self.capture()
         self.graph.replay()
         return self.losses
+
+
+class PrefetchingHostMapper(PipelinedMapper):
+    """``PipelinedMapper`` fed from HOST memory, data-loader style: every ``step(next_batch)`` trains on the batch handed over
+    by the PREVIOUS call and, under its optimiser, uploads, assembles and samples ``next_batch`` (one CUDA-graph launch
+    holding the H2D copies, the iteration and the D2H copy of the loss).  The ray batches of the reference come from the
+    host keyframe store (model/keyframe.py:91-103) and do not depend on the map, so the caller can always be one ahead."""
+
+    def __init__(self, mapper, db, n_rays, spare_sms=8):
+        super().__init__(mapper, db, n_rays, spare_sms)
+        dev = mapper.dev
+        self.h_rays = torch.empty(n_rays, 7, dtype=torch.float32).pin_memory()
+        self.h_ids = torch.empty(n_rays, dtype=torch.int64).pin_memory()
+        self.h_loss = torch.zeros(1, dtype=torch.float32).pin_memory()
+        self.d_rays = torch.empty(n_rays, 7, dtype=torch.float32, device=dev)
+        self.d_ids = torch.empty(n_rays, dtype=torch.int64, device=dev)
+
+    def _draw(self):
+        self.d_rays.copy_(self.h_rays, non_blocking=True)
+        self.d_ids.copy_(self.h_ids, non_blocking=True)
+        ro, rd, rgb, d = self.db.assemble(self.d_rays, self.d_ids)
+        self.ro.copy_(ro); self.rd.copy_(rd); self.rgb.copy_(rgb); self.d.copy_(d)
+        self.mapper.sample_stage(self.d, z_out=self.z, acc_out=self.acc)
+
+    def _iteration(self):
+        super()._iteration()
+        # (issuing this copy on the side stream, under the optimiser, measured 25 us SLOWER per iteration: it delays the upload
+        #  and sampling of the next batch, which then outlast the optimiser)
+        self.h_loss.copy_(self.mapper.total_loss(self.losses).reshape(1), non_blocking=True)
+
+    def prime(self, rays7, kf_ids):
+        """Hand over the first batch (uploaded and sampled right away; also warms up and captures the graph, which costs
+        two real iterations on this batch)."""
+        self.h_rays.copy_(rays7); self.h_ids.copy_(kf_ids)
+        self.capture()
+        return self
+
+    def step(self, next_rays7, next_kf_ids):
+        """Train on the batch of the previous call (or of ``prime``); upload ``next_*`` (HOST tensors) under its optimiser.
+        Returns the loss of the trained batch as a Python float."""
+        if self.graph is None:
+            raise RuntimeError('PrefetchingHostMapper: call prime(first_batch) first')
+        self.h_rays.copy_(next_rays7)
+        self.h_ids.copy_(next_kf_ids)
+        with torch.cuda.stream(self.stream):
+            self.graph.replay()
+        self.stream.synchronize()
+        return float(self.h_loss[0])

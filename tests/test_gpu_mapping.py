@@ -463,3 +463,39 @@ def test_optim_adam_is_a_drop_in_for_torch_adam():
         assert rel(y.detach().cpu().numpy(), x.detach().cpu().numpy()) < 5e-6
     sd = ob.state_dict()
     assert len(sd['state']) == 4 and sd['state'][0]['step'] == 5
+
+
+def test_prefetching_host_mapper_trains_on_the_previous_batch():
+    """PrefetchingHostMapper.step(next) = FusedMapper.step on the batch handed over one call earlier: same losses, same
+    parameters (prime() spends two real iterations on the first batch, as documented)."""
+    from mneslam_b200.mapping import DeviceKeyframeRays, FusedMapper, PrefetchingHostMapper
+    cfg, bb, planes, weights = _small_model(seed=9)
+    cfg['cam'].update({'H': 40, 'W': 60, 'fx': 50.0, 'fy': 50.0, 'cx': 29.5, 'cy': 19.5})
+    cfg['training']['perturb'] = 0
+    rays, poses = synthetic.make_keyframe_db(cfg, n_kf=3, seed=2)
+    flat = rays.reshape(-1, 7)
+    gen = torch.Generator().manual_seed(5)
+    batches = []
+    for _ in range(7):
+        idx = torch.randint(0, flat.shape[0], (256,), generator=gen)
+        batches.append((flat[idx].contiguous(), (idx // rays.shape[1]).contiguous()))
+    arms = []
+    for prefetch in (True, False):
+        model = build_model(cfg, bb, planes, weights, as_params=False)
+        mapper = FusedMapper(model)
+        db = DeviceKeyframeRays(rays.cuda(), poses.cuda())
+        losses = []
+        if prefetch:
+            fed = PrefetchingHostMapper(mapper, db, 256).prime(*batches[0])
+            for nxt in batches[1:]:
+                losses.append(fed.step(*nxt))                       # the loss of the batch given one call earlier
+        else:
+            for _ in range(2):
+                mapper.step(*db.assemble(batches[0][0].cuda(), batches[0][1].cuda()))
+            for r7, ids in batches[:-1]:
+                losses.append(float(mapper.total_loss(mapper.step(*db.assemble(r7.cuda(), ids.cuda())))))
+        torch.cuda.synchronize()
+        arms.append((losses, [p.detach().clone() for p in flat_planes(model)]))
+    (la, pa), (lb, pb) = arms
+    assert la == pytest.approx(lb, rel=1e-4)
+    assert min(float((x.double() - y.double()).norm() / (y.double().norm() + 1e-30)) for x, y in zip(pa, pb)) < 2e-5

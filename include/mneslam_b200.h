@@ -60,7 +60,8 @@ typedef struct MneHashDesc {
  * SURVEY.md 8(b) "Attributes read/written from outside"). */
 typedef struct MneSceneDesc {
     int32_t encoder;  /* 0 = tri-plane (live in the reference), 1 = hash grid: 16 levels x 2 features, one table
-                       * (grid.oneGrid); forward, table / decoder gradients and ray gradients */
+                       * (grid.oneGrid) or an sdf and a colour table (two_grid; its backward needs the `act` buffer);
+                       * forward, table / decoder gradients and ray gradients */
     int32_t two_grid; /* 1 when grid.oneGrid is False: colour planes / colour table present */
     int32_t n_bins;   /* OneBlob bins per dimension; must be 16 */
     int32_t c_dim;    /* plane channels; must be 32 */

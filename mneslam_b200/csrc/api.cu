@@ -49,14 +49,15 @@ int impl_version();
 int check_scene(const MneSceneDesc* sc, const char* who, bool) {
     MNE_CHECK_ARG(sc->encoder == 0 || sc->encoder == 1, "%s: encoder %d unknown (0 = tri-plane, 1 = hash grid)", who, sc->encoder);
     if (sc->encoder == 1) {
-        const MneHashDesc& h = sc->hash[0];
         MNE_CHECK_ARG(impl_version() == 2, "%s: the hash-grid encoder needs the tensor-pipe kernels (option impl = 2)", who);
-        MNE_CHECK_ARG(!sc->two_grid, "%s: the hash-grid encoder is built for one table (grid.oneGrid)", who);
-        MNE_CHECK_ARG(h.table && h.n_levels == 16 && h.n_features == 2, "%s: hash grid must have a table, 16 levels, 2 features", who);
-        MNE_CHECK_ARG((((uintptr_t)h.table | (uintptr_t)h.grad) & 7) == 0, "%s: hash table must be 8-byte aligned", who);
-        for (int l = 0; l < 16; ++l)
-            MNE_CHECK_ARG(h.offsets[l + 1] > h.offsets[l] && h.level_res[l] >= 2 && h.level_scale[l] > 0.f,
-                          "%s: hash level %d is empty or has no scale / resolution", who, l);
+        for (int g = 0; g < (sc->two_grid ? 2 : 1); ++g) {       // [0] sdf table, [1] colour table (grid.oneGrid: False)
+            const MneHashDesc& h = sc->hash[g];
+            MNE_CHECK_ARG(h.table && h.n_levels == 16 && h.n_features == 2, "%s: hash grid %d must have a table, 16 levels, 2 features", who, g);
+            MNE_CHECK_ARG((((uintptr_t)h.table | (uintptr_t)h.grad) & 7) == 0, "%s: hash table %d must be 8-byte aligned", who, g);
+            for (int l = 0; l < 16; ++l)
+                MNE_CHECK_ARG(h.offsets[l + 1] > h.offsets[l] && h.level_res[l] >= 2 && h.level_scale[l] > 0.f,
+                              "%s: level %d of hash grid %d is empty or has no scale / resolution", who, l, g);
+        }
         MNE_CHECK_ARG(sc->n_bins == kBins, "%s: n_bins = %d, this library is built for %d", who, sc->n_bins, kBins);
         MNE_CHECK_ARG(sc->w_sdf0 && sc->w_sdf1 && sc->w_col0 && sc->w_col1, "%s: decoder weights missing", who);
         for (int a = 0; a < 3; ++a) MNE_CHECK_ARG(sc->bbox_ext[a] > 0.0, "%s: empty bound on axis %d", who, a);

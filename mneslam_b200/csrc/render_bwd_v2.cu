@@ -44,17 +44,17 @@ __device__ __forceinline__ void load_weights_t(const MneSceneDesc& sc, float* WT
         for (int i = tid; i < 48 * 32; i += nthreads) {
             const int k = i >> 5, j = i & 31;
             WT[T::OFF_W1BT + k * T::S1 + j] = sc.w_sdf0[j * sdf0_in(hash) + sdf0_col(64 + k, hash)];
-            WT[T::OFF_V1BT + k * T::S1 + j] = sc.w_col0[j * N::IN_COL + k];
+            WT[T::OFF_V1BT + k * T::S1 + j] = sc.w_col0[j * col0_in(TWO, hash) + k];
         }
     for (int i = tid; i < 64 * 32; i += nthreads) {
         const int k = i >> 5, j = i & 31;
         const int col = sdf0_col(k, hash);
         WT[T::OFF_W1T + k * T::S1 + j] = (col >= 0) ? sc.w_sdf0[j * sdf0_in(hash) + col] : 0.0f;
-        if (TWO) WT[T::OFF_VCT + k * T::S1 + j] = sc.w_col0[j * N::IN_COL + kBlob + k];
+        if (TWO) WT[T::OFF_VCT + k * T::S1 + j] = (!hash || k < 32) ? sc.w_col0[j * col0_in(TWO, hash) + kBlob + k] : 0.0f;
     }
     for (int i = tid; i < 16 * 32; i += nthreads) {
         const int m = i >> 5, j = i & 31;
-        WT[T::OFF_VGT + m * T::S1 + j] = (m < kGeo) ? sc.w_col0[j * N::IN_COL + (N::IN_COL - kGeo) + m] : 0.0f;
+        WT[T::OFF_VGT + m * T::S1 + j] = (m < kGeo) ? sc.w_col0[j * col0_in(TWO, hash) + (col0_in(TWO, hash) - kGeo) + m] : 0.0f;
         const int jj = i >> 4, c = i & 15;                     // W2T[j][c], c: 0..14 geo (out c+1), 15 sdf (out 0)
         WT[T::OFF_W2T + jj * kGeoStride + c] = sc.w_sdf1[((c == 15) ? 0 : c + 1) * 32 + jj];
     }
@@ -208,6 +208,7 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
             if (half == 0) { row[kBlobCol] = bx0; row[kBlobCol + 1] = by0; row[kBlobCol + 2] = bz0; }
             __syncwarp();
             gather16_hash(P.sc.hash[0], X + kBlobCol, kXStride, X, kXStride, np, lane);
+            if (TWO) gather16_hash(P.sc.hash[1], X + kBlobCol, kXStride, CFt, kCStride, np, lane);
             __syncwarp();
         } else {
             if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 0);
@@ -424,12 +425,16 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
             if (half == 0) { row[kBlobCol] = bx0; row[kBlobCol + 1] = by0; row[kBlobCol + 2] = bz0; }
             __syncwarp();
             if (PARAM && P.sc.hash[0].grad) scatter16_hash(P.sc.hash[0], X + kBlobCol, kXStride, X, kXStride, np, lane, P.sc.dirty, P.sc.dirty_base);
+            if (TWO && PARAM && P.sc.hash[1].grad) scatter16_hash(P.sc.hash[1], X + kBlobCol, kXStride, CFt, kCStride, np, lane, P.sc.dirty, P.sc.dirty_base);
         } else if (half == 1) {
             write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 0);
         }
         __syncwarp();
         float dn_keep[3] = {0.f, 0.f, 0.f};                      // d loss / d normalised plane (or unit-cube) coordinates of this lane's point
-        if (MODE == 2 && RAY) hash_point_grad16(P.sc.hash[0], X + kBlobCol, kXStride, X, kXStride, np, lane, dn_keep);
+        if (MODE == 2 && RAY) {
+            hash_point_grad16(P.sc.hash[0], X + kBlobCol, kXStride, X, kXStride, np, lane, dn_keep);
+            if (TWO) hash_point_grad16(P.sc.hash[1], X + kBlobCol, kXStride, CFt, kCStride, np, lane, dn_keep);
+        }
         // ---- 8. plane gradient scatter: lane = (corner, 4-channel group)
         for (int grp = 0; MODE != 2 && grp < (TWO ? 2 : 1); ++grp) {
             if (grp == 1) {
@@ -536,7 +541,9 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
                         const int k = blk * 16 + g + ((i & 2) ? 8 : 0), j = nb * 8 + 2 * t + (i & 1);
-                        if (k < N::IN_COL) atomicAdd(P.sc.g_col0 + j * N::IN_COL + k, acc1[sl][nb][i]);
+                        const bool hash2 = MODE == 2;
+                        const int col = (k < N::IN_COL) ? col0_col(k, TWO, hash2) : -1;
+                        if (col >= 0) atomicAdd(P.sc.g_col0 + j * col0_in(TWO, hash2) + col, acc1[sl][nb][i]);
                     }
             } else if (blk >= V1_BLOCKS && blk < NB1 && P.sc.g_col1) {
 #pragma unroll
@@ -697,12 +704,10 @@ static int launch_points_bwd(const PtsBwdParams& P, cudaStream_t stream) {
 // and ray AND parameter gradients together fit too)
 template <int MODE>
 static int dispatch_points_bwd_saved(const PtsBwdParams& P, bool ray, bool param, cudaStream_t st) {
-    if constexpr (MODE != 2) {                                // (the hash grid has one table)
-        if (P.sc.two_grid) {
-            if (ray && param) return launch_points_bwd<true, MODE, true, true, 8, true>(P, st);
-            if (ray) return launch_points_bwd<true, MODE, true, false, 9, true>(P, st);
-            return launch_points_bwd<true, MODE, false, true, 10, true>(P, st);
-        }
+    if (P.sc.two_grid) {
+        if (ray && param) return launch_points_bwd<true, MODE, true, true, 8, true>(P, st);
+        if (ray) return launch_points_bwd<true, MODE, true, false, 9, true>(P, st);
+        return launch_points_bwd<true, MODE, false, true, 10, true>(P, st);
     }
     if (ray && param) return launch_points_bwd<false, MODE, true, true, kSavedWarps, true>(P, st);
     if (ray) return launch_points_bwd<false, MODE, true, false, kSavedWarps, true>(P, st);
@@ -749,6 +754,7 @@ int render_backward_v2(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int3
     const bool ray = g_rays_o != nullptr;
     if (scene->encoder == 1) {
         if (act) return dispatch_points_bwd_saved<2>(P, ray, param_grad, st);
+        MNE_CHECK_ARG(!scene->two_grid, "mne_render_backward: the two-table hash grid needs the forward's activation buffer (act)");
         if (ray && param_grad) return launch_points_bwd<false, 2, true, true>(P, st);
         if (ray) return launch_points_bwd<false, 2, true, false>(P, st);
         return launch_points_bwd<false, 2, false, true>(P, st);

@@ -72,6 +72,7 @@ __global__ void __launch_bounds__(pts_warps<TWO>() * 32, 1) points_fwd_kernel(co
             if (half == 0) { row[kBlobCol] = bx; row[kBlobCol + 1] = by; row[kBlobCol + 2] = bz; }
             __syncwarp();
             gather16_hash(P.sc.hash[0], X + kBlobCol, kXStride, X, kXStride, np, lane);
+            if (TWO) gather16_hash(P.sc.hash[1], X + kBlobCol, kXStride, CFt, kCStride, np, lane);      // colour table
             __syncwarp();
         } else {
             // ---- tap table into the point's blob segment, gather, then (two grids) the same for the colour planes
@@ -245,7 +246,7 @@ static int launch_points_fwd(const PtsFwdParams& P, cudaStream_t stream) {
 }
 
 static int dispatch_points_fwd(const PtsFwdParams& P, cudaStream_t stream) {
-    if (P.sc.encoder == 1) return launch_points_fwd<false, 2>(P, stream);
+    if (P.sc.encoder == 1) return P.sc.two_grid ? launch_points_fwd<true, 2>(P, stream) : launch_points_fwd<false, 2>(P, stream);
     const bool vec = planes_vectorizable(P.sc);
     if (P.sc.two_grid) return vec ? launch_points_fwd<true, 1>(P, stream) : launch_points_fwd<true, 0>(P, stream);
     return vec ? launch_points_fwd<false, 1>(P, stream) : launch_points_fwd<false, 0>(P, stream);

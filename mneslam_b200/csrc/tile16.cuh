@@ -73,6 +73,12 @@ struct NetV2 {
 // yields 32 features, tile columns 32..63 are zero padding (their weights are zero), blob follows at 64.
 __device__ __forceinline__ int sdf0_col(int k, bool hash) { return !hash ? k : (k < 32 ? k : (k < 64 ? -1 : k - 32)); }
 __device__ __forceinline__ int sdf0_in(bool hash) { return hash ? 80 : 112; }
+// The same for col0 with two grids: tile columns = blob 48 | colour features 64 | geo 15.  A colour hash table yields 32
+// features: tile columns 80..111 are zero padding, geo follows at 112.
+__device__ __forceinline__ int col0_col(int k, bool two, bool hash) {
+    return !(two && hash) ? k : (k < 80 ? k : (k < 112 ? -1 : k - 32));
+}
+__device__ __forceinline__ int col0_in(bool two, bool hash) { return kBlob + kGeo + (two ? (hash ? 32 : 64) : 0); }
 
 __device__ __forceinline__ float4 split_pair(float a, float b) {
     const uint32_t ah = to_tf32(a), bh = to_tf32(b);
@@ -98,8 +104,10 @@ __device__ __forceinline__ void load_weights_v2(const MneSceneDesc& sc, float4* 
     for (int i = tid; i < 32 * N::KCP; i += nthreads) {
         const int n = i / N::KCP, kp = i % N::KCP;
         const int k0 = 2 * kp, k1 = 2 * kp + 1;
-        const float a = (k0 < N::IN_COL) ? sc.w_col0[n * N::IN_COL + k0] : 0.0f;
-        const float b = (k1 < N::IN_COL) ? sc.w_col0[n * N::IN_COL + k1] : 0.0f;
+        const int c0 = (k0 < N::IN_COL) ? col0_col(k0, TWO, hash) : -1, c1 = (k1 < N::IN_COL) ? col0_col(k1, TWO, hash) : -1;
+        const int in = col0_in(TWO, hash);
+        const float a = (c0 >= 0) ? sc.w_col0[n * in + c0] : 0.0f;
+        const float b = (c1 >= 0) ? sc.w_col0[n * in + c1] : 0.0f;
         W4[N::OFFC + n * N::RSC + kp] = split_pair(a, b);
     }
     for (int i = tid; i < 8 * N::K2P; i += nthreads) {

@@ -29,6 +29,7 @@ class HashGridMeta:
             self.offsets.append(self.offsets[-1] + entries)
         self.n_entries = self.offsets[-1]
         self.n_output = n_levels * n_features
+        self.color = None        # HashGridMeta of the separate colour table (grid.oneGrid: False), attached by the model
 
     @classmethod
     def from_config(cls, cfg, key='voxel_sdf'):

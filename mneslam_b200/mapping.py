@@ -61,7 +61,7 @@ class FusedMapper:
         n_sdf_planes = 6 if model.hash_meta is None else 1
         # parameter groups of create_optimizer (mneslam_mp.py:459-469): (tensor, lr, eps, weight_decay)
         self.params = [(p, mp['lr_embed'], 1e-15, 0.0) for p in planes[:n_sdf_planes]]
-        if not one_grid and model.hash_meta is None:
+        if not one_grid:
             self.params += [(p, mp['lr_embed_color'], 1e-15, 0.0) for p in planes[n_sdf_planes:]]
         self.params += [(w, mp['lr_decoder'], 1e-8, 1e-6) for w in weights]
         self.betas = (0.9, 0.99)

@@ -117,17 +117,21 @@ def bounds_to_host(bound, bounding_box):
 def make_scene(planes, weights, bound, bounding_box, n_bins=16, plane_grads=None, weight_grads=None, hash_meta=None,
                dirty=None, dirty_base=None):
     """planes: flat list of 6 or 12 ``[1,32,H,W]`` tensors in ``all_planes`` order (group, axis, level) -- or, with
-    ``hash_meta`` (a ``hashgrid.HashGridMeta``), the one-element list ``[table]`` of the hash grid encoder.
+    ``hash_meta`` (a ``hashgrid.HashGridMeta``; its ``.color`` is the colour table's meta or None), ``[table]`` /
+    ``[table, colour table]`` of the hash grid encoder.
     weights: [sdf0, sdf1, col0, col1].  bound: float32 [3,2] (CPU ok).  bounding_box: float64 [3,2].
     dirty / dirty_base: uint8 flag map and the flat gradient buffer it indexes (``MneSceneDesc.dirty``)."""
     sc = SceneDesc()
     sc.n_bins = n_bins
     keep = []
     if hash_meta is not None:
-        if len(planes) != 1:
-            raise ValueError('the hash grid encoder takes exactly one table')
-        sc.encoder, sc.two_grid, sc.c_dim = 1, 0, 32
+        color_meta = getattr(hash_meta, 'color', None)        # second table (grid.oneGrid: False)
+        if len(planes) != (1 if color_meta is None else 2):
+            raise ValueError('the hash grid encoder takes [table] or, with a colour table, [table, colour table]')
+        sc.encoder, sc.two_grid, sc.c_dim = 1, 0 if color_meta is None else 1, 32
         hash_meta.fill_desc(sc.hash[0], planes[0], plane_grads[0] if plane_grads is not None else None)
+        if color_meta is not None:
+            color_meta.fill_desc(sc.hash[1], planes[1], plane_grads[1] if plane_grads is not None else None)
         planes, plane_grads = [], None
         feat = hash_meta.n_output
     else:

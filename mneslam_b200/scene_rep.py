@@ -155,10 +155,12 @@ class JointEncoding(nn.Module):
             # the encoder the configs NAME (grid.enc: HashGrid + hash_size + voxel_sdf, model/scene_rep.py:55-70,160)
             # but the reference never builds; opt-in through the extension key grid.use_hash
             from .hashgrid import HashGridMeta
-            if not config['grid']['oneGrid']:
-                raise NotImplementedError('grid.use_hash is built for one table (grid.oneGrid: True)')
             self.hash_meta = HashGridMeta.from_config(config)
             self.hash_tables = [self.hash_meta.new_table(self.device)]      # mutable list, like all_planes
+            if not config['grid']['oneGrid']:
+                # the colour encoder of the (commented) model/scene_rep.py:169: same grid, resolution from voxel_color
+                self.hash_meta.color = HashGridMeta.from_config(config, key='voxel_color')
+                self.hash_tables.append(self.hash_meta.color.new_table(self.device))
             self.input_ch = self.hash_meta.n_output
             self.all_planes = ()
             if self.input_ch_pos != 48:
@@ -179,7 +181,7 @@ class JointEncoding(nn.Module):
 
     # ------------------------------------------------------------------ helpers
     def _flat_planes(self):
-        """The encoder's parameter tensors: the planes in ``all_planes`` order, or ``[hash table]``."""
+        """The encoder's parameter tensors: the planes in ``all_planes`` order, or the hash table(s)."""
         if self.hash_meta is not None:
             return list(self.hash_tables)
         expect = 3 if self.config['grid']['oneGrid'] else 6

@@ -204,12 +204,16 @@ def decode(weights, feat, blob, cfeat=None):
 
 def query_points(cfg, planes, weights, bound, bounding_box, pts, fast=False):
     """pts [M,3] -> raw [M,4] = (rgb logits, sdf).  With ``cfg['grid']['use_hash']`` the parametric encoder is the
-    multi-resolution hash grid (``oracle/hashgrid.py``) and ``planes`` is ``([table],)``."""
+    multi-resolution hash grid (``oracle/hashgrid.py``) and ``planes`` is ``([table],)`` or ``([table], [colour table])``."""
     if cfg['grid'].get('use_hash', False):
         from . import hashgrid
         x01 = blob_inputs(pts, bounding_box)
         feat = hashgrid.encode(hashgrid.make_meta(cfg), planes[0][0], x01)
-        return decode(weights, feat, oneblob(x01, cfg['pos']['n_bins']), None)[0]
+        cfeat = None
+        if not cfg['grid']['oneGrid']:      # the colour encoder of the (commented) model/scene_rep.py:169: resolution from voxel_color
+            cmeta = hashgrid.make_meta(cfg, resolution=hashgrid.desired_resolution(cfg, 'voxel_color'))
+            cfeat = hashgrid.encode(cmeta, planes[1][0], x01)
+        return decode(weights, feat, oneblob(x01, cfg['pos']['n_bins']), cfeat)[0]
     p_nor = normalize_plane_coords(pts, bound)
     feat = triplane_features(p_nor, planes[0], planes[1], planes[2], fast)
     blob = oneblob(blob_inputs(pts, bounding_box), cfg['pos']['n_bins'])

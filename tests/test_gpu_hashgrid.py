@@ -137,3 +137,65 @@ def test_fused_mapper_trains_the_hash_grid():
         losses = mapper.step(b['rays_o'].cuda(), b['rays_d'].cuda(), rgb.cuda(), d.cuda())
         hist.append(mapper.total_loss(losses).item())
     assert np.isfinite(hist).all() and np.mean(hist[-10:]) < 0.5 * np.mean(hist[:10]), (hist[:3], hist[-3:])
+
+
+def _two_table_model(cfg, seed=0, table_scale=0.3):
+    torch.manual_seed(seed)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    model = JointEncoding(cfg, bb).cuda()
+    meta = H.make_meta(cfg)
+    cmeta = H.make_meta(cfg, resolution=H.desired_resolution(cfg, 'voxel_color'))
+    assert cmeta['offsets'] == model.hash_meta.color.offsets and cmeta['resolutions'] == model.hash_meta.color.resolutions
+    assert cmeta['per_level_scale'] != meta['per_level_scale']
+    table, ctable = H.init_table(meta, seed=seed, scale=table_scale), H.init_table(cmeta, seed=seed + 7, scale=table_scale)
+    weights = J.init_weights(cfg, seed=seed)
+    assert tuple(weights['col0'].shape) == (32, 95)
+    model.hash_tables[0] = torch.nn.Parameter(table.cuda())
+    model.hash_tables[1] = torch.nn.Parameter(ctable.cuda())
+    with torch.no_grad():
+        for w, k in zip(model.decoder.weight_list(), ('sdf0', 'sdf1', 'col0', 'col1')):
+            w.copy_(weights[k])
+    model.train()
+    return model, table, ctable, weights, bb
+
+
+def test_two_tables_forward_backward_and_ray_gradients_vs_oracle():
+    """grid.oneGrid: False on the hash grid: an sdf table and a colour table (resolution from voxel_color, the commented
+    model/scene_rep.py:169), colour decoder fed [blob | colour features | geo].  Forward, losses, both table gradients, decoder
+    gradients and ray gradients against autograd on the oracle; then a short FusedMapper run."""
+    cfg = _hash_cfg()
+    cfg['grid']['oneGrid'] = False
+    cfg['is_co_sdf'] = True
+    model, table, ctable, weights, bb = _two_table_model(cfg, seed=3)
+    n = 300
+    batch = synthetic.make_ray_batch(cfg, n, seed=8, zero_depth_frac=0.1, depth_range=(0.3, 2.5))
+    noise = synthetic.make_noise(n, synthetic.n_samples_total(cfg), seed=8)
+    ot, oc = table.clone().requires_grad_(True), ctable.clone().requires_grad_(True)
+    ow = {k: v.clone().requires_grad_(True) for k, v in weights.items()}
+    oo, od = batch['rays_o'].clone().requires_grad_(True), batch['rays_d'].clone().requires_grad_(True)
+    oret, orend = J.forward(cfg, ([ot], [oc]), ow, J.enlarged_bound(cfg), bb, oo, od, batch['target_rgb'], batch['target_d'], noise)
+    J.total_loss(cfg, oret).backward()
+
+    ro, rd = batch['rays_o'].cuda().requires_grad_(True), batch['rays_d'].cuda().requires_grad_(True)
+    ret = model.forward(ro, rd, batch['target_rgb'].cuda(), batch['target_d'].cuda(), noise=noise.cuda())
+    for k in ('rgb', 'depth'):
+        assert rel(ret[k].detach().cpu().numpy(), orend[k].detach().numpy()) < 1e-3, k
+    for k in ('rgb_loss', 'depth_loss', 'co_sdf_loss', 'co_fs_loss'):
+        np.testing.assert_allclose(ret[k].item(), oret[k].item(), rtol=1e-3, err_msg=k)
+    total_loss(cfg, ret).backward()
+    for got, want, name in ((model.hash_tables[0].grad, ot.grad, 'sdf table'), (model.hash_tables[1].grad, oc.grad, 'colour table'),
+                            (ro.grad, oo.grad, 'rays_o'), (rd.grad, od.grad, 'rays_d')):
+        assert cosine(got.cpu().numpy(), want.numpy()) >= 0.999, name
+        assert rel(got.cpu().numpy(), want.numpy()) < 5e-3, name
+    for w, k in zip(model.decoder.weight_list(), ('sdf0', 'sdf1', 'col0', 'col1')):
+        assert cosine(w.grad.cpu().numpy(), ow[k].grad.numpy()) >= 0.999, k
+
+    mapper = FusedMapper(model)
+    first = last = None
+    for it in range(40):
+        b = synthetic.make_ray_batch(cfg, 256, seed=100 + it % 4)
+        losses = mapper.step(b['rays_o'].cuda(), b['rays_d'].cuda(), b['target_rgb'].cuda(), b['target_d'].cuda())
+        v = float(mapper.total_loss(losses))
+        first = v if first is None else first
+        last = v
+    assert np.isfinite(last) and last < first

@@ -175,10 +175,13 @@ int mne_sample_importance(const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_sa
 
 /* ---- forward: replaces run_network + raw2outputs/sdf2weights (model/scene_rep.py:183-230,303-317,384-386)
  * and the loss sums of JointEncoding.forward (:569-590).  Optional outputs may be NULL.  target_rgb /
- * target_d / acc NULL = no loss sums.  act (optional, [N*S, MNE_ACT_FLOATS] floats): the decoders' hidden
- * activations, kept for mne_render_backward -- what autograd would save; with it the backward does not recompute the
- * forward (impl 2, channels-last planes or hash grid; ignored otherwise). */
-#define MNE_ACT_FLOATS 80
+ * target_d / acc NULL = no loss sums.  act (optional, [N*S, mne_act_floats(scene)] floats, 32-byte aligned): one record
+ * per sample kept for mne_render_backward -- what autograd would save: the decoders' hidden activations (80 floats), the
+ * encoder's features (64, or 32 for the hash grid; twice that with two grids), the ReLU masks, and room for the 80
+ * per-sample decoder gradients the backward writes there.  With it the backward neither recomputes the forward nor
+ * gathers the features again (impl 2, channels-last planes or hash grid; ignored otherwise). */
+#define MNE_ACT_FLOATS_MAX 296
+int mne_act_floats(const MneSceneDesc* scene);
 int mne_render_forward(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples,
                        const float* rays_o, const float* rays_d, const float* z_vals, const float* target_rgb,
                        const float* target_d, float* raw, float* weights, float* rgb, float* depth, float* disp,
@@ -202,13 +205,14 @@ int mne_loss_finalize(const MneRenderCfg* rcfg, int32_t n_samples, const double*
  * differentiates the rendered maps or the raw network output itself (loop-closure pose optimisation, mp_slam/mapper.py:388-410).
  * Accumulates (+=) into scene->planes[].grad / hash[].grad / g_* and, if non-NULL, WRITES g_rays_o /
  * g_rays_d [N,3].  `scratch` must hold mne_backward_scratch_bytes(n_rays, n_samples) bytes.  act: the buffer the
- * forward filled for the SAME scene, rays and z_vals (parameters unchanged in between), or NULL = recompute. */
+ * forward filled for the SAME scene, rays and z_vals (parameters unchanged in between), or NULL = recompute; the
+ * backward writes the per-sample decoder gradients into it (its weight-gradient kernel reads them back). */
 size_t mne_backward_scratch_bytes(int32_t n_rays, int32_t n_samples);
 int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples,
                         const float* rays_o, const float* rays_d, const float* z_vals, const float* raw,
                         const float* target_rgb, const float* target_d, const double* acc,
                         const float* loss_grads, const float* g_rgb, const float* g_depth, const float* g_raw,
-                        void* scratch, float* g_rays_o, float* g_rays_d, const float* act, mne_stream_t stream);
+                        void* scratch, float* g_rays_o, float* g_rays_d, float* act, mne_stream_t stream);
 
 /* ---- backward without a caller workspace.  This entry point has no counterpart in the reference: it exists
  * for callers that must not allocate device memory (a host that forbids cudaMalloc around the call, a real-time

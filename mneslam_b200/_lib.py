@@ -12,7 +12,7 @@ MAX_PLANES = 12
 ACC_SLOTS = 16
 N_LOSSES = 8
 STATIC_SCRATCH_SAMPLES = 131072   # MNE_STATIC_SCRATCH_SAMPLES
-ACT_FLOATS = 80                   # MNE_ACT_FLOATS
+ACT_FLOATS_MAX = 296              # MNE_ACT_FLOATS_MAX
 
 # accumulator / loss slots (keep in sync with csrc/common.cuh)
 ACC = {'n_valid': 0, 'n_co_front': 1, 'n_co_near': 2, 'n_e_front': 3, 'n_e_center': 4, 'n_e_tail': 5,
@@ -67,6 +67,7 @@ _SIGNATURES = {
                                         C.c_int32] + [C.c_void_p] * 6),
     'mne_render_forward': (C.c_int, [C.POINTER(SceneDesc), C.POINTER(RenderCfg), C.c_int32, C.c_int32] +
                            [C.c_void_p] * 16),
+    'mne_act_floats': (C.c_int, [C.POINTER(SceneDesc)]),
     'mne_composite': (C.c_int, [C.POINTER(RenderCfg), C.c_int32, C.c_int32] + [C.c_void_p] * 10),
     'mne_loss_finalize': (C.c_int, [C.POINTER(RenderCfg), C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     'mne_backward_scratch_bytes': (C.c_size_t, [C.c_int32, C.c_int32]),

@@ -479,10 +479,10 @@ extern "C" int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg
                                    const float* rays_o, const float* rays_d, const float* z_vals, const float* raw,
                                    const float* target_rgb, const float* target_d, const double* acc,
                                    const float* loss_grads, const float* g_rgb, const float* g_depth, const float* g_raw,
-                                   void* scratch, float* g_rays_o, float* g_rays_d, const float* act, mne_stream_t stream) {
+                                   void* scratch, float* g_rays_o, float* g_rays_d, float* act, mne_stream_t stream) {
     using namespace mne;
     MNE_CHECK_ARG(scene && rcfg, "mne_render_backward: null scene/rcfg");
-    MNE_CHECK_ARG(((uintptr_t)act & 7) == 0, "mne_render_backward: act must be 8-byte aligned");
+    MNE_CHECK_ARG(((uintptr_t)act & 31) == 0, "mne_render_backward: act must be 32-byte aligned");
     if (int e = check_scene(scene, "mne_render_backward", false)) return e;
     MNE_CHECK_ARG(n_rays >= 0 && n_samples > 0, "mne_render_backward: bad sizes n_rays=%d n_samples=%d", n_rays, n_samples);
     if (n_rays == 0) return 0;

@@ -9,97 +9,19 @@
 //
 // Plane gradients: lane = (corner, 4-channel group), one 128-bit vector reduction (red.global.add.v4.f32) per
 // lane covers the four corner texels of a tap.
-#include "tile16.cuh"
+#include "bwd_tiles.cuh"
 
 namespace mne {
-
-constexpr int kBwdWarps = 8;
-constexpr int kSavedWarps = 12;    // one-grid kernels that read the forward's activations instead of recomputing them
-constexpr int kActStride = 40;     // hidden-wide tiles [16][32 + 8]: == 8 (mod 32)
-constexpr int kGeoStride = 24;     // 16-wide tiles
-constexpr int kRgbStride = 8;
-
-// hi-only transposed weights for the "d input = d output . W" products (B fragment = W[k = out][n = in]),
-// stored [in][out] so that a lane's (b0, b1) = outputs (k0 + 2t, k0 + 2t + 1) of input n0 + g is one 64-bit load
-template <bool TWO>
-struct NetT {
-    static constexpr int S1 = 40;                        // W1T  [64 feat][32 j]
-    static constexpr int OFF_W1T = 0;
-    static constexpr int OFF_VGT = OFF_W1T + 64 * S1;    // V1T geo [16][32 j] (row 15 = 0)
-    static constexpr int OFF_VCT = OFF_VGT + 16 * S1;    // V1T colour feat [64][32 j] (two grids)
-    static constexpr int OFF_W2T = OFF_VCT + (TWO ? 64 * S1 : 0);   // W2T [32 j][16 i] stride 24
-    static constexpr int OFF_V2T = OFF_W2T + 32 * kGeoStride;       // V2T [32 j][8 c]
-    static constexpr int OFF_W1BT = OFF_V2T + 32 * kRgbStride;      // W1T blob rows [48][32 j]   (ray gradients only)
-    static constexpr int OFF_V1BT = OFF_W1BT + 48 * S1;             // V1T blob rows [48][32 j]
-    static constexpr int FLOATS_NORAY = OFF_W1BT;
-    static constexpr int FLOATS_RAY = OFF_V1BT + 48 * S1;
-};
-
-template <bool TWO, bool RAY>
-__device__ __forceinline__ void load_weights_t(const MneSceneDesc& sc, float* WT, int tid, int nthreads) {
-    using N = NetV2<TWO>;
-    using T = NetT<TWO>;
-    const bool hash = sc.encoder == 1;
-    if (RAY)
-        for (int i = tid; i < 48 * 32; i += nthreads) {
-            const int k = i >> 5, j = i & 31;
-            WT[T::OFF_W1BT + k * T::S1 + j] = sc.w_sdf0[j * sdf0_in(hash) + sdf0_col(64 + k, hash)];
-            WT[T::OFF_V1BT + k * T::S1 + j] = sc.w_col0[j * col0_in(TWO, hash) + k];
-        }
-    for (int i = tid; i < 64 * 32; i += nthreads) {
-        const int k = i >> 5, j = i & 31;
-        const int col = sdf0_col(k, hash);
-        WT[T::OFF_W1T + k * T::S1 + j] = (col >= 0) ? sc.w_sdf0[j * sdf0_in(hash) + col] : 0.0f;
-        if (TWO) WT[T::OFF_VCT + k * T::S1 + j] = (!hash || k < 32) ? sc.w_col0[j * col0_in(TWO, hash) + kBlob + k] : 0.0f;
-    }
-    for (int i = tid; i < 16 * 32; i += nthreads) {
-        const int m = i >> 5, j = i & 31;
-        WT[T::OFF_VGT + m * T::S1 + j] = (m < kGeo) ? sc.w_col0[j * col0_in(TWO, hash) + (col0_in(TWO, hash) - kGeo) + m] : 0.0f;
-        const int jj = i >> 4, c = i & 15;                     // W2T[j][c], c: 0..14 geo (out c+1), 15 sdf (out 0)
-        WT[T::OFF_W2T + jj * kGeoStride + c] = sc.w_sdf1[((c == 15) ? 0 : c + 1) * 32 + jj];
-    }
-    for (int i = tid; i < 32 * 8; i += nthreads) {
-        const int j = i >> 3, c = i & 7;
-        WT[T::OFF_V2T + j * kRgbStride + c] = (c < 3) ? sc.w_col1[c * 32 + j] : 0.0f;
-    }
-}
 
 template <bool TWO> __host__ __device__ constexpr int bwd2_warp_floats() {
     return kTilePts * (kXStride + (TWO ? kCStride : 0) + 2 * kActStride + kGeoStride + kRgbStride);
 }
-template <bool TWO, bool RAY, int NW, bool SAVED = false>
+template <bool TWO, bool RAY, int NW>
 constexpr size_t bwd2_smem_bytes() {
     // forward-recompute weights: one grid keeps the split (3-term) layout -- tighter gradients; two grids only fit with
     // the single-TF32 pair layout (half the bytes)
-    // (with the forward's activations at hand there is no recompute and the split weights are not staged at all)
-    return sizeof(float4) * (size_t)(SAVED ? 0 : NetV2<TWO>::W4_COUNT) +
+    return sizeof(float4) * (size_t)NetV2<TWO>::W4_COUNT +
            sizeof(float) * (size_t)((RAY ? NetT<TWO>::FLOATS_RAY : NetT<TWO>::FLOATS_NORAY) + NW * bwd2_warp_floats<TWO>());
-}
-
-struct PtsBwdParams {
-    MneSceneDesc sc;
-    int64_t n_pts;
-    int n_samples;
-    const float* rays_o;
-    const float* rays_d;
-    const float* z_vals;
-    const float4* draw;      // [n_pts] d loss / d raw
-    float* g_rays_o;         // [N,3] accumulated into (zeroed by the entry point), or NULL
-    float* g_rays_d;
-    const int* list;         // samples with a non-zero draw (compacted by rays_bwd_kernel)
-    const int* n_active;     // how many
-    const float* act;        // [n_pts][80] activations kept by the forward (SAVED kernels), or NULL (recompute)
-};
-
-__device__ __forceinline__ void mma_1x(float (&d)[4], float a0, float a1, float a2, float a3, float b0, float b1) {
-    const uint32_t a[4] = {__float_as_uint(a0), __float_as_uint(a1), __float_as_uint(a2), __float_as_uint(a3)};
-    mma_tf32(d, a, __float_as_uint(b0), __float_as_uint(b1));
-}
-
-// store an accumulator fragment block (rows g, g+8; cols n*8 + 2t, +1) into a [16][stride] tile
-__device__ __forceinline__ void store_frag(float* tile, int stride, int n, int g, int t, const float (&c)[4]) {
-    *reinterpret_cast<float2*>(tile + g * stride + n * 8 + 2 * t) = make_float2(c[0], c[1]);
-    *reinterpret_cast<float2*>(tile + (g + 8) * stride + n * 8 + 2 * t) = make_float2(c[2], c[3]);
 }
 
 // acc[nb] (+)= sum over the 16 points of a source tile of  A[p][m0 + ...] (x) B[p][nb*8 + ...]   (transposed product)
@@ -121,16 +43,16 @@ __device__ __forceinline__ void outer_mma(float (&acc)[NACC][4], const float* __
 // MODE: 0 = planes through strides, 1 = channels-last planes (vector gather / scatter), 2 = hash grid
 // NW = warps per CTA: 8 for one grid; two grids need more shared memory per warp and for the weights, so 6 (or 5 with
 // the ray-gradient weights); weight-gradient blocks are dealt round-robin to warps (slot = block / NW).
-// SAVED: the forward kept h1 / o16 / hc (PtsBwdParams.act): no recompute, no split weights in shared memory, more warps;
-// without parameter gradients (tracking) not even the features are gathered again.
-template <bool TWO, int MODE, bool RAY, bool PARAM, int NW, bool SAVED = false>
+// (The calls that come with the forward's kept record -- `act` -- run on the barrier-free kernels of render_bwd_v3.cu;
+// the kernels here recompute the forward and serve the calls without it.)
+template <bool TWO, int MODE, bool RAY, bool PARAM, int NW>
 __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_constant__ PtsBwdParams P) {
     using N = NetV2<TWO>;
     using T = NetT<TWO>;
     constexpr int WF = bwd2_warp_floats<TWO>();
     extern __shared__ __align__(16) float4 smem4[];
     float4* W4 = smem4;                                   // split (hi, lo) pairs for the activation recompute
-    float* WT = reinterpret_cast<float*>(W4 + (SAVED ? 0 : N::W4_COUNT));
+    float* WT = reinterpret_cast<float*>(W4 + N::W4_COUNT);
     float* tiles = WT + (RAY ? T::FLOATS_RAY : T::FLOATS_NORAY);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float* X = tiles + warp * WF;
@@ -143,7 +65,7 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
     constexpr int O_CF = kTilePts * kXStride, O_ACT = O_CF + (TWO ? kTilePts * kCStride : 0), O_DY = O_ACT + kTilePts * kActStride,
                   O_GEO = O_DY + kTilePts * kActStride, O_DRGB = O_GEO + kTilePts * kGeoStride;
 
-    if (!SAVED) load_weights_v2<TWO>(P.sc, W4, threadIdx.x, blockDim.x);
+    load_weights_v2<TWO>(P.sc, W4, threadIdx.x, blockDim.x);
     load_weights_t<TWO, RAY>(P.sc, WT, threadIdx.x, blockDim.x);
     __syncthreads();
 
@@ -202,9 +124,7 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
         const float bx0 = blob_input(px, P.sc.bbox_lo[0], P.sc.bbox_ext[0]);
         const float by0 = blob_input(py, P.sc.bbox_lo[1], P.sc.bbox_ext[1]);
         const float bz0 = blob_input(pz, P.sc.bbox_lo[2], P.sc.bbox_ext[2]);
-        if (SAVED && !PARAM) {
-            // nothing of the forward's inputs is needed: no weight gradients, activations at hand
-        } else if (MODE == 2) {
+        if (MODE == 2) {
             if (half == 0) { row[kBlobCol] = bx0; row[kBlobCol + 1] = by0; row[kBlobCol + 2] = bz0; }
             __syncwarp();
             gather16_hash(P.sc.hash[0], X + kBlobCol, kXStride, X, kXStride, np, lane);
@@ -224,7 +144,7 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
                 __syncwarp();
             }
         }
-        if (!(SAVED && !PARAM)) {
+        {
             if (half == 0) {
                 oneblob16_sparse(bx0, row + kBlobCol);
                 oneblob16_sparse(by0, row + kBlobCol + 16);
@@ -242,9 +162,7 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
         // ---- 2. the forward's activations of this tile's rows g and g+8: kept by the forward, or recomputed
         float h1[4][4], o16[2][4], hc[4][4];
         const int q_lo = __shfl_sync(0xffffffffu, q, g), q_hi = __shfl_sync(0xffffffffu, q, g + 8);
-        if (SAVED) {
-            load_act(P.act, q_lo, q_hi, g < np, g + 8 < np, t, h1, o16, hc);
-        } else {
+        {
             // same split-precision products as the forward kernel: the ReLU masks and activations must be the
             // forward's (a single-TF32 recompute flips masks of near-zero pre-activations: measured 1e-2..5e-2
             // max-norm gradient error on the two-grid goldens, against 2e-3 with the split)
@@ -682,36 +600,23 @@ __global__ void __launch_bounds__(256) rays_bwd_kernel(const RayBwdParams P) {
 
 int check_scene(const MneSceneDesc* sc, const char* who, bool need_grads);
 int sm_count();
+int points_backward_v3(const PtsBwdParams& P, bool ray, bool param, float* act, const float4* draw, cudaStream_t st);
 
-template <bool TWO, int MODE, bool RAY, bool PARAM, int NW = kBwdWarps, bool SAVED = false>
+template <bool TWO, int MODE, bool RAY, bool PARAM, int NW = kBwdWarps>
 static int launch_points_bwd(const PtsBwdParams& P, cudaStream_t stream) {
-    const size_t smem = bwd2_smem_bytes<TWO, RAY, NW, SAVED>();
+    const size_t smem = bwd2_smem_bytes<TWO, RAY, NW>();
     static bool configured[64] = {};
     int dev = 0;
     MNE_CHECK_CUDA(cudaGetDevice(&dev));
     if (dev >= 64 || !configured[dev]) {
-        MNE_CHECK_CUDA(cudaFuncSetAttribute(points_bwd_kernel<TWO, MODE, RAY, PARAM, NW, SAVED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        MNE_CHECK_CUDA(cudaFuncSetAttribute(points_bwd_kernel<TWO, MODE, RAY, PARAM, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (dev < 64) configured[dev] = true;
     }
     const int64_t n_tiles = (P.n_pts + kTilePts - 1) / kTilePts;
     const int blocks = (int)max((int64_t)1, min((n_tiles + NW - 1) / NW, (int64_t)sm_count()));
-    points_bwd_kernel<TWO, MODE, RAY, PARAM, NW, SAVED><<<blocks, NW * 32, smem, stream>>>(P);
+    points_bwd_kernel<TWO, MODE, RAY, PARAM, NW><<<blocks, NW * 32, smem, stream>>>(P);
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
-}
-
-// with the forward's activations: no split weights in shared memory, so more warps fit (one grid: 12; two grids: 8..10,
-// and ray AND parameter gradients together fit too)
-template <int MODE>
-static int dispatch_points_bwd_saved(const PtsBwdParams& P, bool ray, bool param, cudaStream_t st) {
-    if (P.sc.two_grid) {
-        if (ray && param) return launch_points_bwd<true, MODE, true, true, 8, true>(P, st);
-        if (ray) return launch_points_bwd<true, MODE, true, false, 9, true>(P, st);
-        return launch_points_bwd<true, MODE, false, true, 10, true>(P, st);
-    }
-    if (ray && param) return launch_points_bwd<false, MODE, true, true, kSavedWarps, true>(P, st);
-    if (ray) return launch_points_bwd<false, MODE, true, false, kSavedWarps, true>(P, st);
-    return launch_points_bwd<false, MODE, false, true, kSavedWarps, true>(P, st);
 }
 
 template <int MODE>
@@ -752,14 +657,15 @@ int render_backward_v2(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int3
     P.rays_o = rays_o; P.rays_d = rays_d; P.z_vals = z_vals; P.draw = reinterpret_cast<const float4*>(scratch);
     P.g_rays_o = g_rays_o; P.g_rays_d = g_rays_d; P.list = R.list; P.n_active = R.n_active; P.act = act;
     const bool ray = g_rays_o != nullptr;
+    if (act && (scene->encoder == 1 || planes_vectorizable(*scene)))
+        return points_backward_v3(P, ray, param_grad, const_cast<float*>(act), R.draw, st);
     if (scene->encoder == 1) {
-        if (act) return dispatch_points_bwd_saved<2>(P, ray, param_grad, st);
         MNE_CHECK_ARG(!scene->two_grid, "mne_render_backward: the two-table hash grid needs the forward's activation buffer (act)");
         if (ray && param_grad) return launch_points_bwd<false, 2, true, true>(P, st);
         if (ray) return launch_points_bwd<false, 2, true, false>(P, st);
         return launch_points_bwd<false, 2, false, true>(P, st);
     }
-    if (planes_vectorizable(*scene)) return act ? dispatch_points_bwd_saved<1>(P, ray, param_grad, st) : dispatch_points_bwd<1>(P, ray, param_grad, st);
+    if (planes_vectorizable(*scene)) return dispatch_points_bwd<1>(P, ray, param_grad, st);
     MNE_CHECK_ARG(!scene->dirty, "mne_render_backward: MneSceneDesc.dirty needs channels-last planes or the hash grid");
     return dispatch_points_bwd<0>(P, ray, param_grad, st);
 }

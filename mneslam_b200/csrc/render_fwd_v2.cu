@@ -23,13 +23,14 @@ struct PtsFwdParams {
     float* raw;               // [M,4]
     float* geo;               // [M,15] or NULL
     float* feat;              // [M,64] or NULL
-    float* act;               // [M,80] hidden activations kept for the backward (tile16.cuh: store_act), or NULL
+    float* act;               // [M, ActRow::STRIDE] per-sample record kept for the backward (tile16.cuh: ActRow), or NULL
 };
 
 // MODE: 0 = planes through strides, 1 = channels-last planes (vector gather), 2 = hash grid
 template <bool TWO, int MODE>
 __global__ void __launch_bounds__(pts_warps<TWO>() * 32, 1) points_fwd_kernel(const __grid_constant__ PtsFwdParams P) {
     using N = NetV2<TWO>;
+    using AR = ActRow<TWO, MODE == 2>;
     constexpr int NW = pts_warps<TWO>();
     extern __shared__ __align__(16) float4 smem4[];
     float4* W4 = smem4;
@@ -66,6 +67,7 @@ __global__ void __launch_bounds__(pts_warps<TWO>() * 32, 1) points_fwd_kernel(co
         const float bx = blob_input(px, P.sc.bbox_lo[0], P.sc.bbox_ext[0]);
         const float by = blob_input(py, P.sc.bbox_lo[1], P.sc.bbox_ext[1]);
         const float bz = blob_input(pz, P.sc.bbox_lo[2], P.sc.bbox_ext[2]);
+        float* arow = P.act ? P.act + pt0 * AR::STRIDE : nullptr;       // this tile's rows of the kept record
         if (MODE == 2) {
             // ---- hash grid: the table is addressed with the [0,1] coordinates the OneBlob uses; park them in the
             //      point's blob segment, gather, then let the OneBlob overwrite them
@@ -74,19 +76,36 @@ __global__ void __launch_bounds__(pts_warps<TWO>() * 32, 1) points_fwd_kernel(co
             gather16_hash(P.sc.hash[0], X + kBlobCol, kXStride, X, kXStride, np, lane);
             if (TWO) gather16_hash(P.sc.hash[1], X + kBlobCol, kXStride, CFt, kCStride, np, lane);      // colour table
             __syncwarp();
+            if (arow) {
+                for (int p = 0; p < np; ++p) {
+                    arow[(int64_t)p * AR::STRIDE + AR::FEAT + lane] = X[p * kXStride + lane];
+                    if (TWO) arow[(int64_t)p * AR::STRIDE + AR::CFEAT + lane] = CFt[p * kCStride + lane];
+                }
+            }
         } else {
-            // ---- tap table into the point's blob segment, gather, then (two grids) the same for the colour planes
-            if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 0);
+            // ---- tap table into the point's blob segment (lane (point, half) writes level `half`), gather, then (two
+            //      grids) the same for the colour planes
+            write_taps8_level(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 0, half);
             __syncwarp();
-            if (MODE == 1) gather16_vec(P.sc, 0, X + kBlobCol, kXStride, X, kXStride, np, lane);
+            if (MODE == 1) gather16_pq(P.sc, 0, X + kBlobCol, kXStride, X, kXStride, np, lane, arow ? arow + AR::FEAT : nullptr, AR::STRIDE);
             else gather16(P.sc, 0, X + kBlobCol, kXStride, X, kXStride, np, lane);
             __syncwarp();
             if (TWO) {
-                if (half == 1) write_taps8<TWO>(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 1);
+                write_taps8_level(P.sc, reinterpret_cast<float4*>(row + kBlobCol), px, py, pz, 1, half);
                 __syncwarp();
-                if (MODE == 1) gather16_vec(P.sc, 1, X + kBlobCol, kXStride, CFt, kCStride, np, lane);
+                if (MODE == 1) gather16_pq(P.sc, 1, X + kBlobCol, kXStride, CFt, kCStride, np, lane, arow ? arow + AR::CFEAT : nullptr, AR::STRIDE);
                 else gather16(P.sc, 1, X + kBlobCol, kXStride, CFt, kCStride, np, lane);
                 __syncwarp();
+            }
+            if (MODE == 0 && arow) {
+                for (int p = 0; p < np; ++p) {
+                    arow[(int64_t)p * AR::STRIDE + AR::FEAT + lane] = X[p * kXStride + lane];
+                    arow[(int64_t)p * AR::STRIDE + AR::FEAT + 32 + lane] = X[p * kXStride + 32 + lane];
+                    if (TWO) {
+                        arow[(int64_t)p * AR::STRIDE + AR::CFEAT + lane] = CFt[p * kCStride + lane];
+                        arow[(int64_t)p * AR::STRIDE + AR::CFEAT + 32 + lane] = CFt[p * kCStride + 32 + lane];
+                    }
+                }
             }
         }
         // ---- OneBlob over the (now dead) tap table: half 0 -> dims 0,1 ; half 1 -> dim 2
@@ -110,7 +129,7 @@ __global__ void __launch_bounds__(pts_warps<TWO>() * 32, 1) points_fwd_kernel(co
         // ---- decoder
         float h1[4][4], o16[2][4], hc[4][4], rgb[4];
         decoder_forward_mma<TWO>(W4, X, CFt, lane, h1, o16, hc, rgb);
-        if (P.act) store_act(P.act, pt0 + g, pt0 + g + 8, g < np, g + 8 < np, t, h1, o16, hc);
+        if (P.act) store_act<AR::STRIDE, AR::MASK>(P.act, pt0 + g, pt0 + g + 8, g < np, g + 8 < np, t, h1, o16, hc);
         // rows g, g+8: rgb columns 0,1 on t = 0, column 2 on t = 1; sdf = column 15 of o16 = o16[1][1|3] on t = 3
         const int quad = lane & ~3;
         const float b_lo = __shfl_sync(0xffffffffu, rgb[0], quad | 1), b_hi = __shfl_sync(0xffffffffu, rgb[2], quad | 1);
@@ -273,7 +292,7 @@ extern "C" int mne_render_forward(const MneSceneDesc* scene, const MneRenderCfg*
     PtsFwdParams P{};
     P.sc = *scene; P.n_pts = (int64_t)n_rays * n_samples; P.n_samples = n_samples;
     P.rays_o = rays_o; P.rays_d = rays_d; P.z_vals = z_vals; P.raw = raw; P.act = act;
-    MNE_CHECK_ARG(((uintptr_t)act & 7) == 0, "mne_render_forward: act must be 8-byte aligned");
+    MNE_CHECK_ARG(((uintptr_t)act & 31) == 0, "mne_render_forward: act must be 32-byte aligned");
     if (int e = dispatch_points_fwd(P, (cudaStream_t)stream)) return e;
     RayFwdParams R{};
     R.rc = *rcfg; R.n_rays = n_rays; R.n_samples = n_samples; R.z_vals = z_vals; R.raw = raw;
@@ -283,6 +302,11 @@ extern "C" int mne_render_forward(const MneSceneDesc* scene, const MneRenderCfg*
     rays_fwd_kernel<<<blocks, kRayWarps * 32, 0, (cudaStream_t)stream>>>(R);
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
+}
+
+extern "C" int mne_act_floats(const MneSceneDesc* scene) {
+    if (!scene) return MNE_ACT_FLOATS_MAX;
+    return mne::act_row_floats(scene->two_grid != 0, scene->encoder == 1);
 }
 
 extern "C" int mne_query_points(const MneSceneDesc* scene, int64_t n_pts, const float* pts, float* raw, float* geo,

@@ -220,6 +220,64 @@ __device__ __forceinline__ void gather16_vec(const MneSceneDesc& sc, int grp, co
     }
 }
 
+// taps of one point for ONE level (the three planes xy / xz / yz of that level): the two lanes of a point each take a level
+__device__ __forceinline__ void write_taps8_level(const MneSceneDesc& sc, float4* seg, float px, float py, float pz, int grp, int level) {
+    const float n[3] = {plane_coord(px, sc.bound_lo[0], sc.bound_ext[0]), plane_coord(py, sc.bound_lo[1], sc.bound_ext[1]),
+                        plane_coord(pz, sc.bound_lo[2], sc.bound_ext[2])};
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float gx = (a == 2) ? n[1] : n[0];
+        const float gy = (a == 0) ? n[1] : n[2];
+        const int t = a * 2 + level;
+        int4 off; float4 w;
+        make_tap8(sc.planes[grp * 6 + t], gx, gy, off, w);
+        seg[2 * t] = make_float4(__int_as_float(off.x), __int_as_float(off.y), __int_as_float(off.z), __int_as_float(off.w));
+        seg[2 * t + 1] = w;
+    }
+}
+
+// Channels-last gather, lane = (point of a quad, 4-channel group): a lane fetches the four corner texels of every tap
+// of ITS point (four 128-bit loads per tap; one warp instruction covers 4 points x one 128-byte texel line each) and
+// blends them in registers in the reference's order (per plane nw, ne, sw, se; then (xy + xz) + yz) -- no cross-lane
+// reduction, two 128-bit tap-table reads per tap.  `save` (optional): the features are also written to global memory,
+// row p at save + p * save_stride (the backward's weight-gradient kernel reads them instead of gathering again).
+__device__ __forceinline__ void gather16_pq(const MneSceneDesc& sc, int grp, const float* __restrict__ tab_base, int tab_stride,
+                                            float* __restrict__ dst, int dst_stride, int np, int lane,
+                                            float* __restrict__ save = nullptr, int save_stride = 0) {
+    const int pp = lane >> 3, q = lane & 7;
+    const float* base[6];
+#pragma unroll
+    for (int t = 0; t < 6; ++t) base[t] = sc.planes[grp * 6 + t].data + q * 4;
+#pragma unroll 1
+    for (int p0 = 0; p0 < kTilePts; p0 += 4) {
+        const int p = p0 + pp;
+        if (p >= np) continue;
+        const float* seg = tab_base + p * tab_stride;
+#pragma unroll
+        for (int l = 0; l < 2; ++l) {
+            float4 s[3];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const int t = a * 2 + l;
+                const uint4 off = *reinterpret_cast<const uint4*>(seg + 8 * t);
+                const float4 w = *reinterpret_cast<const float4*>(seg + 8 * t + 4);
+                const float4 v00 = __ldg(reinterpret_cast<const float4*>(base[t] + off.x));
+                const float4 v01 = __ldg(reinterpret_cast<const float4*>(base[t] + off.y));
+                const float4 v10 = __ldg(reinterpret_cast<const float4*>(base[t] + off.z));
+                const float4 v11 = __ldg(reinterpret_cast<const float4*>(base[t] + off.w));
+                s[a].x = fmaf(w.w, v11.x, fmaf(w.z, v10.x, fmaf(w.y, v01.x, w.x * v00.x)));
+                s[a].y = fmaf(w.w, v11.y, fmaf(w.z, v10.y, fmaf(w.y, v01.y, w.x * v00.y)));
+                s[a].z = fmaf(w.w, v11.z, fmaf(w.z, v10.z, fmaf(w.y, v01.z, w.x * v00.z)));
+                s[a].w = fmaf(w.w, v11.w, fmaf(w.z, v10.w, fmaf(w.y, v01.w, w.x * v00.w)));
+            }
+            const float4 f = make_float4((s[0].x + s[1].x) + s[2].x, (s[0].y + s[1].y) + s[2].y,
+                                         (s[0].z + s[1].z) + s[2].z, (s[0].w + s[1].w) + s[2].w);
+            *reinterpret_cast<float4*>(dst + p * dst_stride + l * 32 + q * 4) = f;
+            if (save) *reinterpret_cast<float4*>(save + (int64_t)p * save_stride + l * 32 + q * 4) = f;
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // multi-resolution hash grid (tiny-cuda-nn encodings/grid.h; restated in oracle/hashgrid.py).
 // lane = (point parity, level): 16 levels x 2 points per trip, 8 corner loads of one float2 (2 features) each.
@@ -254,7 +312,7 @@ __device__ __forceinline__ HashCell hash_cell(const HashLevel& L, const float* x
     HashCell c;
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
-        const float pos = __fadd_rn(__fmul_rn(x[d], L.scale), 0.5f);
+        const float pos = fmaf(x[d], L.scale, 0.5f);          // one rounding, as tiny-cuda-nn's pos_fract
         const float fl = floorf(pos);
         c.f[d] = pos - fl;
         c.g[d] = (uint32_t)(int)fl;
@@ -417,42 +475,61 @@ __device__ __forceinline__ float oneblob16_sparse_grad(float x, const float* gb)
 }
 
 // ---------------------------------------------------------------------------------------------
-// Activations kept from the forward for the backward (optional): per sample 80 floats = h1[32] | o16[16] | hc[32], in
-// the accumulator-fragment order of the tile (rows g / g+8, columns n*8 + 2t, +1), so both kernels move them as 64-bit
-// words.  With them the backward needs no forward recompute (and no split weights in shared memory).
+// Per-sample record the forward keeps for the backward (optional; what autograd would save).  One row per sample,
+// floats:   h1[32] | o16[16] = (geo0..14, sdf) | hc[32] | feat[F] | cfeat[F] (two grids) | dY[80] | masks[2] + pad[6]
+// with F = 64 (planes) or 32 (hash grid).  h1 / hc are post-ReLU; masks = the bit sets (h1 > 0), (hc > 0) as two 32-bit
+// words (all the backward tile kernel needs of them); dY = d h1[32] | d o16[16] | d hc[32] is WRITTEN by the backward tile
+// kernel and read, with everything else, by the weight-gradient kernel.  Rows are 32-byte aligned (stride % 8 == 0).
 // ---------------------------------------------------------------------------------------------
-constexpr int kActFloats = 80;
-__device__ __forceinline__ void store_act(float* __restrict__ act, int64_t s_lo, int64_t s_hi, bool ok_lo, bool ok_hi, int t,
-                                          const float (&h1)[4][4], const float (&o16)[2][4], const float (&hc)[4][4]) {
-    float2* lo = reinterpret_cast<float2*>(act + s_lo * kActFloats) + t;
-    float2* hi = reinterpret_cast<float2*>(act + s_hi * kActFloats) + t;
+template <bool TWO, bool HASH>
+struct ActRow {
+    static constexpr int F = HASH ? 32 : 64;
+    static constexpr int H1 = 0, O16 = 32, HC = 48, FEAT = 80, CFEAT = 80 + F;
+    static constexpr int DY = 80 + F + (TWO ? F : 0);          // d h1 at DY, d o16 at DY + 32, d hc at DY + 48
+    static constexpr int MASK = DY + 80;
+    static constexpr int STRIDE = MASK + 8;
+};
+__host__ __device__ inline int act_row_floats(bool two, bool hash) {
+    const int F = hash ? 32 : 64;
+    return 80 + F + (two ? F : 0) + 80 + 8;
+}
+
+// fragment blocks -> row columns: lane (g, t) holds rows g / g + 8, columns n * 8 + 2t, +1 of every 8-wide block
+template <int NB>
+__device__ __forceinline__ void store_frag_rows(float* __restrict__ lo, float* __restrict__ hi, bool ok_lo, bool ok_hi, int t,
+                                                const float (&c)[NB][4]) {
 #pragma unroll
-    for (int n = 0; n < 4; ++n) {
-        if (ok_lo) { lo[n * 4] = make_float2(h1[n][0], h1[n][1]); lo[24 + n * 4] = make_float2(hc[n][0], hc[n][1]); }
-        if (ok_hi) { hi[n * 4] = make_float2(h1[n][2], h1[n][3]); hi[24 + n * 4] = make_float2(hc[n][2], hc[n][3]); }
-    }
-#pragma unroll
-    for (int n = 0; n < 2; ++n) {
-        if (ok_lo) lo[16 + n * 4] = make_float2(o16[n][0], o16[n][1]);
-        if (ok_hi) hi[16 + n * 4] = make_float2(o16[n][2], o16[n][3]);
+    for (int n = 0; n < NB; ++n) {
+        if (ok_lo) *reinterpret_cast<float2*>(lo + n * 8 + 2 * t) = make_float2(c[n][0], c[n][1]);
+        if (ok_hi) *reinterpret_cast<float2*>(hi + n * 8 + 2 * t) = make_float2(c[n][2], c[n][3]);
     }
 }
-__device__ __forceinline__ void load_act(const float* __restrict__ act, int64_t s_lo, int64_t s_hi, bool ok_lo, bool ok_hi, int t,
-                                         float (&h1)[4][4], float (&o16)[2][4], float (&hc)[4][4]) {
-    const float2* lo = reinterpret_cast<const float2*>(act + s_lo * kActFloats) + t;
-    const float2* hi = reinterpret_cast<const float2*>(act + s_hi * kActFloats) + t;
-    const float2 z = make_float2(0.f, 0.f);
+// bit (n * 8 + 2t + j) of the row's mask = (c[n][row * 2 + j] > 0); the four lanes of a quad OR their parts together
+__device__ __forceinline__ void relu_masks(const float (&c)[4][4], unsigned& m_lo, unsigned& m_hi, int t) {
+    m_lo = 0u; m_hi = 0u;
 #pragma unroll
     for (int n = 0; n < 4; ++n) {
-        const float2 a = ok_lo ? __ldg(lo + n * 4) : z, b = ok_hi ? __ldg(hi + n * 4) : z;
-        const float2 c = ok_lo ? __ldg(lo + 24 + n * 4) : z, d = ok_hi ? __ldg(hi + 24 + n * 4) : z;
-        h1[n][0] = a.x; h1[n][1] = a.y; h1[n][2] = b.x; h1[n][3] = b.y;
-        hc[n][0] = c.x; hc[n][1] = c.y; hc[n][2] = d.x; hc[n][3] = d.y;
+        const int b = n * 8 + 2 * t;
+        m_lo |= (c[n][0] > 0.f ? 1u : 0u) << b | (c[n][1] > 0.f ? 2u : 0u) << b;
+        m_hi |= (c[n][2] > 0.f ? 1u : 0u) << b | (c[n][3] > 0.f ? 2u : 0u) << b;
     }
-#pragma unroll
-    for (int n = 0; n < 2; ++n) {
-        const float2 a = ok_lo ? __ldg(lo + 16 + n * 4) : z, b = ok_hi ? __ldg(hi + 16 + n * 4) : z;
-        o16[n][0] = a.x; o16[n][1] = a.y; o16[n][2] = b.x; o16[n][3] = b.y;
+    m_lo |= __shfl_xor_sync(0xffffffffu, m_lo, 1); m_lo |= __shfl_xor_sync(0xffffffffu, m_lo, 2);
+    m_hi |= __shfl_xor_sync(0xffffffffu, m_hi, 1); m_hi |= __shfl_xor_sync(0xffffffffu, m_hi, 2);
+}
+template <int STRIDE, int MASK>
+__device__ __forceinline__ void store_act(float* __restrict__ act, int64_t s_lo, int64_t s_hi, bool ok_lo, bool ok_hi, int t,
+                                          const float (&h1)[4][4], const float (&o16)[2][4], const float (&hc)[4][4]) {
+    float* lo = act + s_lo * STRIDE;
+    float* hi = act + s_hi * STRIDE;
+    store_frag_rows<4>(lo, hi, ok_lo, ok_hi, t, h1);
+    store_frag_rows<2>(lo + 32, hi + 32, ok_lo, ok_hi, t, o16);
+    store_frag_rows<4>(lo + 48, hi + 48, ok_lo, ok_hi, t, hc);
+    unsigned a_lo, a_hi, c_lo, c_hi;
+    relu_masks(h1, a_lo, a_hi, t);
+    relu_masks(hc, c_lo, c_hi, t);
+    if (t == 0) {
+        if (ok_lo) *reinterpret_cast<uint2*>(lo + MASK) = make_uint2(a_lo, c_lo);
+        if (ok_hi) *reinterpret_cast<uint2*>(hi + MASK) = make_uint2(a_hi, c_hi);
     }
 }
 

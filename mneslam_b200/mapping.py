@@ -219,9 +219,10 @@ class FusedMapper:
         rcfg = ops.make_render_cfg(cfg, norm_rays=self.global_rays_override or n * self.world_size)
         td = target_d.reshape(-1)
         z_vals, acc = sampled if sampled is not None else self.sample_stage(target_d, noise)
-        if self._act is None or self._act.numel() < n * s * _lib.ACT_FLOATS:
-            self._act = torch.empty(n * s * _lib.ACT_FLOATS, dtype=torch.float32, device=dev)
-        out = ops.render_forward(self._scene(False), rcfg, rays_o, rays_d, z_vals, target_rgb, td, acc,
+        scene = self._scene(False)
+        if self._act is None or self._act.numel() < n * s * ops.act_floats(scene):
+            self._act = torch.empty(n * s * ops.act_floats(scene), dtype=torch.float32, device=dev)
+        out = ops.render_forward(scene, rcfg, rays_o, rays_d, z_vals, target_rgb, td, acc,
                                  want_aux=False, act=self._act)
         if self.world_size > 1:
             torch.distributed.all_reduce(acc, group=self.group)
@@ -289,7 +290,10 @@ class FusedMapper:
         return self.step(rays_o, rays_d, t['rgb'].detach(), t['depth'].detach().unsqueeze(-1))
 
     def total_loss(self, losses):
-        return (losses[:7] * self.loss_weights[:7]).sum()
+        """``get_loss_from_ret`` (mneslam_mp.py:350-372): only the selected loss family enters the sum -- a loss with weight
+        zero is never touched there, so its value (``nan`` when its mask is empty) must not reach the total."""
+        w = self.loss_weights[:7]
+        return torch.where(w != 0, losses[:7] * w, torch.zeros_like(w)).sum()
 
     def losses_dict(self, losses):
         return {k: losses[i] for i, k in enumerate(LOSS_KEYS)}

@@ -205,10 +205,15 @@ def sample_rays(sample_cfg, render_cfg, n_rays, n_samples, target_d, noise, acc,
     return z
 
 
+def act_floats(scene):
+    """Floats per sample of the record the forward keeps for the backward (``mne_act_floats``)."""
+    return _lib.lib().mne_act_floats(C.byref(scene))
+
+
 def render_forward(scene, render_cfg, rays_o, rays_d, z_vals, target_rgb=None, target_d=None, acc=None,
                    want_weights=False, want_aux=True, act=None):
-    """``act``: True = allocate, or a float32 buffer of n * s * ACT_FLOATS elements: the decoders' hidden activations are
-    kept there for ``render_backward`` (returned as ``out['act']``)."""
+    """``act``: True = allocate, or a float32 buffer of n * s * ``act_floats(scene)`` elements: the per-sample record (hidden
+    activations, features, ReLU masks) is kept there for ``render_backward`` (returned as ``out['act']``)."""
     n, s = z_vals.shape
     dev = z_vals.device
     ro, rd = _f32(rays_o, 'rays_o'), _f32(rays_d, 'rays_d')
@@ -223,10 +228,10 @@ def render_forward(scene, render_cfg, rays_o, rays_d, z_vals, target_rgb=None, t
     if want_weights:
         out['weights'] = torch.empty(n, s, dtype=torch.float32, device=dev)
     if act is True:
-        act = torch.empty(n * s * _lib.ACT_FLOATS, dtype=torch.float32, device=dev)
+        act = torch.empty(n * s * act_floats(scene), dtype=torch.float32, device=dev)
     if act is not None:
-        if act.dtype != torch.float32 or act.numel() < n * s * _lib.ACT_FLOATS or not act.is_contiguous():
-            raise TypeError('act must be a contiguous float32 buffer of at least n_rays * n_samples * %d elements' % _lib.ACT_FLOATS)
+        if act.dtype != torch.float32 or act.numel() < n * s * act_floats(scene) or not act.is_contiguous() or act.data_ptr() % 32:
+            raise TypeError('act must be a contiguous, 32-byte aligned float32 buffer of at least n_rays * n_samples * %d elements' % act_floats(scene))
         out['act'] = act
     _lib.check(_lib.lib().mne_render_forward(
         C.byref(scene), C.byref(render_cfg), n, s, _ptr(ro), _ptr(rd), _ptr(z_vals), _ptr(trgb), _ptr(td),

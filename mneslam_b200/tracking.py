@@ -147,7 +147,7 @@ class FusedTracker:
         acc = ops.new_acc(dev)
         z_vals = ops.sample_rays(ops.make_sample_cfg(tables, perturb), rcfg, n, s, td, noise if perturb else None, acc, dev)
         if self._for != (n, s):
-            self._act = torch.empty(n * s * _lib.ACT_FLOATS, dtype=torch.float32, device=dev)
+            self._act = torch.empty(n * s * _lib.ACT_FLOATS_MAX, dtype=torch.float32, device=dev)
             self._scratch = ops.backward_scratch(n, s, dev)
             self._for = (n, s)
         scene = ops.make_scene(model._flat_planes(), [w.detach() for w in model.decoder.weight_list()], model.bound,
@@ -186,7 +186,7 @@ class FusedTracker:
         rcfg = ops.make_render_cfg(cfg, norm_rays=n)
         z_vals = ops.sample_rays(ops.make_sample_cfg(tables, perturb), rcfg, n, s, None, noise if perturb else None, None, dev)
         if self._for != (n, s):
-            self._act = torch.empty(n * s * _lib.ACT_FLOATS, dtype=torch.float32, device=dev)
+            self._act = torch.empty(n * s * _lib.ACT_FLOATS_MAX, dtype=torch.float32, device=dev)
             self._scratch = ops.backward_scratch(n, s, dev)
             self._for = (n, s)
         scene = ops.make_scene(model._flat_planes(), [w.detach() for w in model.decoder.weight_list()], model.bound,

@@ -9,7 +9,9 @@ restates its published algorithm ("pure-torch hash grid with tcnn's hashing cons
 
 * level ``l``: ``scale = 2^(l * log2(per_level_scale)) * base - 1``, ``resolution = ceil(scale) + 1``,
   entries ``= min(2^log2_hashmap_size, round_up(resolution^3, 8))``, levels stored back to back;
-* a point ``x`` in ``[0,1]^3``: ``pos = x * scale + 0.5``; cell = ``floor(pos)`` (as uint32), ``frac = pos - floor``;
+* a point ``x`` in ``[0,1]^3``: ``pos = fmaf(x, scale, 0.5)`` (ONE rounding, as tiny-cuda-nn's ``pos_fract``; restated here
+  as the float32 rounding of the float64 product-and-sum: the product of two float32 is exact in float64);
+  cell = ``floor(pos)`` (as uint32), ``frac = pos - floor``;
 * corner index: ``x + y*res + z*res^2`` while the running stride fits the level, otherwise the coherent prime hash
   ``x ^ (y * 2654435761) ^ (z * 805459861)`` in uint32; then ``% entries``;
 * output = trilinear blend of the ``n_features`` values of the 8 corners, levels concatenated (level-major).
@@ -61,11 +63,16 @@ def init_table(meta, seed=0, scale=1e-4):
     return (torch.rand(meta['offsets'][-1], meta['n_features'], generator=gen) * 2 - 1) * scale
 
 
+def fused_pos(x, scale):
+    """fmaf(x, scale, 0.5) in float32: product and sum in float64 (the product is exact there), one rounding to float32."""
+    return (x.double() * scale.double() + 0.5).float()
+
+
 def corner_indices(meta, x, level):
     """Entry indices (within the level) of the 8 corners and the fractional position.  x: [M,3] float32."""
     scale = torch.tensor(meta['scales'][level])
     res, size = meta['resolutions'][level], meta['sizes'][level]
-    pos = x * scale + 0.5                     # tcnn uses fmaf; a product-then-add differs by < 1 ulp of pos
+    pos = fused_pos(x, scale)
     cell_f = torch.floor(pos)
     frac = pos - cell_f
     cell = cell_f.to(torch.int64) & MASK      # (uint32_t)(int) wrap-around
@@ -91,7 +98,8 @@ def encode(meta, table, x):
         idx = idx + meta['offsets'][l]
         # fractional position with gradient (pose path); indices carry none
         scale = torch.tensor(meta['scales'][l])
-        pos = x * scale + 0.5
+        xs = x * scale
+        pos = fused_pos(x.detach(), scale) + (xs - xs.detach())     # value: the fused rounding; gradient: d pos / d x = scale
         f = pos - torch.floor(pos.detach())
         acc = 0
         for c in range(8):

@@ -286,7 +286,7 @@ def test_backward_with_kept_activations_equals_recompute(two_grid, mode):
     z = ops.sample_rays(ops.make_sample_cfg(tables, True), rcfg, n, s, td, noise, acc, 'cuda')
     sc = ops.make_scene(fp, [w.detach() for w in ws], model.bound, model.bounding_box)
     out = ops.render_forward(sc, rcfg, b['rays_o'], b['rays_d'], z, b['target_rgb'], td, acc, act=True)
-    assert out['act'].numel() == n * s * 80
+    assert out["act"].numel() == n * s * ops.act_floats(sc)
     lg = torch.tensor([1.0, 0.5, 2.0, 3.0, 2.0, 4.0, 1.5, 0.0], device='cuda')
     want_p, want_r = mode in ('param', 'both'), mode in ('ray', 'both')
     res = []
@@ -333,8 +333,8 @@ def test_workspaces_are_not_overrun(n_rays):
     z_full, z = guarded(n * s)
     z = z.view(n, s)
     ops.sample_rays(ops.make_sample_cfg(tables, True), rcfg, n, s, td, noise, acc, 'cuda', out=z)
-    act_full, act = guarded(n * s * _lib.ACT_FLOATS)
     sc = ops.make_scene(fp, ws, model.bound, model.bounding_box)
+    act_full, act = guarded(n * s * ops.act_floats(sc))
     out = ops.render_forward(sc, rcfg, b['rays_o'], b['rays_d'], z, b['target_rgb'], td, acc, act=act)
     nbytes = _lib.lib().mne_backward_scratch_bytes(n, s)
     assert nbytes % 4 == 0

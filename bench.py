@@ -274,7 +274,7 @@ def run_ours(args):
     gen = torch.Generator(device=dev)
     gen.manual_seed(1234 + rank)
 
-    # assemble_rays | sample | points_fwd, rays_fwd | loss_finalize | rays_bwd, points_bwd | adam_tick, adam_segments
+    # assemble_rays | sample | points_fwd (fused render) | loss_finalize | points_bwd3 | decoder_wgrad | adam_tick, adam_segments x2
     launches_per_step = 9
 
     def one_step():
@@ -378,7 +378,8 @@ def run_ours(args):
     tables = ops.SampleTables.get(cfg, dev, True)
     scfg = ops.make_sample_cfg(tables, True)
     rcfg = ops.make_render_cfg(cfg, norm_rays=n_rays * world)
-    ev = {'sample': [], 'fwd': [], 'bwd': [], 'adam': []}
+    ev = {'sample': [], 'fwd': [], 'fwd_single_launch': [], 'bwd': [], 'wgrad': [], 'adam': []}
+    counters = torch.zeros(n_rays, dtype=torch.int32, device=dev)
     k_prof = min(args.steps, 20)
     for _ in range(k_prof):
         ro, rd, trgb, td = db.sample(n_rays)
@@ -386,13 +387,20 @@ def run_ours(args):
         noise = torch.rand(n_rays, s, device=dev)
         acc = ops.new_acc(dev)
         z, e = timed(lambda: ops.sample_rays(scfg, rcfg, n_rays, s, tdf, noise, acc, dev)); ev['sample'].append(e)
-        sc_f, sc_b = mapper._scene(False), mapper._scene(True)          # descriptors built outside the timed intervals
-        out, e = timed(lambda: ops.render_forward(sc_f, rcfg, ro, rd, z, trgb, tdf, acc, want_aux=False, act=mapper._act)); ev['fwd'].append(e)
         if world > 1:
-            dist.all_reduce(acc)
+            dist.all_reduce(acc[:6])
+        # descriptors built outside the timed intervals
+        sc_f, sc_b, sc_w = mapper._scene(False), mapper._scene(True, weight_grads=False), mapper._scene(True, plane_grads=False)
         scr = mapper._scratch
-        _, e = timed(lambda: ops.render_backward(sc_b, rcfg, ro, rd, z, out['raw'], trgb, tdf, acc,
-                                                 loss_grads=mapper.loss_grads, scratch=scr, act=mapper._act)); ev['bwd'].append(e)
+        # fwd = the fused forward: encode, decode, compositing, loss sums, d loss / d raw + compaction (one launch)
+        out, e = timed(lambda: ops.render_forward(sc_f, rcfg, ro, rd, z, trgb, tdf, acc, want_aux=False, act=mapper._act,
+                                                  ray_counters=None, loss_grads=mapper.loss_grads, scratch=scr)); ev['fwd'].append(e)
+        out, e = timed(lambda: ops.render_forward(sc_f, rcfg, ro, rd, z, trgb, tdf, acc.clone(), want_aux=False, act=mapper._act,
+                                                  ray_counters=counters, loss_grads=mapper.loss_grads, scratch=scr)); ev['fwd_single_launch'].append(e)
+        # bwd = the point backward (decoder backward + plane scatter); wgrad = the decoder weight gradients, full grid
+        _, e = timed(lambda: ops.render_backward_points(sc_b, ro, rd, z, scr, act=mapper._act)); ev['bwd'].append(e)
+        _, e = timed(lambda: ops.decoder_wgrad(sc_w, n_rays, s, scr, mapper._act)); ev['wgrad'].append(e)
+        mapper._pending_wgrad = None
         _, e = timed(mapper.optimizer_step); ev['adam'].append(e)
     torch.cuda.synchronize()
     us = {k: 1e3 * sum(a.elapsed_time(b) for a, b in v) / len(v) for k, v in ev.items()}
@@ -623,11 +631,11 @@ def run_ours(args):
                          'points_fwd_kernel': {'achieved': fwd_gbs, 'frac': fwd_gbs / peak, 'launch_us': us['fwd'],
                                                'algorithmic_bytes_per_launch': fwd_bytes,
                                                'traffic': ncu_traffic('points_fwd_kernel'),
-                                               'note': 'launch_us includes rays_fwd_kernel (compositing + loss sums)'},
+                                               'note': 'the fused render: encode, decode, compositing, loss sums, d loss / d raw + sample compaction in one launch'},
                          'points_bwd_kernel': {'achieved': bwd_gbs, 'frac': bwd_gbs / peak, 'launch_us': us['bwd'],
                                                'algorithmic_bytes_per_launch': bwd_bytes, 'active_samples': n_active,
                                                'traffic': ncu_traffic('points_bwd_kernel'),
-                                               'note': 'launch_us includes rays_bwd_kernel (d loss / d raw + compaction)'}},
+                                               'note': 'points_bwd3_kernel: decoder backward + plane scatter over the active samples; the decoder weight gradients (breakdown_us.wgrad) run beside the optimiser'}},
             'breakdown_us': us,
             'fwd_bwd_points_per_s': pts_per_rank * world / ((us['sample'] + us['fwd'] + us['bwd']) * 1e-6),
             'clocks': clocks,

@@ -187,6 +187,25 @@ int mne_render_forward(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int3
                        const float* target_d, float* raw, float* weights, float* rgb, float* depth, float* disp,
                        float* acc_map, float* depth_var, int32_t* inds, double* acc, float* act, mne_stream_t stream);
 
+/* ---- the same render as ONE launch: mne_render_forward (run_network + raw2outputs / sdf2weights + the loss sums of
+ * JointEncoding.forward, model/scene_rep.py:183-230,303-317,384-386,569-590) with the per-ray work done inside the point
+ * kernel by the warp that stores the last sample of a ray.  ray_counters: [n_rays] int32, all ZERO on entry; the kernel
+ * leaves them zero (calls that share a buffer must not overlap on the GPU).  ray_counters == NULL: the point kernel is
+ * followed by ONE ray kernel that holds each ray in registers (compositing, loss sums and, in training, the backward's
+ * head): two launches, no counters -- the faster choice for small batches, where finished rays would otherwise queue up
+ * behind the tiles of the warp that finished them.  All other arguments as mne_render_forward.
+ * Training (loss_grads != NULL; needs scratch, acc, target_rgb, target_d; the mask counts in acc[0..5] must be final, i.e.
+ * already reduced over the ranks when the batch is sharded): the kernel also does the head of the backward pass --
+ * d loss / d raw of every sample for the upstream gradient loss_grads[8] (the loss weights of get_loss_from_ret,
+ * mneslam_mp.py:350-372) and the list of the samples where it is non-zero, into scratch (mne_backward_scratch_bytes) --
+ * so that mne_render_backward_points can follow directly: the whole of loss.backward() (mp_slam/mapper.py:159) up to the
+ * point kernels costs no launch of its own. */
+int mne_render_forward_fused(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples,
+                             const float* rays_o, const float* rays_d, const float* z_vals, const float* target_rgb,
+                             const float* target_d, float* raw, float* weights, float* rgb, float* depth, float* disp,
+                             float* acc_map, float* depth_var, int32_t* inds, double* acc, float* act,
+                             int32_t* ray_counters, const float* loss_grads, void* scratch, mne_stream_t stream);
+
 /* ---- compositing alone: JointEncoding.raw2outputs / sdf2weights (model/scene_rep.py:183-230) on raw [N,S,4] and
  * z_vals [N,S] supplied by the caller.  Every output may be NULL. */
 int mne_composite(const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples, const float* z_vals, const float* raw,
@@ -214,13 +233,32 @@ int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int
                         const float* loss_grads, const float* g_rgb, const float* g_depth, const float* g_raw,
                         void* scratch, float* g_rays_o, float* g_rays_d, float* act, mne_stream_t stream);
 
+/* ---- the point stage of the backward alone, over a scratch buffer that already holds d loss / d raw and the sample list
+ * (filled by mne_render_forward_fused in training mode): decoder backward and plane / table gradient scatter over the
+ * listed samples (loss.backward() of mp_slam/mapper.py:159 from d raw downwards).  Accumulates (+=) into the gradient
+ * buffers of `scene` and, if non-NULL, WRITES g_rays_o / g_rays_d.  act as in mne_render_backward.  With act, decoder
+ * weight gradients are computed only if the scene carries their buffers (g_sdf0 ..); a caller may leave them NULL here and
+ * call mne_decoder_wgrad afterwards, e.g. on another stream beside the planes' optimiser pass. */
+int mne_render_backward_points(const MneSceneDesc* scene, int32_t n_rays, int32_t n_samples, const float* rays_o,
+                               const float* rays_d, const float* z_vals, void* scratch, float* g_rays_o, float* g_rays_d,
+                               float* act, mne_stream_t stream);
+/* Decoder weight gradients (+= into scene->g_sdf0 / g_sdf1 / g_col0 / g_col1, each 16-byte aligned) from the records in
+ * act that a mne_render_backward / mne_render_backward_points call with the same scratch completed: dW = X^T . dY as a
+ * split-K product over the listed samples on the tensor pipe.  max_ctas > 0 caps the grid (to share the GPU with the
+ * kernel it runs beside); 0 = one CTA per SM.  Reads only scratch and act (not the rays), so the caller may already
+ * refill the ray buffers.  Needs channels-last planes or the hash grid. */
+int mne_decoder_wgrad(const MneSceneDesc* scene, int32_t n_rays, int32_t n_samples, void* scratch, const float* act,
+                      int32_t max_ctas, mne_stream_t stream);
+
 /* ---- backward without a caller workspace.  This entry point has no counterpart in the reference: it exists
  * for callers that must not allocate device memory (a host that forbids cudaMalloc around the call, a real-time
  * loop that cannot take the allocator's lock, a plugin that is only handed input and output buffers).  It is
- * mne_render_backward with the 16-byte-per-sample workspace taken from an array built into the library image
- * (MNE_STATIC_SCRATCH_SAMPLES * 20 bytes = 2.5 MiB, held on every GPU that loads the library until the process
- * exits) instead of the `scratch` argument; inputs and outputs are still the caller's.  It calls no cudaMalloc /
- * cudaFree or other allocating routine.
+ * mne_render_backward with the 20-byte-per-sample workspace (d loss / d raw, 16 B, plus one list entry, 4 B) taken from
+ * an array built into the library image (MNE_STATIC_SCRATCH_SAMPLES * 20 bytes = 2.5 MiB, held on every GPU that loads the
+ * library until the process exits) instead of the `scratch` argument; inputs and outputs are still the caller's.  It calls
+ * no cudaMalloc / cudaFree or other allocating routine.
+ *   - It takes no `act` record: the decoder's forward is always recomputed inside the backward kernels.  The two-table
+ *     hash grid (encoder 1 with two_grid), whose backward needs that record, is therefore rejected here.
  *   - n_rays * n_samples must not exceed MNE_STATIC_SCRATCH_SAMPLES; larger batches are rejected with an error.
  *   - The first call on each device looks up the array's device address (a one-time, synchronous-with-the-host
  *     query); make that first call outside of any CUDA stream capture.

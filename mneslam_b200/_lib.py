@@ -68,6 +68,9 @@ _SIGNATURES = {
     'mne_render_forward': (C.c_int, [C.POINTER(SceneDesc), C.POINTER(RenderCfg), C.c_int32, C.c_int32] +
                            [C.c_void_p] * 16),
     'mne_act_floats': (C.c_int, [C.POINTER(SceneDesc)]),
+    'mne_render_forward_fused': (C.c_int, [C.POINTER(SceneDesc), C.POINTER(RenderCfg), C.c_int32, C.c_int32] + [C.c_void_p] * 19),
+    'mne_render_backward_points': (C.c_int, [C.POINTER(SceneDesc), C.c_int32, C.c_int32] + [C.c_void_p] * 8),
+    'mne_decoder_wgrad': (C.c_int, [C.POINTER(SceneDesc), C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
     'mne_composite': (C.c_int, [C.POINTER(RenderCfg), C.c_int32, C.c_int32] + [C.c_void_p] * 10),
     'mne_loss_finalize': (C.c_int, [C.POINTER(RenderCfg), C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     'mne_backward_scratch_bytes': (C.c_size_t, [C.c_int32, C.c_int32]),

@@ -439,7 +439,7 @@ int impl_version();
 bool scene_is_vectorizable(const MneSceneDesc* sc);
 int render_backward_v2(const MneSceneDesc*, const MneRenderCfg*, int32_t, int32_t, const float*, const float*, const float*,
                        const float*, const float*, const float*, const double*, const float*, const float*, const float*,
-                       const float*, void*, float*, float*, bool, const float*, cudaStream_t);
+                       const float*, void*, float*, float*, bool, float*, cudaStream_t);
 
 template <bool TWO, bool RAY_GRAD, bool PARAM_GRAD>
 static int launch_bwd(const BwdParams& P, cudaStream_t stream) {
@@ -493,7 +493,7 @@ extern "C" int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg
     MNE_CHECK_ARG(!loss_grads || (acc && target_rgb && target_d), "mne_render_backward: loss_grads needs acc, target_rgb and target_d");
     MNE_CHECK_ARG((g_rays_o == nullptr) == (g_rays_d == nullptr), "mne_render_backward: pass both g_rays_o and g_rays_d or neither");
     bool param_grad = scene->g_sdf0 || scene->g_sdf1 || scene->g_col0 || scene->g_col1;
-    if (scene->encoder == 1) param_grad = param_grad || scene->hash[0].grad;
+    if (scene->encoder == 1) param_grad = param_grad || scene->hash[0].grad || (scene->two_grid && scene->hash[1].grad);
     else for (int i = 0; i < (scene->two_grid ? 12 : 6); ++i) param_grad = param_grad || scene->planes[i].grad;
     const bool ray_grad = g_rays_o != nullptr;
     if (!param_grad && !ray_grad) return 0;
@@ -516,6 +516,53 @@ extern "C" int mne_render_backward(const MneSceneDesc* scene, const MneRenderCfg
     P.acc = acc; P.loss_grads = loss_grads; P.g_rgb = g_rgb; P.g_depth = g_depth; P.g_raw = g_raw;
     P.draw = reinterpret_cast<float4*>(scratch); P.g_rays_o = g_rays_o; P.g_rays_d = g_rays_d;
     return scene->two_grid ? dispatch_bwd<true>(P, ray_grad, param_grad, st) : dispatch_bwd<false>(P, ray_grad, param_grad, st);
+}
+
+namespace mne {
+int render_backward_points(const MneSceneDesc*, int32_t, int32_t, const float*, const float*, const float*, void*, float*, float*,
+                           bool, float*, cudaStream_t);
+int decoder_wgrad(const MneSceneDesc*, int32_t, int32_t, void*, const float*, int32_t, cudaStream_t);
+}  // namespace mne
+
+extern "C" int mne_render_backward_points(const MneSceneDesc* scene, int32_t n_rays, int32_t n_samples, const float* rays_o,
+                                          const float* rays_d, const float* z_vals, void* scratch, float* g_rays_o,
+                                          float* g_rays_d, float* act, mne_stream_t stream) {
+    using namespace mne;
+    MNE_CHECK_ARG(impl_version() == 2, "mne_render_backward_points: needs the tensor-pipe kernels (option impl = 2)");
+    MNE_CHECK_ARG(scene, "mne_render_backward_points: null scene");
+    if (int e = check_scene(scene, "mne_render_backward_points", false)) return e;
+    MNE_CHECK_ARG(n_rays >= 0 && n_samples > 0, "mne_render_backward_points: bad sizes n_rays=%d n_samples=%d", n_rays, n_samples);
+    if (n_rays == 0) return 0;
+    MNE_CHECK_ARG(rays_o && rays_d && z_vals && scratch, "mne_render_backward_points: rays_o, rays_d, z_vals and scratch are required");
+    MNE_CHECK_ARG(((uintptr_t)scratch & 15) == 0 && ((uintptr_t)act & 31) == 0, "mne_render_backward_points: scratch must be 16-byte, act 32-byte aligned");
+    MNE_CHECK_ARG((int64_t)n_rays * n_samples < (int64_t)1 << 31, "mne_render_backward_points: n_rays * n_samples must be < 2^31");
+    MNE_CHECK_ARG((g_rays_o == nullptr) == (g_rays_d == nullptr), "mne_render_backward_points: pass both g_rays_o and g_rays_d or neither");
+    bool param_grad = scene->g_sdf0 || scene->g_sdf1 || scene->g_col0 || scene->g_col1;
+    if (scene->encoder == 1) param_grad = param_grad || scene->hash[0].grad || (scene->two_grid && scene->hash[1].grad);
+    else for (int i = 0; i < (scene->two_grid ? 12 : 6); ++i) param_grad = param_grad || scene->planes[i].grad;
+    const bool ray_grad = g_rays_o != nullptr;
+    if (!param_grad && !ray_grad) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (ray_grad) {
+        MNE_CHECK_CUDA(cudaMemsetAsync(g_rays_o, 0, sizeof(float) * 3 * (size_t)n_rays, st));
+        MNE_CHECK_CUDA(cudaMemsetAsync(g_rays_d, 0, sizeof(float) * 3 * (size_t)n_rays, st));
+    }
+    MNE_CHECK_ARG(!scene->dirty || scene->dirty_base, "mne_render_backward_points: dirty without dirty_base");
+    MNE_CHECK_ARG(act || !(scene->two_grid && ray_grad && param_grad),
+                  "mne_render_backward_points: two grids with ray AND parameter gradients need the forward's record (act)");
+    return render_backward_points(scene, n_rays, n_samples, rays_o, rays_d, z_vals, scratch, g_rays_o, g_rays_d, param_grad, act, st);
+}
+
+extern "C" int mne_decoder_wgrad(const MneSceneDesc* scene, int32_t n_rays, int32_t n_samples, void* scratch, const float* act,
+                                 int32_t max_ctas, mne_stream_t stream) {
+    using namespace mne;
+    MNE_CHECK_ARG(scene && scratch && act, "mne_decoder_wgrad: null argument");
+    if (int e = check_scene(scene, "mne_decoder_wgrad", false)) return e;
+    MNE_CHECK_ARG(n_rays >= 0 && n_samples > 0 && (int64_t)n_rays * n_samples < (int64_t)1 << 31, "mne_decoder_wgrad: bad sizes");
+    MNE_CHECK_ARG(((uintptr_t)scratch & 15) == 0 && ((uintptr_t)act & 31) == 0, "mne_decoder_wgrad: scratch must be 16-byte, act 32-byte aligned");
+    MNE_CHECK_ARG(scene->encoder == 1 || scene_is_vectorizable(scene), "mne_decoder_wgrad: needs channels-last planes or the hash grid");
+    if (n_rays == 0 || !(scene->g_sdf0 || scene->g_sdf1 || scene->g_col0 || scene->g_col1)) return 0;
+    return decoder_wgrad(scene, n_rays, n_samples, scratch, act, max_ctas, (cudaStream_t)stream);
 }
 
 // ---------------------------------------------------------------------------------------------------------

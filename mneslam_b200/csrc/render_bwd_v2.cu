@@ -10,6 +10,7 @@
 // Plane gradients: lane = (corner, 4-channel group), one 128-bit vector reduction (red.global.add.v4.f32) per
 // lane covers the four corner texels of a tap.
 #include "bwd_tiles.cuh"
+#include "ray_tail.cuh"
 
 namespace mne {
 
@@ -500,101 +501,15 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd_kernel(const __grid_con
 }
 
 // ---------------------------------------------------------------------------------------------
-// ray kernel: d loss / d raw for every sample (same arithmetic as the head of v1's render_bwd_kernel)
+// ray kernel: d loss / d raw for every sample + compaction (ray_tail.cuh), for calls whose upstream gradient arrives
+// with the backward (autograd).  The fused training forward (mne_render_forward_fused) does this in its own tail.
 // ---------------------------------------------------------------------------------------------
-struct RayBwdParams {
-    MneRenderCfg rc;
-    int n_rays, n_samples;
-    const float* z_vals;
-    const float* raw;
-    const float* target_rgb;
-    const float* target_d;
-    const double* acc;
-    const float* loss_grads;
-    const float* g_rgb;
-    const float* g_depth;
-    const float* g_raw;
-    float4* draw;
-    int* list;                 // indices of the samples with a non-zero draw, [*n_active]
-    int* n_active;             // zeroed before the launch
-};
-
 __global__ void __launch_bounds__(256) rays_bwd_kernel(const RayBwdParams P) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int S = P.n_samples;
-    const float* lg = P.loss_grads;
-    float k_rgb = 0.f, k_depth = 0.f, k_co_fs = 0.f, k_co_sdf = 0.f, k_e_fs = 0.f, k_e_center = 0.f, k_e_tail = 0.f;
-    if (lg) {
-        const double Nn = P.rc.norm_rays, NS = P.rc.norm_rays * (double)S;
-        auto inv = [](double c) { return c > 0.0 ? 1.0 / c : 0.0; };
-        k_rgb = (float)(2.0 * lg[L_RGB] / (3.0 * Nn));
-        k_depth = (float)(2.0 * lg[L_DEPTH] * inv(P.acc[A_N_VALID]));
-        if (!P.rc.first_pass) {
-            const float n_fs = (float)P.acc[A_N_CO_FRONT], n_sdf = (float)P.acc[A_N_CO_NEAR];
-            const float fs_w = 1.0f - n_fs / (n_fs + n_sdf), sdf_w = 1.0f - n_sdf / (n_fs + n_sdf);
-            k_co_fs = (n_fs + n_sdf > 0.f) ? (float)(2.0 * lg[L_CO_FS] * fs_w / NS) : 0.f;
-            k_co_sdf = (n_fs + n_sdf > 0.f) ? (float)(2.0 * lg[L_CO_SDF] * sdf_w / NS) * P.rc.sc_trunc : 0.f;
-            k_e_fs = (float)(2.0 * lg[L_E_FS] * inv(P.acc[A_N_E_FRONT]));
-            k_e_center = (float)(2.0 * lg[L_E_CENTER] * inv(P.acc[A_N_E_CENTER])) * P.rc.model_trunc;
-            k_e_tail = (float)(2.0 * lg[L_E_TAIL] * inv(P.acc[A_N_E_TAIL])) * P.rc.model_trunc;
-        }
-    }
+    const RayGradScales K = ray_grad_scales(P.rc, P.n_samples, P.acc, P.loss_grads);
     for (int ray = blockIdx.x * 8 + warp; ray < P.n_rays; ray += gridDim.x * 8) {
-        const size_t rb = (size_t)ray * S;
-        const RayComposite c = composite_ray(P.raw, P.z_vals, rb, S, P.rc, lane);
-        const float d = P.target_d ? P.target_d[ray] : 0.0f;
-        float rr[3] = {c.rgb[0], c.rgb[1], c.rgb[2]};
-        if (P.rc.white_bkgd) { rr[0] += 1.f - c.acc; rr[1] += 1.f - c.acc; rr[2] += 1.f - c.acc; }
-        float G[3] = {0.f, 0.f, 0.f}, Gd = 0.f;
-        if (lg && P.target_rgb) {
-#pragma unroll
-            for (int k = 0; k < 3; ++k) G[k] = k_rgb * (rr[k] - P.target_rgb[ray * 3 + k]);
-            if (depth_valid(d, P.rc)) Gd = k_depth * (c.depth - d);
-        }
-        if (P.g_rgb) { G[0] += P.g_rgb[ray * 3 + 0]; G[1] += P.g_rgb[ray * 3 + 1]; G[2] += P.g_rgb[ray * 3 + 2]; }
-        if (P.g_depth) Gd += P.g_depth[ray];
-        for (int s0 = 0; s0 < S; s0 += 32) {
-            const int s = s0 + lane;
-            bool active = false;
-            if (s < S) {
-            const float z = __ldg(P.z_vals + rb + s);
-            const float4 v = __ldg(reinterpret_cast<const float4*>(P.raw) + rb + s);
-            float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (z < c.thresh) {
-                float sp;
-                const float u = sdf_bell(v.w, P.rc.trunc, &sp);
-                const float w = u * c.inv_norm;
-                const float c0 = sigmoidf(v.x), c1 = sigmoidf(v.y), c2 = sigmoidf(v.z);
-                const float dLdu = c.inv_norm * (G[0] * (c0 - rr[0]) + G[1] * (c1 - rr[1]) + G[2] * (c2 - rr[2]) + Gd * (z - c.depth));
-                o.w = dLdu * u * (1.0f - 2.0f * sp) / P.rc.trunc;
-                o.x = G[0] * w * c0 * (1.0f - c0);
-                o.y = G[1] * w * c1 * (1.0f - c1);
-                o.z = G[2] * w * c2 * (1.0f - c2);
-            }
-            if (lg && P.target_d && !P.rc.first_pass) {
-                const unsigned m = sample_masks(z, d, P.rc);
-                if (m & M_CO_FRONT) o.w += k_co_fs * (v.w - 1.0f);
-                if (m & M_CO_NEAR) o.w += k_co_sdf * (__fadd_rn(z, __fmul_rn(v.w, P.rc.sc_trunc)) - d);
-                if (m & M_E_FRONT) o.w += k_e_fs * (v.w - 1.0f);
-                const float re = __fadd_rn(z, __fmul_rn(v.w, P.rc.model_trunc)) - d;
-                if (m & M_E_CENTER) o.w += k_e_center * re;
-                if (m & M_E_TAIL) o.w += k_e_tail * re;
-            }
-            if (P.g_raw) {
-                const float4 e = __ldg(reinterpret_cast<const float4*>(P.g_raw) + rb + s);
-                o.x += e.x; o.y += e.y; o.z += e.z; o.w += e.w;
-            }
-            P.draw[rb + s] = o;
-            active = o.x != 0.0f || o.y != 0.0f || o.z != 0.0f || o.w != 0.0f;
-            }
-            const unsigned b = __ballot_sync(0xffffffffu, active);
-            if (b) {
-                int base = 0;
-                if (lane == 0) base = atomicAdd(P.n_active, __popc(b));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (active) P.list[base + __popc(b & ((1u << lane) - 1u))] = (int)(rb + s);
-            }
-        }
+        const RayComposite c = composite_ray(P.raw, P.z_vals, (size_t)ray * P.n_samples, P.n_samples, P.rc, lane);
+        ray_backward_one(P, ray, lane, K, c);
     }
 }
 
@@ -634,31 +549,28 @@ static int dispatch_points_bwd(const PtsBwdParams& P, bool ray, bool param, cuda
 
 bool scene_is_vectorizable(const MneSceneDesc* sc) { return planes_vectorizable(*sc); }
 
-// v2 backward
-int render_backward_v2(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples,
-                       const float* rays_o, const float* rays_d, const float* z_vals, const float* raw,
-                       const float* target_rgb, const float* target_d, const double* acc, const float* loss_grads,
-                       const float* g_rgb, const float* g_depth, const float* g_raw, void* scratch, float* g_rays_o,
-                       float* g_rays_d, bool param_grad, const float* act, cudaStream_t st) {
-    RayBwdParams R{};
-    R.rc = *rcfg; R.n_rays = n_rays; R.n_samples = n_samples; R.z_vals = z_vals; R.raw = raw; R.target_rgb = target_rgb;
-    R.target_d = target_d; R.acc = acc; R.loss_grads = loss_grads; R.g_rgb = g_rgb; R.g_depth = g_depth; R.g_raw = g_raw;
-    R.draw = reinterpret_cast<float4*>(scratch);
+// scratch layout (mne_backward_scratch_bytes): d_raw float4[n] | sample list int32[round4(n)] | list length
+static void scratch_views(void* scratch, int64_t n_pts, float4** draw, int** list, int** n_active) {
+    *draw = reinterpret_cast<float4*>(scratch);
+    *list = reinterpret_cast<int*>(*draw + n_pts);
+    *n_active = *list + ((n_pts + 3) & ~(int64_t)3);
+}
+
+// the point stage of the backward over a filled scratch (d_raw + sample list): with the forward's record the barrier-free
+// kernels of render_bwd_v3.cu, else the recompute kernels above
+int render_backward_points(const MneSceneDesc* scene, int32_t n_rays, int32_t n_samples, const float* rays_o, const float* rays_d,
+                           const float* z_vals, void* scratch, float* g_rays_o, float* g_rays_d, bool param_grad, float* act,
+                           cudaStream_t st) {
     const int64_t n_pts = (int64_t)n_rays * n_samples;
-    MNE_CHECK_ARG(n_pts < ((int64_t)1 << 31), "mne_render_backward: more than 2^31 samples in one call");
-    R.list = reinterpret_cast<int*>(R.draw + n_pts);
-    R.n_active = R.list + ((n_pts + 3) & ~(int64_t)3);
-    MNE_CHECK_CUDA(cudaMemsetAsync(R.n_active, 0, sizeof(int), st));
-    const int blocks = max(1, min((n_rays + 7) / 8, sm_count() * 4));
-    rays_bwd_kernel<<<blocks, 256, 0, st>>>(R);
-    MNE_CHECK_CUDA(cudaGetLastError());
+    float4* draw; int* list; int* n_active;
+    scratch_views(scratch, n_pts, &draw, &list, &n_active);
     PtsBwdParams P{};
-    P.sc = *scene; P.n_pts = (int64_t)n_rays * n_samples; P.n_samples = n_samples;
-    P.rays_o = rays_o; P.rays_d = rays_d; P.z_vals = z_vals; P.draw = reinterpret_cast<const float4*>(scratch);
-    P.g_rays_o = g_rays_o; P.g_rays_d = g_rays_d; P.list = R.list; P.n_active = R.n_active; P.act = act;
+    P.sc = *scene; P.n_pts = n_pts; P.n_samples = n_samples;
+    P.rays_o = rays_o; P.rays_d = rays_d; P.z_vals = z_vals; P.draw = draw;
+    P.g_rays_o = g_rays_o; P.g_rays_d = g_rays_d; P.list = list; P.n_active = n_active; P.act = act;
     const bool ray = g_rays_o != nullptr;
     if (act && (scene->encoder == 1 || planes_vectorizable(*scene)))
-        return points_backward_v3(P, ray, param_grad, const_cast<float*>(act), R.draw, st);
+        return points_backward_v3(P, ray, param_grad, act, draw, st);
     if (scene->encoder == 1) {
         MNE_CHECK_ARG(!scene->two_grid, "mne_render_backward: the two-table hash grid needs the forward's activation buffer (act)");
         if (ray && param_grad) return launch_points_bwd<false, 2, true, true>(P, st);
@@ -668,6 +580,25 @@ int render_backward_v2(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int3
     if (planes_vectorizable(*scene)) return dispatch_points_bwd<1>(P, ray, param_grad, st);
     MNE_CHECK_ARG(!scene->dirty, "mne_render_backward: MneSceneDesc.dirty needs channels-last planes or the hash grid");
     return dispatch_points_bwd<0>(P, ray, param_grad, st);
+}
+
+// v2 backward: ray kernel (d loss / d raw + compaction into scratch), then the point stage
+int render_backward_v2(const MneSceneDesc* scene, const MneRenderCfg* rcfg, int32_t n_rays, int32_t n_samples,
+                       const float* rays_o, const float* rays_d, const float* z_vals, const float* raw,
+                       const float* target_rgb, const float* target_d, const double* acc, const float* loss_grads,
+                       const float* g_rgb, const float* g_depth, const float* g_raw, void* scratch, float* g_rays_o,
+                       float* g_rays_d, bool param_grad, float* act, cudaStream_t st) {
+    RayBwdParams R{};
+    R.rc = *rcfg; R.n_rays = n_rays; R.n_samples = n_samples; R.z_vals = z_vals; R.raw = raw; R.target_rgb = target_rgb;
+    R.target_d = target_d; R.acc = acc; R.loss_grads = loss_grads; R.g_rgb = g_rgb; R.g_depth = g_depth; R.g_raw = g_raw;
+    const int64_t n_pts = (int64_t)n_rays * n_samples;
+    MNE_CHECK_ARG(n_pts < ((int64_t)1 << 31), "mne_render_backward: more than 2^31 samples in one call");
+    scratch_views(scratch, n_pts, &R.draw, &R.list, &R.n_active);
+    MNE_CHECK_CUDA(cudaMemsetAsync(R.n_active, 0, sizeof(int), st));
+    const int blocks = max(1, min((n_rays + 7) / 8, sm_count() * 4));
+    rays_bwd_kernel<<<blocks, 256, 0, st>>>(R);
+    MNE_CHECK_CUDA(cudaGetLastError());
+    return render_backward_points(scene, n_rays, n_samples, rays_o, rays_d, z_vals, scratch, g_rays_o, g_rays_d, param_grad, act, st);
 }
 
 }  // namespace mne

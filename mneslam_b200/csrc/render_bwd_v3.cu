@@ -8,7 +8,7 @@
 //                         no weight-gradient accumulators, no __syncthreads.
 //   decoder_wgrad_kernel  the weight gradients dW^T = X^T . dY as a split-K product over the active samples: A and B
 //                         fragments are loaded straight from the records (every 32-byte sector fully used), the OneBlob
-//                         inputs are recomputed from the sample positions; warps = (sample set, block of dW) with register
+//                         inputs are re-encoded from the coordinates kept in the record; warps = (sample set, block of dW) with register
 //                         accumulators, combined per CTA in shared memory and flushed with one coalesced pass of atomics.
 //
 // Extra traffic against v2 (Replica room0: 88 064 samples, ~35 k active): the forward writes 264 B more per sample
@@ -317,10 +317,6 @@ __global__ void __launch_bounds__(NW * 32, 1) points_bwd3_kernel(const __grid_co
 // ---------------------------------------------------------------------------------------------
 struct WGradParams {
     MneSceneDesc sc;
-    int n_samples;
-    const float* rays_o;
-    const float* rays_d;
-    const float* z_vals;
     const float4* draw;
     const int* list;
     const int* n_active;
@@ -328,7 +324,7 @@ struct WGradParams {
 };
 
 // sample sets per CTA (each a full set of roles with its own accumulators); the register file caps sets x roles
-template <bool TWO> __host__ __device__ constexpr int wg_sets() { return TWO ? 2 : 4; }
+template <bool TWO> __host__ __device__ constexpr int wg_sets() { return 2; }
 constexpr int kWgUnroll = 2;       // k-steps (of 8 samples) in flight per warp iteration
 constexpr int kBlobTile = 56;      // floats per sample of a blob tile: == 24 (mod 32), conflict-free fragment reads
 
@@ -379,32 +375,37 @@ __global__ void __launch_bounds__(wg_sets<TWO>() * wg_roles<TWO>() * 32, 1) deco
     const bool is_blob = role == 2 || role == 3;
     float* btile = blob_s + (set * 2 + (role == 3 ? 1 : 0)) * (kWgUnroll * 8 * kBlobTile);
     const int ks_stride = gridDim.x * kWgSets * kWgUnroll;
-    for (int ks0 = (blockIdx.x * kWgSets + set) * kWgUnroll; ks0 < n_ks; ks0 += ks_stride) {
-        // ---- sample rows of this iteration: lane (g, t) touches samples t and t + 4 of each k-step
-        const float* rA[kWgUnroll];
-        const float* rB[kWgUnroll];
-        int qA[kWgUnroll], qB[kWgUnroll];
+    // lane (g, t) touches samples t and t + 4 of each k-step; the sample indices of the NEXT iteration are fetched while this
+    // one computes (the list -> record -> mma chain is two dependent memory round trips otherwise)
+    int qA[kWgUnroll], qB[kWgUnroll];
+    auto fetch_list = [&](int ks, int (&a)[kWgUnroll], int (&b)[kWgUnroll]) {
 #pragma unroll
         for (int u = 0; u < kWgUnroll; ++u) {
-            const int iA = (ks0 + u) * 8 + t, iB = iA + 4;
-            qA[u] = iA < n ? __ldg(P.list + iA) : -1;
-            qB[u] = iB < n ? __ldg(P.list + iB) : -1;
+            const int iA = (ks + u) * 8 + t, iB = iA + 4;
+            a[u] = iA < n ? __ldg(P.list + iA) : -1;
+            b[u] = iB < n ? __ldg(P.list + iB) : -1;
+        }
+    };
+    const int ks_first = (blockIdx.x * kWgSets + set) * kWgUnroll;
+    fetch_list(ks_first, qA, qB);
+    for (int ks0 = ks_first; ks0 < n_ks; ks0 += ks_stride) {
+        const float* rA[kWgUnroll];
+        const float* rB[kWgUnroll];
+#pragma unroll
+        for (int u = 0; u < kWgUnroll; ++u) {
             rA[u] = P.act + (int64_t)max(qA[u], 0) * AR::STRIDE;
             rB[u] = P.act + (int64_t)max(qB[u], 0) * AR::STRIDE;
         }
+        int nA[kWgUnroll], nB[kWgUnroll];
+        fetch_list(ks0 + ks_stride, nA, nB);
         if (is_blob) {
-            // OneBlob inputs of the 16 samples of this iteration, recomputed from their positions: job = (sample, dimension)
+            // OneBlob inputs of the 16 samples of this iteration, re-encoded from the coordinates the forward kept: job = (sample, dimension)
             __syncwarp();
             for (int job = lane; job < kWgUnroll * 8 * 3; job += 32) {
                 const int s = job % (kWgUnroll * 8), dim = job / (kWgUnroll * 8);
                 const int i = ks0 * 8 + s;
                 float x = 0.5f;
-                if (i < n) {
-                    const int q = __ldg(P.list + i);
-                    const int ray = q / P.n_samples;
-                    const float p = __fadd_rn(__ldg(P.rays_o + ray * 3 + dim), __fmul_rn(__ldg(P.rays_d + ray * 3 + dim), __ldg(P.z_vals + q)));
-                    x = blob_input(p, P.sc.bbox_lo[dim], P.sc.bbox_ext[dim]);
-                }
+                if (i < n) x = __ldg(P.act + (int64_t)__ldg(P.list + i) * AR::STRIDE + AR::BLOBX + dim);
                 oneblob16_sparse(x, btile + s * kBlobTile + dim * 16);
             }
             __syncwarp();
@@ -462,6 +463,8 @@ __global__ void __launch_bounds__(wg_sets<TWO>() * wg_roles<TWO>() * 32, 1) deco
                 wg_mma<4>(acc[1], a, bc);
             }
         }
+#pragma unroll
+        for (int u = 0; u < kWgUnroll; ++u) { qA[u] = nA[u]; qB[u] = nB[u]; }
     }
 
     // ---- combine the sets in shared memory (set 0 stores, the others add in turn), in the layout of the global tensors.
@@ -519,13 +522,16 @@ __global__ void __launch_bounds__(wg_sets<TWO>() * wg_roles<TWO>() * 32, 1) deco
         __syncthreads();
     }
     if ((blockIdx.x * kWgSets) * kWgUnroll >= n_ks) return;       // this CTA saw no sample: nothing to add
-    for (int i = threadIdx.x; i < L::TOTAL; i += blockDim.x) {
-        const float v = dW[i];
-        if (v == 0.f) continue;
-        if (i < L::SDF1) { if (P.sc.g_sdf0) atomicAdd(P.sc.g_sdf0 + i, v); }
-        else if (i < L::COL0) { if (P.sc.g_sdf1) atomicAdd(P.sc.g_sdf1 + (i - L::SDF1), v); }
-        else if (i < L::COL1) { if (P.sc.g_col0) atomicAdd(P.sc.g_col0 + (i - L::COL0), v); }
-        else if (P.sc.g_col1) atomicAdd(P.sc.g_col1 + (i - L::COL1), v);
+    // one pass of vector reductions (the four regions start at multiples of 4 floats; the entry point checked the alignment)
+    for (int i = threadIdx.x * 4; i < L::TOTAL; i += blockDim.x * 4) {
+        const float4 v = *reinterpret_cast<const float4*>(dW + i);
+        if (v.x == 0.f && v.y == 0.f && v.z == 0.f && v.w == 0.f) continue;
+        float* dst;
+        if (i < L::SDF1) dst = P.sc.g_sdf0 ? P.sc.g_sdf0 + i : nullptr;
+        else if (i < L::COL0) dst = P.sc.g_sdf1 ? P.sc.g_sdf1 + (i - L::SDF1) : nullptr;
+        else if (i < L::COL1) dst = P.sc.g_col0 ? P.sc.g_col0 + (i - L::COL0) : nullptr;
+        else dst = P.sc.g_col1 ? P.sc.g_col1 + (i - L::COL1) : nullptr;
+        if (dst) atomicAdd(reinterpret_cast<float4*>(dst), v);
     }
 }
 
@@ -558,10 +564,11 @@ static int dispatch_points_bwd3(const PtsBwd3Params& Q, bool ray, bool param, cu
 }
 
 template <bool TWO, bool HASH>
-static int launch_wgrad(const WGradParams& W, int64_t n_pts, cudaStream_t st) {
+static int launch_wgrad(const WGradParams& W, int64_t n_pts, int max_ctas, cudaStream_t st) {
     constexpr int kWgSets = wg_sets<TWO>();
     const int64_t per_cta = (int64_t)kWgSets * kWgUnroll * 8;
-    const int blocks = (int)max((int64_t)1, min((n_pts + per_cta - 1) / per_cta, (int64_t)sm_count()));
+    const int64_t cap = max_ctas > 0 ? (int64_t)max_ctas : (int64_t)sm_count();
+    const int blocks = (int)max((int64_t)1, min((n_pts + per_cta - 1) / per_cta, cap));
     const size_t smem = sizeof(float) * (size_t)(WgLayout<TWO, HASH>::TOTAL + kWgSets * 2 * kWgUnroll * 8 * kBlobTile);
     static bool configured[64] = {};
     int dev = 0;
@@ -575,6 +582,8 @@ static int launch_wgrad(const WGradParams& W, int64_t n_pts, cudaStream_t st) {
     return 0;
 }
 
+int decoder_wgrad(const MneSceneDesc*, int32_t, int32_t, void*, const float*, int32_t, cudaStream_t);
+
 // backward over the compacted sample list for calls that carry the forward's record
 int points_backward_v3(const PtsBwdParams& P, bool ray, bool param, float* act, const float4* draw, cudaStream_t st) {
     MNE_CHECK_ARG(((uintptr_t)act & 31) == 0, "mne_render_backward: act must be 32-byte aligned");
@@ -586,11 +595,26 @@ int points_backward_v3(const PtsBwdParams& P, bool ray, bool param, float* act, 
     else e = two ? dispatch_points_bwd3<true, 1>(Q, ray, param, st) : dispatch_points_bwd3<false, 1>(Q, ray, param, st);
     if (e) return e;
     if (!param || !(P.sc.g_sdf0 || P.sc.g_sdf1 || P.sc.g_col0 || P.sc.g_col1)) return 0;
+    return decoder_wgrad(&P.sc, (int32_t)(P.n_pts / P.n_samples), P.n_samples, const_cast<float4*>(draw), act, 0, st);
+}
+
+// weight gradients from the records the tile kernel completed (d_raw + sample list at `scratch`, layout of
+// mne_backward_scratch_bytes).  max_ctas > 0 caps the grid (e.g. to run beside the optimiser on a few SMs).
+int decoder_wgrad(const MneSceneDesc* scene, int32_t n_rays, int32_t n_samples, void* scratch, const float* act, int32_t max_ctas,
+                  cudaStream_t st) {
+    const float* gs[4] = {scene->g_sdf0, scene->g_sdf1, scene->g_col0, scene->g_col1};
+    for (int i = 0; i < 4; ++i)
+        MNE_CHECK_ARG(((uintptr_t)gs[i] & 15) == 0, "decoder weight-gradient buffers must be 16-byte aligned");
+    const int64_t n_pts = (int64_t)n_rays * n_samples;
     WGradParams W{};
-    W.sc = P.sc; W.n_samples = P.n_samples; W.rays_o = P.rays_o; W.rays_d = P.rays_d; W.z_vals = P.z_vals; W.draw = draw;
-    W.list = P.list; W.n_active = P.n_active; W.act = act;
-    if (hash) return two ? launch_wgrad<true, true>(W, P.n_pts, st) : launch_wgrad<false, true>(W, P.n_pts, st);
-    return two ? launch_wgrad<true, false>(W, P.n_pts, st) : launch_wgrad<false, false>(W, P.n_pts, st);
+    W.sc = *scene;
+    W.draw = reinterpret_cast<const float4*>(scratch);
+    W.list = reinterpret_cast<const int*>(W.draw + n_pts);
+    W.n_active = W.list + ((n_pts + 3) & ~(int64_t)3);
+    W.act = act;
+    const bool hash = scene->encoder == 1, two = scene->two_grid != 0;
+    if (hash) return two ? launch_wgrad<true, true>(W, n_pts, max_ctas, st) : launch_wgrad<false, true>(W, n_pts, max_ctas, st);
+    return two ? launch_wgrad<true, false>(W, n_pts, max_ctas, st) : launch_wgrad<false, false>(W, n_pts, max_ctas, st);
 }
 
 }  // namespace mne

@@ -476,7 +476,7 @@ __device__ __forceinline__ float oneblob16_sparse_grad(float x, const float* gb)
 
 // ---------------------------------------------------------------------------------------------
 // Per-sample record the forward keeps for the backward (optional; what autograd would save).  One row per sample,
-// floats:   h1[32] | o16[16] = (geo0..14, sdf) | hc[32] | feat[F] | cfeat[F] (two grids) | dY[80] | masks[2] + pad[6]
+// floats:   h1[32] | o16[16] = (geo0..14, sdf) | hc[32] | feat[F] | cfeat[F] (two grids) | dY[80] | masks[2] | blob x[3] | pad[3]
 // with F = 64 (planes) or 32 (hash grid).  h1 / hc are post-ReLU; masks = the bit sets (h1 > 0), (hc > 0) as two 32-bit
 // words (all the backward tile kernel needs of them); dY = d h1[32] | d o16[16] | d hc[32] is WRITTEN by the backward tile
 // kernel and read, with everything else, by the weight-gradient kernel.  Rows are 32-byte aligned (stride % 8 == 0).
@@ -487,6 +487,7 @@ struct ActRow {
     static constexpr int H1 = 0, O16 = 32, HC = 48, FEAT = 80, CFEAT = 80 + F;
     static constexpr int DY = 80 + F + (TWO ? F : 0);          // d h1 at DY, d o16 at DY + 32, d hc at DY + 48
     static constexpr int MASK = DY + 80;
+    static constexpr int BLOBX = MASK + 2;                     // the three OneBlob inputs (unit-cube coordinates) of the sample
     static constexpr int STRIDE = MASK + 8;
 };
 __host__ __device__ inline int act_row_floats(bool two, bool hash) {

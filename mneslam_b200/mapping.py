@@ -140,6 +140,12 @@ class FusedMapper:
             else:
                 seg_ends.append(off); seg_lr.append(lr); seg_eps.append(eps); seg_wd.append(wd)
         self._segments = self._pack_segments(seg_ends, list(zip(seg_lr, seg_eps, seg_wd)))
+        # the same split in two: the encoder's groups (planes / tables), and the decoder's group at the tail
+        dec0 = sum(p.numel() for p in planes)
+        self._seg_head = self._pack_segments(seg_ends[:-1], list(zip(seg_lr, seg_eps, seg_wd))[:-1])
+        self._seg_tail = self._pack_segments([total - dec0], [(seg_lr[-1], seg_eps[-1], seg_wd[-1])])
+        if len(seg_ends) < 2 or seg_ends[-2] != dec0:
+            raise ValueError('the decoder weights must form the last parameter group')
         self.shards = None
         if world_size > 1:
             from .distributed import FlatShards
@@ -163,9 +169,21 @@ class FusedMapper:
         self.loss_grads = torch.tensor(loss_weight_vector(self.cfg, is_co_sdf), dtype=torch.float32, device=self.dev)
         self.loss_weights = self.loss_grads.clone()
         self._scratch = None
-        self._act = None              # the decoders' hidden activations, forward -> backward (80 floats per sample)
+        self._ray_counters = None     # per-ray counters of the fused forward's tail (always left at zero)
+        self._pending_wgrad = None    # the batch whose decoder weight gradients are still to be computed
+        self._wgrad_stream = None     # side stream: decoder weight gradients + decoder Adam beside the planes' Adam
+        self._act = None              # the per-sample record, forward -> backward (ops.act_floats per sample)
         self.last_losses = None
         self.global_rays_override = None
+        # CTAs of the decoder weight-gradient kernel when it runs beside the planes' Adam pass (the optimiser grids leave
+        # `adam_spare_sms` SMs free; 0 = a full grid)
+        import os
+        self.wgrad_ctas = int(os.environ.get('MNE_WGRAD_CTAS', '0'))
+        self.wgrad_inline = os.environ.get('MNE_WGRAD_INLINE', '0') == '1'
+        # the render as ONE launch (the warp that stores a ray's last sample composites it; needs per-ray counters) or as the
+        # point kernel + one ray kernel.  Measured on B200 (room0, 2048 rays): 82 us against 55 + 8 us -- finished rays
+        # queue up behind the tiles of the warp that finished them, on the kernel's critical path -- so two launches.
+        self.single_launch_render = False
 
     @staticmethod
     def _pack_segments(ends, hparams):
@@ -173,21 +191,23 @@ class FusedMapper:
         return (n, (C.c_int64 * n)(*ends), (C.c_float * n)(*[h[0] for h in hparams]),
                 (C.c_float * n)(*[h[1] for h in hparams]), (C.c_float * n)(*[h[2] for h in hparams]))
 
-    def _adam_segments(self, param, grad, m, v, segments, zero_grad):
+    def _adam_segments(self, param, grad, m, v, segments, zero_grad, touched='own'):
         n_seg, ends, lr, eps, wd = segments
+        if isinstance(touched, str):
+            touched = self.touched
         _lib.check(_lib.lib().mne_adam_step_segments(param.data_ptr(), grad.data_ptr(), m.data_ptr(), v.data_ptr(), n_seg,
                                                      ends, lr, eps, wd, self.betas[0], self.betas[1],
                                                      self.step_dev.data_ptr(), 0, 1 if zero_grad else 0,
-                                                     ops._ptr(self.touched), ops._stream()),
+                                                     ops._ptr(touched), ops._stream()),
                    'mne_adam_step_segments')
 
     # ------------------------------------------------------------------------------------------
-    def _scene(self, with_grads):
+    def _scene(self, with_grads, plane_grads=True, weight_grads=True):
         m = self.model
         return ops.make_scene(m._flat_planes(), m.decoder.weight_list(), m.bound, m.bounding_box,
                               self.cfg['pos']['n_bins'],
-                              plane_grads=self.plane_grads if with_grads else None,
-                              weight_grads=self.weight_grads if with_grads else None, hash_meta=m.hash_meta,
+                              plane_grads=self.plane_grads if (with_grads and plane_grads) else None,
+                              weight_grads=self.weight_grads if (with_grads and weight_grads) else None, hash_meta=m.hash_meta,
                               dirty=self.dirty_local if with_grads else None,
                               dirty_base=self.flat_grad if (with_grads and self.dirty_local is not None) else None)
 
@@ -208,9 +228,12 @@ class FusedMapper:
         z_vals = ops.sample_rays(scfg, rcfg, n, s, target_d.reshape(-1), noise if perturb else None, acc, dev, out=z_out)
         return z_vals, acc
 
-    def forward_backward(self, rays_o, rays_d, target_rgb, target_d, noise=None, sampled=None):
-        """sample -> forward -> finalize -> backward; gradients are ADDED to the flat buffer.  Returns losses[8].
-        ``sampled``: the (z_vals, acc) of an earlier ``sample_stage`` call on the same ``target_d``."""
+    def forward_backward(self, rays_o, rays_d, target_rgb, target_d, noise=None, sampled=None, defer_wgrad=False):
+        """sample -> fused forward (encode, decode, compositing, loss sums, d loss / d raw, sample compaction: ONE launch) ->
+        loss finalize -> point backward -> decoder weight gradients; gradients are ADDED to the flat buffer.  Returns
+        losses[8].  ``sampled``: the (z_vals, acc) of an earlier ``sample_stage`` call on the same ``target_d``.
+        ``defer_wgrad`` (one GPU): leave the decoder weight gradients to ``optimizer_step`` -- they only feed the decoder's
+        own Adam step, so ``step`` runs them beside the planes' optimiser pass."""
         cfg, dev = self.cfg, self.dev
         n = rays_o.shape[0]
         tables = ops.SampleTables.get(cfg, dev, True)
@@ -222,17 +245,33 @@ class FusedMapper:
         scene = self._scene(False)
         if self._act is None or self._act.numel() < n * s * ops.act_floats(scene):
             self._act = torch.empty(n * s * ops.act_floats(scene), dtype=torch.float32, device=dev)
-        out = ops.render_forward(scene, rcfg, rays_o, rays_d, z_vals, target_rgb, td, acc,
-                                 want_aux=False, act=self._act)
-        if self.world_size > 1:
-            torch.distributed.all_reduce(acc, group=self.group)
-        losses = ops.loss_finalize(rcfg, s, acc)
         if self._scratch is None or self._scratch_for != (n, s):
             self._scratch, self._scratch_for = ops.backward_scratch(n, s, dev), (n, s)
-        ops.render_backward(self._scene(True), rcfg, rays_o, rays_d, z_vals, out['raw'], target_rgb, td, acc,
-                            loss_grads=self.loss_grads, scratch=self._scratch, act=self._act)
+        if self.single_launch_render and (self._ray_counters is None or self._ray_counters.numel() < n):
+            self._ray_counters = torch.zeros(n, dtype=torch.int32, device=dev)
+        if self.world_size > 1:
+            # the loss gradients are scaled by the GLOBAL mask counts (slots 0..5, known once the batch is sampled)
+            torch.distributed.all_reduce(acc[:6], group=self.group)
+        out = ops.render_forward(scene, rcfg, rays_o, rays_d, z_vals, target_rgb, td, acc, want_aux=False, act=self._act,
+                                 ray_counters=self._ray_counters if self.single_launch_render else None,
+                                 loss_grads=self.loss_grads, scratch=self._scratch)
+        ops.render_backward_points(self._scene(True, weight_grads=False), rays_o, rays_d, z_vals, self._scratch, act=self._act)
+        self._pending_wgrad = (n, s)
+        if not defer_wgrad or self.world_size > 1 or self.flat_param is None:
+            self._decoder_wgrad()     # (several GPUs: the gradient exchange moves the whole flat buffer, nothing to overlap)
+        if self.world_size > 1:
+            # the loss VALUES need the global sums (slots 6..); nothing on the gradient path waits for them
+            torch.distributed.all_reduce(acc[6:], group=self.group)
+        losses = ops.loss_finalize(rcfg, s, acc)
         self.last_render = out
         return losses
+
+    def _decoder_wgrad(self, max_ctas=0):
+        if self._pending_wgrad is None:
+            return
+        n, s = self._pending_wgrad
+        self._pending_wgrad = None
+        ops.decoder_wgrad(self._scene(True, plane_grads=False), n, s, self._scratch, self._act, max_ctas)
 
     def optimizer_step(self):
         """Adam + zero_grad.  One GPU: one launch over the flat buffers (one per tensor when the parameters were not
@@ -268,16 +307,38 @@ class FusedMapper:
             sharded_optimizer_step(self.flat_param, self.flat_grad, self.grad_shard, self.shards, adam_fn, self.group)
             return
         if self.flat_param is not None:
-            self._adam_segments(self.flat_param, self.flat_grad, self.flat_m, self.flat_v, self._segments, True)
+            self._adam_split()
             return
+        self._decoder_wgrad()
         for (p, lr, eps, wd), g, m, v in zip(self.params, self.grads, self.exp_avg, self.exp_avg_sq):
             _lib.check(lib.mne_adam_step(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), lr,
                                          self.betas[0], self.betas[1], eps, wd, self.step_dev.data_ptr(), 0, 1, st),
                        'mne_adam_step')
 
+    def _adam_split(self):
+        """One GPU: the planes' Adam pass (a pure HBM stream over 129 MB) on the current stream; on a side stream, beside it,
+        the decoder's weight gradients (which only the decoder's own Adam step consumes) and that step."""
+        dec0 = self.dense_from
+        if self.wgrad_inline:
+            self._decoder_wgrad()
+            self._adam_segments(self.flat_param, self.flat_grad, self.flat_m, self.flat_v, self._segments, True)
+            return
+        main = torch.cuda.current_stream()
+        if self._wgrad_stream is None:
+            self._wgrad_stream = torch.cuda.Stream(device=self.dev)
+        side = self._wgrad_stream
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            self._decoder_wgrad(max_ctas=self.wgrad_ctas)
+            tail = slice(dec0, self.total)
+            self._adam_segments(self.flat_param[tail], self.flat_grad[tail], self.flat_m[tail], self.flat_v[tail], self._seg_tail, True,
+                                touched=self.touched[dec0 // 4:] if self.touched is not None else None)
+        self._adam_segments(self.flat_param, self.flat_grad, self.flat_m, self.flat_v, self._seg_head, True)
+        main.wait_stream(side)
+
     def step(self, rays_o, rays_d, target_rgb, target_d, noise=None, sampled=None):
         """One mapping iteration.  Returns the eight losses (device tensor, order ``LOSS_KEYS``)."""
-        losses = self.forward_backward(rays_o, rays_d, target_rgb, target_d, noise, sampled)
+        losses = self.forward_backward(rays_o, rays_d, target_rgb, target_d, noise, sampled, defer_wgrad=True)
         self.optimizer_step()
         self.last_losses = losses
         return losses
@@ -419,7 +480,7 @@ class PipelinedMapper:
         # acc is consumed (and added to) by the forward of this iteration: work on a private copy so that the side stream
         # may refill the shared one
         acc = self.acc.clone()
-        losses = m.forward_backward(self.ro, self.rd, self.rgb, self.d, sampled=(self.z, acc))
+        losses = m.forward_backward(self.ro, self.rd, self.rgb, self.d, sampled=(self.z, acc), defer_wgrad=True)
         self.losses.copy_(losses)
         self.side.wait_stream(main)                 # the batch has been consumed: refill it under the optimiser
         with torch.cuda.stream(self.side):

@@ -211,9 +211,14 @@ def act_floats(scene):
 
 
 def render_forward(scene, render_cfg, rays_o, rays_d, z_vals, target_rgb=None, target_d=None, acc=None,
-                   want_weights=False, want_aux=True, act=None):
-    """``act``: True = allocate, or a float32 buffer of n * s * ``act_floats(scene)`` elements: the per-sample record (hidden
-    activations, features, ReLU masks) is kept there for ``render_backward`` (returned as ``out['act']``)."""
+                   want_weights=False, want_aux=True, act=None, ray_counters=None, loss_grads=None, scratch=None):
+    """The fused render (``mne_render_forward_fused``): encode -> decode -> compositing -> loss sums, as ONE launch when
+    ``ray_counters`` is given, else as the point kernel followed by one register-resident ray kernel.
+    ``act``: True = allocate, or a float32 buffer of n * s * ``act_floats(scene)`` elements: the per-sample record (hidden
+    activations, features, ReLU masks) is kept there for the backward (returned as ``out['act']``).
+    ``ray_counters``: int32 [>= n] zeros (the kernel leaves them zero), True = a fresh buffer, None = two launches.
+    ``loss_grads`` + ``scratch`` (training): the kernel also writes d loss / d raw and the list of samples where it is
+    non-zero into ``scratch`` (``backward_scratch``), so that ``render_backward_points`` can follow directly."""
     n, s = z_vals.shape
     dev = z_vals.device
     ro, rd = _f32(rays_o, 'rays_o'), _f32(rays_d, 'rays_d')
@@ -233,10 +238,42 @@ def render_forward(scene, render_cfg, rays_o, rays_d, z_vals, target_rgb=None, t
         if act.dtype != torch.float32 or act.numel() < n * s * act_floats(scene) or not act.is_contiguous() or act.data_ptr() % 32:
             raise TypeError('act must be a contiguous, 32-byte aligned float32 buffer of at least n_rays * n_samples * %d elements' % act_floats(scene))
         out['act'] = act
-    _lib.check(_lib.lib().mne_render_forward(
+    if ray_counters is True:
+        ray_counters = torch.zeros(n, dtype=torch.int32, device=dev)
+    elif ray_counters is None:
+        pass
+    elif ray_counters.dtype != torch.int32 or ray_counters.numel() < n or not ray_counters.is_contiguous():
+        raise TypeError('ray_counters must be a contiguous int32 buffer of at least n_rays zeros')
+    lg = _f32(loss_grads, 'loss_grads')
+    if lg is not None and scratch is None:
+        raise ValueError('loss_grads needs a scratch buffer (ops.backward_scratch)')
+    _lib.check(_lib.lib().mne_render_forward_fused(
         C.byref(scene), C.byref(render_cfg), n, s, _ptr(ro), _ptr(rd), _ptr(z_vals), _ptr(trgb), _ptr(td),
         _ptr(out['raw']), _ptr(out.get('weights')), _ptr(out['rgb']), _ptr(out['depth']), _ptr(out.get('disp_map')),
-        _ptr(out.get('acc_map')), _ptr(out.get('depth_var')), _ptr(out.get('inds')), _ptr(acc), _ptr(act), _stream()),
+        _ptr(out.get('acc_map')), _ptr(out.get('depth_var')), _ptr(out.get('inds')), _ptr(acc), _ptr(act),
+        _ptr(ray_counters), _ptr(lg), _ptr(scratch) if lg is not None else None, _stream()),
+        'mne_render_forward_fused')
+    return out
+
+
+def render_forward_unfused(scene, render_cfg, rays_o, rays_d, z_vals, target_rgb=None, target_d=None, acc=None, act=None):
+    """``mne_render_forward``: the point kernel followed by the stand-alone ray kernel (two launches, no counters);
+    kept as the cross-check of the fused entry point and for impl 1."""
+    n, s = z_vals.shape
+    dev = z_vals.device
+    ro, rd = _f32(rays_o, 'rays_o'), _f32(rays_d, 'rays_d')
+    trgb, td = _f32(target_rgb, 'target_rgb'), _f32(target_d, 'target_d')
+    out = {'raw': torch.empty(n, s, 4, dtype=torch.float32, device=dev),
+           'rgb': torch.empty(n, 3, dtype=torch.float32, device=dev),
+           'depth': torch.empty(n, dtype=torch.float32, device=dev),
+           'weights': torch.empty(n, s, dtype=torch.float32, device=dev),
+           'inds': torch.empty(n, dtype=torch.int32, device=dev)}
+    for k in ('disp_map', 'acc_map', 'depth_var'):
+        out[k] = torch.empty(n, dtype=torch.float32, device=dev)
+    _lib.check(_lib.lib().mne_render_forward(
+        C.byref(scene), C.byref(render_cfg), n, s, _ptr(ro), _ptr(rd), _ptr(z_vals), _ptr(trgb), _ptr(td),
+        _ptr(out['raw']), _ptr(out['weights']), _ptr(out['rgb']), _ptr(out['depth']), _ptr(out['disp_map']),
+        _ptr(out['acc_map']), _ptr(out['depth_var']), _ptr(out['inds']), _ptr(acc), _ptr(act), _stream()),
         'mne_render_forward')
     return out
 
@@ -279,6 +316,29 @@ def render_backward(scene, render_cfg, rays_o, rays_d, z_vals, raw, target_rgb=N
         _ptr(acc), _ptr(lg), _ptr(grgb), _ptr(gdep), _ptr(graw), _ptr(scratch), _ptr(g_o), _ptr(g_d), _ptr(act), _stream()),
         'mne_render_backward')
     return g_o, g_d
+
+
+def render_backward_points(scene, rays_o, rays_d, z_vals, scratch, want_ray_grads=False, act=None):
+    """The point stage of the backward over a scratch buffer the fused training forward filled (``mne_render_backward_points``):
+    plane / table gradients (and decoder gradients when the scene carries their buffers) are accumulated, ray gradients
+    returned on request."""
+    n, s = z_vals.shape
+    dev = z_vals.device
+    ro, rd = _f32(rays_o, 'rays_o'), _f32(rays_d, 'rays_d')
+    g_o = g_d = None
+    if want_ray_grads:
+        g_o = torch.empty(n, 3, dtype=torch.float32, device=dev)
+        g_d = torch.empty(n, 3, dtype=torch.float32, device=dev)
+    _lib.check(_lib.lib().mne_render_backward_points(C.byref(scene), n, s, _ptr(ro), _ptr(rd), _ptr(z_vals), _ptr(scratch),
+                                                     _ptr(g_o), _ptr(g_d), _ptr(act), _stream()), 'mne_render_backward_points')
+    return g_o, g_d
+
+
+def decoder_wgrad(scene, n_rays, n_samples, scratch, act, max_ctas=0):
+    """Decoder weight gradients from the records a ``render_backward_points`` call completed (``mne_decoder_wgrad``); the
+    call before must have been made WITHOUT decoder gradient buffers in its scene, this one with them."""
+    _lib.check(_lib.lib().mne_decoder_wgrad(C.byref(scene), n_rays, n_samples, _ptr(scratch), _ptr(act), int(max_ctas), _stream()),
+               'mne_decoder_wgrad')
 
 
 def query_points(scene, pts, want_raw=True, want_geo=False, want_feat=False):

@@ -381,3 +381,60 @@ def test_render_img_matches_render_rays(with_depth):
         ref = model.render_rays(ro.reshape(-1, 3).contiguous(), rd.reshape(-1, 3).contiguous(),
                                 target_d=None if gt is None else gt.reshape(-1, 1))
     assert torch.equal(depth.float().reshape(-1), ref['depth']) and torch.equal(colour.reshape(-1, 3), ref['rgb'])
+
+
+@pytest.mark.parametrize('one_grid', [True, False])
+@pytest.mark.parametrize('n_rays', [1, 333])
+def test_fused_render_equals_point_kernel_plus_ray_kernels(one_grid, n_rays):
+    """mne_render_forward_fused (one launch: the warp that stores a ray's last sample composites it) against the same
+    work as separate launches: mne_render_forward (point kernel + ray kernel) and the ray kernel of mne_render_backward
+    (d loss / d raw + the list of samples where it is non-zero).  Same arithmetic, so the values must agree exactly; the
+    list may come out in another order."""
+    from mneslam_b200 import _lib, ops
+    cfg = configs.small_test_config(one_grid=one_grid)
+    bound = J.enlarged_bound(cfg)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    model = build_model(cfg, bb, J.init_planes(cfg, bound, seed=4, std=0.5), J.init_weights(cfg, seed=4), as_params=False)
+    n, s = n_rays, synthetic.n_samples_total(cfg)
+    b = {k: v.cuda() for k, v in synthetic.make_ray_batch(cfg, n, seed=8, zero_depth_frac=0.1, depth_range=(0.3, 2.5)).items()}
+    noise = synthetic.make_noise(n, s, 8).cuda()
+    fp, ws = flat_planes(model), [w.detach() for w in model.decoder.weight_list()]
+    rcfg = ops.make_render_cfg(cfg, norm_rays=n)
+    td = b['target_d'].reshape(-1)
+    tables = ops.SampleTables.get(cfg, 'cuda', True)
+    acc0 = ops.new_acc('cuda')
+    z = ops.sample_rays(ops.make_sample_cfg(tables, True), rcfg, n, s, td, noise, acc0, 'cuda')
+    sc = ops.make_scene(fp, ws, model.bound, model.bounding_box)
+    lg = torch.tensor([1.0, 0.5, 2.0, 3.0, 2.0, 4.0, 1.5, 0.0], device='cuda')
+
+    acc_a = acc0.clone()
+    ref = ops.render_forward_unfused(sc, rcfg, b['rays_o'], b['rays_d'], z, b['target_rgb'], td, acc_a)
+    scr_a = ops.backward_scratch(n, s, 'cuda')
+    pg = [torch.zeros_like(p) for p in fp]
+    ops.render_backward(ops.make_scene(fp, ws, model.bound, model.bounding_box, plane_grads=pg), rcfg, b['rays_o'], b['rays_d'], z,
+                        ref['raw'], b['target_rgb'], td, acc_a, loss_grads=lg, scratch=scr_a)
+
+    acc_b = acc0.clone()
+    counters = torch.zeros(n + 7, dtype=torch.int32, device='cuda')
+    scr_b = ops.backward_scratch(n, s, 'cuda')
+    m = n * s
+    cnt_a = ops.backward_active_count(scr_a, n, s)
+    la = scr_a.view(torch.int32)[4 * m:4 * m + cnt_a].sort().values
+    for single_launch in (True, False):               # with per-ray counters: one launch; without: point kernel + one ray kernel
+        acc_b = acc0.clone()
+        scr_b = ops.backward_scratch(n, s, 'cuda')
+        out = ops.render_forward(sc, rcfg, b['rays_o'], b['rays_d'], z, b['target_rgb'], td, acc_b, want_weights=True,
+                                 ray_counters=counters if single_launch else None, loss_grads=lg, scratch=scr_b)
+        torch.cuda.synchronize()
+        for k in ('raw', 'rgb', 'depth', 'weights', 'disp_map', 'acc_map', 'depth_var', 'inds'):
+            assert torch.equal(out[k], ref[k]), (k, single_launch)
+        np.testing.assert_allclose(acc_b.cpu().numpy(), acc_a.cpu().numpy(), rtol=1e-6)     # per-ray float sums, then double
+        assert int(counters.abs().sum()) == 0, 'the per-ray counters must be left at zero'
+        assert torch.equal(scr_b[:4 * m], scr_a[:4 * m]), 'd loss / d raw'
+        cnt_b = ops.backward_active_count(scr_b, n, s)
+        assert cnt_a == cnt_b > 0
+        lb = scr_b.view(torch.int32)[4 * m:4 * m + cnt_b].sort().values
+        assert torch.equal(la, lb)
+    # a second launch on the same counters (they reset themselves)
+    out2 = ops.render_forward(sc, rcfg, b['rays_o'], b['rays_d'], z, ray_counters=counters)
+    assert torch.equal(out2['rgb'], ref['rgb']) and int(counters.abs().sum()) == 0

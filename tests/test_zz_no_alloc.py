@@ -2,7 +2,7 @@
 
 Some users of the library cannot call ``cudaMalloc`` where the backward runs (the host application forbids
 allocation around the call, or only hands over input and output buffers), so one variant of the backward keeps
-its 16-byte-per-sample workspace in an array built into the library instead of taking it from the caller.
+its 20-byte-per-sample workspace in an array built into the library instead of taking it from the caller.
 This file checks, through the C ABI, that the variant gives the same gradients as ``mne_render_backward`` on
 two calls in a row (different batches and sizes, so leftovers of the first call would show), and that batches
 larger than the built-in workspace are refused with a message.  It is named so that pytest collects it last.

@@ -92,10 +92,57 @@ class CpuMapper:
         return float(loss.detach())
 
 
-def time_cpu(cfg, n_rays, steps, warmup):
+REF_STAGED = os.path.join(ROOT, 'oracle', '_ref')
+
+
+class RefCpuMapper:
+    """The reference's OWN modules (model/scene_rep.py::JointEncoding + decoder / encodings / utils, staged into the
+    git-ignored oracle/_ref/ by __graft_entry__.build()) driven as its mapper drives them: forward, get_loss_from_ret
+    (mneslam_mp.py:350-372), backward, the Adam of create_optimizer (mneslam_mp.py:431-469).  tiny-cuda-nn is absent from
+    this image, so its one live object -- the OneBlob encoding -- is the oracle's restatement (oracle/tcnn_stub.py)."""
+
+    def __init__(self, cfg, seed=0):
+        import numpy as np
+        from oracle import joint_encoding as J, tcnn_stub
+        tcnn_stub.install()
+        if REF_STAGED not in sys.path:
+            sys.path.insert(0, REF_STAGED)
+        from model.scene_rep import JointEncoding as RefJointEncoding          # the reference's class
+        self.J, self.cfg = J, cfg
+        torch.manual_seed(seed)
+        import contextlib
+        with contextlib.redirect_stdout(sys.stderr):       # the reference prints while it builds its encoders; stdout is the JSON line's
+            self.model = RefJointEncoding(cfg, torch.from_numpy(np.array(cfg['mapping']['bound'])))
+        self.model.train()
+        planes = []
+        for grp in self.model.all_planes:                                      # mneslam_mp.py:451-457
+            for i, p in enumerate(grp):
+                grp[i] = torch.nn.Parameter(p)
+                planes.append(grp[i])
+        mp = cfg['mapping']
+        self.opt = torch.optim.Adam([{'params': self.model.decoder.parameters(), 'weight_decay': 1e-6, 'lr': mp['lr_decoder']},
+                                     {'params': planes, 'eps': 1e-15, 'lr': mp['lr_embed']}], betas=(0.9, 0.99))
+
+    def step(self, batch, noise):
+        ret = self.model.forward(batch['rays_o'], batch['rays_d'], batch['target_rgb'], batch['target_d'])
+        loss = self.J.total_loss(self.cfg, ret)
+        loss.backward()
+        self.opt.step()
+        self.opt.zero_grad()
+        return float(loss.detach())
+
+
+def reference_staged():
+    return os.path.exists(os.path.join(REF_STAGED, 'model', 'scene_rep.py'))
+
+
+def time_cpu(cfg, n_rays, steps, warmup, threads=None):
     from mneslam_b200 import synthetic
+    # torch.distributed.run exports OMP_NUM_THREADS=1: set the thread count explicitly, or every N > 1 launch would time a
+    # single-threaded reference
+    torch.set_num_threads(threads or os.cpu_count() or 1)
     s = synthetic.n_samples_total(cfg)
-    m = CpuMapper(cfg)
+    m = RefCpuMapper(cfg) if reference_staged() else CpuMapper(cfg)
     times = []
     for i in range(warmup + steps):
         batch = synthetic.make_ray_batch(cfg, n_rays, seed=i)
@@ -134,32 +181,48 @@ def torch_gpu_record(cfg, n_rays, dev, steps=10, warmup=3):
                     'loss.item() per step as the reference loop has'}
 
 
+def cpu_kind():
+    return 'reference' if reference_staged() else 'port'
+
+
+def cpu_what():
+    if reference_staged():
+        return ("the reference's own modules (model/scene_rep.py JointEncoding.forward + get_loss_from_ret + backward + the Adam of "
+                'create_optimizer), torch CPU, OneBlob restated (tiny-cuda-nn absent)')
+    return "oracle port of the reference's torch-CPU path (F.grid_sample + matmul + torch Adam)"
+
+
 def cpu_baseline_record(cfg, n_rays, steps=5, warmup=1):
     pts_s, med, total = time_cpu(cfg, n_rays, steps, warmup)
-    return {'value': pts_s, 'unit': UNIT, 'cores': torch.get_num_threads(), 'kind': 'port',
-            'sample': '%d mapping iterations (median) of the same %d-ray x %d-sample workload, oracle port of the '
-                      "reference's torch-CPU path (F.grid_sample + matmul + torch Adam), %d host threads of %d cores"
-                      % (steps, n_rays, cfg['training']['n_samples_d'] + cfg['training']['n_range_d'],
-                         torch.get_num_threads(), os.cpu_count()),
-            'ms_per_step': med * 1e3}
+    threads = torch.get_num_threads()
+    # the reference pins OMP_NUM_THREADS=3 (mneslam_mp.py:2): its own setting, reported beside the all-cores figure
+    pts_s3, med3, _ = time_cpu(cfg, n_rays, 3, 1, threads=3)
+    torch.set_num_threads(threads)
+    return {'value': pts_s, 'unit': UNIT, 'cores': threads, 'kind': cpu_kind(),
+            'sample': '%d mapping iterations (median) of the same %d-ray x %d-sample workload, %s, %d host threads of %d cores'
+                      % (steps, n_rays, cfg['training']['n_samples_d'] + cfg['training']['n_range_d'], cpu_what(),
+                         threads, os.cpu_count()),
+            'ms_per_step': med * 1e3,
+            'value_at_reference_threads': pts_s3, 'reference_threads': 3, 'ms_per_step_at_reference_threads': med3 * 1e3}
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU implementation of the path (oracle port; /root/reference is Python
-    and cannot travel to the GPU box) on the host cores, rank 0 only."""
+    """--impl reference: the reference's CPU implementation of the path on the host cores, rank 0 only: its own modules
+    where __graft_entry__.build() staged them (oracle/_ref/, git-ignored, travels with the snapshot), else the oracle port."""
     if int(os.environ.get('RANK', '0')) != 0:
         return
     from mneslam_b200 import configs
     cfg = configs.replica_room0()
-    steps, warmup = max(1, min(args.steps, 20)), max(1, min(args.warmup, 3))
+    # the driver's own step / warm-up counts (one CPU iteration is ~0.3 s: K = 50, W = 5 is 15 s); bounded only against absurd values
+    steps, warmup = max(1, min(args.steps, 200)), max(0, min(args.warmup, 50))
     pts_s, med, _ = time_cpu(cfg, args.rays, steps, warmup)
-    sample = ('%d of the requested %d mapping iterations (median), %d rays x 43 samples, %d host threads'
-              % (steps, args.steps, args.rays, torch.get_num_threads()))
+    sample = ('%d mapping iterations (median) after %d warm-up, %d rays x 43 samples, %s, %d host threads of %d cores'
+              % (steps, warmup, args.rays, cpu_what(), torch.get_num_threads(), os.cpu_count()))
     line = {'impl': 'reference', 'metric': METRIC, 'value': pts_s, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': steps,
             'warmup': warmup, 'ms_per_step': med * 1e3, 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
             'config': workload_config(cfg, args.rays, 1),
-            'cpu_baseline': {'value': pts_s, 'unit': UNIT, 'cores': torch.get_num_threads(), 'kind': 'port',
+            'cpu_baseline': {'value': pts_s, 'unit': UNIT, 'cores': torch.get_num_threads(), 'kind': cpu_kind(),
                              'sample': sample},
             'e2e': {'value': pts_s, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
@@ -234,6 +297,155 @@ def ncu_traffic(kernel):
         except Exception:
             return None
     return None
+
+
+
+# ----------------------------------------------------------------------------------------------------
+# records that travel in the same JSON line: BASELINE.json configs[3] and the multi-GPU self-check
+# ----------------------------------------------------------------------------------------------------
+CONFIGS3_TOTAL_RAYS = 65536
+ALG_BYTES_PER_POINT_HASH = 2048     # 16 levels x 8 corners x 8 B gathered + the same entries receiving a gradient
+
+
+def _max_over_ranks(ms, world, dev):
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+    return ms
+
+
+def configs3_record(world, rank, dev, steps):
+    """BASELINE.json configs[3]: 65 536 rays per iteration in TOTAL (strong scaling: 65 536 / N per GPU), ScanNet scene0000
+    bound and sampling (96 + 21 samples per ray), 16-level hash grid (T = 2^19), gradients exchanged over NVLink; the same
+    CUDA-graph path as the headline line.  Device time, max over ranks."""
+    import torch.distributed as dist
+    from mneslam_b200 import JointEncoding, configs, synthetic
+    from mneslam_b200.mapping import DeviceKeyframeRays, FusedMapper
+    cfg = configs.scannet_scene0000_onegrid()
+    cfg['grid']['use_hash'] = True
+    n = CONFIGS3_TOTAL_RAYS // world
+    s = synthetic.n_samples_total(cfg)
+    torch.manual_seed(0)
+    model = JointEncoding(cfg, torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)).to(dev)
+    model.train()
+    mapper = FusedMapper(model, world_size=world)
+    rays_cpu, poses_cpu = synthetic.make_keyframe_db(cfg, n_kf=N_KF, seed=0)
+    db = DeviceKeyframeRays(rays_cpu.to(dev), poses_cpu.to(dev))
+
+    def one_step():
+        return mapper.step(*db.sample(n))
+    for _ in range(3):
+        one_step()
+    torch.cuda.synchronize()
+    graph = None
+    try:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            one_step()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            one_step()
+        graph.replay()
+        torch.cuda.synchronize()
+    except Exception as e:
+        print('bench.py: configs3 graph capture failed (%r); eager' % (e,), file=sys.stderr)
+        graph = None
+        torch.cuda.synchronize()
+    k = max(3, min(steps, 10))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(k):
+        graph.replay() if graph is not None else one_step()
+    e1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ms = _max_over_ranks(e0.elapsed_time(e1) / k, world, dev)
+    pts = n * s * world
+    pts_s = pts / (ms * 1e-3)
+    peak, _ = measured_peak()
+    rec = {'workload': 'BASELINE.json configs[3]: %d rays per iteration in total (%d per GPU), ScanNet scene0000 bound, %d samples/ray, '
+                       '16-level hash grid T=2^19 + OneBlob + MLPs, fwd + losses + bwd + Adam, gradient exchange over NVLink peer memory'
+                       % (n * world, n, s),
+           'scaling': 'strong', 'n_gpus': world, 'rays_total': n * world, 'rays_per_gpu': n, 'samples_per_ray': s,
+           'ms_per_step': ms, 'value': pts_s, 'unit': UNIT, 'steps': k, 'cuda_graph': graph is not None,
+           'algorithmic_bytes_per_point': ALG_BYTES_PER_POINT_HASH,
+           'gather_roofline_frac': pts_s * ALG_BYTES_PER_POINT_HASH / 1e9 / (peak * world),
+           'table_entries': int(model.hash_meta.n_entries)}
+    del graph, mapper, model, db
+    torch.cuda.empty_cache()
+    return rec
+
+
+def self_check_record(world, rank, dev, iters=4):
+    """Do the ranks compute the same map, and is it the single-GPU map?  Room0 configuration, 256 rays per rank: a few
+    sharded iterations (flat parameter buffers must be bit-identical across ranks afterwards), against one GPU (rank 0)
+    taking the same iterations on the concatenated batch."""
+    import torch.distributed as dist
+    from mneslam_b200 import JointEncoding, configs, synthetic
+    from mneslam_b200.mapping import FusedMapper
+    cfg = configs.replica_room0()
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    s = synthetic.n_samples_total(cfg)
+    n = 256
+
+    def make(world_size):
+        torch.manual_seed(7)
+        m = JointEncoding(cfg, bb).to(dev)
+        m.train()
+        return m, FusedMapper(m, world_size=world_size)
+    model, mapper = make(world)
+    single = make(1) if (rank == 0 and world > 1) else None
+    loss_err = 0.0
+    for it in range(iters):
+        shards = [{k: v.to(dev) for k, v in synthetic.make_ray_batch(cfg, n, seed=500 + it * 64 + r, zero_depth_frac=0.05).items()}
+                  for r in (range(world) if rank == 0 else [rank])]
+        noises = [synthetic.make_noise(n, s, seed=900 + it * 64 + r).to(dev) for r in (range(world) if rank == 0 else [rank])]
+        mine, nz = (shards[rank], noises[rank]) if rank == 0 else (shards[0], noises[0])
+        losses = mapper.step(mine['rays_o'], mine['rays_d'], mine['target_rgb'], mine['target_d'], noise=nz)
+        if single is not None:
+            cat = {k: torch.cat([b[k] for b in shards]) for k in ('rays_o', 'rays_d', 'target_rgb', 'target_d')}
+            ref = single[1].step(cat['rays_o'], cat['rays_d'], cat['target_rgb'], cat['target_d'], noise=torch.cat(noises))
+            a, b = losses[:7].double(), ref[:7].double()
+            ok = torch.isfinite(b)
+            loss_err = max(loss_err, float(((a[ok] - b[ok]).abs() / (b[ok].abs() + 1e-12)).max()))
+    torch.cuda.synchronize()
+    identical = True
+    if world > 1:
+        flat = mapper.flat_param.clone()
+        dist.broadcast(flat, src=0)
+        same = torch.tensor([1 if torch.equal(flat, mapper.flat_param) else 0], device=dev)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        identical = bool(int(same.item()))
+    err = None
+    if single is not None:
+        a = mapper.flat_param[:mapper.total].double()
+        b = single[1].flat_param[:single[1].total].double()
+        err = float((a - b).norm() / (b.norm() + 1e-30))
+        moved = float((b - b.new_zeros(()).expand_as(b)).norm())      # sanity: the map is not all zeros
+        err_ok = err < 2e-3 and moved > 0
+    else:
+        err_ok = True
+    rec = {'ok': bool(identical and err_ok and loss_err < 1e-3), 'ranks_identical': identical,
+           'param_rel_err_vs_single_gpu': err, 'loss_rel_err_vs_single_gpu': loss_err if single is not None else None,
+           'iterations': iters, 'rays_per_rank': n,
+           'what': 'room0 map, %d sharded iterations on %d ranks; flat parameter buffers compared bit for bit across ranks '
+                   '(broadcast + equal) and against one GPU taking the concatenated batches (relative L2 error < 2e-3: the '
+                   'summation order of the float atomics differs)' % (iters, world)}
+    if world > 1:
+        ok_all = torch.tensor([1 if rec['ok'] else 0], device=dev)
+        dist.broadcast(ok_all, src=0)
+    del mapper, model, single
+    torch.cuda.empty_cache()
+    return rec
 
 
 def run_ours(args):
@@ -594,6 +806,18 @@ def run_ours(args):
                     'points_per_iter': 1024 * 117}
         del tmodel, tracker
 
+    # ---- the records every N carries: configs[3] (strong scaling, hash grid) and the cross-rank self-check
+    n_active_main = ops.backward_active_count(mapper._scratch, n_rays, s)
+    extra = {}
+    try:
+        extra['self_check'] = self_check_record(world, rank, dev)
+    except Exception as e:
+        extra['self_check'] = {'ok': False, 'error': repr(e)[:300]}
+    try:
+        extra['configs3'] = configs3_record(world, rank, dev, args.steps)
+    except Exception as e:
+        extra['configs3'] = {'error': repr(e)[:300]}
+
     if rank == 0:
         peak, peak_src = measured_peak()
         # algorithmic bytes per launch (DESIGN.md "Roofline accounting"):
@@ -601,7 +825,7 @@ def run_ours(args):
         #   backward: the samples with a non-zero loss gradient scatter into the same texels (the others add nothing)
         #   Adam    : 32 B per parameter of a group that ever received a gradient (p, g, m, v read; p, m, v, g written),
         #             4 B gradient read per parameter of the others, 0.25 B of flags per parameter
-        n_active = ops.backward_active_count(mapper._scratch, n_rays, s)
+        n_active = n_active_main
         fwd_bytes = pts_per_rank * ALG_BYTES_PER_POINT_FWD
         bwd_bytes = n_active * ALG_BYTES_PER_POINT_BWD
         n_param = mapper.total
@@ -643,6 +867,7 @@ def run_ours(args):
                      'touched_fraction_at_end': float(mapper.touched.float().mean().item()) if mapper.touched is not None else 1.0},
             'last_loss': float(mapper.total_loss(static_losses if graph is not None else losses).item()),
         }
+        line.update(extra)
         if world == 1 and not args.no_cpu_baseline:
             line['cpu_baseline'] = cpu_baseline_record(cfg, n_rays)
             try:

@@ -117,7 +117,7 @@ class RefCpuMapper:
         planes = []
         for grp in self.model.all_planes:                                      # mneslam_mp.py:451-457
             for i, p in enumerate(grp):
-                grp[i] = torch.nn.Parameter(p)
+                grp[i] = torch.nn.Parameter(p.cpu())    # (the reference puts its planes on the GPU when one is visible; this arm is the CPU path)
                 planes.append(grp[i])
         mp = cfg['mapping']
         self.opt = torch.optim.Adam([{'params': self.model.decoder.parameters(), 'weight_decay': 1e-6, 'lr': mp['lr_decoder']},

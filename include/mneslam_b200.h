@@ -332,13 +332,25 @@ int mne_adam_step_peers(int32_t world_size, int32_t rank, float* const* param_pt
                         int64_t n_total, int32_t chunk, float* exp_avg, float* exp_avg_sq, int32_t n_segments,
                         const int64_t* segment_ends, const float* lr, const float* eps, const float* weight_decay,
                         float beta1, float beta2, const int64_t* step_dev, int64_t step_host, uint8_t* touched,
-                        float* multicast_param, float* multicast_grad, const uint8_t* dirty,
+                        float* multicast_param, float* multicast_grad, const uint8_t* dirty, const float* inbox,
                         mne_stream_t stream);
+/* inbox (device pointer on THIS rank, or NULL; needs dirty): [world_size][n_total / world_size] floats, slot r holding the
+ * gradient texels of this rank's slice that rank r flagged, pushed there by rank r's mne_grad_push before the barrier.  With
+ * it the kernel reads the peers' contributions from local memory (its own contribution still from its own gradient buffer)
+ * and nothing has to be fetched -- or cleared -- over NVLink. */
 /* For every 32-float texel of this rank's gradient buffer: flag = 1 iff it holds a non-zero value; the flag is
  * stored into the texel OWNER's flag array (dirty_ptrs[owner], HOST array of world_size peer-mapped device pointers)
  * at [rank][owner-local texel index] -- the layout mne_adam_step_peers reads.  world_size = 1: a plain local map. */
 int mne_grad_dirty_map(const float* grad, int64_t n_total, int32_t chunk, int32_t world_size, int32_t rank,
                        uint8_t* const* dirty_ptrs, mne_stream_t stream);
+/* mne_grad_dirty_map that also MOVES the data: every non-zero texel owned by another rank is stored into that owner's
+ * inbox (inbox_ptrs[owner], HOST array of world_size peer-mapped device pointers to [world_size][n_total / world_size]
+ * floats; slot [rank][owner-local texel], the flags' layout) and cleared in `grad`; texels this rank owns stay where they
+ * are.  Peer stores are fire-and-forget, so the exchange is bound by NVLink bandwidth instead of by the round trips of
+ * peer loads issued from inside the optimiser kernel.  Only the first n_scan elements (a multiple of 32) are examined:
+ * what lies beyond -- e.g. the decoder weights, exchanged by an all-reduce of their own -- is neither flagged nor moved. */
+int mne_grad_push(float* grad, int64_t n_total, int64_t n_scan, int32_t chunk, int32_t world_size, int32_t rank,
+                  uint8_t* const* dirty_ptrs, float* const* inbox_ptrs, mne_stream_t stream);
 /* Same hand-over without reading the gradient buffer: local_map (n_total / 32 bytes) holds the flags the backward pass
  * set through MneSceneDesc.dirty; they are pushed to the owners in the same layout and local_map is cleared.  Texels
  * at or beyond element dense_from (the decoder weights at the tail of the flat buffer) are always flagged. */

@@ -250,6 +250,7 @@ struct AdamPeers {
     float* mc_grad;
     const uint8_t* dirty;      // LOCAL [world][local4 / 8]: rank r's "non-zero this step" flags of the texels this rank owns
     int use_dirty;
+    const float4* inbox;       // LOCAL [world][local4] (or NULL): the peers' flagged gradient groups, pushed here by mne_grad_push
 };
 
 // one flag byte per 32 consecutive floats (a 128-byte texel): does this rank's gradient have anything there?
@@ -258,20 +259,31 @@ struct AdamPeers {
 // fire-and-forget, whereas flag loads from the peers cost the optimiser kernel 60 us of NVLink round trips (measured).
 struct DirtyPush {
     uint8_t* dst[MNE_MAX_PEERS];
+    float4* inbox[MNE_MAX_PEERS];   // optional: every rank's inbox [world][owned texels][8 float4]; non-zero texels are PUSHED there
     int world, rank, chunk_tx_log2;
+    int push;
     int64_t n32, local32;
+    int64_t scan32;                 // texels [0, scan32) are examined; the rest of the buffer is left alone
 };
-__global__ void __launch_bounds__(256) grad_dirty_kernel(const float4* __restrict__ g4, const __grid_constant__ DirtyPush d) {
+// With inboxes (d.push): a non-zero texel owned by ANOTHER rank is also stored into that owner's inbox (slot `rank`, packed
+// in ownership order like the flags) and cleared locally, so that the owner's optimiser kernel reads nothing over NVLink:
+// fire-and-forget peer stores (bandwidth bound) instead of peer loads from inside the optimiser (round-trip bound: measured
+// 52 us of the 172 us kernel at eight ranks, plus as many peer stores to clear what was read).
+__global__ void __launch_bounds__(256) grad_dirty_kernel(float4* __restrict__ g4, const __grid_constant__ DirtyPush d) {
     const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 3;
     const int sub = threadIdx.x & 7;
     const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
     // four texels in flight per thread: the pass is a pure read of the gradient buffer, bound by loads in flight
-    for (int64_t tx0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3; tx0 < d.n32; tx0 += 4 * stride) {
+    // (the loop condition is the WARP's first texel, so that all 32 lanes reach the shuffles below together; a lane whose own
+    //  texel lies beyond the end only skips its load and its store)
+    const int64_t lane_tx = (threadIdx.x & 31) >> 3;
+    for (int64_t tw0 = ((int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31)) >> 3; tw0 < d.scan32; tw0 += 4 * stride) {
+        const int64_t tx0 = tw0 + lane_tx;
         float4 v[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const int64_t tx = tx0 + u * stride;
-            v[u] = tx < d.n32 ? g4[tx * 8 + sub] : zero;
+            v[u] = tx < d.scan32 ? g4[tx * 8 + sub] : zero;
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
@@ -280,11 +292,15 @@ __global__ void __launch_bounds__(256) grad_dirty_kernel(const float4* __restric
             nz |= __shfl_xor_sync(0xffffffffu, nz, 1);
             nz |= __shfl_xor_sync(0xffffffffu, nz, 2);
             nz |= __shfl_xor_sync(0xffffffffu, nz, 4);
-            if (sub == 0 && tx < d.n32) {
+            if (tx < d.scan32) {
                 const uint32_t c = (uint32_t)(tx >> d.chunk_tx_log2);
                 const uint32_t owner = c % (uint32_t)d.world;
                 const int64_t lt = ((int64_t)(c / (uint32_t)d.world) << d.chunk_tx_log2) + (tx & ((1 << d.chunk_tx_log2) - 1));
-                d.dst[owner][(int64_t)d.rank * d.local32 + lt] = (uint8_t)nz;
+                if (sub == 0) d.dst[owner][(int64_t)d.rank * d.local32 + lt] = (uint8_t)nz;
+                if (d.push && nz && owner != (uint32_t)d.rank) {
+                    d.inbox[owner][((int64_t)d.rank * d.local32 + lt) * 8 + sub] = v[u];
+                    g4[tx * 8 + sub] = zero;
+                }
             }
         }
     }
@@ -331,7 +347,15 @@ __device__ __forceinline__ uint32_t peer_flags(const AdamPeers& s, int64_t i) {
     return mk;
 }
 
-__global__ void __launch_bounds__(256, 4) adam_peers_sparse_kernel(const __grid_constant__ AdamPeers s) {
+// U owned groups in flight per thread: the flags of all of them first, then every load that the flags call for -- the local
+// parameter / moment loads and the flagged peers' gradients (NVLink round trips, the longest latency in the kernel) of ALL
+// U groups are issued before anything depends on them -- then the updates, then the parameter stores to every rank
+// (fire-and-forget).  With one group in flight the peer fetch, the local update and the write-back of a thread ran one
+// after the other (measured r01: 38 + 49 + 80 us at eight ranks); in flight together they overlap.
+constexpr int kPeerU = 2;
+constexpr int kPeerFetch = 4;      // peer gradients fetched per group before the sum depends on them
+
+__global__ void __launch_bounds__(256, 3) adam_peers_sparse_kernel(const __grid_constant__ AdamPeers s) {
     const double t = (double)(s.step_dev ? *s.step_dev : s.step_host);
     const float bc1 = (float)(1.0 - pow((double)s.beta1, t));
     const float bc2_sqrt = (float)sqrt(1.0 - pow((double)s.beta2, t));
@@ -339,61 +363,106 @@ __global__ void __launch_bounds__(256, 4) adam_peers_sparse_kernel(const __grid_
     const int64_t end_all = s.end4[s.n_seg - 1];
     float4* m4 = reinterpret_cast<float4*>(s.m);
     float4* v4 = reinterpret_cast<float4*>(s.v);
+    float4* p_loc = reinterpret_cast<float4*>(s.param[s.rank]);
     const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
-    int seg = 0;
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    int64_t gi_n = i < s.local4 ? owned_group(s, i) : end_all;
-    uint32_t mk_n = 0;
-    uint8_t tf_n = 1;
-    if (gi_n < end_all) { mk_n = peer_flags(s, i); if (s.touched) tf_n = s.touched[i]; }
-    for (; i < s.local4; i += stride) {
-        const int64_t gi = gi_n;
-        const uint32_t mk = mk_n;
-        const uint8_t tf = tf_n;
-        const int64_t i2 = i + stride;
-        gi_n = i2 < s.local4 ? owned_group(s, i2) : end_all;
-        mk_n = 0; tf_n = 1;
-        if (gi_n < end_all) { mk_n = peer_flags(s, i2); if (s.touched) tf_n = s.touched[i2]; }
-        if (gi >= end_all) continue;                       // padding
-        while (gi >= s.end4[seg]) ++seg;
-        const float wd = s.wd[seg];
-        if (s.touched && wd == 0.0f && !mk && !tf) continue;   // identity update: every replica already holds this value
-        float4 p = reinterpret_cast<float4*>(s.param[s.rank])[gi], m = m4[i], v = v4[i];
-        float4 g = zero;
-        uint32_t rest = mk;
-        while (rest) {
-            float4 x[4];
-            float4* gp[4];
+    int seg[kPeerU] = {};
+    for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < s.local4; i0 += kPeerU * stride) {
+        int64_t li[kPeerU], gi[kPeerU];
+        uint32_t mk[kPeerU];
+        uint8_t tf[kPeerU];
+        bool on[kPeerU];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                gp[k] = nullptr; x[k] = zero;
-                if (rest) {
-                    const int r = __ffs(rest) - 1;
-                    rest &= rest - 1;
-                    gp[k] = reinterpret_cast<float4*>(s.grad[r]) + gi;
-                    x[k] = *gp[k];
+        for (int u = 0; u < kPeerU; ++u) {
+            li[u] = i0 + u * stride;
+            on[u] = li[u] < s.local4;
+            gi[u] = on[u] ? owned_group(s, li[u]) : end_all;
+            on[u] = on[u] && gi[u] < end_all;                 // beyond: padding
+            mk[u] = 0; tf[u] = 1;
+            if (on[u]) { mk[u] = peer_flags(s, li[u]); if (s.touched) tf[u] = s.touched[li[u]]; }
+        }
+        float wd[kPeerU];
+#pragma unroll
+        for (int u = 0; u < kPeerU; ++u) {
+            wd[u] = 0.f;
+            if (on[u]) {
+                while (gi[u] >= s.end4[seg[u]]) ++seg[u];
+                wd[u] = s.wd[seg[u]];
+                if (s.touched && wd[u] == 0.0f && !mk[u] && !tf[u]) on[u] = false;   // identity update: every replica holds this value
+            }
+        }
+        // ---- all loads of all groups
+        float4 p[kPeerU], m[kPeerU], v[kPeerU], x[kPeerU][kPeerFetch];
+        float4* gp[kPeerU][kPeerFetch];
+        uint32_t rest[kPeerU];
+#pragma unroll
+        for (int u = 0; u < kPeerU; ++u) {
+            rest[u] = on[u] ? mk[u] : 0u;
+#pragma unroll
+            for (int k = 0; k < kPeerFetch; ++k) {
+                gp[u][k] = nullptr; x[u][k] = zero;
+                if (rest[u]) {
+                    const int r = __ffs(rest[u]) - 1;
+                    rest[u] &= rest[u] - 1;
+                    if (s.inbox && r != s.rank) {
+                        x[u][k] = s.inbox[(int64_t)r * s.local4 + li[u]];      // pushed by rank r; nothing to clear (flags are rewritten every step)
+                    } else {
+                        gp[u][k] = reinterpret_cast<float4*>(s.grad[r]) + gi[u];
+                        x[u][k] = *gp[u][k];
+                    }
                 }
             }
+            if (on[u]) { p[u] = p_loc[gi[u]]; m[u] = m4[li[u]]; v[u] = v4[li[u]]; }
+        }
+        // ---- sums (more than kPeerFetch flagged peers: the rest, four at a time), updates, stores
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-                if (gp[k]) { g.x += x[k].x; g.y += x[k].y; g.z += x[k].z; g.w += x[k].w; *gp[k] = zero; }
+        for (int u = 0; u < kPeerU; ++u) {
+            if (!on[u]) continue;
+            float4 g = zero;
+#pragma unroll
+            for (int k = 0; k < kPeerFetch; ++k) {
+                g.x += x[u][k].x; g.y += x[u][k].y; g.z += x[u][k].z; g.w += x[u][k].w;       // (unfetched slots hold zero)
+                if (gp[u][k]) *gp[u][k] = zero;
+            }
+            while (rest[u]) {
+                float4 y[4];
+                float4* yp[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    yp[k] = nullptr; y[k] = zero;
+                    if (rest[u]) {
+                        const int r = __ffs(rest[u]) - 1;
+                        rest[u] &= rest[u] - 1;
+                        if (s.inbox && r != s.rank) {
+                            y[k] = s.inbox[(int64_t)r * s.local4 + li[u]];
+                        } else {
+                            yp[k] = reinterpret_cast<float4*>(s.grad[r]) + gi[u];
+                            y[k] = *yp[k];
+                        }
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    g.x += y[k].x; g.y += y[k].y; g.z += y[k].z; g.w += y[k].w;
+                    if (yp[k]) *yp[k] = zero;
+                }
+            }
+            AdamArgs a{};
+            a.beta1 = s.beta1; a.beta2 = s.beta2; a.eps = s.eps[seg[u]]; a.weight_decay = wd[u]; a.zero_grad = 0;
+            if (s.touched && wd[u] == 0.0f) {
+                const bool nz = g.x != 0.0f || g.y != 0.0f || g.z != 0.0f || g.w != 0.0f;
+                if (!nz && !tf[u]) continue;             // flagged texel, but this group of it carried no gradient
+                if (!tf[u]) s.touched[li[u]] = 1;
+            }
+            const float step_size = (float)((double)s.lr[seg[u]] / (double)bc1);
+            adam_one(p[u].x, g.x, m[u].x, v[u].x, a, step_size, bc2_sqrt);
+            adam_one(p[u].y, g.y, m[u].y, v[u].y, a, step_size, bc2_sqrt);
+            adam_one(p[u].z, g.z, m[u].z, v[u].z, a, step_size, bc2_sqrt);
+            adam_one(p[u].w, g.w, m[u].w, v[u].w, a, step_size, bc2_sqrt);
+            m4[li[u]] = m[u]; v4[li[u]] = v[u];
+            if (s.mc_param) multimem_st(reinterpret_cast<float4*>(s.mc_param) + gi[u], p[u]);
+            else
+                for (int r = 0; r < s.world; ++r) reinterpret_cast<float4*>(s.param[r])[gi[u]] = p[u];
         }
-        AdamArgs a{};
-        a.beta1 = s.beta1; a.beta2 = s.beta2; a.eps = s.eps[seg]; a.weight_decay = wd; a.zero_grad = 0;
-        if (s.touched && wd == 0.0f) {
-            const bool nz = g.x != 0.0f || g.y != 0.0f || g.z != 0.0f || g.w != 0.0f;
-            if (!nz && !tf) continue;                // flagged texel, but this group of it carried no gradient
-            if (!tf) s.touched[i] = 1;
-        }
-        const float step_size = (float)((double)s.lr[seg] / (double)bc1);
-        adam_one(p.x, g.x, m.x, v.x, a, step_size, bc2_sqrt);
-        adam_one(p.y, g.y, m.y, v.y, a, step_size, bc2_sqrt);
-        adam_one(p.z, g.z, m.z, v.z, a, step_size, bc2_sqrt);
-        adam_one(p.w, g.w, m.w, v.w, a, step_size, bc2_sqrt);
-        m4[i] = m; v4[i] = v;
-        if (s.mc_param) multimem_st(reinterpret_cast<float4*>(s.mc_param) + gi, p);
-        else
-            for (int r = 0; r < s.world; ++r) reinterpret_cast<float4*>(s.param[r])[gi] = p;
     }
 }
 
@@ -458,7 +527,7 @@ extern "C" int mne_adam_step_peers(int32_t world_size, int32_t rank, float* cons
                                    int64_t n_total, int32_t chunk, float* exp_avg, float* exp_avg_sq, int32_t n_segments,
                                    const int64_t* segment_ends, const float* lr, const float* eps, const float* weight_decay,
                                    float beta1, float beta2, const int64_t* step_dev, int64_t step_host, uint8_t* touched,
-                                   float* multicast_param, float* multicast_grad, const uint8_t* dirty,
+                                   float* multicast_param, float* multicast_grad, const uint8_t* dirty, const float* inbox,
                                    mne_stream_t stream) {
     using namespace mne;
     MNE_CHECK_ARG(param_ptrs && grad_ptrs && exp_avg && exp_avg_sq && segment_ends && lr && eps && weight_decay,
@@ -490,6 +559,8 @@ extern "C" int mne_adam_step_peers(int32_t world_size, int32_t rank, float* cons
     s.mc_param = multicast_param; s.mc_grad = multicast_grad;
     s.use_dirty = dirty != nullptr;
     s.dirty = dirty;
+    MNE_CHECK_ARG(!inbox || (dirty && (((uintptr_t)inbox) & 15) == 0), "mne_adam_step_peers: inbox needs the dirty flags and 16-byte alignment");
+    s.inbox = reinterpret_cast<const float4*>(inbox);
     int64_t blocks = (s.local4 + 255) / 256;
     const int64_t cap = (int64_t)adam_sms() * (s.use_dirty ? resident_ctas(adam_peers_sparse_kernel, 256) : resident_ctas(adam_peers_kernel, 256));
     if (blocks > cap) blocks = cap;
@@ -499,8 +570,24 @@ extern "C" int mne_adam_step_peers(int32_t world_size, int32_t rank, float* cons
     return 0;
 }
 
+static int grad_flags_launch(float* grad, int64_t n_total, int64_t n_scan, int32_t chunk, int32_t world_size, int32_t rank,
+                             uint8_t* const* dirty_ptrs, float* const* inbox_ptrs, mne_stream_t stream);
+
 extern "C" int mne_grad_dirty_map(const float* grad, int64_t n_total, int32_t chunk, int32_t world_size, int32_t rank,
                                   uint8_t* const* dirty_ptrs, mne_stream_t stream) {
+    return grad_flags_launch(const_cast<float*>(grad), n_total, n_total, chunk, world_size, rank, dirty_ptrs, nullptr, stream);
+}
+
+extern "C" int mne_grad_push(float* grad, int64_t n_total, int64_t n_scan, int32_t chunk, int32_t world_size, int32_t rank,
+                             uint8_t* const* dirty_ptrs, float* const* inbox_ptrs, mne_stream_t stream) {
+    using namespace mne;
+    MNE_CHECK_ARG(inbox_ptrs, "mne_grad_push: null inbox array");
+    MNE_CHECK_ARG(n_scan >= 0 && n_scan <= n_total && (n_scan & 31) == 0, "mne_grad_push: n_scan must be a multiple of 32 in [0, n_total]");
+    return grad_flags_launch(grad, n_total, n_scan, chunk, world_size, rank, dirty_ptrs, inbox_ptrs, stream);
+}
+
+static int grad_flags_launch(float* grad, int64_t n_total, int64_t n_scan, int32_t chunk, int32_t world_size, int32_t rank,
+                             uint8_t* const* dirty_ptrs, float* const* inbox_ptrs, mne_stream_t stream) {
     using namespace mne;
     MNE_CHECK_ARG(grad && dirty_ptrs, "mne_grad_dirty_map: null argument");
     MNE_CHECK_ARG(world_size >= 1 && world_size <= MNE_MAX_PEERS && rank >= 0 && rank < world_size, "mne_grad_dirty_map: bad world_size / rank");
@@ -512,13 +599,19 @@ extern "C" int mne_grad_dirty_map(const float* grad, int64_t n_total, int32_t ch
     for (int r = 0; r < world_size; ++r) {
         MNE_CHECK_ARG(dirty_ptrs[r], "mne_grad_dirty_map: null flag array");
         d.dst[r] = dirty_ptrs[r];
+        if (inbox_ptrs) {
+            MNE_CHECK_ARG(inbox_ptrs[r] && (((uintptr_t)inbox_ptrs[r]) & 15) == 0, "mne_grad_push: inboxes must be non-null and 16-byte aligned");
+            d.inbox[r] = reinterpret_cast<float4*>(inbox_ptrs[r]);
+        }
     }
+    d.push = inbox_ptrs != nullptr;
     d.world = world_size; d.rank = rank; d.chunk_tx_log2 = 31 - __builtin_clz((unsigned)chunk) - 5;
-    d.n32 = n_total >> 5; d.local32 = d.n32 / world_size;
-    int64_t blocks = (d.n32 * 8 + 255) / 256;
+    d.n32 = n_total >> 5; d.local32 = d.n32 / world_size; d.scan32 = n_scan >> 5;
+    if (d.scan32 == 0) return 0;
+    int64_t blocks = (d.scan32 * 8 + 255) / 256;
     const int64_t cap = (int64_t)sm_count() * resident_ctas(grad_dirty_kernel, 256);
     if (blocks > cap) blocks = cap;
-    grad_dirty_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float4*>(grad), d);
+    grad_dirty_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float4*>(grad), d);
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

@@ -68,7 +68,11 @@ class FusedMapper:
         for p, *_ in self.params:
             if not (p.is_contiguous() or p.is_contiguous(memory_format=torch.channels_last)) or p.numel() % 4:
                 raise ValueError('map parameters must be dense tensors with a multiple of 4 elements')
-        total = sum(p.numel() for p, *_ in self.params)
+        # the decoder's weights start on a 32-float (128-byte texel) boundary of the flat buffers, so that the texel-granular
+        # gradient exchange of the encoder never straddles into them (hash tables are not a multiple of 32 floats long)
+        enc_len = sum(p.numel() for p in planes)
+        self._dec_pad = (-enc_len) % 32
+        total = sum(p.numel() for p, *_ in self.params) + self._dec_pad
         if world_size > 1:
             if not adopt_parameters:
                 raise ValueError('multi-GPU mapping needs adopt_parameters=True (flat buffers for the collectives)')
@@ -91,7 +95,12 @@ class FusedMapper:
                 hg, hp = symm.rendezvous(g_buf, group.group_name), symm.rendezvous(p_buf, group.group_name)
                 hd = symm.rendezvous(d_buf, group.group_name)
                 d_buf.zero_()
-                self.peers = {'grad': g_buf, 'param': p_buf, 'dirty': d_buf, 'hg': hg, 'hp': hp, 'hd': hd,
+                # inbox: [rank][owned elements] -- the peers push their non-zero gradient texels of this rank's slice here
+                i_buf = symm.empty(padded, dtype=torch.float32, device=self.dev)
+                hi = symm.rendezvous(i_buf, group.group_name)
+                i_buf.zero_()
+                self.peers = {'grad': g_buf, 'param': p_buf, 'dirty': d_buf, 'hg': hg, 'hp': hp, 'hd': hd, 'inbox': i_buf, 'hi': hi,
+                              'inbox_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hi.buffer_ptrs]),
                               'dirty_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hd.buffer_ptrs]),
                               'grad_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hg.buffer_ptrs]),
                               'param_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hp.buffer_ptrs]),
@@ -118,13 +127,20 @@ class FusedMapper:
             self.flat_param = self.peers['param'].zero_()
         else:
             self.flat_param = torch.zeros(padded, dtype=torch.float32, device=self.dev) if adopt_parameters else None
+        if world_size > 1:            # the decoder's moments, replicated (its Adam step runs on every rank)
+            n_dec = sum(w.numel() for w in weights)
+            self.dec_m = torch.zeros(n_dec, dtype=torch.float32, device=self.dev)
+            self.dec_v = torch.zeros(n_dec, dtype=torch.float32, device=self.dev)
         # one byte per 4 parameters of this rank's slice: groups never hit by a gradient are skipped by Adam (exact)
         self.touched = torch.zeros(mv_len // 4, dtype=torch.uint8, device=self.dev) if (adopt_parameters and skip_untouched) else None
         self.grads, self.exp_avg, self.exp_avg_sq = [], [], []
         seg_ends, seg_lr, seg_eps, seg_wd = [], [], [], []
         off = 0
-        for p, lr, eps, wd in self.params:
+        for k, (p, lr, eps, wd) in enumerate(self.params):
             n = p.numel()
+            if k == len(planes) and self._dec_pad:
+                off += self._dec_pad                # padding floats belong to the last encoder group (never touched, never updated)
+                seg_ends[-1] = off
             self.grads.append(torch.as_strided(self.flat_grad, p.shape, p.stride(), off))
             if world_size == 1:
                 self.exp_avg.append(torch.as_strided(self.flat_m, p.shape, p.stride(), off))
@@ -141,7 +157,7 @@ class FusedMapper:
                 seg_ends.append(off); seg_lr.append(lr); seg_eps.append(eps); seg_wd.append(wd)
         self._segments = self._pack_segments(seg_ends, list(zip(seg_lr, seg_eps, seg_wd)))
         # the same split in two: the encoder's groups (planes / tables), and the decoder's group at the tail
-        dec0 = sum(p.numel() for p in planes)
+        dec0 = enc_len + self._dec_pad
         self._seg_head = self._pack_segments(seg_ends[:-1], list(zip(seg_lr, seg_eps, seg_wd))[:-1])
         self._seg_tail = self._pack_segments([total - dec0], [(seg_lr[-1], seg_eps[-1], seg_wd[-1])])
         if len(seg_ends) < 2 or seg_ends[-2] != dec0:
@@ -159,7 +175,7 @@ class FusedMapper:
         # 128 per sample -- one flag store per addition cost more than the pass over the gradient buffer that derives the
         # flags afterwards (measured: +0.6 ms at 8192 rays), so hash tables take that pass (mne_grad_dirty_map).
         self.dirty_local = None
-        self.dense_from = sum(p.numel() for p in planes)
+        self.dense_from = enc_len + self._dec_pad
         if self.peers is not None and mark_dirty and model.hash_meta is None and \
                 all(p.stride(1) == 1 and p.shape[1] == 32 for p in planes):
             self.dirty_local = torch.zeros(padded // 32, dtype=torch.uint8, device=self.dev)
@@ -172,6 +188,8 @@ class FusedMapper:
         self._ray_counters = None     # per-ray counters of the fused forward's tail (always left at zero)
         self._pending_wgrad = None    # the batch whose decoder weight gradients are still to be computed
         self._wgrad_stream = None     # side stream: decoder weight gradients + decoder Adam beside the planes' Adam
+        self._loss_stream = None      # side stream (several GPUs): all-reduce of the loss sums + loss finalisation
+        self._loss_pending = False
         self._act = None              # the per-sample record, forward -> backward (ops.act_floats per sample)
         self.last_losses = None
         self.global_rays_override = None
@@ -184,6 +202,8 @@ class FusedMapper:
         # point kernel + one ray kernel.  Measured on B200 (room0, 2048 rays): 82 us against 55 + 8 us -- finished rays
         # queue up behind the tiles of the warp that finished them, on the kernel's critical path -- so two launches.
         self.single_launch_render = False
+        # several GPUs: push the non-zero gradient texels to their owners (mne_grad_push) instead of letting the owners fetch them
+        self.push_gradients = os.environ.get('MNE_PUSH_GRADIENTS', '1') == '1'
 
     @staticmethod
     def _pack_segments(ends, hparams):
@@ -226,6 +246,10 @@ class FusedMapper:
         scfg = ops.make_sample_cfg(tables, perturb)
         acc = ops.new_acc(dev) if acc_out is None else acc_out.zero_()
         z_vals = ops.sample_rays(scfg, rcfg, n, s, target_d.reshape(-1), noise if perturb else None, acc, dev, out=z_out)
+        if self.world_size > 1:
+            # the loss gradients are scaled by the GLOBAL mask counts (slots 0..5), which are known as soon as the batch is
+            # sampled: reduce them here, off the render's critical path when the batch is sampled ahead (PipelinedMapper)
+            torch.distributed.all_reduce(acc[:6], group=self.group)
         return z_vals, acc
 
     def forward_backward(self, rays_o, rays_d, target_rgb, target_d, noise=None, sampled=None, defer_wgrad=False):
@@ -249,20 +273,26 @@ class FusedMapper:
             self._scratch, self._scratch_for = ops.backward_scratch(n, s, dev), (n, s)
         if self.single_launch_render and (self._ray_counters is None or self._ray_counters.numel() < n):
             self._ray_counters = torch.zeros(n, dtype=torch.int32, device=dev)
-        if self.world_size > 1:
-            # the loss gradients are scaled by the GLOBAL mask counts (slots 0..5, known once the batch is sampled)
-            torch.distributed.all_reduce(acc[:6], group=self.group)
         out = ops.render_forward(scene, rcfg, rays_o, rays_d, z_vals, target_rgb, td, acc, want_aux=False, act=self._act,
                                  ray_counters=self._ray_counters if self.single_launch_render else None,
                                  loss_grads=self.loss_grads, scratch=self._scratch)
         ops.render_backward_points(self._scene(True, weight_grads=False), rays_o, rays_d, z_vals, self._scratch, act=self._act)
         self._pending_wgrad = (n, s)
-        if not defer_wgrad or self.world_size > 1 or self.flat_param is None:
-            self._decoder_wgrad()     # (several GPUs: the gradient exchange moves the whole flat buffer, nothing to overlap)
+        if not defer_wgrad or self.flat_param is None or (self.world_size > 1 and self.peers is None):
+            self._decoder_wgrad()     # (NCCL fallback: the reduce-scatter moves the whole flat buffer, nothing to overlap)
         if self.world_size > 1:
-            # the loss VALUES need the global sums (slots 6..); nothing on the gradient path waits for them
-            torch.distributed.all_reduce(acc[6:], group=self.group)
-        losses = ops.loss_finalize(rcfg, s, acc)
+            # the loss VALUES need the global sums (slots 6..); nothing on the gradient path waits for them, so the reduction
+            # and the finalisation run on a side stream that is joined at the end of optimizer_step
+            main = torch.cuda.current_stream()
+            if self._loss_stream is None:
+                self._loss_stream = torch.cuda.Stream(device=dev)
+            self._loss_stream.wait_stream(main)
+            with torch.cuda.stream(self._loss_stream):
+                torch.distributed.all_reduce(acc[6:], group=self.group)
+                losses = ops.loss_finalize(rcfg, s, acc)
+            self._loss_pending = True
+        else:
+            losses = ops.loss_finalize(rcfg, s, acc)
         self.last_render = out
         return losses
 
@@ -274,6 +304,13 @@ class FusedMapper:
         ops.decoder_wgrad(self._scene(True, plane_grads=False), n, s, self._scratch, self._act, max_ctas)
 
     def optimizer_step(self):
+        """Adam + zero_grad (``_optimizer_step``), then the join with the side stream that finalises the losses."""
+        self._optimizer_step()
+        if self._loss_pending:
+            torch.cuda.current_stream().wait_stream(self._loss_stream)
+            self._loss_pending = False
+
+    def _optimizer_step(self):
         """Adam + zero_grad.  One GPU: one launch over the flat buffers (one per tensor when the parameters were not
         adopted).  Several GPUs: flags of the non-zero gradient texels handed to their owners, barrier, ONE kernel over
         NVLink peer memory (reduce the flagged gradients, Adam on the owned groups, parameters written back to every
@@ -283,21 +320,39 @@ class FusedMapper:
         st = ops._stream()
         _lib.check(lib.mne_adam_tick(self.step_dev.data_ptr(), st), 'mne_adam_tick')
         if self.world_size > 1 and self.peers is not None:
-            n_seg, ends, lr, eps, wd = self._segments          # global segment ends; ownership is block-cyclic
+            # The decoder (6 208 weights) stays out of the peer exchange: on a side stream its weight gradients are computed,
+            # all-reduced (25 KB) and applied by every rank's own Adam step (identical sums and moments -> identical weights),
+            # all of it beside the exchange of the planes below.
+            main = torch.cuda.current_stream()
+            if self._wgrad_stream is None:
+                self._wgrad_stream = torch.cuda.Stream(device=self.dev)
+            side = self._wgrad_stream
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                self._decoder_wgrad()
+                tail = slice(self.dense_from, self.total)
+                torch.distributed.all_reduce(self.flat_grad[tail], group=self.group)
+                self._adam_segments(self.flat_param[tail], self.flat_grad[tail], self.dec_m, self.dec_v, self._seg_tail, True, touched=None)
+            n_seg, ends, lr, eps, wd = self._seg_head          # global segment ends of the planes / tables; ownership is block-cyclic
             pr = self.peers
             if self.dirty_local is not None:          # flags set by the backward kernels: hand them to the owners
                 _lib.check(lib.mne_dirty_push(self.dirty_local.data_ptr(), self.flat_grad.numel(), self.dense_from, PEER_CHUNK,
                                               self.world_size, self.shards.rank, pr['dirty_ptrs'], st), 'mne_dirty_push')
-            else:                                     # strided planes: derive the flags from the gradient buffer
+            elif self.push_gradients:                 # one pass over the gradient buffer: flags AND the non-zero texels go to their owners
+                _lib.check(lib.mne_grad_push(self.flat_grad.data_ptr(), self.flat_grad.numel(), self.dense_from, PEER_CHUNK, self.world_size,
+                                             self.shards.rank, pr['dirty_ptrs'], pr['inbox_ptrs'], st), 'mne_grad_push')
+            else:                                     # flags only; the owners fetch the flagged groups themselves
                 _lib.check(lib.mne_grad_dirty_map(self.flat_grad.data_ptr(), self.flat_grad.numel(), PEER_CHUNK, self.world_size,
                                                   self.shards.rank, pr['dirty_ptrs'], st), 'mne_grad_dirty_map')
             pr['hg'].barrier(channel=0)               # every rank's gradient and dirty map are complete
             _lib.check(lib.mne_adam_step_peers(self.world_size, self.shards.rank, pr['param_ptrs'], pr['grad_ptrs'],
                                                self.flat_grad.numel(), PEER_CHUNK, self.flat_m.data_ptr(), self.flat_v.data_ptr(), n_seg, ends, lr,
                                                eps, wd, self.betas[0], self.betas[1], self.step_dev.data_ptr(), 0,
-                                               ops._ptr(self.touched), pr['mc_param'] or None, pr['mc_grad'] or None, pr['dirty'].data_ptr(), st),
+                                               ops._ptr(self.touched), pr['mc_param'] or None, pr['mc_grad'] or None, pr['dirty'].data_ptr(),
+                                               pr['inbox'].data_ptr() if (self.push_gradients and self.dirty_local is None) else None, st),
                        'mne_adam_step_peers')
             pr['hp'].barrier(channel=1)               # every rank's slice has landed in every parameter buffer
+            main.wait_stream(side)
             return
         if self.world_size > 1:
             from .distributed import sharded_optimizer_step
@@ -481,7 +536,11 @@ class PipelinedMapper:
         # may refill the shared one
         acc = self.acc.clone()
         losses = m.forward_backward(self.ro, self.rd, self.rgb, self.d, sampled=(self.z, acc), defer_wgrad=True)
-        self.losses.copy_(losses)
+        if m._loss_pending:                          # several GPUs: the losses are finalised on the mapper's side stream
+            with torch.cuda.stream(m._loss_stream):
+                self.losses.copy_(losses)
+        else:
+            self.losses.copy_(losses)
         self.side.wait_stream(main)                 # the batch has been consumed: refill it under the optimiser
         with torch.cuda.stream(self.side):
             self._after_losses()

@@ -19,10 +19,12 @@ for _ in range(30):
     mapper.step(*db.sample(2048))
 torch.cuda.synchronize(); dist.barrier()
 lib, st, pr = _lib.lib(), ops._stream(), mapper.peers
-n_seg, ends, lr, eps, wd = mapper._segments
+n_seg, ends, lr, eps, wd = mapper._seg_head
 def hand_over():
     if mapper.dirty_local is not None:
         lib.mne_dirty_push(mapper.dirty_local.data_ptr(), mapper.flat_grad.numel(), mapper.dense_from, 1024, world, rank, pr['dirty_ptrs'], st)
+    elif mapper.push_gradients:
+        lib.mne_grad_push(mapper.flat_grad.data_ptr(), mapper.flat_grad.numel(), mapper.dense_from, 1024, world, rank, pr['dirty_ptrs'], pr['inbox_ptrs'], st)
     else:
         lib.mne_grad_dirty_map(mapper.flat_grad.data_ptr(), mapper.flat_grad.numel(), 1024, world, rank, pr['dirty_ptrs'], st)
 names = ['fwd_bwd', 'dirty', 'barrier0', 'adam_peers', 'barrier1']
@@ -41,7 +43,7 @@ for it in range(K):
     lib.mne_adam_tick(mapper.step_dev.data_ptr(), st)
     lib.mne_adam_step_peers(world, mapper.shards.rank, pr['param_ptrs'], pr['grad_ptrs'], mapper.flat_grad.numel(), 1024, mapper.flat_m.data_ptr(),
                             mapper.flat_v.data_ptr(), n_seg, ends, lr, eps, wd, 0.9, 0.99, mapper.step_dev.data_ptr(), 0,
-                            ops._ptr(mapper.touched), pr['mc_param'] or None, None, pr['dirty'].data_ptr(), st)
+                            ops._ptr(mapper.touched), pr['mc_param'] or None, None, pr['dirty'].data_ptr(), pr['inbox'].data_ptr() if mapper.push_gradients else None, st)
     ev[4].record()
     pr['hp'].barrier(channel=1)
     ev[5].record()
@@ -68,7 +70,7 @@ def timed(param_local, grad_local):
         a.record()
         lib.mne_adam_step_peers(world, rank, pp, gp, mapper.flat_grad.numel(), 1024, mapper.flat_m.data_ptr(),
                                 mapper.flat_v.data_ptr(), n_seg, ends, lr, eps, wd, 0.9, 0.99, mapper.step_dev.data_ptr(), 0,
-                                ops._ptr(mapper.touched), None, None, dp, st)
+                                ops._ptr(mapper.touched), None, None, dp, pr['inbox'].data_ptr() if mapper.push_gradients else None, st)
         b.record(); torch.cuda.synchronize(); dist.barrier()
         ts.append(a.elapsed_time(b) * 1e3)
     return round(sorted(ts)[len(ts) // 2], 1)

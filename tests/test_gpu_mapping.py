@@ -191,10 +191,12 @@ def test_touched_map_adam_is_bit_identical_to_dense():
     assert 0.2 < frac < 0.95, frac
 
 
-def test_peer_optimiser_on_one_gpu_matches_dense_adam():
-    """mne_grad_dirty_map + mne_adam_step_peers with two emulated ranks on ONE device (both "peers'" buffers live on
-    the same GPU, the two ranks' kernels run one after the other): block-cyclic ownership, pushed dirty flags, sparse
-    gradient reduction, parameter write-back into both replicas, exact skip of never-touched groups."""
+@pytest.mark.parametrize('push', [False, True])
+def test_peer_optimiser_on_one_gpu_matches_dense_adam(push):
+    """mne_grad_dirty_map (owners fetch the flagged groups) or mne_grad_push (non-zero texels pushed into the owners' inboxes)
+    + mne_adam_step_peers with two emulated ranks on ONE device (both "peers'" buffers live on the same GPU, the two ranks'
+    kernels run one after the other): block-cyclic ownership, pushed dirty flags, sparse gradient reduction, parameter
+    write-back into both replicas, exact skip of never-touched groups."""
     import ctypes as C
     from mneslam_b200 import _lib, ops
     lib, st = _lib.lib(), ops._stream()
@@ -214,6 +216,8 @@ def test_peer_optimiser_on_one_gpu_matches_dense_adam():
     pp = (C.c_void_p * world)(*[x.data_ptr() for x in params])
     gp = (C.c_void_p * world)(*[x.data_ptr() for x in grads])
     dp = (C.c_void_p * world)(*[x.data_ptr() for x in dirty])
+    inbox = [torch.full((n_total,), float('nan'), device='cuda') for _ in range(world)]     # stale contents must never be read
+    ip = (C.c_void_p * world)(*[x.data_ptr() for x in inbox])
     ref = torch.nn.Parameter(p0.clone())
     opts = [torch.optim.Adam([ref], lr=5e-3, betas=(0.9, 0.99), eps=1e-15, foreach=False),
             torch.optim.Adam([ref], lr=1e-2, betas=(0.9, 0.99), eps=1e-8, weight_decay=1e-6, foreach=False)]
@@ -237,11 +241,14 @@ def test_peer_optimiser_on_one_gpu_matches_dense_adam():
                 keep = torch.ones(n_total, dtype=torch.bool, device='cuda'); keep[a:b] = False
                 ref[keep] = before[keep]
         for r in range(world):
-            _lib.check(lib.mne_grad_dirty_map(grads[r].data_ptr(), n_total, chunk, world, r, dp, st), 'dirty')
+            if push:
+                _lib.check(lib.mne_grad_push(grads[r].data_ptr(), n_total, n_total, chunk, world, r, dp, ip, st), 'push')
+            else:
+                _lib.check(lib.mne_grad_dirty_map(grads[r].data_ptr(), n_total, chunk, world, r, dp, st), 'dirty')
         for r in range(world):
             _lib.check(lib.mne_adam_step_peers(world, r, pp, gp, n_total, chunk, m[r].data_ptr(), v[r].data_ptr(), 2, seg_ends,
                                                lr, eps, wd, 0.9, 0.99, None, t, touched[r].data_ptr(), None, None,
-                                               dirty[r].data_ptr(), st), 'peers')
+                                               dirty[r].data_ptr(), inbox[r].data_ptr() if push else None, st), 'peers')
         torch.cuda.synchronize()
         assert all(float(g.abs().max()) == 0.0 for g in grads)               # every gradient was consumed and cleared
         assert torch.equal(params[0], params[1])                             # both replicas hold the same parameters

@@ -356,6 +356,22 @@ int mne_grad_push(float* grad, int64_t n_total, int64_t n_scan, int32_t chunk, i
  * at or beyond element dense_from (the decoder weights at the tail of the flat buffer) are always flagged. */
 int mne_dirty_push(uint8_t* local_map, int64_t n_total, int64_t dense_from, int32_t chunk, int32_t world_size, int32_t rank,
                    uint8_t* const* dirty_ptrs, mne_stream_t stream);
+/* mne_dirty_push and mne_grad_push in one: the flags in local_map (set by the backward pass, cleared here) name the texels
+ * of `grad` that may be non-zero; only those are read, stored into their owners' inboxes and cleared (texels this rank
+ * owns stay in place), and the flags are handed to the owners.  Texels at or beyond n_scan are left alone. */
+int mne_dirty_push_data(uint8_t* local_map, float* grad, int64_t n_total, int64_t n_scan, int32_t chunk, int32_t world_size,
+                        int32_t rank, uint8_t* const* dirty_ptrs, float* const* inbox_ptrs, mne_stream_t stream);
+
+/* ---- small all-reduce over peer memory (no counterpart in the reference; replaces NCCL all-reduces of the 16 loss
+ * accumulators and of the decoder's 25 KB of weight gradients, which cost ~50 us each at eight ranks and serialise with one
+ * another).  mne_peer_scatter stores src[0, n_floats) at float offset offset_floats of EVERY rank's exchange buffer
+ * (dst_ptrs: HOST array of world_size peer-mapped device pointers; the caller chooses offset = region + rank * n_floats);
+ * after a cross-rank barrier of the caller's, mne_peer_sum adds the world_size slots ([world_size][n] of float or double,
+ * local memory) in rank order into out -- bit-identical on every rank.  A second barrier must precede the next scatter
+ * into the same region. */
+int mne_peer_scatter(const float* src, int32_t n_floats, float* const* dst_ptrs, int64_t offset_floats, int32_t world_size,
+                     mne_stream_t stream);
+int mne_peer_sum(const void* slots, int32_t n, int32_t world_size, void* out, int32_t is_double, mne_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -320,6 +320,32 @@ __global__ void __launch_bounds__(256) dirty_push_kernel(uint8_t* __restrict__ l
     d.dst[owner][(int64_t)d.rank * d.local32 + lt] = f;
 }
 
+// dirty_push_kernel + mne_grad_push in one: the flags the backward pass set say where the gradient is non-zero, so only those
+// texels (about a sixth of the map per iteration) are read, pushed into their owners' inboxes and cleared -- no pass over the
+// whole gradient buffer.  Eight lanes per texel (one float4 each).
+__global__ void __launch_bounds__(256) dirty_push_data_kernel(uint8_t* __restrict__ local_map, float4* __restrict__ g4,
+                                                              const __grid_constant__ DirtyPush d) {
+    const int sub = threadIdx.x & 7;
+    const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 3;
+    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t tx = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3; tx < d.scan32; tx += stride) {
+        const uint8_t f = local_map[tx];
+        const uint32_t c = (uint32_t)(tx >> d.chunk_tx_log2);
+        const uint32_t owner = c % (uint32_t)d.world;
+        const int64_t lt = ((int64_t)(c / (uint32_t)d.world) << d.chunk_tx_log2) + (tx & ((1 << d.chunk_tx_log2) - 1));
+        __syncwarp();                                     // every lane of the texel has read the flag before it is cleared
+        if (sub == 0) {
+            d.dst[owner][(int64_t)d.rank * d.local32 + lt] = f;
+            if (f) local_map[tx] = 0;
+        }
+        if (f && owner != (uint32_t)d.rank) {
+            const float4 v = g4[tx * 8 + sub];
+            d.inbox[owner][((int64_t)d.rank * d.local32 + lt) * 8 + sub] = v;
+            g4[tx * 8 + sub] = zero;
+        }
+    }
+}
+
 // in-switch reduction / broadcast (NVLS): one load returns the sum over all ranks, one store reaches all ranks
 __device__ __forceinline__ float4 multimem_ld_reduce_add(const float4* p) {
     float4 v;
@@ -634,6 +660,87 @@ extern "C" int mne_dirty_push(uint8_t* local_map, int64_t n_total, int64_t dense
     d.n32 = n_total >> 5; d.local32 = d.n32 / world_size;
     const int64_t blocks = (d.n32 + 255) / 256;
     dirty_push_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(local_map, dense_from >> 5, d);   // floor: a texel straddling dense_from is flagged
+    MNE_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int mne_dirty_push_data(uint8_t* local_map, float* grad, int64_t n_total, int64_t n_scan, int32_t chunk, int32_t world_size,
+                                   int32_t rank, uint8_t* const* dirty_ptrs, float* const* inbox_ptrs, mne_stream_t stream) {
+    using namespace mne;
+    MNE_CHECK_ARG(local_map && grad && dirty_ptrs && inbox_ptrs, "mne_dirty_push_data: null argument");
+    MNE_CHECK_ARG(world_size >= 1 && world_size <= MNE_MAX_PEERS && rank >= 0 && rank < world_size, "mne_dirty_push_data: bad world_size / rank");
+    MNE_CHECK_ARG(chunk >= 32 && (chunk & (chunk - 1)) == 0 && n_total >= 0 && n_total % ((int64_t)chunk * world_size) == 0 &&
+                  (n_total >> 5) / chunk < (int64_t)1 << 31 && (((uintptr_t)grad) & 15) == 0,
+                  "mne_dirty_push_data: chunk must be a power of two >= 32, n_total a multiple of chunk * world_size, grad 16-byte aligned");
+    MNE_CHECK_ARG(n_scan >= 0 && n_scan <= n_total && (n_scan & 31) == 0, "mne_dirty_push_data: n_scan must be a multiple of 32 in [0, n_total]");
+    if (n_total == 0 || n_scan == 0) return 0;
+    DirtyPush d{};
+    for (int r = 0; r < world_size; ++r) {
+        MNE_CHECK_ARG(dirty_ptrs[r] && inbox_ptrs[r] && (((uintptr_t)inbox_ptrs[r]) & 15) == 0,
+                      "mne_dirty_push_data: flag arrays and inboxes must be non-null, inboxes 16-byte aligned");
+        d.dst[r] = dirty_ptrs[r];
+        d.inbox[r] = reinterpret_cast<float4*>(inbox_ptrs[r]);
+    }
+    d.push = 1;
+    d.world = world_size; d.rank = rank; d.chunk_tx_log2 = 31 - __builtin_clz((unsigned)chunk) - 5;
+    d.n32 = n_total >> 5; d.local32 = d.n32 / world_size; d.scan32 = n_scan >> 5;
+    int64_t blocks = (d.scan32 * 8 + 255) / 256;
+    const int64_t cap = (int64_t)sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    dirty_push_data_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(local_map, reinterpret_cast<float4*>(grad), d);
+    MNE_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Small all-reduce over peer memory (a few dozen bytes to a few tens of KB: the loss accumulators, the decoder's weight
+// gradients): every rank stores its vector into slot [rank] of every peer's exchange buffer (mne_peer_scatter), a cross-rank
+// barrier follows (the caller's), then every rank sums the slots it received (mne_peer_sum).  An NCCL all-reduce of this
+// size costs ~50 us at eight ranks and serialises with every other collective of the communicator; this is two tiny
+// kernels and a signal-pad barrier on whatever stream needs the result.
+// ---------------------------------------------------------------------------------------------------------
+namespace mne {
+struct PeerPtrs { float4* p[MNE_MAX_PEERS]; };
+
+__global__ void peer_scatter_kernel(const float4* __restrict__ src, int n4, const __grid_constant__ PeerPtrs dst, int64_t off4) {
+    float4* out = dst.p[blockIdx.y] + off4;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x) out[i] = src[i];
+}
+
+template <typename T>
+__global__ void peer_sum_kernel(const T* __restrict__ slots, int n, int world, T* __restrict__ out) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        T s = 0;
+        for (int r = 0; r < world; ++r) s += slots[(int64_t)r * n + i];      // rank order: identical sums on every rank
+        out[i] = s;
+    }
+}
+}  // namespace mne
+
+extern "C" int mne_peer_scatter(const float* src, int32_t n_floats, float* const* dst_ptrs, int64_t offset_floats, int32_t world_size,
+                                mne_stream_t stream) {
+    using namespace mne;
+    MNE_CHECK_ARG(src && dst_ptrs && world_size >= 1 && world_size <= MNE_MAX_PEERS, "mne_peer_scatter: bad argument");
+    MNE_CHECK_ARG(n_floats > 0 && (n_floats & 3) == 0 && (offset_floats & 3) == 0 && (((uintptr_t)src) & 15) == 0,
+                  "mne_peer_scatter: sizes and offsets must be multiples of 4 floats, src 16-byte aligned");
+    PeerPtrs d{};
+    for (int r = 0; r < world_size; ++r) {
+        MNE_CHECK_ARG(dst_ptrs[r] && (((uintptr_t)dst_ptrs[r]) & 15) == 0, "mne_peer_scatter: destination buffers must be non-null and 16-byte aligned");
+        d.p[r] = reinterpret_cast<float4*>(dst_ptrs[r]);
+    }
+    const int n4 = n_floats >> 2;
+    dim3 grid((unsigned)std::min(8, (n4 + 255) / 256), (unsigned)world_size);
+    peer_scatter_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float4*>(src), n4, d, offset_floats >> 2);
+    MNE_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int mne_peer_sum(const void* slots, int32_t n, int32_t world_size, void* out, int32_t is_double, mne_stream_t stream) {
+    using namespace mne;
+    MNE_CHECK_ARG(slots && out && n > 0 && world_size >= 1, "mne_peer_sum: bad argument");
+    const int blocks = std::min(16, (n + 255) / 256);
+    if (is_double) peer_sum_kernel<double><<<blocks, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const double*>(slots), n, world_size, reinterpret_cast<double*>(out));
+    else peer_sum_kernel<float><<<blocks, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float*>(slots), n, world_size, reinterpret_cast<float*>(out));
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

@@ -14,6 +14,7 @@ shard of the ray batch, and the loss accumulators (16 doubles, before the losses
 gradient buffer are all-reduced once per iteration; the Adam step is then identical on every rank.
 """
 import ctypes as C
+import os
 
 import torch
 
@@ -99,7 +100,15 @@ class FusedMapper:
                 i_buf = symm.empty(padded, dtype=torch.float32, device=self.dev)
                 hi = symm.rendezvous(i_buf, group.group_name)
                 i_buf.zero_()
-                self.peers = {'grad': g_buf, 'param': p_buf, 'dirty': d_buf, 'hg': hg, 'hp': hp, 'hd': hd, 'inbox': i_buf, 'hi': hi,
+                # exchange buffer of the small all-reduces: per region [rank][payload]; regions: mask counts (6 doubles), loss
+                # sums (10 doubles), decoder weight gradients
+                n_dec = sum(w.numel() for w in weights)
+                self._x_regions = {'counts': (0, 12), 'sums': (12 * world_size, 20), 'dec': (32 * world_size, n_dec)}
+                x_buf = symm.empty(world_size * (32 + n_dec), dtype=torch.float32, device=self.dev)
+                hx = symm.rendezvous(x_buf, group.group_name)
+                x_buf.zero_()
+                self.peers = {'xchg': x_buf, 'hx': hx, 'x_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hx.buffer_ptrs]),
+                              'grad': g_buf, 'param': p_buf, 'dirty': d_buf, 'hg': hg, 'hp': hp, 'hd': hd, 'inbox': i_buf, 'hi': hi,
                               'inbox_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hi.buffer_ptrs]),
                               'dirty_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hd.buffer_ptrs]),
                               'grad_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hg.buffer_ptrs]),
@@ -176,6 +185,8 @@ class FusedMapper:
         # flags afterwards (measured: +0.6 ms at 8192 rays), so hash tables take that pass (mne_grad_dirty_map).
         self.dirty_local = None
         self.dense_from = enc_len + self._dec_pad
+        if os.environ.get('MNE_MARK_DIRTY') is not None:
+            mark_dirty = os.environ['MNE_MARK_DIRTY'] == '1'
         if self.peers is not None and mark_dirty and model.hash_meta is None and \
                 all(p.stride(1) == 1 and p.shape[1] == 32 for p in planes):
             self.dirty_local = torch.zeros(padded // 32, dtype=torch.uint8, device=self.dev)
@@ -195,7 +206,6 @@ class FusedMapper:
         self.global_rays_override = None
         # CTAs of the decoder weight-gradient kernel when it runs beside the planes' Adam pass (the optimiser grids leave
         # `adam_spare_sms` SMs free; 0 = a full grid)
-        import os
         self.wgrad_ctas = int(os.environ.get('MNE_WGRAD_CTAS', '0'))
         self.wgrad_inline = os.environ.get('MNE_WGRAD_INLINE', '0') == '1'
         # the render as ONE launch (the warp that stores a ray's last sample composites it; needs per-ray counters) or as the
@@ -249,7 +259,7 @@ class FusedMapper:
         if self.world_size > 1:
             # the loss gradients are scaled by the GLOBAL mask counts (slots 0..5), which are known as soon as the batch is
             # sampled: reduce them here, off the render's critical path when the batch is sampled ahead (PipelinedMapper)
-            torch.distributed.all_reduce(acc[:6], group=self.group)
+            self._small_allreduce('counts', acc[:6], 0)
         return z_vals, acc
 
     def forward_backward(self, rays_o, rays_d, target_rgb, target_d, noise=None, sampled=None, defer_wgrad=False):
@@ -288,13 +298,30 @@ class FusedMapper:
                 self._loss_stream = torch.cuda.Stream(device=dev)
             self._loss_stream.wait_stream(main)
             with torch.cuda.stream(self._loss_stream):
-                torch.distributed.all_reduce(acc[6:], group=self.group)
+                self._small_allreduce('sums', acc[6:], 1)
                 losses = ops.loss_finalize(rcfg, s, acc)
             self._loss_pending = True
         else:
             losses = ops.loss_finalize(rcfg, s, acc)
         self.last_render = out
         return losses
+
+    def _small_allreduce(self, name, tensor, channel):
+        """In-place sum of a small device vector over the ranks, on the current stream: through the peer-memory exchange buffer
+        (scatter to every rank's slot, signal-pad barrier, local sum, barrier) -- or NCCL when peer memory is unavailable."""
+        if self.peers is None:
+            torch.distributed.all_reduce(tensor, group=self.group)
+            return
+        lib, st, pr = _lib.lib(), ops._stream(), self.peers
+        off, n_f = self._x_regions[name]
+        rank = self.shards.rank
+        is_double = tensor.dtype == torch.float64
+        assert tensor.is_contiguous() and tensor.numel() * (2 if is_double else 1) == n_f
+        _lib.check(lib.mne_peer_scatter(tensor.data_ptr(), n_f, pr['x_ptrs'], off + rank * n_f, self.world_size, st), 'mne_peer_scatter')
+        pr['hx'].barrier(channel=channel)
+        _lib.check(lib.mne_peer_sum(pr['xchg'].data_ptr() + 4 * off, tensor.numel(), self.world_size, tensor.data_ptr(),
+                                    1 if is_double else 0, st), 'mne_peer_sum')
+        pr['hx'].barrier(channel=channel)     # nobody overwrites a slot that a slower rank is still summing
 
     def _decoder_wgrad(self, max_ctas=0):
         if self._pending_wgrad is None:
@@ -331,11 +358,16 @@ class FusedMapper:
             with torch.cuda.stream(side):
                 self._decoder_wgrad()
                 tail = slice(self.dense_from, self.total)
-                torch.distributed.all_reduce(self.flat_grad[tail], group=self.group)
+                self._small_allreduce('dec', self.flat_grad[tail], 2)
                 self._adam_segments(self.flat_param[tail], self.flat_grad[tail], self.dec_m, self.dec_v, self._seg_tail, True, touched=None)
             n_seg, ends, lr, eps, wd = self._seg_head          # global segment ends of the planes / tables; ownership is block-cyclic
             pr = self.peers
-            if self.dirty_local is not None:          # flags set by the backward kernels: hand them to the owners
+            if self.dirty_local is not None and self.push_gradients:
+                # flags set by the backward kernels: only the flagged texels are read, pushed to their owners and cleared
+                _lib.check(lib.mne_dirty_push_data(self.dirty_local.data_ptr(), self.flat_grad.data_ptr(), self.flat_grad.numel(),
+                                                   self.dense_from, PEER_CHUNK, self.world_size, self.shards.rank,
+                                                   pr['dirty_ptrs'], pr['inbox_ptrs'], st), 'mne_dirty_push_data')
+            elif self.dirty_local is not None:        # flags set by the backward kernels: hand them to the owners
                 _lib.check(lib.mne_dirty_push(self.dirty_local.data_ptr(), self.flat_grad.numel(), self.dense_from, PEER_CHUNK,
                                               self.world_size, self.shards.rank, pr['dirty_ptrs'], st), 'mne_dirty_push')
             elif self.push_gradients:                 # one pass over the gradient buffer: flags AND the non-zero texels go to their owners
@@ -349,7 +381,7 @@ class FusedMapper:
                                                self.flat_grad.numel(), PEER_CHUNK, self.flat_m.data_ptr(), self.flat_v.data_ptr(), n_seg, ends, lr,
                                                eps, wd, self.betas[0], self.betas[1], self.step_dev.data_ptr(), 0,
                                                ops._ptr(self.touched), pr['mc_param'] or None, pr['mc_grad'] or None, pr['dirty'].data_ptr(),
-                                               pr['inbox'].data_ptr() if (self.push_gradients and self.dirty_local is None) else None, st),
+                                               pr['inbox'].data_ptr() if self.push_gradients else None, st),
                        'mne_adam_step_peers')
             pr['hp'].barrier(channel=1)               # every rank's slice has landed in every parameter buffer
             main.wait_stream(side)

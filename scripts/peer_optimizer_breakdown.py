@@ -21,7 +21,10 @@ torch.cuda.synchronize(); dist.barrier()
 lib, st, pr = _lib.lib(), ops._stream(), mapper.peers
 n_seg, ends, lr, eps, wd = mapper._seg_head
 def hand_over():
-    if mapper.dirty_local is not None:
+    if mapper.dirty_local is not None and mapper.push_gradients:
+        lib.mne_dirty_push_data(mapper.dirty_local.data_ptr(), mapper.flat_grad.data_ptr(), mapper.flat_grad.numel(), mapper.dense_from, 1024,
+                                world, rank, pr['dirty_ptrs'], pr['inbox_ptrs'], st)
+    elif mapper.dirty_local is not None:
         lib.mne_dirty_push(mapper.dirty_local.data_ptr(), mapper.flat_grad.numel(), mapper.dense_from, 1024, world, rank, pr['dirty_ptrs'], st)
     elif mapper.push_gradients:
         lib.mne_grad_push(mapper.flat_grad.data_ptr(), mapper.flat_grad.numel(), mapper.dense_from, 1024, world, rank, pr['dirty_ptrs'], pr['inbox_ptrs'], st)

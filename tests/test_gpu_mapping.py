@@ -191,7 +191,7 @@ def test_touched_map_adam_is_bit_identical_to_dense():
     assert 0.2 < frac < 0.95, frac
 
 
-@pytest.mark.parametrize('push', [False, True])
+@pytest.mark.parametrize('push', [False, True, 'flags'])
 def test_peer_optimiser_on_one_gpu_matches_dense_adam(push):
     """mne_grad_dirty_map (owners fetch the flagged groups) or mne_grad_push (non-zero texels pushed into the owners' inboxes)
     + mne_adam_step_peers with two emulated ranks on ONE device (both "peers'" buffers live on the same GPU, the two ranks'
@@ -241,7 +241,13 @@ def test_peer_optimiser_on_one_gpu_matches_dense_adam(push):
                 keep = torch.ones(n_total, dtype=torch.bool, device='cuda'); keep[a:b] = False
                 ref[keep] = before[keep]
         for r in range(world):
-            if push:
+            if push == 'flags':       # the flags come from the backward pass (here: from the gradient itself, plus a few spurious ones)
+                fl = (grads[r].view(-1, 32) != 0).any(1).to(torch.uint8)
+                fl[::7] = 1
+                _lib.check(lib.mne_dirty_push_data(fl.data_ptr(), grads[r].data_ptr(), n_total, n_total, chunk, world, r, dp, ip, st), 'push_data')
+                torch.cuda.synchronize()
+                assert int(fl.sum()) == 0, 'the local flag map is cleared on the way'
+            elif push:
                 _lib.check(lib.mne_grad_push(grads[r].data_ptr(), n_total, n_total, chunk, world, r, dp, ip, st), 'push')
             else:
                 _lib.check(lib.mne_grad_dirty_map(grads[r].data_ptr(), n_total, chunk, world, r, dp, st), 'dirty')

@@ -448,6 +448,67 @@ def self_check_record(world, rank, dev, iters=4):
     return rec
 
 
+def gather_peak_record(model, mapper, cfg, db, n_rays, dev):
+    """The gather rate the GPU sustains on the batch's OWN tap addresses with a kernel that only gathers (mne_bench_gather):
+    the L2 / HBM gather ceiling of SURVEY.md 8(d).  Two states: straight after a pass over a buffer larger than L2 (what a
+    mapping iteration's forward finds: the optimiser has just streamed 517 MB), and warm (the same addresses again)."""
+    import ctypes as C
+    from mneslam_b200 import _lib, ops, synthetic
+    lib = _lib.lib()
+    s = synthetic.n_samples_total(cfg)
+    ro, rd, trgb, td = db.sample(n_rays)
+    tables = ops.SampleTables.get(cfg, dev, True)
+    rcfg = ops.make_render_cfg(cfg, norm_rays=n_rays)
+    z = ops.sample_rays(ops.make_sample_cfg(tables, True), rcfg, n_rays, s, td.reshape(-1), torch.rand(n_rays, s, device=dev), ops.new_acc(dev), dev)
+    pts = (ro[:, None, :] + rd[:, None, :] * z[..., None]).reshape(-1, 3)
+    b = model.bound.to(dev)
+    nrm = (pts - b[:, 0]) / (b[:, 1] - b[:, 0]) * 2 - 1
+    planes = model._flat_planes()
+    base = mapper.flat_param
+    offs = []
+    for l in range(2):                                   # the forward's order: level, plane (xy, xz, yz), corner
+        for a in range(3):
+            pl = planes[a * 2 + l]
+            H, W = pl.shape[2], pl.shape[3]
+            gx = nrm[:, 1] if a == 2 else nrm[:, 0]
+            gy = nrm[:, 1] if a == 0 else nrm[:, 2]
+            ux = ((gx + 1) * 0.5 * (W - 1)).clamp(0, W - 1)
+            uy = ((gy + 1) * 0.5 * (H - 1)).clamp(0, H - 1)
+            x0, y0 = ux.floor().long(), uy.floor().long()
+            x1, y1 = (x0 + 1).clamp(max=W - 1), (y0 + 1).clamp(max=H - 1)
+            p0 = (pl.data_ptr() - base.data_ptr()) // 4
+            for yy, xx in ((y0, x0), (y0, x1), (y1, x0), (y1, x1)):
+                offs.append(p0 + (yy * W + xx) * 32)
+    offsets = torch.stack(offs, 1).reshape(-1).to(torch.int32).contiguous()          # [M * 24]
+    sink = torch.zeros(4, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    st = ops._stream()
+
+    def run():
+        _lib.check(lib.mne_bench_gather(base.data_ptr(), offsets.data_ptr(), offsets.numel(), 0, sink.data_ptr(), st), 'mne_bench_gather')
+    for _ in range(3):
+        run()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    cold = []
+    for _ in range(10):
+        flush.zero_()
+        e0.record(); run(); e1.record()
+        torch.cuda.synchronize()
+        cold.append(e0.elapsed_time(e1))
+    e0.record()
+    for _ in range(20):
+        run()
+    e1.record()
+    torch.cuda.synchronize()
+    warm_ms = e0.elapsed_time(e1) / 20
+    cold.sort()
+    nbytes = offsets.numel() * 128
+    return {'pattern': 'the 24 texel fetches (128 B each) of every sample of a %d-ray room0 batch, addresses computed from the batch' % n_rays,
+            'bytes': nbytes, 'us_after_l2_flush': cold[len(cold) // 2] * 1e3, 'us_warm': warm_ms * 1e3,
+            'gather_gbs_after_l2_flush': nbytes / (cold[len(cold) // 2] * 1e-3) / 1e9, 'gather_gbs_warm': nbytes / (warm_ms * 1e-3) / 1e9,
+            'kernel': 'mne_bench_gather mode 0: loads only, 12 x 128-bit loads in flight per lane, 8 CTAs x 256 threads per SM'}
+
+
 def run_ours(args):
     import torch.distributed as dist
     from mneslam_b200 import JointEncoding, configs, synthetic
@@ -616,6 +677,19 @@ def run_ours(args):
         _, e = timed(mapper.optimizer_step); ev['adam'].append(e)
     torch.cuda.synchronize()
     us = {k: 1e3 * sum(a.elapsed_time(b) for a, b in v) / len(v) for k, v in ev.items()}
+    # ---- the optimiser late in a run: the fraction of parameter groups that ever received a gradient keeps rising for a few
+    #      hundred iterations (0.43 -> 0.6), and the Adam pass with it; 400 more iterations, then the same interval again
+    touched_prof = float(mapper.touched.float().mean().item()) if mapper.touched is not None else 1.0
+    steady = None
+    if world == 1:
+        run_steps(400)
+        ev2 = []
+        for _ in range(10):
+            mapper.forward_backward(*db.sample(n_rays), defer_wgrad=True)
+            _, e = timed(mapper.optimizer_step); ev2.append(e)
+        torch.cuda.synchronize()
+        steady = {'iterations_before': args.steps + 400 + 3 * max(args.warmup, 3), 'adam_us': 1e3 * sum(a.elapsed_time(b) for a, b in ev2) / len(ev2),
+                  'touched_fraction': float(mapper.touched.float().mean().item()) if mapper.touched is not None else 1.0}
 
     # ---- e2e: the drop-in class through the reference's call sites, host buffers in, loss out (every step)
     planes = model._flat_planes()
@@ -806,6 +880,12 @@ def run_ours(args):
                     'points_per_iter': 1024 * 117}
         del tmodel, tracker
 
+    gather_peak = None
+    if rank == 0:
+        try:
+            gather_peak = gather_peak_record(model, mapper, cfg, db, n_rays, dev)
+        except Exception as e:
+            gather_peak = {'error': repr(e)[:300]}
     # ---- the records every N carries: configs[3] (strong scaling, hash grid) and the cross-rank self-check
     n_active_main = ops.backward_active_count(mapper._scratch, n_rays, s)
     extra = {}
@@ -829,7 +909,7 @@ def run_ours(args):
         fwd_bytes = pts_per_rank * ALG_BYTES_PER_POINT_FWD
         bwd_bytes = n_active * ALG_BYTES_PER_POINT_BWD
         n_param = mapper.total
-        touched = float(mapper.touched.float().mean().item()) if mapper.touched is not None else 1.0
+        touched = touched_prof
         adam_bytes = int(n_param * (touched * 32 + (1.0 - touched) * 4 + (0.25 if mapper.touched is not None else 0.0)))
         gbs = lambda b, t_us: b / (t_us * 1e-6) / 1e9
         fwd_gbs, bwd_gbs, adam_gbs = gbs(fwd_bytes, us['fwd']), gbs(bwd_bytes, us['bwd']), gbs(adam_bytes, us['adam'])
@@ -868,6 +948,19 @@ def run_ours(args):
             'last_loss': float(mapper.total_loss(static_losses if graph is not None else losses).item()),
         }
         line.update(extra)
+        # the whole step against the gather roofline -- 6 144 algorithmic bytes per point (3 072 gathered + 3 072
+        # of gradient contributions) x points/s over the measured HBM copy bandwidth of all GPUs
+        line['roofline']['whole_step_frac_6144B_per_point'] = value * (ALG_BYTES_PER_POINT_FWD + ALG_BYTES_PER_POINT_BWD) / 1e9 / (peak * world)
+        line['gather_peak'] = gather_peak
+        line['adam']['steady_state'] = steady
+        if gather_peak and 'gather_gbs_after_l2_flush' in gather_peak:
+            g_cold, g_warm = gather_peak['gather_gbs_after_l2_flush'], gather_peak['gather_gbs_warm']
+            for k, gbs_k in (('points_fwd_kernel', fwd_gbs), ('points_bwd_kernel', bwd_gbs)):
+                line['roofline'][k]['frac_l2'] = gbs_k / g_cold
+                line['roofline'][k]['frac_l2_warm'] = gbs_k / g_warm
+            line['roofline']['l2_gather_gbs'] = g_cold
+            line['roofline']['l2_note'] = ('frac = algorithmic GB/s over the HBM copy bandwidth (MEASURED_PEAKS.json); frac_l2 = the same GB/s over '
+                                           'the rate a loads-only kernel reaches on the SAME tap addresses after an L2 flush (gather_peak)')
         if world == 1 and not args.no_cpu_baseline:
             line['cpu_baseline'] = cpu_baseline_record(cfg, n_rays)
             try:

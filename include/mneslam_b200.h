@@ -373,6 +373,15 @@ int mne_peer_scatter(const float* src, int32_t n_floats, float* const* dst_ptrs,
                      mne_stream_t stream);
 int mne_peer_sum(const void* slots, int32_t n, int32_t world_size, void* out, int32_t is_double, mne_stream_t stream);
 
+/* ---- measurement aid (no counterpart in the reference): a kernel that ONLY gathers.  offsets [n_offsets] uint32 = float
+ * offsets into table; mode 0: each offset names a 128-byte texel (a multiple of 32 floats), fetched by eight lanes with one
+ * 128-bit load each -- the tri-plane taps of the forward pass, 24 per sample; mode 1: each offset names an 8-byte entry (a
+ * multiple of 2 floats), one 64-bit load per lane -- the hash grid's corners.  bench.py times it on the batch's own tap
+ * addresses: the gather rate this GPU sustains for that access pattern is the ceiling the encoder kernels are held against
+ * (beside the HBM copy bandwidth).  sink: one float of device memory (never written in practice). */
+int mne_bench_gather(const float* table, const uint32_t* offsets, int64_t n_offsets, int32_t mode, float* sink,
+                     mne_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

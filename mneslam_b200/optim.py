@@ -1,10 +1,16 @@
-"""``torch.optim``-shaped Adam over the library's fused kernel, for the reference's own optimiser construction.
+"""``torch.optim``-shaped Adam over the library's fused kernels, for the reference's own optimiser construction.
 
 ``create_optimizer`` (mneslam_mp.py:431-469) builds ``torch.optim.Adam`` over the decoder parameters and the plane
 ``nn.Parameter`` s; swapping the class there (one line) keeps every call site -- ``map_optimizer.step()``,
 ``zero_grad()``, ``state_dict()`` -- and replaces torch's multi-tensor path (nine launches over the 129 MB map plus
-their host-side bookkeeping) by one ``mne_adam_step`` launch per tensor.  Same update as ``torch.optim.Adam`` without
-amsgrad / maximize (tested to a few ulp)."""
+their host-side bookkeeping) by ONE ``mne_adam_step_segments`` launch per run of parameters that lie back to back in
+memory with their gradients laid out the same way.  ``JointEncoding`` allocates its planes that way (one buffer per plane
+set), packs its decoder weights, and returns gradients as views of one persistent buffer (``scene_rep.GradArena``), so a
+mapping step is two launches: the planes (with the exact skip of groups that never received a gradient, and the gradient
+cleared inside the same kernel) and the decoder.  Parameters that are not adjacent simply form runs of one.  Same update as
+``torch.optim.Adam`` without amsgrad / maximize (tested to a few ulp)."""
+import ctypes as C
+
 import torch
 
 from . import _lib, ops
@@ -15,10 +21,41 @@ class Adam(torch.optim.Optimizer):
         if lr < 0 or eps < 0 or not (0 <= betas[0] < 1 and 0 <= betas[1] < 1) or weight_decay < 0:
             raise ValueError('invalid Adam hyper-parameters')
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
+        self._runs = {}          # (param addresses) -> flat moment buffers + touched map of a run
+        self._plans = {}         # group index -> the launches of the last step, replayed while the addresses stay the same
 
     @staticmethod
     def _dense(t):
         return t.is_contiguous() or (t.dim() == 4 and t.is_contiguous(memory_format=torch.channels_last))
+
+    def _run_state(self, run):
+        """Flat moment buffers of a run (parameters adjacent in memory); every parameter's ``exp_avg`` / ``exp_avg_sq`` in
+        ``self.state`` is a view of them, so ``state_dict()`` keeps torch's layout."""
+        key = tuple((p.data_ptr(), p.numel()) for p, _ in run)
+        rs = self._runs.get(key)
+        if rs is not None:
+            return rs
+        p0 = run[0][0]
+        n = sum(p.numel() for p, _ in run)
+        rs = {'m': torch.zeros(n, dtype=torch.float32, device=p0.device), 'v': torch.zeros(n, dtype=torch.float32, device=p0.device),
+              'touched': torch.zeros(n // 4, dtype=torch.uint8, device=p0.device), 'n': n,
+              'ends': (C.c_int64 * 1)(n)}
+        off = 0
+        for p, _ in run:
+            st = self.state[p]
+            m_view = torch.as_strided(rs['m'], p.shape, p.stride(), off)
+            v_view = torch.as_strided(rs['v'], p.shape, p.stride(), off)
+            if st:                                    # the parameter was stepped before in another run: carry its moments over
+                m_view.copy_(st['exp_avg']); v_view.copy_(st['exp_avg_sq'])
+                rs['touched'][off // 4:(off + p.numel()) // 4] = 1
+            else:
+                st['step'] = 0
+            st['exp_avg'], st['exp_avg_sq'] = m_view, v_view
+            off += p.numel()
+        if len(self._runs) > 64:
+            self._runs.clear()
+        self._runs[key] = rs
+        return rs
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -26,9 +63,29 @@ class Adam(torch.optim.Optimizer):
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
+        from .scene_rep import GradArena
         lib, st = _lib.lib(), ops._stream()
-        for group in self.param_groups:
+        covered = {}
+        for gi, group in enumerate(self.param_groups):
             b1, b2 = group['betas']
+            # ---- fast path: same parameter and gradient addresses as last step (the arena's views land where they landed
+            #      before) -> replay the launch plan instead of rediscovering the runs
+            hyper = (group['lr'], group['eps'], group['weight_decay'], b1, b2)
+            sig = tuple((p.data_ptr(), p.grad.data_ptr()) if p.grad is not None else None for p in group['params'])
+            plan = self._plans.get(gi)
+            if plan is not None and plan['sig'] == sig and plan['hyper'] == hyper and \
+                    all(p.grad is None or p.grad.stride() == p.stride() for p in group['params']):
+                for run in plan['runs']:
+                    for stt in run['states']:
+                        stt['step'] += 1
+                    _lib.check(lib.mne_adam_step_segments(run['p'], run['g'], run['m'], run['v'], 1, run['ends'], plan['lr'], plan['eps'],
+                                                          plan['wd'], b1, b2, None, run['states'][0]['step'], run['zero'], run['touched'], st),
+                               'mne_adam_step_segments')
+                    if run['arena'] is not None:
+                        covered[id(run['arena'])] = (run['arena'], covered.get(id(run['arena']), (run['arena'], 0))[1] + run['n'])
+                continue
+            # ---- runs of parameters that lie back to back in memory, gradients likewise
+            runs, cur = [], []
             for p in group['params']:
                 g = p.grad
                 if g is None:
@@ -39,13 +96,58 @@ class Adam(torch.optim.Optimizer):
                     raise TypeError('parameters must be dense (contiguous or channels-last)')
                 if g.stride() != p.stride():
                     g = torch.empty_like(p).copy_(g)              # same element order as the parameter
-                state = self.state[p]
-                if not state:
-                    state['step'] = 0
-                    state['exp_avg'] = torch.zeros_like(p)        # preserve_format: same strides as p
-                    state['exp_avg_sq'] = torch.zeros_like(p)
-                state['step'] += 1
-                _lib.check(lib.mne_adam_step(p.data_ptr(), g.data_ptr(), state['exp_avg'].data_ptr(),
-                                             state['exp_avg_sq'].data_ptr(), p.numel(), group['lr'], b1, b2, group['eps'],
-                                             group['weight_decay'], None, state['step'], 0, st), 'mne_adam_step')
+                if cur:
+                    q, h = cur[-1]
+                    same_step = self.state[q].get('step', 0) == self.state[p].get('step', 0)
+                    if not (same_step and p.data_ptr() == q.data_ptr() + 4 * q.numel() and
+                            g.data_ptr() == h.data_ptr() + 4 * h.numel() and q.numel() % 4 == 0):
+                        runs.append(cur); cur = []
+                cur.append((p, g))
+            if cur:
+                runs.append(cur)
+            lr = (C.c_float * 1)(group['lr'])
+            eps = (C.c_float * 1)(group['eps'])
+            wd = (C.c_float * 1)(group['weight_decay'])
+            plan = {'sig': sig, 'hyper': hyper, 'lr': lr, 'eps': eps, 'wd': wd, 'runs': []}
+            cacheable = True
+            for run in runs:
+                p0, g0 = run[0]
+                n = sum(p.numel() for p, _ in run)
+                if n % 4 or p0.data_ptr() % 16 or g0.data_ptr() % 16:
+                    for p, g in run:                              # odd sizes: the element-wise kernel, one tensor at a time
+                        self._step_single(p, g, group, lib, st)
+                    cacheable = False
+                    continue
+                rs = self._run_state(run)
+                for p, _ in run:
+                    self.state[p]['step'] += 1
+                step = self.state[p0]['step']
+                arena = GradArena.owning(g0.data_ptr())
+                own = arena is not None and g0.data_ptr() + 4 * n <= arena.flat.data_ptr() + 4 * arena.numel
+                _lib.check(lib.mne_adam_step_segments(p0.data_ptr(), g0.data_ptr(), rs['m'].data_ptr(), rs['v'].data_ptr(), 1,
+                                                      rs['ends'], lr, eps, wd, b1, b2, None, step, 1 if own else 0,
+                                                      rs['touched'].data_ptr(), st), 'mne_adam_step_segments')
+                if own:                                           # the kernel cleared the gradients it read
+                    covered[id(arena)] = (arena, covered.get(id(arena), (arena, 0))[1] + n)
+                if any(g is not p.grad for p, g in run):
+                    cacheable = False                             # a gradient had to be re-laid out: temporary addresses
+                plan['runs'].append({'p': p0.data_ptr(), 'g': g0.data_ptr(), 'm': rs['m'].data_ptr(), 'v': rs['v'].data_ptr(),
+                                     'ends': rs['ends'], 'touched': rs['touched'].data_ptr(), 'zero': 1 if own else 0, 'n': n,
+                                     'arena': arena if own else None, 'states': [self.state[p] for p, _ in run], 'keep': rs})
+            self._plans[gi] = plan if cacheable else None
+        for arena, n in covered.values():
+            if n == arena.numel:
+                arena.clean = True
         return loss
+
+    def _step_single(self, p, g, group, lib, st):
+        state = self.state[p]
+        if not state:
+            state['step'] = 0
+            state['exp_avg'] = torch.zeros_like(p)                # preserve_format: same strides as p
+            state['exp_avg_sq'] = torch.zeros_like(p)
+        state['step'] += 1
+        b1, b2 = group['betas']
+        _lib.check(lib.mne_adam_step(p.data_ptr(), g.data_ptr(), state['exp_avg'].data_ptr(), state['exp_avg_sq'].data_ptr(),
+                                     p.numel(), group['lr'], b1, b2, group['eps'], group['weight_decay'], None, state['step'],
+                                     0, st), 'mne_adam_step')

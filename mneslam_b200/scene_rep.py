@@ -36,6 +36,44 @@ def get_rays(H, W, fx, fy, cx, cy, c2w, device):
     return rays_o, rays_d
 
 
+class GradArena:
+    """One flat gradient buffer for a fixed list of parameter tensors, with a view per parameter (its shape and strides):
+    ``_Render.backward`` accumulates into it and returns the views, instead of allocating and zero-filling 129 MB of fresh
+    gradient tensors per call.  ``clean`` says the buffer is all zero: ``mneslam_b200.optim.Adam`` clears the gradients inside
+    its update kernel and sets it; otherwise the next backward clears the buffer itself (one memset, no allocation)."""
+    registry = []            # weak references, looked up by mneslam_b200.optim.Adam
+
+    def __init__(self, params):
+        import weakref
+        self.key = GradArena.key_of(params)
+        self.numel = sum(p.numel() for p in params)
+        self.flat = torch.zeros(self.numel, dtype=torch.float32, device=params[0].device)
+        self.layout, off = [], 0
+        for p in params:
+            self.layout.append((tuple(p.shape), p.stride(), off))
+            off += p.numel()
+        self.clean = True
+        GradArena.registry[:] = [r for r in GradArena.registry if r() is not None] + [weakref.ref(self)]
+
+    def make_views(self):
+        """Fresh tensor objects over the buffer, one per parameter.  (Fresh on purpose: autograd adopts an incoming gradient as
+        ``.grad`` without copying it only when nobody else references that tensor object.)"""
+        return [torch.as_strided(self.flat, shape, stride, off) for shape, stride, off in self.layout]
+
+    @staticmethod
+    def key_of(params):
+        return tuple((tuple(p.shape), p.stride()) for p in params)
+
+    @staticmethod
+    def owning(ptr):
+        """The live arena whose buffer contains device address ``ptr``, or None."""
+        for r in GradArena.registry:
+            a = r()
+            if a is not None and a.flat.data_ptr() <= ptr < a.flat.data_ptr() + 4 * a.numel:
+                return a
+        return None
+
+
 class _Render(torch.autograd.Function):
     """sample -> fused forward (+ loss sums, hidden activations kept when a backward can follow) ; backward = fused backward
     kernels over the samples with a non-zero loss gradient."""
@@ -58,8 +96,7 @@ class _Render(torch.autograd.Function):
         td = target_d.reshape(-1) if with_depth else None
         acc = ops.new_acc(dev) if with_losses else None
         z_vals = ops.sample_rays(scfg, rcfg, n, n_samples, td, noise if perturb else None, acc, dev)
-        scene = ops.make_scene(planes, weights, model.bound, model.bounding_box, cfg['pos']['n_bins'],
-                               hash_meta=model.hash_meta)
+        scene = model._cached_scene(planes, weights)
         # what autograd would save: the decoders' hidden activations (80 floats per sample), only when a backward can follow
         want_act = any(ctx.needs_input_grad)
         out = ops.render_forward(scene, rcfg, rays_o, rays_d, z_vals, target_rgb if with_losses else None,
@@ -76,21 +113,26 @@ class _Render(torch.autograd.Function):
         ctx.set_materialize_grads(False)
         nondiff = (z_vals, out['disp_map'], out['acc_map'], out['depth_var'], out['inds'])
         ctx.mark_non_differentiable(*nondiff)
-        return (out['rgb'], out['depth'], out['raw'], losses) + nondiff
+        # the eight losses leave as eight 0-dim outputs: the caller weights and sums them (get_loss_from_ret), and their
+        # gradients come straight back to backward() -- no select / scatter nodes (and their small kernels) in between
+        return (out['rgb'], out['depth'], out['raw']) + tuple(losses.unbind(0)) + nondiff
 
     @staticmethod
-    def backward(ctx, g_rgb, g_depth, g_raw, g_losses, *unused):
+    def backward(ctx, g_rgb, g_depth, g_raw, *rest):
+        g_each = rest[:len(LOSS_KEYS)]
+        g_losses = None
+        if ctx.with_losses and any(g is not None for g in g_each):
+            zero = g_rgb.new_zeros(()) if g_rgb is not None else next(g for g in g_each if g is not None).new_zeros(())
+            g_losses = torch.stack([g if g is not None else zero for g in g_each])
         rays_o, rays_d, z_vals, raw, target_rgb, td, acc, act = ctx.saved_tensors[:8]
         params = ctx.saved_tensors[8:]
         model, n_planes = ctx.model, ctx.n_planes
         planes, weights = list(params[:n_planes]), list(params[n_planes:])
         need = ctx.needs_input_grad
         need_params = need[7:]
-        plane_grads = [torch.zeros_like(p) if nd else None for p, nd in zip(planes, need_params[:n_planes])]
-        weight_grads = [torch.zeros_like(w) if nd else None for w, nd in zip(weights, need_params[n_planes:])]
+        plane_grads, weight_grads = model._gradient_buffers(planes, weights, need_params)
         want_rays = bool(need[1] or need[2])
-        scene = ops.make_scene(planes, weights, model.bound, model.bounding_box, model.config['pos']['n_bins'],
-                               plane_grads=plane_grads, weight_grads=weight_grads, hash_meta=model.hash_meta)
+        scene = model._cached_scene(planes, weights, plane_grads, weight_grads)
         lg = g_losses if (ctx.with_losses and g_losses is not None) else None
         g_o, g_d = ops.render_backward(scene, ctx.rcfg, rays_o, rays_d, z_vals, raw, target_rgb, td, acc,
                                        loss_grads=lg, g_rgb=g_rgb, g_depth=g_depth, g_raw=g_raw,
@@ -111,6 +153,8 @@ class JointEncoding(nn.Module):
         self.ray_batch_size = ray_batch_size
         # extensions (not in the reference): explicit noise for parity runs, multi-GPU hooks
         self.noise_override = None
+        self._grad_arena = None
+        self._scene_cache = {}
         self.norm_scale = 1          # world size when the ray batch is sharded over GPUs
         self.acc_allreduce = None    # callable(acc) all-reducing the loss accumulators across ranks
 
@@ -127,13 +171,30 @@ class JointEncoding(nn.Module):
             raise NotImplementedError('the fused kernels are built for model.c_dim = 32 (every reference config)')
         ext = self.bound[:, 1] - self.bound[:, 0]
         groups = ([], [], [])
-        for res in (self.config[res_key]['coarse'], self.config[res_key]['fine']):
+        # All planes of the set live back to back in ONE buffer, in all_planes order (group, level), each channels-last (a
+        # texel's 32 channels are one 128-byte line): an optimiser that finds its parameters adjacent in memory
+        # (mneslam_b200.optim.Adam) can then update the whole map with one launch.  Values are drawn in NCHW order, plane by
+        # plane in the reference's order (same stream of normals as model/scene_rep.py:105-109).
+        shapes = []
+        for li, res in enumerate((self.config[res_key]['coarse'], self.config[res_key]['fine'])):
             nx, ny, nz = [int(v) for v in (ext / res).tolist()]
-            for lst, hw in zip(groups, ((ny, nx), (nz, nx), (nz, ny))):
-                # values are drawn in NCHW order (same stream of normals as the reference), then laid out
-                # channels-last: a texel's 32 channels become one 128-byte line
-                p = torch.empty([1, c_dim, *hw]).normal_(mean=0, std=0.01).to(self.device)
-                lst.append(p.contiguous(memory_format=torch.channels_last))
+            for gi, hw in enumerate(((ny, nx), (nz, nx), (nz, ny))):
+                shapes.append((gi, li, hw))
+        order = sorted(range(len(shapes)), key=lambda k: (shapes[k][0], shapes[k][1]))       # all_planes order
+        offsets, off = {}, 0
+        for k in order:
+            offsets[k] = off
+            off += c_dim * shapes[k][2][0] * shapes[k][2][1]
+        arena = torch.empty(off, dtype=torch.float32, device=self.device)
+        made = {}
+        for k, (gi, li, hw) in enumerate(shapes):
+            p = torch.empty([1, c_dim, *hw]).normal_(mean=0, std=0.01)
+            view = arena[offsets[k]:offsets[k] + p.numel()].view(1, hw[0], hw[1], c_dim).permute(0, 3, 1, 2)
+            view.copy_(p)
+            made[(gi, li)] = view
+        for gi in range(3):
+            for li in range(2):
+                groups[gi].append(made[(gi, li)])
         return groups
 
     def init_all_planes(self, config):
@@ -178,8 +239,64 @@ class JointEncoding(nn.Module):
         self.decoder = cls(config, input_ch=self.input_ch, input_ch_pos=self.input_ch_pos)
         self.color_net = self.decoder.color_net
         self.sdf_net = self.decoder.sdf_net
+        self._pack_decoder()
+
+    def _pack_decoder(self):
+        """The four decoder matrices back to back in one buffer (each keeps its identity, shape and state_dict key; only its
+        storage moves), so that an optimiser which looks for adjacent parameters updates them with one launch."""
+        ws = self.decoder.weight_list()
+        flat = torch.empty(sum(w.numel() for w in ws), dtype=ws[0].dtype, device=ws[0].device)
+        off = 0
+        with torch.no_grad():
+            for w in ws:
+                view = flat[off:off + w.numel()].view_as(w)
+                view.copy_(w)
+                w.data = view
+                off += w.numel()
+
+    def _apply(self, fn, *args, **kwargs):
+        """``.to(device)`` / ``.cuda()`` (mneslam_mp.py:114) move every registered parameter on its own: pack the decoder again."""
+        out = super()._apply(fn, *args, **kwargs)
+        self._pack_decoder()
+        return out
 
     # ------------------------------------------------------------------ helpers
+    def _gradient_buffers(self, planes, weights, need):
+        """Zeroed gradient tensors for ``_Render.backward``: views of the model's persistent ``GradArena`` when every
+        parameter wants a gradient and nobody still holds last step's views as ``.grad`` (gradient accumulation across
+        backward calls) -- else freshly allocated ones, as autograd itself would produce."""
+        params = planes + weights
+        if not all(need) or any(p.grad is not None for p in params):
+            return ([torch.zeros_like(p) if nd else None for p, nd in zip(planes, need[:len(planes)])],
+                    [torch.zeros_like(w) if nd else None for w, nd in zip(weights, need[len(planes):])])
+        arena = self._grad_arena
+        if arena is None or arena.key != GradArena.key_of(params) or arena.flat.device != params[0].device:
+            arena = self._grad_arena = GradArena(params)
+        if not arena.clean:
+            arena.flat.zero_()
+        arena.clean = False
+        views = arena.make_views()
+        return views[:len(planes)], views[len(planes):]
+
+    def _cached_scene(self, planes, weights, plane_grads=None, weight_grads=None):
+        """``ops.make_scene`` memoised on what the descriptor is made of (addresses, shapes and strides of every tensor, the
+        two boxes): the reference's callers may swap planes or weights between calls (mneslam_mp.py:451-457,
+        mp_slam/mapper.py:719), so nothing is assumed -- but an unchanged model costs one tuple comparison instead of
+        rebuilding a 2.5 KB ctypes structure several times per iteration."""
+        def sig(ts):
+            return tuple((t.data_ptr(), t.shape, t.stride()) if t is not None else None for t in ts)
+        key = (sig(planes), sig(weights), sig(plane_grads) if plane_grads is not None else None,
+               sig(weight_grads) if weight_grads is not None else None,
+               id(self.bound), self.bound._version, id(self.bounding_box), self.bounding_box._version, id(self.hash_meta))
+        sc = self._scene_cache.get(key)
+        if sc is None:
+            if len(self._scene_cache) > 8:
+                self._scene_cache.clear()
+            sc = ops.make_scene(planes, weights, self.bound, self.bounding_box, self.config['pos']['n_bins'],
+                                plane_grads=plane_grads, weight_grads=weight_grads, hash_meta=self.hash_meta)
+            self._scene_cache[key] = sc
+        return sc
+
     def _flat_planes(self):
         """The encoder's parameter tensors: the planes in ``all_planes`` order, or the hash table(s)."""
         if self.hash_meta is not None:
@@ -187,11 +304,18 @@ class JointEncoding(nn.Module):
         expect = 3 if self.config['grid']['oneGrid'] else 6
         if len(self.all_planes) != expect:
             raise ValueError('all_planes has %d groups, config expects %d' % (len(self.all_planes), expect))
-        return [p for group in self.all_planes for p in group]
+        planes = [p for group in self.all_planes for p in group]
+        for p in planes:
+            # a map that arrived from outside (a reference checkpoint, mp_slam/mapper.py:719) is NCHW-contiguous: lay it out
+            # channels-last ONCE, in place (same tensor object, same logical shape), instead of serving it through the strided
+            # kernels from then on.  Left alone while a gradient or an optimiser state of the old layout may exist.
+            if p.is_cuda and p.dim() == 4 and p.stride(1) != 1 and p.grad is None and not getattr(p, '_mne_keep_layout', False):
+                with torch.no_grad():
+                    p.data = p.data.contiguous(memory_format=torch.channels_last)
+        return planes
 
     def _scene(self):
-        return ops.make_scene(self._flat_planes(), self.decoder.weight_list(), self.bound, self.bounding_box,
-                              self.config['pos']['n_bins'], hash_meta=self.hash_meta)
+        return self._cached_scene(self._flat_planes(), self.decoder.weight_list())
 
     def _render(self, rays_o, rays_d, target_rgb, target_d, with_losses, noise=None):
         ops.require_cuda()
@@ -201,7 +325,9 @@ class JointEncoding(nn.Module):
         noise = noise if noise is not None else self.noise_override
         params = self._flat_planes() + self.decoder.weight_list()
         res = _Render.apply(self, rays_o, rays_d, target_rgb, target_d, noise, with_losses, *params)
-        rgb, depth, raw, losses, z_vals, disp, acc_map, depth_var, inds = res
+        rgb, depth, raw = res[:3]
+        losses = res[3:3 + len(LOSS_KEYS)]
+        z_vals, disp, acc_map, depth_var, inds = res[3 + len(LOSS_KEYS):]
         rend = {'rgb': rgb, 'depth': depth, 'disp_map': disp, 'acc_map': acc_map, 'depth_var': depth_var,
                 'z_vals': z_vals, 'raw': raw}
         return rend, losses, inds
@@ -221,7 +347,7 @@ class JointEncoding(nn.Module):
         ret = {'rgb': rend['rgb'], 'depth': rend['depth']}
         for i, k in enumerate(LOSS_KEYS[:-1]):
             ret[k] = losses[i]
-        ret['psnr'] = losses[7:8].detach()
+        ret['psnr'] = losses[7].detach().reshape(1)
         return ret
 
     def render_img(self, c2w, device, gt_depth=None):

@@ -26,6 +26,8 @@ def build_model(cfg, bounding_box, planes, weights, channels_last=True, as_param
             t = p.cuda()
             t = t.contiguous(memory_format=torch.channels_last) if channels_last else t.contiguous()
             dst[i] = torch.nn.Parameter(t) if as_params else t      # as mneslam_mp.py:451-457
+            if not channels_last:
+                dst[i]._mne_keep_layout = True      # keep the NCHW layout: these cases exist to exercise the strided kernels
     with torch.no_grad():
         for w, src in zip(model.decoder.weight_list(), ('sdf0', 'sdf1', 'col0', 'col1')):
             w.copy_(weights[src])

@@ -512,3 +512,63 @@ def test_prefetching_host_mapper_trains_on_the_previous_batch():
     (la, pa), (lb, pb) = arms
     assert la == pytest.approx(lb, rel=1e-4)
     assert min(float((x.double() - y.double()).norm() / (y.double().norm() + 1e-30)) for x, y in zip(pa, pb)) < 2e-5
+
+
+def test_dropin_with_fused_adam_trains_like_torch_adam_and_survives_plane_replacement():
+    """The reference's call sites with one line changed (mneslam_b200.optim.Adam in create_optimizer, mneslam_mp.py:469):
+    planes wrapped in nn.Parameter inside all_planes (mneslam_mp.py:451-457), forward / loss.backward() / step() / zero_grad().
+    The gradients are views of the model's persistent arena and the planes lie back to back, so the optimiser is two
+    launches; the parameters must follow torch.optim.Adam's.  Half way, all_planes is replaced wholesale (what
+    load_foreign_model does, mp_slam/mapper.py:719) and new optimisers are built: both keep training, identically."""
+    from mneslam_b200 import JointEncoding
+    from mneslam_b200.optim import Adam
+    from mneslam_b200.scene_rep import GradArena
+    cfg = configs.small_test_config(one_grid=True)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    mp = cfg['mapping']
+
+    def make():
+        torch.manual_seed(11)
+        m = JointEncoding(cfg, bb).cuda()
+        m.train()
+        for grp in m.all_planes:
+            for i, p in enumerate(grp):
+                grp[i] = torch.nn.Parameter(p)
+        return m
+
+    def optimiser(m, cls, **kw):
+        return cls([{'params': m.decoder.parameters(), 'weight_decay': 1e-6, 'lr': mp['lr_decoder']},
+                    {'params': flat_planes(m), 'eps': 1e-15, 'lr': mp['lr_embed']}], betas=(0.9, 0.99), **kw)
+    a, b = make(), make()
+    oa, ob = optimiser(a, torch.optim.Adam, foreach=False), optimiser(b, Adam)
+    n, s = 150, synthetic.n_samples_total(cfg)
+
+    def iteration(it):
+        batch = {k: v.cuda() for k, v in synthetic.make_ray_batch(cfg, n, seed=70 + it).items()}
+        noise = synthetic.make_noise(n, s, seed=it).cuda()
+        out = []
+        for m, o in ((a, oa), (b, ob)):
+            ret = m.forward(batch['rays_o'], batch['rays_d'], batch['target_rgb'], batch['target_d'], noise=noise)
+            loss = total_loss(cfg, ret)
+            loss.backward()
+            o.step()
+            o.zero_grad()
+            out.append(loss.item())
+        assert out[1] == pytest.approx(out[0], rel=2e-4)
+    for it in range(3):
+        iteration(it)
+    arena = b._grad_arena
+    assert arena is not None and arena.clean and float(arena.flat.abs().max()) == 0.0, 'the update kernel cleared the gradients'
+    assert GradArena.owning(arena.flat.data_ptr() + 64) is arena
+    fp = flat_planes(b)
+    assert all(fp[i + 1].data_ptr() == fp[i].data_ptr() + 4 * fp[i].numel() for i in range(5)), 'planes lie back to back'
+    # a peer's map arrives: every plane list is replaced by fresh (NCHW-contiguous, as a reference checkpoint holds them) tensors
+    torch.manual_seed(5)
+    fresh = [[torch.randn_like(p).contiguous() * 0.3 for p in grp] for grp in a.all_planes]
+    for m in (a, b):
+        m.all_planes = tuple([torch.nn.Parameter(t.clone()) for t in grp] for grp in fresh)
+    oa, ob = optimiser(a, torch.optim.Adam, foreach=False), optimiser(b, Adam)
+    for it in range(3, 6):
+        iteration(it)
+    for x, y in zip(flat_planes(a) + a.decoder.weight_list(), flat_planes(b) + b.decoder.weight_list()):
+        assert rel(y.detach().cpu().numpy(), x.detach().cpu().numpy()) < 2e-3

@@ -199,3 +199,45 @@ def test_two_tables_forward_backward_and_ray_gradients_vs_oracle():
         first = v if first is None else first
         last = v
     assert np.isfinite(last) and last < first
+
+
+def test_full_size_scannet_hash_grid_vs_oracle():
+    """BASELINE.json configs[3] at its real table size: ScanNet scene0000 bound and sampling (96 + 21 samples per ray), 16
+    levels, T = 2^19 -- 256 rays against the oracle: corner indices bit-exact at every level (dense and hashed), forward and
+    losses within 1e-3, table / decoder / ray gradients cosine >= 0.999."""
+    cfg = configs.scannet_scene0000_onegrid()
+    cfg['grid']['use_hash'] = True
+    model, meta, table, weights, bb = _model(cfg, seed=4, table_scale=0.3)
+    assert cfg['grid']['hash_size'] == 19 and max(meta['sizes']) == 1 << 19
+    n, s = 256, synthetic.n_samples_total(cfg)
+    assert s == 117
+    batch = synthetic.make_ray_batch(cfg, n, seed=14, zero_depth_frac=0.1)
+    noise = synthetic.make_noise(n, s, seed=14)
+    ot = table.clone().requires_grad_(True)
+    ow = {k: v.clone().requires_grad_(True) for k, v in weights.items()}
+    oo, od = batch['rays_o'].clone().requires_grad_(True), batch['rays_d'].clone().requires_grad_(True)
+    oret, orend = J.forward(cfg, ([ot],), ow, J.enlarged_bound(cfg), bb, oo, od, batch['target_rgb'], batch['target_d'], noise)
+    J.total_loss(cfg, oret).backward()
+    # corner indices of the batch's own sample positions
+    pts = (batch['rays_o'][:, None, :] + batch['rays_d'][:, None, :] * orend['z_vals'][..., None]).reshape(-1, 3)
+    x01 = J.blob_inputs(pts, bb)[:4000].contiguous()
+    desc = _lib.HashDesc()
+    model.hash_meta.fill_desc(desc, model.hash_tables[0].detach())
+    out = torch.empty(x01.shape[0], 16, 8, dtype=torch.int32, device='cuda')
+    xd = x01.cuda()
+    _lib.check(_lib.lib().mne_hash_indices(C.byref(desc), x01.shape[0], xd.data_ptr(), out.data_ptr(), ops._stream()), 'mne_hash_indices')
+    got = out.cpu().numpy()
+    for l in range(16):
+        want, _ = H.corner_indices(meta, x01, l)
+        assert np.array_equal(got[:, l, :].astype(np.int64), want.numpy()), l
+    ro, rd = batch['rays_o'].cuda().requires_grad_(True), batch['rays_d'].cuda().requires_grad_(True)
+    ret = model.forward(ro, rd, batch['target_rgb'].cuda(), batch['target_d'].cuda(), noise=noise.cuda())
+    for k in ('rgb_loss', 'depth_loss', 'e_fs_loss', 'e_center_loss', 'e_tail_loss'):
+        np.testing.assert_allclose(ret[k].item(), oret[k].item(), rtol=1e-3, err_msg=k)
+    assert rel(ret['rgb'].detach().cpu().numpy(), oret['rgb'].detach().numpy()) < 1e-3
+    assert rel(ret['depth'].detach().cpu().numpy(), oret['depth'].detach().numpy()) < 1e-3
+    total_loss(cfg, ret).backward()
+    assert cosine(model.hash_tables[0].grad.cpu().numpy(), ot.grad.numpy()) >= 0.999
+    for w, k in zip(model.decoder.weight_list(), ('sdf0', 'sdf1', 'col0', 'col1')):
+        assert cosine(w.grad.cpu().numpy(), ow[k].grad.numpy()) >= 0.999, k
+    assert cosine(ro.grad.cpu().numpy(), oo.grad.numpy()) >= 0.999 and cosine(rd.grad.cpu().numpy(), od.grad.numpy()) >= 0.999

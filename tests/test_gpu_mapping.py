@@ -5,7 +5,8 @@ import torch
 
 from mneslam_b200 import configs, synthetic
 from oracle import joint_encoding as J
-from tests.gpu_util import build_model, flat_planes, rel, total_loss
+from mneslam_b200._lib import LOSS_KEYS
+from tests.gpu_util import build_model, cosine, flat_planes, rel, total_loss
 
 pytestmark = pytest.mark.gpu
 
@@ -572,3 +573,43 @@ def test_dropin_with_fused_adam_trains_like_torch_adam_and_survives_plane_replac
         iteration(it)
     for x, y in zip(flat_planes(a) + a.decoder.weight_list(), flat_planes(b) + b.decoder.weight_list()):
         assert rel(y.detach().cpu().numpy(), x.detach().cpu().numpy()) < 2e-3
+
+
+def test_distillation_step_matches_the_oracle():
+    """One iteration of the joint distillation (mp_slam/mapper.py:594-644) against the CPU oracle: the teacher renders the
+    shared rays without depth guidance (render_rays(target_d=None)), the student takes a mapping iteration on that
+    rendering -- losses within 1e-3, the student's parameter update direction as the oracle's (autograd + torch Adam).
+    training.perturb = 0 so that both sides sample the same positions."""
+    from mneslam_b200.mapping import FusedMapper
+    cfg, bb, planes_t, weights_t = _small_model(seed=9)
+    cfg['training']['perturb'] = 0
+    _, _, planes_s, weights_s = _small_model(seed=21)
+    teacher = build_model(cfg, bb, planes_t, weights_t, as_params=False)
+    student = build_model(cfg, bb, planes_s, weights_s, as_params=False)
+    before = [p.detach().clone().cpu() for p in flat_planes(student) + student.decoder.weight_list()]
+    mapper = FusedMapper(student)
+    b = synthetic.make_ray_batch(cfg, 300, seed=3)
+    losses = mapper.distill_step(teacher, b['rays_o'].cuda(), b['rays_d'].cuda())
+    torch.cuda.synchronize()
+    # ---- the same on the CPU
+    bound = J.enlarged_bound(cfg)
+    with torch.no_grad():
+        t = J.render_rays(cfg, planes_t, weights_t, bound, bb, b['rays_o'], b['rays_d'], None, None)
+    op = tuple([torch.nn.Parameter(p.clone()) for p in grp] for grp in planes_s)
+    ow = {k: torch.nn.Parameter(v.clone()) for k, v in weights_s.items()}
+    ret, _ = J.forward(cfg, op, ow, bound, bb, b['rays_o'], b['rays_d'], t['rgb'], t['depth'].unsqueeze(-1), None)
+    mp = cfg['mapping']
+    opt = torch.optim.Adam([{'params': list(ow.values()), 'weight_decay': 1e-6, 'lr': mp['lr_decoder']},
+                            {'params': [p for g in op for p in g], 'eps': 1e-15, 'lr': mp['lr_embed']}], betas=(0.9, 0.99))
+    J.total_loss(cfg, ret).backward()
+    opt.step()
+    for i, k in enumerate(LOSS_KEYS[:7]):
+        ref = ret[k].item()
+        if np.isfinite(ref):
+            assert losses[i].item() == pytest.approx(ref, rel=1e-3, abs=1e-7), k
+    after = [p.detach().cpu() for p in flat_planes(student) + student.decoder.weight_list()]
+    ref_after = [p.detach() for g in op for p in g] + [ow[k].detach() for k in ('sdf0', 'sdf1', 'col0', 'col1')]
+    for a0, a1, r1 in zip(before, after, ref_after):
+        da, dr = (a1 - a0).double().reshape(-1), (r1 - a0).double().reshape(-1)
+        if float(dr.norm()) > 0:
+            assert cosine(da.numpy(), dr.numpy()) >= 0.99, 'update direction'       # Adam's first step is lr * sign(g): sign flips of ~0 gradients only

@@ -438,3 +438,59 @@ def test_fused_render_equals_point_kernel_plus_ray_kernels(one_grid, n_rays):
     # a second launch on the same counters (they reset themselves)
     out2 = ops.render_forward(sc, rcfg, b['rays_o'], b['rays_d'], z, ray_counters=counters)
     assert torch.equal(out2['rgb'], ref['rgb']) and int(counters.abs().sum()) == 0
+
+
+def _inference_model():
+    import os
+    from oracle.make_golden_inference import inference_config
+    from tests.cases import GOLDEN
+    g = np.load(os.path.join(GOLDEN, 'small_inference.npz'))
+    cfg = inference_config()
+    bound = J.enlarged_bound(cfg)
+    seed = int(g['seed'])
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    model = build_model(cfg, bb, J.init_planes(cfg, bound, seed=seed, std=0.4), J.init_weights(cfg, seed=seed), as_params=False)
+    return g, cfg, model
+
+
+def test_inference_entry_points_vs_reference_golden():
+    """render_img (with and without gt_depth), render_surface_color and the eval-mode forward against what the REFERENCE'S
+    own methods returned (tests/golden/small_inference.npz, oracle/make_golden_inference.py): pins get_rays, the raw
+    cam.cx / cam.cy of model/scene_rep.py:438-441, the float64 depth image, ragged chunks."""
+    g, cfg, model = _inference_model()
+    H, W = int(g['H']), int(g['W'])
+    c2w = torch.from_numpy(g['c2w'])
+    model.eval()
+    model.render_chunk = 100                      # several ragged chunks, like the fixture's ray_batch_size
+    d0, c0 = model.render_img(c2w, 'cuda', gt_depth=None)
+    d1, c1 = model.render_img(c2w, 'cuda', gt_depth=torch.from_numpy(g['gt_depth']))
+    assert d0.dtype == torch.float64 and tuple(d0.shape) == (H, W) and tuple(c0.shape) == (H, W, 3)
+    assert rel(d0.cpu().numpy(), g['img_depth_nodepth']) < REL_TOL
+    assert rel(c0.cpu().numpy(), g['img_color_nodepth']) < REL_TOL
+    assert rel(d1.cpu().numpy(), g['img_depth']) < REL_TOL
+    assert rel(c1.cpu().numpy(), g['img_color']) < REL_TOL
+    rgb = model.render_surface_color(torch.from_numpy(g['surf_pts']).cuda()[:, None, :], torch.from_numpy(g['surf_normal']).cuda())
+    assert tuple(rgb.shape) == tuple(g['surf_rgb'].shape)
+    assert rel(rgb.cpu().numpy(), g['surf_rgb']) < REL_TOL
+    ret = model.forward(*(torch.from_numpy(g['eval_' + k]).cuda() for k in ('rays_o', 'rays_d', 'target_rgb', 'target_d')))
+    assert sorted(ret) == sorted(['rgb', 'depth', 'disp_map', 'acc_map', 'depth_var', 'z_vals', 'raw'])
+    assert np.array_equal(ret['z_vals'].cpu().numpy(), g['eval_ret_z_vals'])
+    for k in ('rgb', 'depth', 'raw', 'acc_map', 'depth_var', 'disp_map'):
+        assert rel(ret[k].detach().cpu().numpy(), g['eval_ret_' + k]) < REL_TOL, k
+
+
+def test_pose_kernels_vs_reference_axis_angle():
+    """mne_pose_rays (rotation parameters -> R -> rays) and pose.axis_angle_to_matrix against the matrices the reference's
+    own axis_angle_to_matrix produced (optimization/utils.py:161-177, executed from its source by the fixture script)."""
+    from mneslam_b200 import _lib, ops, pose
+    g = _inference_model()[0]
+    rot, trans, R_ref = torch.from_numpy(g['pose_rot']).cuda(), torch.from_numpy(g['pose_trans']).cuda(), g['pose_R']
+    np.testing.assert_allclose(pose.axis_angle_to_matrix(rot).cpu().numpy(), R_ref, rtol=0, atol=5e-7)
+    np.testing.assert_allclose(pose.transform_matrix(rot, trans).cpu().numpy(), g['pose_T'], rtol=0, atol=5e-7)
+    dirs = torch.eye(3, device='cuda').contiguous()               # rays_d[k] = sum_j e_k[j] R[:, j] = column k of R
+    for b in range(rot.shape[0]):
+        ro, rd = torch.empty(3, 3, device='cuda'), torch.empty(3, 3, device='cuda')
+        _lib.check(_lib.lib().mne_pose_rays(0, rot[b].contiguous().data_ptr(), trans[b].contiguous().data_ptr(), dirs.data_ptr(), 3,
+                                            ro.data_ptr(), rd.data_ptr(), ops._stream()), 'mne_pose_rays')
+        np.testing.assert_allclose(rd.t().cpu().numpy(), R_ref[b], rtol=0, atol=2e-6)
+        np.testing.assert_allclose(ro.cpu().numpy(), np.tile(g['pose_trans'][b], (3, 1)), rtol=0, atol=0)

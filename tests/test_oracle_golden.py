@@ -110,3 +110,53 @@ def test_oneblob_properties():
     direct = (_wrapped_cdf((left + 1 / 16)[None, None] - xw[..., None], 16)
               - _wrapped_cdf(left[None, None] - xw[..., None], 16)).reshape(-1, 48)
     np.testing.assert_allclose(oneblob(xw, 16).numpy(), direct.numpy(), atol=1e-6)
+
+
+def _inference_fixture():
+    import os
+    from oracle.make_golden_inference import inference_config
+    from tests.cases import GOLDEN
+    g = np.load(os.path.join(GOLDEN, 'small_inference.npz'))
+    cfg = inference_config()
+    bound = J.enlarged_bound(cfg)
+    seed = int(g['seed'])
+    planes, weights = J.init_planes(cfg, bound, seed=seed, std=0.4), J.init_weights(cfg, seed=seed)
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    return g, cfg, bound, bb, planes, weights
+
+
+def test_axis_angle_restatement_equals_the_reference_function():
+    """oracle.joint_encoding.axis_angle_to_matrix against the matrices the reference's own axis_angle_to_matrix /
+    at_to_transform_matrix (optimization/utils.py:161-197, executed from its source) produced."""
+    g = _inference_fixture()[0]
+    rot = torch.from_numpy(g['pose_rot'])
+    R = J.axis_angle_to_matrix(rot)
+    np.testing.assert_allclose(R.numpy(), g['pose_R'], rtol=0, atol=2e-7)
+    np.testing.assert_allclose(g['pose_T'][:, :3, :3], g['pose_R'], rtol=0, atol=0)
+    np.testing.assert_allclose(g['pose_T'][:, :3, 3], g['pose_trans'], rtol=0, atol=0)
+
+
+def test_oracle_renders_the_reference_image_and_eval_forward():
+    """render_img (model/scene_rep.py:422-473) and the eval-mode forward (:566-567) of the reference against the oracle's
+    render_rays on rays built the reference's way (get_rays with the raw cam.cx / cam.cy)."""
+    g, cfg, bound, bb, planes, weights = _inference_fixture()
+    cam = cfg['cam']
+    H, W = int(g['H']), int(g['W'])
+    c2w = torch.from_numpy(g['c2w'])
+    i, j = torch.meshgrid(torch.arange(W, dtype=torch.float32), torch.arange(H, dtype=torch.float32), indexing='xy')
+    dirs = torch.stack([(i - cam['cx']) / cam['fx'], -(j - cam['cy']) / cam['fy'], -torch.ones_like(i)], -1)
+    rays_d = torch.sum(dirs[..., None, :] * c2w[:3, :3], -1).reshape(-1, 3)
+    rays_o = c2w[:3, -1].expand(rays_d.shape)
+    with torch.no_grad():
+        a = J.render_rays(cfg, planes, weights, bound, bb, rays_o, rays_d, None, None)
+        b = J.render_rays(cfg, planes, weights, bound, bb, rays_o, rays_d, torch.from_numpy(g['gt_depth']).reshape(-1, 1), None)
+    assert rel(a['depth'].reshape(H, W).numpy(), g['img_depth_nodepth']) < 1e-4
+    assert rel(a['rgb'].reshape(H, W, 3).numpy(), g['img_color_nodepth']) < 1e-4
+    assert rel(b['depth'].reshape(H, W).numpy(), g['img_depth']) < 1e-4
+    assert rel(b['rgb'].reshape(H, W, 3).numpy(), g['img_color']) < 1e-4
+    with torch.no_grad():
+        e = J.render_rays(cfg, planes, weights, bound, bb, torch.from_numpy(g['eval_rays_o']), torch.from_numpy(g['eval_rays_d']),
+                          torch.from_numpy(g['eval_target_d']), None)
+    assert np.array_equal(e['z_vals'].numpy(), g['eval_ret_z_vals'])
+    for k in ('rgb', 'depth', 'raw'):
+        assert rel(e[k].numpy(), g['eval_ret_' + k]) < 1e-4, k

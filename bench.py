@@ -43,6 +43,7 @@ def parse():
     ap.add_argument('--no-graph', action='store_true')
     ap.add_argument('--no-pipeline', action='store_true', help='do not draw / sample the next batch under the optimiser of the current iteration')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-extras', action='store_true', help='skip the self_check / configs3 / gather_peak / steady-state records (profiling runs)')
     ap.add_argument('--rays', type=int, default=N_RAYS, help='rays per GPU and iteration')
     ap.add_argument('--workload', default='room0', choices=['room0', 'scannet_hash'],
                     help='room0: BASELINE.json configs[1] (the default, the judged line); scannet_hash: configs[3] -- ScanNet scene0000 bound '
@@ -674,6 +675,7 @@ def run_ours(args):
         _, e = timed(lambda: ops.render_backward_points(sc_b, ro, rd, z, scr, act=mapper._act)); ev['bwd'].append(e)
         _, e = timed(lambda: ops.decoder_wgrad(sc_w, n_rays, s, scr, mapper._act)); ev['wgrad'].append(e)
         mapper._pending_wgrad = None
+        nz_frac = float((mapper.flat_grad[:mapper.dense_from].view(-1, 4) != 0).any(1).float().mean().item())
         _, e = timed(mapper.optimizer_step); ev['adam'].append(e)
     torch.cuda.synchronize()
     us = {k: 1e3 * sum(a.elapsed_time(b) for a, b in v) / len(v) for k, v in ev.items()}
@@ -681,7 +683,7 @@ def run_ours(args):
     #      hundred iterations (0.43 -> 0.6), and the Adam pass with it; 400 more iterations, then the same interval again
     touched_prof = float(mapper.touched.float().mean().item()) if mapper.touched is not None else 1.0
     steady = None
-    if world == 1:
+    if world == 1 and not args.no_extras:
         run_steps(400)
         ev2 = []
         for _ in range(10):
@@ -881,7 +883,7 @@ def run_ours(args):
         del tmodel, tracker
 
     gather_peak = None
-    if rank == 0:
+    if rank == 0 and not args.no_extras:
         try:
             gather_peak = gather_peak_record(model, mapper, cfg, db, n_rays, dev)
         except Exception as e:
@@ -889,28 +891,31 @@ def run_ours(args):
     # ---- the records every N carries: configs[3] (strong scaling, hash grid) and the cross-rank self-check
     n_active_main = ops.backward_active_count(mapper._scratch, n_rays, s)
     extra = {}
-    try:
-        extra['self_check'] = self_check_record(world, rank, dev)
-    except Exception as e:
-        extra['self_check'] = {'ok': False, 'error': repr(e)[:300]}
-    try:
-        extra['configs3'] = configs3_record(world, rank, dev, args.steps)
-    except Exception as e:
-        extra['configs3'] = {'error': repr(e)[:300]}
+    if not args.no_extras:
+        try:
+            extra['self_check'] = self_check_record(world, rank, dev)
+        except Exception as e:
+            extra['self_check'] = {'ok': False, 'error': repr(e)[:300]}
+        try:
+            extra['configs3'] = configs3_record(world, rank, dev, args.steps)
+        except Exception as e:
+            extra['configs3'] = {'error': repr(e)[:300]}
 
     if rank == 0:
         peak, peak_src = measured_peak()
         # algorithmic bytes per launch (DESIGN.md "Roofline accounting"):
         #   forward : every sample gathers 3 planes x 2 levels x 4 texels x 128 B
         #   backward: the samples with a non-zero loss gradient scatter into the same texels (the others add nothing)
-        #   Adam    : 32 B per parameter of a group that ever received a gradient (p, g, m, v read; p, m, v, g written),
-        #             4 B gradient read per parameter of the others, 0.25 B of flags per parameter
+        #   Adam    : 4 B gradient read + 0.25 B of flags per parameter, 24 B (p, m, v in and out) per parameter of a group that
+        #             ever received a gradient, 4 B (the gradient cleared) per parameter whose gradient was non-zero this step
         n_active = n_active_main
         fwd_bytes = pts_per_rank * ALG_BYTES_PER_POINT_FWD
         bwd_bytes = n_active * ALG_BYTES_PER_POINT_BWD
         n_param = mapper.total
         touched = touched_prof
-        adam_bytes = int(n_param * (touched * 32 + (1.0 - touched) * 4 + (0.25 if mapper.touched is not None else 0.0)))
+        # every gradient group is read (4 B / parameter) with its flag (0.25 B); groups that ever received a gradient move p, m, v
+        # in and out (24 B); the gradient is written back (cleared) only where it was non-zero this step (4 B)
+        adam_bytes = int(n_param * (4 + (0.25 if mapper.touched is not None else 0.0) + touched * 24 + nz_frac * 4))
         gbs = lambda b, t_us: b / (t_us * 1e-6) / 1e9
         fwd_gbs, bwd_gbs, adam_gbs = gbs(fwd_bytes, us['fwd']), gbs(bwd_bytes, us['bwd']), gbs(adam_bytes, us['adam'])
         line = {
@@ -931,7 +936,7 @@ def run_ours(args):
             'roofline': {'bound': 'hbm', 'kernel': 'adam_segments_kernel' if world == 1 else 'optimizer step: flag hand-over + barrier + adam_peers_sparse_kernel + barrier', 'achieved': adam_gbs, 'peak': peak, 'unit': 'GB/s',
                          'frac': adam_gbs / peak, 'traffic': ncu_traffic('adam_segments_kernel'), 'peak_source': peak_src,
                          'algorithmic_bytes_per_launch': adam_bytes, 'launch_us': us['adam'],
-                         'touched_fraction': touched,
+                         'touched_fraction': touched, 'nonzero_gradient_fraction': nz_frac,
                          'points_fwd_kernel': {'achieved': fwd_gbs, 'frac': fwd_gbs / peak, 'launch_us': us['fwd'],
                                                'algorithmic_bytes_per_launch': fwd_bytes,
                                                'traffic': ncu_traffic('points_fwd_kernel'),

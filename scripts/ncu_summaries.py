@@ -55,8 +55,11 @@ def kernels(rep, title):
     head, units, rows = raw_rows(rep)
     k_name, k_grid, k_block = head.index('Kernel Name'), head.index('Grid Size'), head.index('Block Size')
     seen = OrderedDict()
-    for r in rows:
-        seen.setdefault(r[k_name].split('(')[0], r)          # first captured launch of each kernel
+    k_dur = head.index('gpu__time_duration.sum')
+    for r in rows:                                           # the LONGEST captured launch of each kernel (the optimiser runs twice:
+        name = r[k_name].split('(')[0]                       # the planes' pass and the decoder's few blocks)
+        if name not in seen or float(r[k_dur].replace(',', '')) > float(seen[name][k_dur].replace(',', '')):
+            seen[name] = r
     print('# ' + title)
     for name, r in seen.items():
         print('\n## %s  grid %s block %s' % (name, r[k_grid], r[k_block]))
@@ -71,12 +74,11 @@ def traffic(rep):
     rd, wr = head.index('dram__bytes_read.sum'), head.index('dram__bytes_write.sum')
     scale = {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
     out = OrderedDict()
-    for r in rows:
+    for r in rows:                                           # the launch with the most traffic of each kernel
         name = r[k_name].split('(')[0].replace('void ', '').replace('mne::', '')
-        if name not in out:
-            out[name] = int(float(r[rd]) * scale[units[rd]] + float(r[wr]) * scale[units[wr]])
+        out[name] = max(out.get(name, 0), int(float(r[rd]) * scale[units[rd]] + float(r[wr]) * scale[units[wr]]))
     print(json.dumps({'dram_bytes_per_launch': out, 'source': 'ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, '
-                      'first captured launch of each kernel (%s)' % rep}, indent=1))
+                      'largest captured launch of each kernel (%s)' % rep}, indent=1))
 
 
 if __name__ == '__main__':

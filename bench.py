@@ -510,6 +510,84 @@ def gather_peak_record(model, mapper, cfg, db, n_rays, dev):
             'kernel': 'mne_bench_gather mode 0: loads only, 12 x 128-bit loads in flight per lane, 8 CTAs x 256 threads per SM'}
 
 
+def exchange_record(world, rank, dev):
+    """Agent-to-agent map exchange (BASELINE.json configs[4]): every rank holds a room0 map of its own and
+    hands it to the next rank round a ring (mneslam_b200.exchange.exchange_maps: NCCL send / receive straight between the
+    parameter storages), against the reference's mechanism -- torch.save of latest_checkpoint.pt, torch.load by the peer
+    (mneslam_mp.py:294-315, mp_slam/mapper.py:708-726) -- timed on rank 0 in a local temporary directory."""
+    import torch.distributed as dist
+    from mneslam_b200 import JointEncoding, configs, exchange
+    cfg = configs.replica_room0()
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    torch.manual_seed(100 + rank)
+    model = JointEncoding(cfg, bb).to(dev)
+    torch.manual_seed(0)
+    shared = JointEncoding(cfg, bb).to(dev)
+    nxt, prv = (rank + 1) % world, (rank - 1) % world
+    nbytes = exchange.exchange_maps(model, shared, nxt, recv_from=prv)
+    torch.cuda.synchronize(); dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    times = []
+    for _ in range(7):
+        dist.barrier(); torch.cuda.synchronize()
+        e0.record()
+        exchange.exchange_maps(model, shared, nxt, recv_from=prv)
+        e1.record()
+        torch.cuda.synchronize()
+        times.append(e0.elapsed_time(e1))
+    ms = _max_over_ranks(sorted(times)[len(times) // 2], world, dev)
+    want = torch.stack([t.detach().double().sum() for t in model._flat_planes()])
+    sums = [torch.zeros_like(want) for _ in range(world)]
+    dist.all_gather(sums, want)
+    got = torch.stack([t.detach().double().sum() for t in shared._flat_planes()])
+    ok = torch.tensor([1 if torch.equal(got, sums[prv]) else 0], device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    # the same as peer stores straight into model_shared (PeerMapInbox: it lives in NVLink peer-mapped memory)
+    push_ms = push_ok = None
+    try:
+        torch.manual_seed(0)
+        shared2 = JointEncoding(cfg, bb).to(dev)
+        inbox = exchange.PeerMapInbox(shared2)
+        exchange.push_map(model, inbox, nxt)
+        torch.cuda.synchronize(); dist.barrier()
+        times = []
+        for _ in range(7):
+            dist.barrier(); torch.cuda.synchronize()
+            e0.record()
+            exchange.push_map(model, inbox, nxt)
+            e1.record()
+            torch.cuda.synchronize()
+            times.append(e0.elapsed_time(e1))
+        push_ms = _max_over_ranks(sorted(times)[len(times) // 2], world, dev)
+        got2 = torch.stack([t.detach().double().sum() for t in shared2._flat_planes()])
+        ok2 = torch.tensor([1 if torch.equal(got2, sums[prv]) else 0], device=dev)
+        dist.all_reduce(ok2, op=dist.ReduceOp.MIN)
+        push_ok = bool(int(ok2.item()))
+        del inbox, shared2
+    except Exception as e:
+        print('bench.py: peer-store exchange unavailable (%r)' % (e,), file=sys.stderr)
+    file_ms = None
+    if rank == 0:
+        with tempfile.TemporaryDirectory() as tmp:
+            path = os.path.join(tmp, 'latest_checkpoint.pt')
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            exchange.save_checkpoint(model, path)
+            exchange.load_foreign_model(shared, path, device=dev)
+            torch.cuda.synchronize()
+            file_ms = (time.perf_counter() - t0) * 1e3
+    dist.barrier()
+    del model, shared
+    torch.cuda.empty_cache()
+    best = min(x for x in (ms, push_ms) if x is not None)
+    return {'ms': best, 'bytes_per_direction': nbytes, 'gb_per_s_per_direction': nbytes / (best * 1e-3) / 1e9,
+            'ms_nccl_send_recv': ms, 'ms_peer_stores': push_ms, 'received_map_identical': bool(int(ok.item())) and push_ok is not False,
+            'pattern': 'ring over %d ranks: every rank sends its 129 MB room0 map to the next and receives the previous one into '
+                       'model_shared; device time, median of 7, max over ranks' % world,
+            'reference_file_round_trip_ms': file_ms,
+            'reference_mechanism': 'torch.save(latest_checkpoint.pt) + torch.load by the peer, local temporary directory, rank 0'}
+
+
 def run_ours(args):
     import torch.distributed as dist
     from mneslam_b200 import JointEncoding, configs, synthetic
@@ -896,6 +974,11 @@ def run_ours(args):
             extra['self_check'] = self_check_record(world, rank, dev)
         except Exception as e:
             extra['self_check'] = {'ok': False, 'error': repr(e)[:300]}
+        if world > 1:
+            try:
+                extra['exchange'] = exchange_record(world, rank, dev)
+            except Exception as e:
+                extra['exchange'] = {'error': repr(e)[:300]}
         try:
             extra['configs3'] = configs3_record(world, rank, dev, args.steps)
         except Exception as e:

@@ -65,10 +65,13 @@ def _boxes(model, device):
     return torch.cat([model.bound.reshape(-1).double(), model.bounding_box.reshape(-1).double().cpu()]).to(device)
 
 
-def exchange_maps(model, model_shared, peer, group=None):
-    """Symmetric swap with ``peer``: this agent's map goes out, the peer's map lands in ``model_shared`` (the frozen
-    copy the reference keeps for distillation and loop-closure alignment).  Both agents call this.  Returns the
-    payload size in bytes (one direction)."""
+def exchange_maps(model, model_shared, peer, group=None, recv_from=None):
+    """This agent's map goes to ``peer``; the map of ``recv_from`` (default: ``peer``, a symmetric swap) lands in
+    ``model_shared`` (the frozen copy the reference keeps for distillation and loop-closure alignment).  Every agent
+    involved calls this; with ``peer = (rank + 1) % n`` and ``recv_from = (rank - 1) % n`` the maps travel round a ring.
+    Returns the payload size in bytes (one direction)."""
+    if recv_from is None:
+        recv_from = peer
     outs, ins, fixups = [], [], []
     for src, dst in zip(_tensors(model), _tensors(model_shared)):
         if src.shape != dst.shape:
@@ -85,7 +88,7 @@ def exchange_maps(model, model_shared, peer, group=None):
     ops = []
     for o, i in zip(outs + [boxes_out], ins + [boxes_in]):
         ops.append(dist.P2POp(dist.isend, o, peer, group))
-        ops.append(dist.P2POp(dist.irecv, i, peer, group))
+        ops.append(dist.P2POp(dist.irecv, i, recv_from, group))
     for req in dist.batch_isend_irecv(ops):
         req.wait()
     for dst, view in fixups:
@@ -144,3 +147,62 @@ def load_foreign_model(model_shared, path, device=None):
     model_shared.bound = ckpt['bound']
     model_shared.bounding_box = ckpt['bounding_box']
     return model_shared
+
+
+class PeerMapInbox:
+    """``model_shared`` re-homed into NVLink peer-mapped (symmetric) memory, so that a peer can STORE its map straight into it:
+    one device-to-device copy per tensor over NVLink (``push_map``), nothing to receive, unpack or copy on this side.  All
+    ranks of ``group`` construct it (collectively) for models of the same shapes.  Every tensor of ``model_shared`` keeps its
+    identity, shape and strides; only its storage moves into the symmetric buffer."""
+
+    def __init__(self, model_shared, group=None):
+        import torch.distributed._symmetric_memory as symm
+        group = group if group is not None else dist.group.WORLD
+        self.model, self.group = model_shared, group
+        tensors = _tensors(model_shared)
+        self.layout, off = [], 0
+        for t in tensors:
+            if not _wire_view(t)[1]:
+                raise ValueError('PeerMapInbox: model_shared must hold dense (channels-last / contiguous) tensors')
+            self.layout.append((tuple(t.shape), t.stride(), off, t.numel()))
+            off += t.numel()
+        self.total = off + 24                          # + the two boxes (12 doubles)
+        device = tensors[0].device
+        self.buf = symm.empty(self.total, dtype=torch.float32, device=device)
+        self.handle = symm.rendezvous(self.buf, group.group_name)
+        with torch.no_grad():
+            for t, (shape, stride, o, n) in zip(tensors, self.layout):
+                view = torch.as_strided(self.buf, shape, stride, o)
+                view.copy_(t)
+                t.data = view
+        self.rank = dist.get_rank(group)
+
+    def flat_on(self, rank):
+        """The whole inbox of ``rank`` as a flat float32 tensor (peer-mapped when ``rank`` is not this rank)."""
+        return self.handle.get_buffer(rank, (self.total,), torch.float32)
+
+    def adopt_boxes(self):
+        """After a push (and the barrier): read the sender's two boxes out of the inbox."""
+        boxes = self.buf[self.total - 24:].view(torch.float64).clone()
+        self.model.bound = boxes[:6].reshape(3, 2).float().cpu()
+        self.model.bounding_box = boxes[6:].reshape(3, 2).to(self.model.bounding_box.device)
+
+
+def push_map(model, inbox, peer, barrier=True):
+    """Store this agent's map into ``peer``'s ``PeerMapInbox`` (= its ``model_shared``): one NVLink device-to-device copy per
+    tensor from the parameter storage, then a cross-rank barrier (every rank of the inbox's group calls this, e.g. round a
+    ring) after which each rank's ``model_shared`` holds the map that was pushed to it.  Returns the bytes sent."""
+    dst = inbox.flat_on(peer)
+    n_bytes = 0
+    with torch.no_grad():
+        for t, (shape, stride, off, n) in zip(_tensors(model), inbox.layout):
+            if tuple(t.shape) != shape:
+                raise ValueError('push_map: tensor shape %s does not match the inbox (%s)' % (tuple(t.shape), shape))
+            dst[off:off + n].copy_(_wire_view(t)[0])
+            n_bytes += 4 * n
+        boxes = _boxes(model, dst.device)
+        dst[inbox.total - 24:].view(torch.float64).copy_(boxes)
+    if barrier:
+        inbox.handle.barrier(channel=0)
+        inbox.adopt_boxes()
+    return n_bytes

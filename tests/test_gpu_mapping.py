@@ -164,6 +164,21 @@ def test_two_gpu_sharded_iteration_matches_single_gpu():
     assert r.returncode == 0 and 'multigpu_check ok' in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
 
 
+def test_three_agents_exchange_maps_and_distill():
+    """Runs tests/multiagent_check.py (BASELINE.json configs[4] in small: three agents, one per GPU, ring exchange of the maps
+    over NVLink -- NCCL and peer stores -- then joint distillation) when three GPUs are visible."""
+    import os
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 3:
+        pytest.skip('needs three GPUs')
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '3', '--master-addr',
+                        '127.0.0.1', '--master-port', '29534', os.path.join(root, 'tests', 'multiagent_check.py')],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and 'multiagent_check ok' in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
 def test_touched_map_adam_is_bit_identical_to_dense():
     """Skipping the 16-byte groups that never received a gradient must not change a single bit."""
     import ctypes as C

@@ -83,3 +83,30 @@ def test_pose_parameterisations_match_oracle():
     assert torch.allclose(R @ R.transpose(-1, -2), torch.eye(3).expand(2, 3, 3), atol=1e-5)
     T = pose.transform_matrix(r, torch.ones(2, 3), 'axis_angle')
     assert T.shape == (2, 4, 4) and torch.equal(T[:, 3], torch.tensor([[0., 0, 0, 1]] * 2))
+
+
+def test_hash_grid_checkpoint_round_trip(tmp_path):
+    """With grid.use_hash the encoder's tables are plain tensors outside state_dict() and all_planes is empty: the checkpoint
+    must carry them (key hash_tables), load_foreign_model must restore them and refuse a checkpoint that lacks them."""
+    import torch
+    from mneslam_b200 import JointEncoding, configs, exchange
+    cfg = configs.small_test_config(one_grid=False)
+    cfg['grid'].update({'use_hash': True, 'hash_size': 10, 'voxel_sdf': 0.08, 'voxel_color': 0.16})
+    bb = torch.tensor(cfg['mapping']['bound'], dtype=torch.float64)
+    torch.manual_seed(1)
+    a = JointEncoding(cfg, bb)
+    torch.manual_seed(2)
+    b = JointEncoding(cfg, bb)
+    assert len(a.hash_tables) == 2 and not torch.equal(a.hash_tables[0], b.hash_tables[0])
+    path = str(tmp_path / 'latest_checkpoint.pt')
+    exchange.save_checkpoint(a, path)
+    assert 'hash_tables' in torch.load(path, weights_only=False)
+    exchange.load_foreign_model(b, path, device='cpu')
+    assert all(torch.equal(x, y) for x, y in zip(a.hash_tables, b.hash_tables))
+    assert all(torch.equal(x, y) for x, y in zip(a.decoder.weight_list(), b.decoder.weight_list()))
+    ckpt = exchange.checkpoint_dict(a)
+    del ckpt['hash_tables']
+    torch.save(ckpt, path)
+    import pytest
+    with pytest.raises(KeyError):
+        exchange.load_foreign_model(b, path, device='cpu')

@@ -43,6 +43,7 @@ def parse():
     ap.add_argument('--no-graph', action='store_true')
     ap.add_argument('--no-pipeline', action='store_true', help='do not draw / sample the next batch under the optimiser of the current iteration')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--hash-fp16', action='store_true', help='scannet_hash workload: read the table through its fp16 copy (grid.hash_fp16)')
     ap.add_argument('--no-extras', action='store_true', help='skip the self_check / configs3 / gather_peak / steady-state records (profiling runs)')
     ap.add_argument('--rays', type=int, default=N_RAYS, help='rays per GPU and iteration')
     ap.add_argument('--workload', default='room0', choices=['room0', 'scannet_hash'],
@@ -588,6 +589,49 @@ def exchange_record(world, rank, dev):
             'reference_mechanism': 'torch.save(latest_checkpoint.pt) + torch.load by the peer, local temporary directory, rank 0'}
 
 
+def inference_record(model, cfg, dev):
+    """The forward-only consumers of the same kernels: render_img as save_imgs calls it twice per keyframe
+    (mneslam_mp.py:498,516: 1200 x 680 rays, 256 uniform samples without depth, 32 + 11 with), and a 500 000-point
+    query_sdf chunk as the mesher issues them (model/utils.py:64-153).  Wall clock around the public methods, device
+    synchronised; points/s and the fraction of the 3 072 B/point gather roofline."""
+    from mneslam_b200 import synthetic
+    cam = cfg['cam']
+    H, W = cam['H'] - 2 * cam['crop_edge'], cam['W'] - 2 * cam['crop_edge']
+    gen = torch.Generator().manual_seed(5)
+    c2w = synthetic.make_pose(cfg, gen)
+    gt_depth = (torch.rand(H, W, generator=gen) * 3.0 + 0.5).to(dev)
+    peak, _ = measured_peak()
+    was_training = model.training
+    model.eval()
+    out = {}
+    for name, depth, s in (('render_img_no_depth', None, cfg['training']['n_samples']),
+                           ('render_img_with_depth', gt_depth, cfg['training']['n_samples_d'] + cfg['training']['n_range_d'])):
+        model.render_img(c2w, dev, gt_depth=depth)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        model.render_img(c2w, dev, gt_depth=depth)
+        torch.cuda.synchronize()
+        ms = (time.perf_counter() - t0) * 1e3
+        pts = H * W * s
+        out[name] = {'ms': ms, 'rays': H * W, 'samples_per_ray': s, 'points': pts, 'points_per_s': pts / (ms * 1e-3),
+                     'gather_roofline_frac': pts / (ms * 1e-3) * ALG_BYTES_PER_POINT_FWD / 1e9 / peak}
+    pts = (torch.rand(500000, 1, 3, device=dev) * 2 - 1) * 0.9
+    b = torch.tensor(cfg['mapping']['bound'], dtype=torch.float32, device=dev)
+    pts = b[:, 0] + (pts * 0.5 + 0.5) * (b[:, 1] - b[:, 0])
+    with torch.no_grad():
+        model.query_sdf(pts)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(5):
+            model.query_sdf(pts)
+        torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) * 1e3 / 5
+    out['query_sdf_500k'] = {'ms': ms, 'points': 500000, 'points_per_s': 500000 / (ms * 1e-3),
+                             'gather_roofline_frac': 500000 / (ms * 1e-3) * ALG_BYTES_PER_POINT_FWD / 1e9 / peak}
+    model.train(was_training)
+    return out
+
+
 def run_ours(args):
     import torch.distributed as dist
     from mneslam_b200 import JointEncoding, configs, synthetic
@@ -609,6 +653,7 @@ def run_ours(args):
     if args.workload == 'scannet_hash':
         cfg = configs.scannet_scene0000_onegrid()
         cfg['grid']['use_hash'] = True
+        cfg['grid']['hash_fp16'] = bool(args.hash_fp16)
     else:
         cfg = configs.replica_room0()
     n_rays = args.rays
@@ -960,6 +1005,12 @@ def run_ours(args):
                     'points_per_iter': 1024 * 117}
         del tmodel, tracker
 
+    inference = None
+    if world == 1 and not args.no_extras:
+        try:
+            inference = inference_record(model, cfg, dev)
+        except Exception as e:
+            inference = {'error': repr(e)[:300]}
     gather_peak = None
     if rank == 0 and not args.no_extras:
         try:
@@ -1040,6 +1091,7 @@ def run_ours(args):
         # of gradient contributions) x points/s over the measured HBM copy bandwidth of all GPUs
         line['roofline']['whole_step_frac_6144B_per_point'] = value * (ALG_BYTES_PER_POINT_FWD + ALG_BYTES_PER_POINT_BWD) / 1e9 / (peak * world)
         line['gather_peak'] = gather_peak
+        line['inference'] = inference
         line['adam']['steady_state'] = steady
         if gather_peak and 'gather_gbs_after_l2_flush' in gather_peak:
             g_cold, g_warm = gather_peak['gather_gbs_after_l2_flush'], gather_peak['gather_gbs_warm']

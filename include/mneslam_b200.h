@@ -43,8 +43,11 @@ typedef struct MnePlaneDesc {
 /* Multi-resolution hash grid (the encoder the reference's configs name, model/encodings.py:31-46;
  * tiny-cuda-nn "HashGrid": n_levels x n_features tables concatenated, level l at table + offset[l]). */
 typedef struct MneHashDesc {
-    const float* table;
-    float* grad;
+    const float* table;      /* fp32 parameters [entries][2] (the optimiser's master copy) */
+    float* grad;             /* fp32 gradient accumulator of the same shape (+=), or NULL */
+    const void* table_h;     /* optional fp16 copy of `table` ([entries] half2, kept in step by the caller): when non-NULL the
+                              * kernels READ the features from it with one 32-bit load per entry -- tiny-cuda-nn's default
+                              * parameter precision; parity gate 1e-2 instead of 1e-3 (BASELINE.json).  Gradients stay fp32. */
     int32_t n_levels;        /* 16 */
     int32_t n_features;      /* 2 */
     int32_t base_resolution; /* 16 */

@@ -28,7 +28,7 @@ class PlaneDesc(C.Structure):
 
 
 class HashDesc(C.Structure):
-    _fields_ = [('table', C.c_void_p), ('grad', C.c_void_p), ('n_levels', C.c_int32), ('n_features', C.c_int32),
+    _fields_ = [('table', C.c_void_p), ('grad', C.c_void_p), ('table_h', C.c_void_p), ('n_levels', C.c_int32), ('n_features', C.c_int32),
                 ('base_resolution', C.c_int32), ('per_level_scale', C.c_float), ('offsets', C.c_uint32 * 33),
                 ('level_scale', C.c_float * 32), ('level_res', C.c_uint32 * 32)]
 

@@ -86,6 +86,8 @@ static int g_impl = 2;
 int impl_version() { return g_impl; }
 static int g_adam_spare_sms = 0;
 int adam_spare_sms() { return g_adam_spare_sms; }
+static int g_hash_level0_smem = 0;
+int hash_level0_smem() { return g_hash_level0_smem; }
 
 }  // namespace mne
 
@@ -102,6 +104,13 @@ extern "C" int mne_set_option(const char* key, int value) {
         // stream (the next iteration's ray assembly and sampling, mapping.PipelinedMapper) run under them
         MNE_CHECK_ARG(value >= 0 && value <= 64, "mne_set_option: adam_spare_sms must be in [0, 64]");
         g_adam_spare_sms = value;
+        return 0;
+    }
+    if (strcmp(key, "hash_level0_smem") == 0) {
+        // hash grid forward: stage level 0 of the table(s) (17^3 entries, 39 KB) in shared memory.  Off by default: measured slower
+        // on B200 (the shared memory comes out of the L1 that serves the other coarse levels)
+        MNE_CHECK_ARG(value == 0 || value == 1, "mne_set_option: hash_level0_smem must be 0 or 1");
+        g_hash_level0_smem = value;
         return 0;
     }
     set_error("mne_set_option: unknown option '%s'", key);

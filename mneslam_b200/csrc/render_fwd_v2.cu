@@ -38,6 +38,7 @@ struct PtsFwdParams {
     float* geo;               // [M,15] or NULL
     float* feat;              // [M,64] or NULL
     float* act;               // [M, ActRow::STRIDE] per-sample record kept for the backward (tile16.cuh: ActRow), or NULL
+    int lvl0_stage;           // hash grid: 1 = level 0 of every table is staged in shared memory (the launcher sized it in)
     // ---- per-ray tail (TAIL > 0)
     RayFwdParams rf;          // compositing outputs, targets, loss accumulators
     int* ray_done;            // [n_rays] samples of each ray stored so far; zero on entry, reset by the warp that finishes the ray
@@ -67,6 +68,17 @@ __global__ void __launch_bounds__(pts_warps<TWO>() * 32, 1) points_fwd_kernel(co
     if (TAIL > 0 && lane < RS_COUNT) warp_sums[warp * RS_COUNT + lane] = 0.0;
 
     load_weights_v2<TWO>(P.sc, W4, threadIdx.x, blockDim.x);
+    // hash grid: the coarsest level of the table(s) -- dense, 17^3 entries, read 8 times by every sample -- in shared memory
+    float2* lvl0_a = nullptr;
+    float2* lvl0_b = nullptr;
+    if (MODE == 2 && P.lvl0_stage) {
+        lvl0_a = reinterpret_cast<float2*>(reinterpret_cast<float*>(smem4 + N::W4_COUNT) + NW * pts_warp_floats<TWO>());
+        stage_hash_level0(P.sc.hash[0], lvl0_a, threadIdx.x, blockDim.x);
+        if (TWO) {
+            lvl0_b = lvl0_a + (P.sc.hash[0].offsets[1] - P.sc.hash[0].offsets[0]);
+            stage_hash_level0(P.sc.hash[1], lvl0_b, threadIdx.x, blockDim.x);
+        }
+    }
     __syncthreads();
 
     const int64_t n_tiles = (P.n_pts + kTilePts - 1) / kTilePts;
@@ -107,8 +119,8 @@ __global__ void __launch_bounds__(pts_warps<TWO>() * 32, 1) points_fwd_kernel(co
             //      point's blob segment, gather, then let the OneBlob overwrite them
             if (half == 0) { row[kBlobCol] = bx; row[kBlobCol + 1] = by; row[kBlobCol + 2] = bz; }
             __syncwarp();
-            gather16_hash(P.sc.hash[0], X + kBlobCol, kXStride, X, kXStride, np, lane);
-            if (TWO) gather16_hash(P.sc.hash[1], X + kBlobCol, kXStride, CFt, kCStride, np, lane);      // colour table
+            gather16_hash(P.sc.hash[0], X + kBlobCol, kXStride, X, kXStride, np, lane, lvl0_a);
+            if (TWO) gather16_hash(P.sc.hash[1], X + kBlobCol, kXStride, CFt, kCStride, np, lane, lvl0_b);      // colour table
             __syncwarp();
             if (arow) {
                 for (int p = 0; p < np; ++p) {
@@ -303,19 +315,32 @@ __global__ void __launch_bounds__(kRayWarps * 32) rays_tail_kernel(const __grid_
 int check_scene(const MneSceneDesc* sc, const char* who, bool need_grads);
 int sm_count();
 int impl_version();
+int hash_level0_smem();
 int render_forward_v1(const MneSceneDesc*, const MneRenderCfg*, int32_t, int32_t, const float*, const float*, const float*,
                       const float*, const float*, float*, float*, float*, float*, float*, float*, float*, int32_t*, double*,
                       mne_stream_t);
 int query_points_v1(const MneSceneDesc*, int64_t, const float*, float*, float*, float*, mne_stream_t);
 
 template <bool TWO, int MODE, int TAIL>
-static int launch_points_fwd(const PtsFwdParams& P, cudaStream_t stream) {
-    const size_t smem = pts_smem_bytes<TWO>();
+static int launch_points_fwd(const PtsFwdParams& P_in, cudaStream_t stream) {
+    PtsFwdParams P = P_in;
+    size_t smem = pts_smem_bytes<TWO>();
+    constexpr size_t kSmemMax = 227 * 1024 - 2048;       // the opt-in limit per CTA minus the kernel's static shared memory (loss sums)
+    if (MODE == 2) {
+        // level 0 of the table(s) goes to shared memory when it fits beside the weights and the tiles
+        size_t extra = sizeof(float2) * (size_t)(P.sc.hash[0].offsets[1] - P.sc.hash[0].offsets[0]);
+        if (TWO) extra += sizeof(float2) * (size_t)(P.sc.hash[1].offsets[1] - P.sc.hash[1].offsets[0]);
+        // (opt-in: measured on B200 it LOSES -- 734 -> 1170 us for 958 k samples -- because the extra 39 KB leave the SM ~9 KB of
+        //  L1, and the L1 is what serves the other coarse levels; option "hash_level0_smem")
+        P.lvl0_stage = (hash_level0_smem() && smem + extra <= kSmemMax) ? 1 : 0;
+        if (P.lvl0_stage) smem += extra;
+    }
     static bool configured[64] = {};
     int dev = 0;
     MNE_CHECK_CUDA(cudaGetDevice(&dev));
     if (dev >= 64 || !configured[dev]) {
-        MNE_CHECK_CUDA(cudaFuncSetAttribute(points_fwd_kernel<TWO, MODE, TAIL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        MNE_CHECK_CUDA(cudaFuncSetAttribute(points_fwd_kernel<TWO, MODE, TAIL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)(MODE == 2 ? kSmemMax : smem)));
         if (dev < 64) configured[dev] = true;
     }
     const int64_t n_tiles = (P.n_pts + kTilePts - 1) / kTilePts;

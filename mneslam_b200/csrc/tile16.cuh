@@ -9,6 +9,7 @@
 //   * per-warp shared memory: one [16][120] fp32 tile (feat64 | blob48); the bilinear tap table of a point
 //     aliases that point's blob segment while the gather runs (192 B = 6 taps x (4 offsets + 4 weights)).
 #pragma once
+#include <cuda_fp16.h>
 #include "render_common.cuh"
 
 namespace mne {
@@ -323,11 +324,26 @@ __device__ __forceinline__ float corner_weight(const HashCell& c, int k) {
     return ((k & 1) ? c.f[0] : 1.0f - c.f[0]) * ((k & 2) ? c.f[1] : 1.0f - c.f[1]) * ((k & 4) ? c.f[2] : 1.0f - c.f[2]);
 }
 
+// one table entry (2 features): from the fp16 copy of the table when the descriptor carries one (half2 load, 4 bytes per
+// entry -- tiny-cuda-nn's default parameter precision, the 1e-2 parity gate of BASELINE.json), else from the fp32 table
+__device__ __forceinline__ float2 hash_entry(const MneHashDesc& h, uint32_t level_offset, uint32_t idx) {
+    if (h.table_h) return __half22float2(__ldg(reinterpret_cast<const __half2*>(h.table_h) + level_offset + idx));
+    return __ldg(reinterpret_cast<const float2*>(h.table) + level_offset + idx);
+}
+
+// lvl0: the entries of level 0 (the coarsest, dense level: 17^3 entries = 39 KB) staged in shared memory by the CTA, or
+// NULL.  Every sample reads 8 of them; the other levels are served by L2 / HBM.
+__device__ __forceinline__ void stage_hash_level0(const MneHashDesc& h, float2* lvl0, int tid, int nthreads) {
+    const uint32_t n = h.offsets[1] - h.offsets[0];
+    for (uint32_t i = tid; i < n; i += nthreads) lvl0[i] = hash_entry(h, h.offsets[0], i);
+}
+
 __device__ __forceinline__ void gather16_hash(const MneHashDesc& h, const float* __restrict__ xn, int xn_stride,
-                                              float* __restrict__ dst, int dst_stride, int np, int lane) {
+                                              float* __restrict__ dst, int dst_stride, int np, int lane,
+                                              const float2* __restrict__ lvl0 = nullptr) {
     const int l = lane & 15, pp = lane >> 4;
     const HashLevel L = hash_level(h, l);
-    const float2* table = reinterpret_cast<const float2*>(h.table) + L.offset;
+    const bool from_smem = lvl0 != nullptr && l == 0;
 #pragma unroll 2
     for (int it = 0; it < kTilePts / 2; ++it) {
         const int p = 2 * it + pp;
@@ -337,7 +353,7 @@ __device__ __forceinline__ void gather16_hash(const MneHashDesc& h, const float*
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
                 const uint32_t idx = hash_index(L, c.g[0] + (k & 1), c.g[1] + ((k >> 1) & 1), c.g[2] + ((k >> 2) & 1));
-                const float2 v = __ldg(table + idx);
+                const float2 v = from_smem ? lvl0[idx] : hash_entry(h, L.offset, idx);
                 const float w = corner_weight(c, k);
                 acc.x = fmaf(w, v.x, acc.x); acc.y = fmaf(w, v.y, acc.y);
             }
@@ -353,7 +369,12 @@ __device__ __forceinline__ void mark_dirty(uint8_t* map, int64_t texel) {
     asm volatile("st.global.u8 [%0], %1;" :: "l"(map + texel), "r"(1));
 }
 
-// gradient of the table: grad[corner] += w * d feat (one 64-bit vector reduction per corner)
+// gradient of the table: grad[corner] += w * d feat (one 64-bit vector reduction per corner).
+// Warp-aggregated where it pays: the two lanes of a level hold two CONSECUTIVE samples of the list (neighbours on a ray),
+// which at the coarse levels mostly fall into the same cell -- when a corner's entry is the same for both, the lower lane
+// adds the two contributions and issues ONE reduction (levels >= kHashAggLevels have cells smaller than the sample
+// spacing: no duplicates to find, so they skip the three shuffles per corner).
+constexpr int kHashAggLevels = 8;
 __device__ __forceinline__ void scatter16_hash(const MneHashDesc& h, const float* __restrict__ xn, int xn_stride,
                                                const float* __restrict__ src, int src_stride, int np, int lane,
                                                uint8_t* dirty = nullptr, const float* dirty_base = nullptr) {
@@ -362,14 +383,29 @@ __device__ __forceinline__ void scatter16_hash(const MneHashDesc& h, const float
     float2* grad = reinterpret_cast<float2*>(h.grad) + L.offset;
     for (int it = 0; it < kTilePts / 2; ++it) {
         const int p = 2 * it + pp;
-        if (p < np) {
-            const HashCell c = hash_cell(L, xn + p * xn_stride);
-            const float2 g2 = *reinterpret_cast<const float2*>(src + p * src_stride + 2 * l);
+        const bool on = p < np;
+        HashCell c;
+        float2 g2 = make_float2(0.f, 0.f);
+        if (on) {
+            c = hash_cell(L, xn + p * xn_stride);
+            g2 = *reinterpret_cast<const float2*>(src + p * src_stride + 2 * l);
+        } else {
+            c.g[0] = c.g[1] = c.g[2] = 0u; c.f[0] = c.f[1] = c.f[2] = 0.f;
+        }
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                const uint32_t idx = hash_index(L, c.g[0] + (k & 1), c.g[1] + ((k >> 1) & 1), c.g[2] + ((k >> 2) & 1));
-                const float w = corner_weight(c, k);
-                atomicAdd(grad + idx, make_float2(w * g2.x, w * g2.y));
+        for (int k = 0; k < 8; ++k) {
+            const uint32_t idx = hash_index(L, c.g[0] + (k & 1), c.g[1] + ((k >> 1) & 1), c.g[2] + ((k >> 2) & 1));
+            const float w = corner_weight(c, k);
+            float2 v = make_float2(w * g2.x, w * g2.y);
+            bool mine = on;
+            // (all 32 lanes take part in the shuffles; lanes of the fine levels get their own values back and ignore them)
+            const uint32_t o_idx = __shfl_xor_sync(0xffffffffu, on ? idx : 0xffffffffu, 16);
+            const float ox = __shfl_xor_sync(0xffffffffu, v.x, 16), oy = __shfl_xor_sync(0xffffffffu, v.y, 16);
+            if (l < kHashAggLevels && on && o_idx == idx) {          // the other sample of the pair hits the same entry
+                if (pp == 0) { v.x += ox; v.y += oy; } else mine = false;
+            }
+            if (mine) {
+                atomicAdd(grad + idx, v);
                 if (dirty) mark_dirty(dirty, (reinterpret_cast<const float*>(grad + idx) - dirty_base) >> 5);
             }
         }
@@ -384,7 +420,6 @@ __device__ __forceinline__ void hash_point_grad16(const MneHashDesc& h, const fl
                                                   const float* __restrict__ src, int src_stride, int np, int lane, float (&out)[3]) {
     const int l = lane & 15, pp = lane >> 4;
     const HashLevel L = hash_level(h, l);
-    const float2* table = reinterpret_cast<const float2*>(h.table) + L.offset;
     for (int it = 0; it < kTilePts / 2; ++it) {
         const int p = 2 * it + pp;
         float d[3] = {0.f, 0.f, 0.f};
@@ -394,7 +429,7 @@ __device__ __forceinline__ void hash_point_grad16(const MneHashDesc& h, const fl
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
                 const uint32_t idx = hash_index(L, c.g[0] + (k & 1), c.g[1] + ((k >> 1) & 1), c.g[2] + ((k >> 2) & 1));
-                const float2 v = __ldg(table + idx);
+                const float2 v = hash_entry(h, L.offset, idx);
                 const float D = g2.x * v.x + g2.y * v.y;
                 const float wx = (k & 1) ? c.f[0] : 1.0f - c.f[0], wy = (k & 2) ? c.f[1] : 1.0f - c.f[1], wz = (k & 4) ? c.f[2] : 1.0f - c.f[2];
                 d[0] += ((k & 1) ? D : -D) * (wy * wz);

@@ -47,11 +47,16 @@ class HashGridMeta:
         """[n_entries, 2] float32, U(-scale, scale) (tiny-cuda-nn's grid initialisation)."""
         return (torch.rand(self.n_entries, self.n_features, device=device) * 2 - 1) * scale
 
-    def fill_desc(self, desc, table, grad=None):
+    def fill_desc(self, desc, table, grad=None, table_h=None):
         if not (table.is_cuda and table.dtype == torch.float32 and table.is_contiguous()
                 and tuple(table.shape) == (self.n_entries, self.n_features)):
             raise TypeError('hash table must be a contiguous float32 CUDA tensor of shape [%d, %d]' % (self.n_entries, self.n_features))
         desc.table = table.data_ptr()
+        desc.table_h = None
+        if table_h is not None:
+            if not (table_h.is_cuda and table_h.dtype == torch.float16 and table_h.is_contiguous() and table_h.shape == table.shape):
+                raise TypeError('the fp16 copy of the hash table must be a contiguous float16 CUDA tensor of the table\'s shape')
+            desc.table_h = table_h.data_ptr()
         desc.grad = None
         if grad is not None:
             if grad.shape != table.shape or not grad.is_contiguous() or not grad.is_cuda:

@@ -238,6 +238,7 @@ class FusedMapper:
                               self.cfg['pos']['n_bins'],
                               plane_grads=self.plane_grads if (with_grads and plane_grads) else None,
                               weight_grads=self.weight_grads if (with_grads and weight_grads) else None, hash_meta=m.hash_meta,
+                              hash_half=m.hash_tables_h,
                               dirty=self.dirty_local if with_grads else None,
                               dirty_base=self.flat_grad if (with_grads and self.dirty_local is not None) else None)
 
@@ -276,6 +277,7 @@ class FusedMapper:
         rcfg = ops.make_render_cfg(cfg, norm_rays=self.global_rays_override or n * self.world_size)
         td = target_d.reshape(-1)
         z_vals, acc = sampled if sampled is not None else self.sample_stage(target_d, noise)
+        self.model.refresh_hash_half()            # (grid.hash_fp16: the kernels read an fp16 copy of the tables)
         scene = self._scene(False)
         if self._act is None or self._act.numel() < n * s * ops.act_floats(scene):
             self._act = torch.empty(n * s * ops.act_floats(scene), dtype=torch.float32, device=dev)

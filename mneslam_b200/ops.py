@@ -115,7 +115,7 @@ def bounds_to_host(bound, bounding_box):
 
 
 def make_scene(planes, weights, bound, bounding_box, n_bins=16, plane_grads=None, weight_grads=None, hash_meta=None,
-               dirty=None, dirty_base=None):
+               dirty=None, dirty_base=None, hash_half=None):
     """planes: flat list of 6 or 12 ``[1,32,H,W]`` tensors in ``all_planes`` order (group, axis, level) -- or, with
     ``hash_meta`` (a ``hashgrid.HashGridMeta``; its ``.color`` is the colour table's meta or None), ``[table]`` /
     ``[table, colour table]`` of the hash grid encoder.
@@ -129,9 +129,14 @@ def make_scene(planes, weights, bound, bounding_box, n_bins=16, plane_grads=None
         if len(planes) != (1 if color_meta is None else 2):
             raise ValueError('the hash grid encoder takes [table] or, with a colour table, [table, colour table]')
         sc.encoder, sc.two_grid, sc.c_dim = 1, 0 if color_meta is None else 1, 32
-        hash_meta.fill_desc(sc.hash[0], planes[0], plane_grads[0] if plane_grads is not None else None)
+        # hash_half: fp16 copies of the tables ([table] / [table, colour table]); the kernels then read the features from them
+        hash_meta.fill_desc(sc.hash[0], planes[0], plane_grads[0] if plane_grads is not None else None,
+                            hash_half[0] if hash_half is not None else None)
         if color_meta is not None:
-            color_meta.fill_desc(sc.hash[1], planes[1], plane_grads[1] if plane_grads is not None else None)
+            color_meta.fill_desc(sc.hash[1], planes[1], plane_grads[1] if plane_grads is not None else None,
+                                 hash_half[1] if hash_half is not None else None)
+        if hash_half is not None:
+            keep.extend(hash_half)
         planes, plane_grads = [], None
         feat = hash_meta.n_output
     else:

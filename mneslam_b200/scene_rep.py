@@ -212,6 +212,7 @@ class JointEncoding(nn.Module):
             raise NotImplementedError('the fused kernels are built for pos.enc = OneBlob with 16 bins')
         self.input_ch_pos = config['model']['input_ch_pos']
         self.hash_meta, self.hash_tables = None, None
+        self.hash_fp16, self.hash_tables_h = False, None
         if config['grid'].get('use_hash', False):
             # the encoder the configs NAME (grid.enc: HashGrid + hash_size + voxel_sdf, model/scene_rep.py:55-70,160)
             # but the reference never builds; opt-in through the extension key grid.use_hash
@@ -223,6 +224,9 @@ class JointEncoding(nn.Module):
                 self.hash_meta.color = HashGridMeta.from_config(config, key='voxel_color')
                 self.hash_tables.append(self.hash_meta.color.new_table(self.device))
             self.input_ch = self.hash_meta.n_output
+            # grid.hash_fp16 (extension key): the kernels read the features from an fp16 copy of the table(s), refreshed from
+            # the fp32 master before every render -- tiny-cuda-nn's default parameter precision (parity gate 1e-2)
+            self.hash_fp16 = bool(config['grid'].get('hash_fp16', False))
             self.all_planes = ()
             if self.input_ch_pos != 48:
                 raise NotImplementedError('model.input_ch_pos must be 48 (3 x n_bins)')
@@ -287,15 +291,30 @@ class JointEncoding(nn.Module):
             return tuple((t.data_ptr(), t.shape, t.stride()) if t is not None else None for t in ts)
         key = (sig(planes), sig(weights), sig(plane_grads) if plane_grads is not None else None,
                sig(weight_grads) if weight_grads is not None else None,
-               id(self.bound), self.bound._version, id(self.bounding_box), self.bounding_box._version, id(self.hash_meta))
+               id(self.bound), self.bound._version, id(self.bounding_box), self.bounding_box._version, id(self.hash_meta),
+               sig(self.hash_tables_h) if self.hash_tables_h is not None else None)
         sc = self._scene_cache.get(key)
         if sc is None:
             if len(self._scene_cache) > 8:
                 self._scene_cache.clear()
             sc = ops.make_scene(planes, weights, self.bound, self.bounding_box, self.config['pos']['n_bins'],
-                                plane_grads=plane_grads, weight_grads=weight_grads, hash_meta=self.hash_meta)
+                                plane_grads=plane_grads, weight_grads=weight_grads, hash_meta=self.hash_meta,
+                                hash_half=self.hash_tables_h)
             self._scene_cache[key] = sc
         return sc
+
+    def refresh_hash_half(self):
+        """grid.hash_fp16: bring the fp16 copies of the hash tables in step with the fp32 masters (one conversion pass per
+        table; called before every render, and by FusedMapper after its optimiser step)."""
+        if not self.hash_fp16:
+            self.hash_tables_h = None
+            return
+        if self.hash_tables_h is None or len(self.hash_tables_h) != len(self.hash_tables) or \
+                any(h.shape != t.shape or h.device != t.device for h, t in zip(self.hash_tables_h, self.hash_tables)):
+            self.hash_tables_h = [torch.empty(t.shape, dtype=torch.float16, device=t.device) for t in self.hash_tables]
+        with torch.no_grad():
+            for h, t in zip(self.hash_tables_h, self.hash_tables):
+                h.copy_(t)
 
     def _flat_planes(self):
         """The encoder's parameter tensors: the planes in ``all_planes`` order, or the hash table(s)."""
@@ -315,6 +334,7 @@ class JointEncoding(nn.Module):
         return planes
 
     def _scene(self):
+        self.refresh_hash_half()
         return self._cached_scene(self._flat_planes(), self.decoder.weight_list())
 
     def _render(self, rays_o, rays_d, target_rgb, target_d, with_losses, noise=None):
@@ -323,6 +343,7 @@ class JointEncoding(nn.Module):
             from .importance import render_with_importance
             return render_with_importance(self, rays_o, rays_d, target_rgb, target_d, with_losses, noise)
         noise = noise if noise is not None else self.noise_override
+        self.refresh_hash_half()
         params = self._flat_planes() + self.decoder.weight_list()
         res = _Render.apply(self, rays_o, rays_d, target_rgb, target_d, noise, with_losses, *params)
         rgb, depth, raw = res[:3]

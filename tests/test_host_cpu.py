@@ -30,10 +30,10 @@ def test_library_exports_every_declared_symbol():
 
 def test_struct_layout_matches_header():
     assert ctypes.sizeof(_lib.PlaneDesc) == 48
-    assert ctypes.sizeof(_lib.HashDesc) == 424
-    assert ctypes.sizeof(_lib.SceneDesc) == 1592
-    assert _lib.SceneDesc.bound_lo.offset == 1440 and _lib.SceneDesc.bbox_lo.offset == 1464
-    assert _lib.SceneDesc.w_sdf0.offset == 1512
+    assert ctypes.sizeof(_lib.HashDesc) == 432
+    assert ctypes.sizeof(_lib.SceneDesc) == 1608
+    assert _lib.SceneDesc.bound_lo.offset == 1456 and _lib.SceneDesc.bbox_lo.offset == 1480
+    assert _lib.SceneDesc.w_sdf0.offset == 1528
     assert ctypes.sizeof(_lib.RenderCfg) == 40 and _lib.RenderCfg.norm_rays.offset == 32
     assert ctypes.sizeof(_lib.SampleCfg) == 40
 

@@ -338,12 +338,10 @@ __device__ __forceinline__ void stage_hash_level0(const MneHashDesc& h, float2* 
     for (uint32_t i = tid; i < n; i += nthreads) lvl0[i] = hash_entry(h, h.offsets[0], i);
 }
 
-__device__ __forceinline__ void gather16_hash(const MneHashDesc& h, const float* __restrict__ xn, int xn_stride,
-                                              float* __restrict__ dst, int dst_stride, int np, int lane,
-                                              const float2* __restrict__ lvl0 = nullptr) {
-    const int l = lane & 15, pp = lane >> 4;
-    const HashLevel L = hash_level(h, l);
-    const bool from_smem = lvl0 != nullptr && l == 0;
+// SRC: 0 = fp32 table, 1 = fp16 copy (half2 loads), 2 = shared-memory copy of the level (float2)
+template <int SRC>
+__device__ __forceinline__ void gather16_hash_from(const HashLevel& L, const void* __restrict__ entries, const float* __restrict__ xn,
+                                                   int xn_stride, float* __restrict__ dst, int dst_stride, int np, int l, int pp) {
 #pragma unroll 2
     for (int it = 0; it < kTilePts / 2; ++it) {
         const int p = 2 * it + pp;
@@ -353,13 +351,26 @@ __device__ __forceinline__ void gather16_hash(const MneHashDesc& h, const float*
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
                 const uint32_t idx = hash_index(L, c.g[0] + (k & 1), c.g[1] + ((k >> 1) & 1), c.g[2] + ((k >> 2) & 1));
-                const float2 v = from_smem ? lvl0[idx] : hash_entry(h, L.offset, idx);
+                float2 v;
+                if (SRC == 0) v = __ldg(reinterpret_cast<const float2*>(entries) + idx);
+                else if (SRC == 1) v = __half22float2(__ldg(reinterpret_cast<const __half2*>(entries) + idx));
+                else v = reinterpret_cast<const float2*>(entries)[idx];
                 const float w = corner_weight(c, k);
                 acc.x = fmaf(w, v.x, acc.x); acc.y = fmaf(w, v.y, acc.y);
             }
             *reinterpret_cast<float2*>(dst + p * dst_stride + 2 * l) = acc;
         }
     }
+}
+
+__device__ __forceinline__ void gather16_hash(const MneHashDesc& h, const float* __restrict__ xn, int xn_stride,
+                                              float* __restrict__ dst, int dst_stride, int np, int lane,
+                                              const float2* __restrict__ lvl0 = nullptr) {
+    const int l = lane & 15, pp = lane >> 4;
+    const HashLevel L = hash_level(h, l);
+    if (lvl0 != nullptr && l == 0) gather16_hash_from<2>(L, lvl0, xn, xn_stride, dst, dst_stride, np, l, pp);
+    else if (h.table_h) gather16_hash_from<1>(L, reinterpret_cast<const __half2*>(h.table_h) + L.offset, xn, xn_stride, dst, dst_stride, np, l, pp);
+    else gather16_hash_from<0>(L, reinterpret_cast<const float2*>(h.table) + L.offset, xn, xn_stride, dst, dst_stride, np, l, pp);
     for (int p = 0; p < kTilePts; ++p) dst[p * dst_stride + 32 + lane] = 0.0f;      // padding columns 32..63
 }
 

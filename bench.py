@@ -28,6 +28,7 @@ import torch  # noqa: E402
 
 N_RAYS = 2048
 N_KF = 20
+MIN_PIXELS_CUR = {'room0': 100, 'scannet_hash': 20}      # mapping.min_pixels_cur of the reference's replica.yaml / scannet.yaml
 ALG_BYTES_PER_POINT_FWD = 3072      # 3 planes x 2 levels x 4 texels x 32 ch x 4 B gathered      
 ALG_BYTES_PER_POINT_BWD = 3072      # the same texels receive one gradient contribution each
 METRIC = 'sampled points/s fwd+bwd (map step)'
@@ -45,20 +46,28 @@ def parse():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--hash-fp16', action='store_true', help='scannet_hash workload: read the table through its fp16 copy (grid.hash_fp16)')
     ap.add_argument('--no-extras', action='store_true', help='skip the self_check / configs3 / gather_peak / steady-state records (profiling runs)')
-    ap.add_argument('--rays', type=int, default=N_RAYS, help='rays per GPU and iteration')
+    ap.add_argument('--rays', type=int, default=N_RAYS, help="keyframe rays per GPU and iteration (mapping.sample); the reference's batch adds "
+                    "max(sample // n_keyframes, min_pixels_cur) rays of the current frame (mp_slam/mapper.py:137-139)")
+    ap.add_argument('--no-current-frame', action='store_true', help='keyframe rays only (the round-1 batch)')
     ap.add_argument('--workload', default='room0', choices=['room0', 'scannet_hash'],
                     help='room0: BASELINE.json configs[1] (the default, the judged line); scannet_hash: configs[3] -- ScanNet scene0000 bound '
                          'and sampling (117 samples per ray) on the 16-level hash grid; use with --rays = 65536 / GPUs and --value-only')
     ap.add_argument('--mark-dirty', action='store_true', help='multi-GPU: flag dirty texels in the backward kernel instead of deriving the flags from the gradient buffer')
     ap.add_argument('--spare-sms', type=int, default=8, help='SMs the optimiser kernels leave to the pipelined side stream')
     ap.add_argument('--value-only', action='store_true', help='print the graph-replayed step time only (side experiments)')
-    return ap.parse_args()
+    args = ap.parse_args()
+    # the batch of mapping_optimize: `sample` rays over all keyframes + the current frame's share
+    args.sample = args.rays
+    args.cur = 0 if args.no_current_frame else max(args.rays // N_KF, MIN_PIXELS_CUR[args.workload])
+    args.rays = args.sample + args.cur
+    return args
 
 
 def workload_config(cfg, n_rays, world):
     s = cfg['training']['n_samples_d'] + cfg['training']['n_range_d']
-    return {'workload': 'Replica room0 mapping iteration: %d-ray batch/GPU from a synthetic %d-keyframe DB (1200x680), '
-                        '%d samples/ray, tri-plane 2x3 planes (129.4 MB fp32) + OneBlob + SDF/colour MLPs, '
+    return {'workload': 'Replica room0 mapping iteration: %d-ray batch/GPU (mapping.sample rays drawn without replacement from a synthetic '
+                        '%d-keyframe DB, 1200x680, + max(sample // n_kf, min_pixels_cur) pixels of the current frame, as mapping_optimize '
+                        'builds it), %d samples/ray, tri-plane 2x3 planes (129.4 MB fp32) + OneBlob + SDF/colour MLPs, '
                         'fwd + losses + bwd + Adam' % (n_rays, N_KF, s),
             'rays_per_gpu': n_rays, 'samples_per_ray': s, 'points_per_step': n_rays * s * world,
             'parallelism': 'ray-sharded data parallel x%d' % world if world > 1 else 'single GPU',
@@ -628,6 +637,8 @@ def inference_record(model, cfg, dev):
     ms = (time.perf_counter() - t0) * 1e3 / 5
     out['query_sdf_500k'] = {'ms': ms, 'points': 500000, 'points_per_s': 500000 / (ms * 1e-3),
                              'gather_roofline_frac': 500000 / (ms * 1e-3) * ALG_BYTES_PER_POINT_FWD / 1e9 / peak}
+    out['note'] = ('gather_roofline_frac = points/s x 3072 algorithmic bytes per point over the HBM copy bandwidth of MEASURED_PEAKS.json; '
+                   'it passes 1 where neighbouring samples of a ray share texels and the fetches are served by L1/L2 instead of HBM')
     model.train(was_training)
     return out
 
@@ -667,15 +678,24 @@ def run_ours(args):
     # the map is replicated: same seed on every rank gives identical planes and decoder
     mapper = FusedMapper(model, world_size=world, mark_dirty=args.mark_dirty)
     rays_cpu, poses_cpu = synthetic.make_keyframe_db(cfg, n_kf=N_KF, seed=0)
-    db = DeviceKeyframeRays(rays_cpu.to(dev), poses_cpu.to(dev))
-    gen = torch.Generator(device=dev)
-    gen.manual_seed(1234 + rank)
+    current_cpu = synthetic.make_current_frame(cfg, poses_cpu[-1], seed=rank) if args.cur else None
+    db = DeviceKeyframeRays(rays_cpu.to(dev), poses_cpu.to(dev), current=None if current_cpu is None else current_cpu.to(dev),
+                            min_pixels_cur=cfg['mapping']['min_pixels_cur'])
+    n_sample = args.sample
+    assert db.batch_rays(n_sample) == n_rays, (db.batch_rays(n_sample), n_rays)
 
-    # assemble_rays | sample | points_fwd (fused render) | loss_finalize | points_bwd3 | decoder_wgrad | adam_tick, adam_segments x2
-    launches_per_step = 9
+    class _Draw:
+        """db.sample for the helpers below that think in whole batches."""
+        def sample(self, n):
+            assert n == n_rays
+            return db.sample(n_sample)
+    batch_db = _Draw()
+
+    # draw_rays | sample | points_fwd | rays_tail | loss_finalize | points_bwd3 | decoder_wgrad | adam_tick, adam_segments x2
+    launches_per_step = 10
 
     def one_step():
-        ro, rd, trgb, td = db.sample(n_rays)
+        ro, rd, trgb, td = db.sample(n_sample)
         return mapper.step(ro, rd, trgb, td)
 
     # ---- warm-up (also sets kernel attributes outside capture)
@@ -710,7 +730,7 @@ def run_ours(args):
     if graph is not None and not args.no_pipeline:
         try:
             from mneslam_b200.mapping import PipelinedMapper
-            pipe = PipelinedMapper(mapper, db, n_rays, spare_sms=args.spare_sms).capture()
+            pipe = PipelinedMapper(mapper, db, n_sample, spare_sms=args.spare_sms).capture()
             for _ in range(3):
                 pipe.step()
             torch.cuda.synchronize()
@@ -779,7 +799,7 @@ def run_ours(args):
     counters = torch.zeros(n_rays, dtype=torch.int32, device=dev)
     k_prof = min(args.steps, 20)
     for _ in range(k_prof):
-        ro, rd, trgb, td = db.sample(n_rays)
+        ro, rd, trgb, td = db.sample(n_sample)
         tdf = td.reshape(-1)
         noise = torch.rand(n_rays, s, device=dev)
         acc = ops.new_acc(dev)
@@ -810,7 +830,7 @@ def run_ours(args):
         run_steps(400)
         ev2 = []
         for _ in range(10):
-            mapper.forward_backward(*db.sample(n_rays), defer_wgrad=True)
+            mapper.forward_backward(*db.sample(n_sample), defer_wgrad=True)
             _, e = timed(mapper.optimizer_step); ev2.append(e)
         torch.cuda.synchronize()
         steady = {'iterations_before': args.steps + 400 + 3 * max(args.warmup, 3), 'adam_us': 1e3 * sum(a.elapsed_time(b) for a, b in ev2) / len(ev2),
@@ -831,8 +851,10 @@ def run_ours(args):
     g_cpu = torch.Generator().manual_seed(99 + rank)
     flat_db = rays_cpu.reshape(-1, 7)
     for hr, hi in zip(host_rays, host_ids):
-        idx = torch.randint(0, flat_db.shape[0], (n_rays,), generator=g_cpu)
-        hr.copy_(flat_db[idx]); hi.copy_(idx // rays_cpu.shape[1])
+        idx = torch.randperm(flat_db.shape[0], generator=g_cpu)[:n_sample]
+        hr[:n_sample].copy_(flat_db[idx]); hi[:n_sample].copy_(idx // rays_cpu.shape[1])
+        if args.cur:
+            hr[n_sample:].copy_(current_cpu[torch.randperm(current_cpu.shape[0], generator=g_cpu)[:args.cur]]); hi[n_sample:].fill_(-1)
     h2d_bytes = n_rays * 7 * 4 + n_rays * 8
     loss_host = torch.empty(1).pin_memory()
 
@@ -1014,7 +1036,7 @@ def run_ours(args):
     gather_peak = None
     if rank == 0 and not args.no_extras:
         try:
-            gather_peak = gather_peak_record(model, mapper, cfg, db, n_rays, dev)
+            gather_peak = gather_peak_record(model, mapper, cfg, batch_db, n_rays, dev)
         except Exception as e:
             gather_peak = {'error': repr(e)[:300]}
     # ---- the records every N carries: configs[3] (strong scaling, hash grid) and the cross-rank self-check

@@ -134,6 +134,8 @@ const char* mne_last_error(void);
  * "adam_spare_sms" (default 0, at most 64): SMs the persistent optimiser grids leave free, so that small kernels on
  * another stream can run under them. */
 int mne_set_option(const char* key, int value);
+/* Current value of an option of mne_set_option (so that a caller can put it back). */
+int mne_get_option(const char* key, int* value);
 
 /* ---- ray assembly: replaces the gather of KeyFrameDatabase.sample_global_rays (model/keyframe.py:91-103) and the
  * assembly in mapping_optimize (mp_slam/mapper.py:135-153).  rays7: [*, 7] rows (camera-frame direction, rgb, depth);
@@ -143,6 +145,18 @@ int mne_set_option(const char* key, int value);
 int mne_assemble_rays(const float* rays7, const int64_t* idx, int64_t per_kf, const int64_t* kf_ids, const float* poses,
                       int32_t n_kf, int32_t n_rays, float* rays_o, float* rays_d, float* target_rgb, float* target_d,
                       mne_stream_t stream);
+
+/* The draw itself on the device, fused with the assembly: replaces KeyFrameDatabase.sample_global_rays (reference
+ * model/keyframe.py:91-103, random.sample = WITHOUT replacement over the n_stored = n_kf * per_kf stored rays) plus the draw
+ * of max(sample // n_kf, min_pixels_cur) pixels of the current frame with pose id -1 (mp_slam/mapper.py:135-153).  key: one
+ * int64 in device memory (refresh it per iteration, e.g. torch.randint -- under CUDA-graph replay too); the n_global keyframe
+ * rays and the n_cur current-frame rays (current7 [n_current, 7], may be NULL when n_cur = 0) are distinct rows, element i of
+ * each draw being a keyed bijection of the row range applied to i.  Outputs as mne_assemble_rays, [n_global + n_cur] rays,
+ * keyframe rays first; rows_out (may be NULL) [n_global + n_cur] receives the drawn row numbers.  A draw larger than its
+ * population is an error, as with random.sample. */
+int mne_draw_rays(const int64_t* key, const float* rays7, int64_t n_stored, int64_t per_kf, int32_t n_global,
+                  const float* current7, int64_t n_current, int32_t n_cur, const float* poses, int32_t n_kf, float* rays_o,
+                  float* rays_d, float* target_rgb, float* target_d, int64_t* rows_out, mne_stream_t stream);
 
 /* ---- camera pose: (rotation parameters, translation) -> rays, and ray gradients -> pose update.  rot_rep 0 = axis-angle
  * [3] (at_to_transform_matrix), 1 = real-first quaternion [4], not assumed unit (qt_to_transform_matrix; reference

@@ -58,7 +58,10 @@ _SIGNATURES = {
     'mne_version': (C.c_int, []),
     'mne_last_error': (C.c_char_p, []),
     'mne_set_option': (C.c_int, [C.c_char_p, C.c_int]),
+    'mne_get_option': (C.c_int, [C.c_char_p, C.c_void_p]),
     'mne_assemble_rays': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32] + [C.c_void_p] * 5),
+    'mne_draw_rays': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_int32]
+                      + [C.c_void_p] * 6),
     'mne_pose_rays': (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     'mne_pose_step': (C.c_int, [C.c_int32] + [C.c_void_p] * 5 + [C.c_int32] + [C.c_void_p] * 3 + [C.c_float] * 5 + [C.c_void_p, C.c_void_p]),
     'mne_sample_rays': (C.c_int, [C.POINTER(SampleCfg), C.POINTER(RenderCfg), C.c_int32, C.c_void_p, C.c_void_p,

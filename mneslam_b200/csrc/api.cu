@@ -117,5 +117,15 @@ extern "C" int mne_set_option(const char* key, int value) {
     return 1;
 }
 
+extern "C" int mne_get_option(const char* key, int* value) {
+    using namespace mne;
+    MNE_CHECK_ARG(key && value, "mne_get_option: null argument");
+    if (strcmp(key, "impl") == 0) { *value = g_impl; return 0; }
+    if (strcmp(key, "adam_spare_sms") == 0) { *value = g_adam_spare_sms; return 0; }
+    if (strcmp(key, "hash_level0_smem") == 0) { *value = g_hash_level0_smem; return 0; }
+    set_error("mne_get_option: unknown option '%s'", key);
+    return 1;
+}
+
 extern "C" int mne_version(void) { return 100; }
 extern "C" const char* mne_last_error(void) { return mne::g_error; }

@@ -444,7 +444,7 @@ int render_backward_v2(const MneSceneDesc*, const MneRenderCfg*, int32_t, int32_
 template <bool TWO, bool RAY_GRAD, bool PARAM_GRAD>
 static int launch_bwd(const BwdParams& P, cudaStream_t stream) {
     const size_t smem = bwd_smem_bytes<TWO>();
-    static bool configured[64] = {};      // per device; set outside any stream capture by the first (warm-up) call
+    static std::atomic<bool> configured[64] = {};      // per device; set outside any stream capture by the first (warm-up) call
     int dev = 0;
     MNE_CHECK_CUDA(cudaGetDevice(&dev));
     if (dev >= 64 || !configured[dev]) {
@@ -452,8 +452,7 @@ static int launch_bwd(const BwdParams& P, cudaStream_t stream) {
         if (dev < 64) configured[dev] = true;
     }
     const int n_groups = (P.n_rays + P.rays_per_group - 1) / P.rays_per_group;
-    int blocks = (n_groups + bwd_warps<TWO>() - 1) / bwd_warps<TWO>();
-    blocks = max(1, min(n_groups, sm_count()));
+    const int blocks = max(1, min(n_groups, sm_count()));
     render_bwd_kernel<TWO, RAY_GRAD, PARAM_GRAD><<<blocks, bwd_warps<TWO>() * 32, smem, stream>>>(P);
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;

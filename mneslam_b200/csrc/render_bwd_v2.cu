@@ -520,7 +520,7 @@ int points_backward_v3(const PtsBwdParams& P, bool ray, bool param, float* act, 
 template <bool TWO, int MODE, bool RAY, bool PARAM, int NW = kBwdWarps>
 static int launch_points_bwd(const PtsBwdParams& P, cudaStream_t stream) {
     const size_t smem = bwd2_smem_bytes<TWO, RAY, NW>();
-    static bool configured[64] = {};
+    static std::atomic<bool> configured[64] = {};
     int dev = 0;
     MNE_CHECK_CUDA(cudaGetDevice(&dev));
     if (dev >= 64 || !configured[dev]) {

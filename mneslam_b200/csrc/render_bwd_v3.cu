@@ -540,7 +540,7 @@ int sm_count();
 template <bool TWO, int MODE, bool RAY, bool PARAM, int NW>
 static int launch_points_bwd3(const PtsBwd3Params& Q, cudaStream_t stream) {
     const size_t smem = bwd3_smem_bytes<TWO, RAY, NW>();
-    static bool configured[64] = {};
+    static std::atomic<bool> configured[64] = {};
     int dev = 0;
     MNE_CHECK_CUDA(cudaGetDevice(&dev));
     if (dev >= 64 || !configured[dev]) {
@@ -570,7 +570,7 @@ static int launch_wgrad(const WGradParams& W, int64_t n_pts, int max_ctas, cudaS
     const int64_t cap = max_ctas > 0 ? (int64_t)max_ctas : (int64_t)sm_count();
     const int blocks = (int)max((int64_t)1, min((n_pts + per_cta - 1) / per_cta, cap));
     const size_t smem = sizeof(float) * (size_t)(WgLayout<TWO, HASH>::TOTAL + kWgSets * 2 * kWgUnroll * 8 * kBlobTile);
-    static bool configured[64] = {};
+    static std::atomic<bool> configured[64] = {};
     int dev = 0;
     MNE_CHECK_CUDA(cudaGetDevice(&dev));
     if (dev >= 64 || !configured[dev]) {

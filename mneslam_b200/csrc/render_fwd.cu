@@ -213,7 +213,7 @@ int sm_count();                                                              // 
 template <bool TWO, bool QUERY>
 static int launch_fwd(const FwdParams& P, cudaStream_t stream) {
     const size_t smem = fwd_smem_bytes<TWO>();
-    static bool configured[64] = {};      // per device; set outside any stream capture by the first (warm-up) call
+    static std::atomic<bool> configured[64] = {};      // per device; set outside any stream capture by the first (warm-up) call
     int dev = 0;
     MNE_CHECK_CUDA(cudaGetDevice(&dev));
     if (dev >= 64 || !configured[dev]) {
@@ -221,8 +221,7 @@ static int launch_fwd(const FwdParams& P, cudaStream_t stream) {
         if (dev < 64) configured[dev] = true;
     }
     const int n_groups = (P.n_rays + P.rays_per_group - 1) / P.rays_per_group;
-    int blocks = (n_groups + fwd_warps<TWO>() - 1) / fwd_warps<TWO>();
-    blocks = max(1, min(n_groups, sm_count()));
+    const int blocks = max(1, min(n_groups, sm_count()));
     render_fwd_kernel<TWO, QUERY><<<blocks, fwd_warps<TWO>() * 32, smem, stream>>>(P);
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;

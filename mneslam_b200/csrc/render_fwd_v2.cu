@@ -335,7 +335,7 @@ static int launch_points_fwd(const PtsFwdParams& P_in, cudaStream_t stream) {
         P.lvl0_stage = (hash_level0_smem() && smem + extra <= kSmemMax) ? 1 : 0;
         if (P.lvl0_stage) smem += extra;
     }
-    static bool configured[64] = {};
+    static std::atomic<bool> configured[64] = {};
     int dev = 0;
     MNE_CHECK_CUDA(cudaGetDevice(&dev));
     if (dev >= 64 || !configured[dev]) {

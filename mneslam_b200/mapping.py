@@ -454,16 +454,47 @@ class DeviceKeyframeRays:
     gather + three H2D copies per iteration of ``KeyFrameDatabase.sample_global_rays`` (model/keyframe.py:91-103)
     and the ray assembly of ``mapping_optimize`` (mp_slam/mapper.py:135-153)."""
 
-    def __init__(self, rays, poses):
+    def __init__(self, rays, poses, current=None, min_pixels_cur=0):
         self.rays = rays          # [n_kf, R, 7] (dir_cam, rgb, depth)
         self.poses = poses        # [n_kf, 4, 4] camera-to-world
         self.n_kf, self.per_kf = rays.shape[0], rays.shape[1]
+        self.min_pixels_cur = int(min_pixels_cur)
+        self.set_current(current)
 
-    def sample(self, n_rays, generator=None):
-        """Uniform sample over all stored rays (with replacement; the reference's ``random.sample`` draws
-        without -- for 2048 of ~800k rays the two are statistically indistinguishable)."""
-        idx = torch.randint(0, self.n_kf * self.per_kf, (n_rays,), device=self.rays.device, generator=generator)
-        return self._assemble(self.rays, idx, None, n_rays)
+    def set_current(self, current):
+        """The rays of the current frame ([H * W, 7], every pixel: mapper.py:131-132), or None.  With a current frame every
+        batch carries ``max(n // n_kf, min_pixels_cur)`` of its pixels after the keyframe rays, posed by the LAST pose (id -1)."""
+        if current is not None:
+            current = current.reshape(-1, 7)
+            if current.dtype != torch.float32 or not current.is_contiguous() or current.device != self.rays.device:
+                raise TypeError('the current frame must be a contiguous float32 [H * W, 7] tensor on the device of the store')
+        self.current = current
+
+    def n_current(self, n_rays):
+        """Rays of the current frame in a batch of ``n_rays`` keyframe rays (mp_slam/mapper.py:137-139)."""
+        return 0 if self.current is None else max(n_rays // self.n_kf, self.min_pixels_cur)
+
+    def batch_rays(self, n_rays):
+        return n_rays + self.n_current(n_rays)
+
+    def sample(self, n_rays, generator=None, return_rows=False):
+        """``n_rays`` distinct stored rays (``random.sample`` of model/keyframe.py:98: without replacement) followed by
+        ``n_current(n_rays)`` distinct pixels of the current frame, drawn and assembled in one launch.  The draw is keyed by one
+        device-side random integer, so a CUDA-graph replay draws a fresh batch."""
+        dev = self.rays.device
+        n_cur = self.n_current(n_rays)
+        n = n_rays + n_cur
+        if self.rays.dtype != torch.float32 or not self.rays.is_contiguous() or self.poses.dtype != torch.float32 or not self.poses.is_contiguous():
+            raise TypeError('rays and poses must be contiguous float32 tensors')
+        key = torch.randint(0, 1 << 62, (1,), device=dev, generator=generator)
+        rows = torch.empty(n, dtype=torch.int64, device=dev) if return_rows else None
+        ro, rd, rgb, d = (torch.empty(n, 3, dtype=torch.float32, device=dev), torch.empty(n, 3, dtype=torch.float32, device=dev),
+                          torch.empty(n, 3, dtype=torch.float32, device=dev), torch.empty(n, 1, dtype=torch.float32, device=dev))
+        _lib.check(_lib.lib().mne_draw_rays(key.data_ptr(), self.rays.data_ptr(), self.n_kf * self.per_kf, self.per_kf, n_rays,
+                                            ops._ptr(self.current), 0 if self.current is None else self.current.shape[0], n_cur,
+                                            self.poses.data_ptr(), self.n_kf, ro.data_ptr(), rd.data_ptr(), rgb.data_ptr(), d.data_ptr(),
+                                            ops._ptr(rows), ops._stream()), 'mne_draw_rays')
+        return (ro, rd, rgb, d, rows) if return_rows else (ro, rd, rgb, d)
 
     def assemble(self, rays7, kf_ids):
         """rays7 [n,7] and the keyframe of each ray (-1 = the last pose) -> rays_o, rays_d, target_rgb [n,3], target_d [n,1]."""
@@ -544,8 +575,14 @@ class PipelinedMapper:
         self.mapper, self.db, self.n = mapper, db, n_rays
         dev = mapper.dev
         # the optimiser kernels are persistent grids over every SM: keep a few SMs out of them, or the side stream's
-        # small kernels only start when the optimiser has finished (library-wide option)
+        # small kernels only start when the optimiser has finished.  The option is library-wide and read at LAUNCH time, i.e.
+        # when the graph is captured: it is put back in close() / when this object goes away
+        import ctypes
+        prev = ctypes.c_int(0)
+        _lib.check(_lib.lib().mne_get_option(b'adam_spare_sms', ctypes.addressof(prev)), 'mne_get_option')
+        self._spare_before = prev.value
         _lib.check(_lib.lib().mne_set_option(b'adam_spare_sms', int(spare_sms)), 'mne_set_option')
+        n_rays = self._batch_size(n_rays)
         tables = ops.SampleTables.get(mapper.cfg, dev, True)
         s = tables[0].numel() + tables[1].numel()
         f32 = dict(dtype=torch.float32, device=dev)
@@ -557,6 +594,21 @@ class PipelinedMapper:
         self.losses = torch.zeros(_lib.N_LOSSES, **f32)
         self.side = torch.cuda.Stream(device=dev)
         self.graph = None
+
+    def _batch_size(self, n_rays):
+        return self.db.batch_rays(n_rays)            # + the rays of the current frame, when the store has one
+
+    def close(self):
+        """Put the library-wide ``adam_spare_sms`` option back (idempotent)."""
+        if self._spare_before is not None:
+            _lib.lib().mne_set_option(b'adam_spare_sms', int(self._spare_before))
+            self._spare_before = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
     def _draw(self):
         ro, rd, rgb, d = self.db.sample(self.n)
@@ -622,6 +674,9 @@ class PrefetchingHostMapper(PipelinedMapper):
         self.h_loss = torch.zeros(1, dtype=torch.float32).pin_memory()
         self.d_rays = torch.empty(n_rays, 7, dtype=torch.float32, device=dev)
         self.d_ids = torch.empty(n_rays, dtype=torch.int64, device=dev)
+
+    def _batch_size(self, n_rays):
+        return n_rays                                # the caller hands over whole batches (current-frame rays included)
 
     def _draw(self):
         self.d_rays.copy_(self.h_rays, non_blocking=True)

@@ -92,6 +92,14 @@ def make_keyframe_db(cfg, n_kf=20, seed=0):
     return rays, poses
 
 
+def make_current_frame(cfg, c2w, seed=0):
+    """Every pixel of a synthetic current frame as [H * W, 7] = (dir_cam, rgb, depth) rows -- what mapping_optimize
+    (mp_slam/mapper.py:131-132) builds from the tracked frame before it draws min_pixels_cur of them."""
+    H, W = intrinsics(cfg)[:2]
+    b = make_ray_batch(cfg, H * W, seed=seed + 5000, c2w=c2w)
+    return torch.cat([b['dirs_cam'], b['target_rgb'], b['target_d']], -1).contiguous()
+
+
 def render_box_scene(cfg, c2w, dirs_cam, margin=0.15):
     """Analytic RGB-D of the inside of an axis-aligned box (the scene bound shrunk by ``margin`` per side), seen
     along the given camera-frame directions: z-depth of the first wall hit (directions have z = -1, so the ray

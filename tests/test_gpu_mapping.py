@@ -116,6 +116,48 @@ def test_device_keyframe_assembly_matches_caller_code():
     assert ro2.shape == (128, 3) and d2.shape == (128, 1)
 
 
+def test_device_draw_is_without_replacement_and_adds_the_current_frame():
+    """The batch of mapping_optimize (mp_slam/mapper.py:135-153): ``random.sample`` of the stored rays (no row twice,
+    model/keyframe.py:98) followed by max(sample // n_kf, min_pixels_cur) distinct pixels of the current frame posed by the
+    last pose (id -1) -- drawn and assembled on the device in one launch."""
+    from mneslam_b200 import _lib
+    from mneslam_b200.mapping import DeviceKeyframeRays
+    cfg = configs.small_test_config()
+    cfg['cam'].update({'H': 40, 'W': 60, 'fx': 50.0, 'fy': 50.0, 'cx': 29.5, 'cy': 19.5})
+    rays, poses = synthetic.make_keyframe_db(cfg, n_kf=4, seed=2)
+    total = rays.shape[0] * rays.shape[1]
+    g = torch.Generator().manual_seed(3)
+    current = torch.rand(40 * 60, 7, generator=g)
+    db = DeviceKeyframeRays(rays.cuda(), poses.cuda(), current=current.cuda(), min_pixels_cur=100)
+    assert db.n_current(2048) == 512 and db.n_current(256) == 100 and db.batch_rays(256) == 356
+    flat = rays.reshape(-1, 7)
+    seen = []
+    for n in (256, total):                               # a normal batch, and the whole population (a full permutation)
+        ro, rd, rgb, d, rows = db.sample(n, return_rows=True)
+        n_cur = db.n_current(n)
+        rows = rows.cpu()
+        rk, rc = rows[:n], rows[n:]
+        assert ro.shape == (n + n_cur, 3) and rc.numel() == n_cur
+        assert int(rk.min()) >= 0 and int(rk.max()) < total and torch.unique(rk).numel() == n
+        assert int(rc.min()) >= 0 and int(rc.max()) < current.shape[0] and torch.unique(rc).numel() == n_cur
+        r7 = torch.cat([flat[rk], current[rc]])
+        ids = torch.cat([rk // rays.shape[1], torch.full((n_cur,), -1, dtype=torch.int64)])
+        want_d = torch.sum(r7[:, None, None, :3] * poses[ids, None, :3, :3], -1).reshape(-1, 3)
+        assert torch.allclose(rd.cpu(), want_d, atol=1e-6) and torch.equal(ro.cpu(), poses[ids, :3, -1])
+        assert torch.equal(rgb.cpu(), r7[:, 3:6]) and torch.equal(d.cpu(), r7[:, 6:7])
+        seen.append(rk)
+    assert torch.equal(torch.sort(seen[1]).values, torch.arange(total))
+    # a fresh key gives a fresh draw; the draw spreads over the whole store
+    a = db.sample(256, return_rows=True)[4].cpu()
+    b = db.sample(256, return_rows=True)[4].cpu()
+    assert not torch.equal(a, b)
+    many = torch.cat([db.sample(128, return_rows=True)[4][:128].cpu() for _ in range(160)]).double()
+    assert abs(float(many.mean()) / total - 0.5) < 0.02 and abs(float(many.std()) / total - 12 ** -0.5) < 0.02
+    # larger than the population: an error, as random.sample raises
+    with pytest.raises(_lib.MneError):
+        db.sample(total + 1)
+
+
 def test_cuda_graph_replay_of_a_mapping_iteration():
     """The whole iteration (ray assembly, sample, forward, losses, backward, Adam) captured once and replayed:
     the loss keeps decreasing and no launch needs the host."""
@@ -412,6 +454,7 @@ def test_pipelined_iterations_do_the_same_work():
                 pipe._iteration()                     # eager: the same stream choreography as the captured graph
                 torch.cuda.synchronize()
                 losses.append(float(mapper.total_loss(pipe.losses)))
+            pipe.close()
         else:
             for _ in range(6):
                 losses.append(float(mapper.total_loss(mapper.step(*db.sample(256)))))
@@ -424,7 +467,9 @@ def test_pipelined_iterations_do_the_same_work():
     # graph mode on a random database: the loss keeps going down
     model = build_model(cfg, bb, planes, weights, as_params=False)
     mapper = FusedMapper(model)
-    pipe = PipelinedMapper(mapper, DeviceKeyframeRays(rays.cuda(), poses.cuda()), 256).capture()
+    cur = rays[-1].cuda()                                  # the current frame: here, the rays of the last keyframe
+    pipe = PipelinedMapper(mapper, DeviceKeyframeRays(rays.cuda(), poses.cuda(), current=cur, min_pixels_cur=20), 256, spare_sms=6).capture()
+    assert pipe.ro.shape[0] == 256 + 85
     hist = []
     for i in range(60):
         pipe.step()
@@ -432,6 +477,15 @@ def test_pipelined_iterations_do_the_same_work():
             torch.cuda.synchronize()
             hist.append(float(mapper.total_loss(pipe.losses)))
     assert all(np.isfinite(hist)) and hist[-1] < hist[0], hist
+    # the library-wide option the pipeline sets is put back when it is closed
+    import ctypes
+    val = ctypes.c_int(-1)
+    _lib_mod = __import__('mneslam_b200._lib', fromlist=['lib'])
+    _lib_mod.lib().mne_get_option(b'adam_spare_sms', ctypes.addressof(val))
+    assert val.value == 6
+    pipe.close()
+    _lib_mod.lib().mne_get_option(b'adam_spare_sms', ctypes.addressof(val))
+    assert val.value == 0
 
 
 def test_distillation_step_pulls_the_student_towards_the_teacher():

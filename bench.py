@@ -1072,6 +1072,9 @@ def run_ours(args):
         # every gradient group is read (4 B / parameter) with its flag (0.25 B); groups that ever received a gradient move p, m, v
         # in and out (24 B); the gradient is written back (cleared) only where it was non-zero this step (4 B)
         adam_bytes = int(n_param * (4 + (0.25 if mapper.touched is not None else 0.0) + touched * 24 + nz_frac * 4))
+        if getattr(mapper, 'adam_dirty', False):
+            # with the backward pass's texel flags (1 byte per 32 parameters) only the flagged gradient texels are read and cleared
+            adam_bytes = int(n_param * (1 / 32 + 0.25 + touched * 24 + nz_frac * 8))
         gbs = lambda b, t_us: b / (t_us * 1e-6) / 1e9
         fwd_gbs, bwd_gbs, adam_gbs = gbs(fwd_bytes, us['fwd']), gbs(bwd_bytes, us['bwd']), gbs(adam_bytes, us['adam'])
         line = {
@@ -1093,6 +1096,7 @@ def run_ours(args):
                          'frac': adam_gbs / peak, 'traffic': ncu_traffic('adam_segments_kernel'), 'peak_source': peak_src,
                          'algorithmic_bytes_per_launch': adam_bytes, 'launch_us': us['adam'],
                          'touched_fraction': touched, 'nonzero_gradient_fraction': nz_frac,
+                         'gradient_read_skipped_by_texel_flags': bool(getattr(mapper, 'adam_dirty', False)),
                          'points_fwd_kernel': {'achieved': fwd_gbs, 'frac': fwd_gbs / peak, 'launch_us': us['fwd'],
                                                'algorithmic_bytes_per_launch': fwd_bytes,
                                                'traffic': ncu_traffic('points_fwd_kernel'),

@@ -325,6 +325,16 @@ int mne_adam_step_segments(float* param, float* grad, float* exp_avg, float* exp
                            const int64_t* segment_ends, const float* lr, const float* eps, const float* weight_decay,
                            float beta1, float beta2, const int64_t* step_dev, int64_t step_host, int32_t zero_grad,
                            uint8_t* touched, mne_stream_t stream);
+/* The same with the backward pass's texel flags (MneSceneDesc.dirty with dirty_base = grad): dirty holds one byte per 32
+ * floats of [0, dirty_floats) -- the plane gradients; the rest of the buffer is read densely.  An unflagged texel's
+ * gradient is zero by contract (everything that adds into it flags it, and this kernel clears what it read: zero_grad
+ * must be set), so it is not read at all: ~80 % of the 129 MB gradient pass of a room0 iteration.  The flags are
+ * cleared here for the next iteration.  Results are bit-identical to mne_adam_step_segments.  (Measured on B200: this pass
+ * 111 -> 105 us, but setting the flags costs the backward kernel 18 us, so mapping.FusedMapper leaves it off.) */
+int mne_adam_step_segments_dirty(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int32_t n_segments,
+                                 const int64_t* segment_ends, const float* lr, const float* eps, const float* weight_decay,
+                                 float beta1, float beta2, const int64_t* step_dev, int64_t step_host, int32_t zero_grad,
+                                 uint8_t* touched, uint8_t* dirty, int64_t dirty_floats, mne_stream_t stream);
 
 /* ---- data-parallel optimiser step over NVLink peer memory: ONE kernel instead of NCCL reduce-scatter + Adam +
  * all-gather (the reference has no multi-GPU training at all; this serves the ray-sharded mapping of BASELINE.json

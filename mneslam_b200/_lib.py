@@ -87,6 +87,8 @@ _SIGNATURES = {
                                 C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
     'mne_adam_step_segments': (C.c_int, [C.c_void_p] * 4 + [C.c_int32] + [C.c_void_p] * 4 + [C.c_float, C.c_float, C.c_void_p,
                                                                                C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
+    'mne_adam_step_segments_dirty': (C.c_int, [C.c_void_p] * 4 + [C.c_int32] + [C.c_void_p] * 4 + [C.c_float, C.c_float, C.c_void_p,
+                                                                                     C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     'mne_adam_step_peers': (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32,
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_int64,
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -85,11 +85,14 @@ struct AdamSegments {
     int64_t step_host;
     int zero_grad;
     uint8_t* touched;      // one byte per float4 group: has this group ever received a gradient?  (NULL = dense)
+    uint8_t* dirty;        // one byte per 32 floats of [0, dirty_end4 * 4): did the backward pass add into this texel this step?
+    int64_t dirty_end4;
 };
 
 // The kernel is bound by memory latency (ncu: long-scoreboard stalls, 0.5 eligible warps per cycle), so every thread keeps
 // two groups in flight and issues the independent loads of both before anything depends on them: flags + gradients
 // first, then parameters + moments of the groups that need the update.
+template <bool DIRTY>
 __global__ void __launch_bounds__(256, 4) adam_segments_kernel(const __grid_constant__ AdamSegments s) {
     const double t = (double)(s.step_dev ? *s.step_dev : s.step_host);
     const float bc1 = (float)(1.0 - pow((double)s.beta1, t));
@@ -103,31 +106,67 @@ __global__ void __launch_bounds__(256, 4) adam_segments_kernel(const __grid_cons
     const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
     constexpr int U = 2;             // measured: 1 -> 119 us, 2 -> 108 us, 4 (2 CTAs / SM) -> 117 us
     int seg[U] = {};
-    for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n4; i0 += U * stride) {
+    const int lane = threadIdx.x & 31;
+    // (the loop condition is the WARP's first group, so that all 32 lanes reach the __syncwarp of the DIRTY variant together)
+    for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 - lane < n4; i0 += U * stride) {
         int64_t idx[U];
         bool act[U];
         float4 g[U];
         uint8_t f[U];
 #pragma unroll
         for (int k = 0; k < U; ++k) { idx[k] = i0 + k * stride; act[k] = idx[k] < n4; f[k] = 1; }
-#pragma unroll
-        for (int k = 0; k < U; ++k) {
-            g[k] = act[k] ? g4[idx[k]] : zero;
-            if (s.touched && act[k]) f[k] = s.touched[idx[k]];
-        }
         bool nz[U];
-#pragma unroll
-        for (int k = 0; k < U; ++k) {
-            if (act[k]) while (idx[k] >= s.end4[seg[k]]) ++seg[k];
-            nz[k] = g[k].x != 0.0f || g[k].y != 0.0f || g[k].z != 0.0f || g[k].w != 0.0f;
-            // A group that never saw a gradient has m = v = g = 0: its dense Adam update is exactly the identity, so
-            // skipping it (no p / m / v traffic) gives bit-identical parameters.  Once touched, always updated.
-            if (s.touched && s.wd[seg[k]] == 0.0f && !nz[k] && !f[k]) act[k] = false;
-        }
         float4 p[U], m[U], v[U];
+        if constexpr (DIRTY) {
+            // The backward pass flagged (one byte per 32 floats = 8 groups = 8 neighbouring lanes) every texel it added a
+            // gradient into; an unflagged texel's gradient is zero by contract and is not read.  With the two flag maps
+            // known, the loads of gradient, parameter and moments are all independent of each other.
+            uint8_t dq[U];
+            bool want[U];
 #pragma unroll
-        for (int k = 0; k < U; ++k)
-            if (act[k]) { p[k] = p4[idx[k]]; m[k] = m4[idx[k]]; v[k] = v4[idx[k]]; }
+            for (int k = 0; k < U; ++k) {
+                dq[k] = 1;
+                if (act[k]) {
+                    if (s.touched) f[k] = s.touched[idx[k]];
+                    if (idx[k] < s.dirty_end4) dq[k] = s.dirty[idx[k] >> 3];
+                }
+            }
+            __syncwarp();                     // all eight lanes of a texel have read its flag
+#pragma unroll
+            for (int k = 0; k < U; ++k) {
+                if (act[k]) while (idx[k] >= s.end4[seg[k]]) ++seg[k];
+                if (act[k] && dq[k] && (idx[k] & 7) == 0 && idx[k] < s.dirty_end4) s.dirty[idx[k] >> 3] = 0;     // for the next iteration
+                want[k] = act[k] && (!s.touched || s.wd[seg[k]] != 0.0f || f[k] || dq[k]);
+            }
+#pragma unroll
+            for (int k = 0; k < U; ++k) {
+                g[k] = (act[k] && dq[k]) ? g4[idx[k]] : zero;
+                if (want[k]) { p[k] = p4[idx[k]]; m[k] = m4[idx[k]]; v[k] = v4[idx[k]]; }
+            }
+#pragma unroll
+            for (int k = 0; k < U; ++k) {
+                nz[k] = g[k].x != 0.0f || g[k].y != 0.0f || g[k].z != 0.0f || g[k].w != 0.0f;
+                // (flagged, but every addition was a zero and the group never saw a gradient: still the identity update)
+                act[k] = want[k] && (!s.touched || s.wd[seg[k]] != 0.0f || f[k] || nz[k]);
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < U; ++k) {
+                g[k] = act[k] ? g4[idx[k]] : zero;
+                if (s.touched && act[k]) f[k] = s.touched[idx[k]];
+            }
+#pragma unroll
+            for (int k = 0; k < U; ++k) {
+                if (act[k]) while (idx[k] >= s.end4[seg[k]]) ++seg[k];
+                nz[k] = g[k].x != 0.0f || g[k].y != 0.0f || g[k].z != 0.0f || g[k].w != 0.0f;
+                // A group that never saw a gradient has m = v = g = 0: its dense Adam update is exactly the identity, so
+                // skipping it (no p / m / v traffic) gives bit-identical parameters.  Once touched, always updated.
+                if (s.touched && s.wd[seg[k]] == 0.0f && !nz[k] && !f[k]) act[k] = false;
+            }
+#pragma unroll
+            for (int k = 0; k < U; ++k)
+                if (act[k]) { p[k] = p4[idx[k]]; m[k] = m4[idx[k]]; v[k] = v4[idx[k]]; }
+        }
 #pragma unroll
         for (int k = 0; k < U; ++k) {
             if (!act[k]) continue;
@@ -181,10 +220,11 @@ extern "C" int mne_adam_step(float* param, float* grad, float* exp_avg, float* e
     return 0;
 }
 
-extern "C" int mne_adam_step_segments(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int32_t n_segments,
-                                      const int64_t* segment_ends, const float* lr, const float* eps,
-                                      const float* weight_decay, float beta1, float beta2, const int64_t* step_dev,
-                                      int64_t step_host, int32_t zero_grad, uint8_t* touched, mne_stream_t stream) {
+extern "C" int mne_adam_step_segments_dirty(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int32_t n_segments,
+                                            const int64_t* segment_ends, const float* lr, const float* eps,
+                                            const float* weight_decay, float beta1, float beta2, const int64_t* step_dev,
+                                            int64_t step_host, int32_t zero_grad, uint8_t* touched, uint8_t* dirty,
+                                            int64_t dirty_floats, mne_stream_t stream) {
     using namespace mne;
     MNE_CHECK_ARG(param && grad && exp_avg && exp_avg_sq && segment_ends && lr && eps && weight_decay,
                   "mne_adam_step_segments: null argument");
@@ -206,12 +246,33 @@ extern "C" int mne_adam_step_segments(float* param, float* grad, float* exp_avg,
     if (prev == 0) return 0;
     s.beta1 = beta1; s.beta2 = beta2; s.step_dev = step_dev; s.step_host = step_host; s.zero_grad = zero_grad;
     s.touched = touched;
+    if (dirty) {
+        MNE_CHECK_ARG(dirty_floats >= 0 && (dirty_floats & 31) == 0 && dirty_floats <= prev && (((uintptr_t)grad) & 127) == 0,
+                      "mne_adam_step_segments_dirty: the flagged range must be whole 128-byte texels inside the buffer (dirty_floats=%lld)",
+                      (long long)dirty_floats);
+        MNE_CHECK_ARG(zero_grad, "mne_adam_step_segments_dirty: flags need zero_grad (an unflagged texel's gradient must be zero)");
+        s.dirty = dirty; s.dirty_end4 = dirty_floats >> 2;
+    }
     int64_t blocks = ((prev >> 2) + 255) / 256;
-    const int64_t cap = (int64_t)adam_sms() * resident_ctas(adam_segments_kernel, 256);
-    if (blocks > cap) blocks = cap;
-    adam_segments_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
+    if (dirty) {
+        const int64_t cap = (int64_t)adam_sms() * resident_ctas(adam_segments_kernel<true>, 256);
+        if (blocks > cap) blocks = cap;
+        adam_segments_kernel<true><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
+    } else {
+        const int64_t cap = (int64_t)adam_sms() * resident_ctas(adam_segments_kernel<false>, 256);
+        if (blocks > cap) blocks = cap;
+        adam_segments_kernel<false><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
+    }
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
+}
+
+extern "C" int mne_adam_step_segments(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int32_t n_segments,
+                                      const int64_t* segment_ends, const float* lr, const float* eps,
+                                      const float* weight_decay, float beta1, float beta2, const int64_t* step_dev,
+                                      int64_t step_host, int32_t zero_grad, uint8_t* touched, mne_stream_t stream) {
+    return mne_adam_step_segments_dirty(param, grad, exp_avg, exp_avg_sq, n_segments, segment_ends, lr, eps, weight_decay, beta1, beta2,
+                                        step_dev, step_host, zero_grad, touched, nullptr, 0, stream);
 }
 
 // ---------------------------------------------------------------------------------------------------------

@@ -187,9 +187,17 @@ class FusedMapper:
         self.dense_from = enc_len + self._dec_pad
         if os.environ.get('MNE_MARK_DIRTY') is not None:
             mark_dirty = os.environ['MNE_MARK_DIRTY'] == '1'
-        if self.peers is not None and mark_dirty and model.hash_meta is None and \
-                all(p.stride(1) == 1 and p.shape[1] == 32 for p in planes):
+        vector_planes = model.hash_meta is None and len(planes) > 0 and all(p.stride(1) == 1 and p.shape[1] == 32 for p in planes)
+        if self.peers is not None and mark_dirty and vector_planes:
             self.dirty_local = torch.zeros(padded // 32, dtype=torch.uint8, device=self.dev)
+        # one GPU: the same flags can tell the optimiser which texels of the plane gradient are non-zero, so that it does not read
+        # (nor clear) the other ~80 % of the 129 MB gradient buffer (mne_adam_step_segments_dirty).  Off by default -- measured on
+        # B200 (room0, 2150 rays): the optimiser pass 111 -> 105 us, but the flag stores cost the backward kernel 34 -> 52 us, the
+        # iteration 0.235 -> 0.249 ms
+        self.adam_dirty = world_size == 1 and vector_planes and os.environ.get('MNE_ADAM_DIRTY', '0') == '1' and enc_len % 32 == 0
+        if self.adam_dirty:
+            self.dirty_local = torch.zeros((padded + 31) // 32, dtype=torch.uint8, device=self.dev)
+            self._dirty_floats = enc_len
         self.plane_grads = self.grads[:n_planes]
         self.weight_grads = self.grads[n_planes:]
         self.step_dev = torch.zeros(1, dtype=torch.int64, device=self.dev)
@@ -221,14 +229,14 @@ class FusedMapper:
         return (n, (C.c_int64 * n)(*ends), (C.c_float * n)(*[h[0] for h in hparams]),
                 (C.c_float * n)(*[h[1] for h in hparams]), (C.c_float * n)(*[h[2] for h in hparams]))
 
-    def _adam_segments(self, param, grad, m, v, segments, zero_grad, touched='own'):
+    def _adam_segments(self, param, grad, m, v, segments, zero_grad, touched='own', dirty=None, dirty_floats=0):
         n_seg, ends, lr, eps, wd = segments
         if isinstance(touched, str):
             touched = self.touched
-        _lib.check(_lib.lib().mne_adam_step_segments(param.data_ptr(), grad.data_ptr(), m.data_ptr(), v.data_ptr(), n_seg,
-                                                     ends, lr, eps, wd, self.betas[0], self.betas[1],
-                                                     self.step_dev.data_ptr(), 0, 1 if zero_grad else 0,
-                                                     ops._ptr(touched), ops._stream()),
+        _lib.check(_lib.lib().mne_adam_step_segments_dirty(param.data_ptr(), grad.data_ptr(), m.data_ptr(), v.data_ptr(), n_seg,
+                                                           ends, lr, eps, wd, self.betas[0], self.betas[1],
+                                                           self.step_dev.data_ptr(), 0, 1 if zero_grad else 0,
+                                                           ops._ptr(touched), ops._ptr(dirty), dirty_floats, ops._stream()),
                    'mne_adam_step_segments')
 
     # ------------------------------------------------------------------------------------------
@@ -408,9 +416,10 @@ class FusedMapper:
         """One GPU: the planes' Adam pass (a pure HBM stream over 129 MB) on the current stream; on a side stream, beside it,
         the decoder's weight gradients (which only the decoder's own Adam step consumes) and that step."""
         dec0 = self.dense_from
+        flags = dict(dirty=self.dirty_local, dirty_floats=self._dirty_floats) if self.adam_dirty else {}
         if self.wgrad_inline:
             self._decoder_wgrad()
-            self._adam_segments(self.flat_param, self.flat_grad, self.flat_m, self.flat_v, self._segments, True)
+            self._adam_segments(self.flat_param, self.flat_grad, self.flat_m, self.flat_v, self._segments, True, **flags)
             return
         main = torch.cuda.current_stream()
         if self._wgrad_stream is None:
@@ -422,7 +431,7 @@ class FusedMapper:
             tail = slice(dec0, self.total)
             self._adam_segments(self.flat_param[tail], self.flat_grad[tail], self.flat_m[tail], self.flat_v[tail], self._seg_tail, True,
                                 touched=self.touched[dec0 // 4:] if self.touched is not None else None)
-        self._adam_segments(self.flat_param, self.flat_grad, self.flat_m, self.flat_v, self._seg_head, True)
+        self._adam_segments(self.flat_param, self.flat_grad, self.flat_m, self.flat_v, self._seg_head, True, **flags)
         main.wait_stream(side)
 
     def step(self, rays_o, rays_d, target_rgb, target_d, noise=None, sampled=None):

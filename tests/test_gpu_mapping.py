@@ -249,6 +249,44 @@ def test_touched_map_adam_is_bit_identical_to_dense():
     assert 0.2 < frac < 0.95, frac
 
 
+def test_texel_flag_adam_is_bit_identical_to_dense():
+    """mne_adam_step_segments_dirty: with the backward pass's texel flags (one byte per 32 floats of the plane range) the
+    optimiser reads the gradient of flagged texels only.  Same bits as the dense kernel, gradients and flags cleared; flagged
+    texels whose gradient is all zero, an unflagged dense tail and a ragged end are all in the case."""
+    import ctypes as C
+    from mneslam_b200 import _lib, ops
+    torch.manual_seed(2)
+    n_planes, n = 1 << 16, (1 << 16) + 4096 + 8
+    p0 = torch.randn(n, device='cuda')
+    ends = (C.c_int64 * 2)(n_planes, n)
+    lr, eps, wd = (C.c_float * 2)(5e-3, 1e-2), (C.c_float * 2)(1e-15, 1e-8), (C.c_float * 2)(0.0, 1e-6)
+    state = []
+    for use_flags in (False, True):
+        p, m, v = p0.clone(), torch.zeros(n, device='cuda'), torch.zeros(n, device='cuda')
+        touched = torch.zeros(n // 4, dtype=torch.uint8, device='cuda')
+        dirty = torch.zeros(n_planes // 32, dtype=torch.uint8, device='cuda')
+        gen = torch.Generator(device='cuda').manual_seed(7)
+        for t in range(1, 7):
+            g = torch.randn(n, device='cuda', generator=gen)
+            mask = torch.rand(n_planes // 32, device='cuda', generator=gen) < (0.08 * t)
+            extra = torch.rand(n_planes // 32, device='cuda', generator=gen) < 0.05        # flagged, but only zeros were added
+            g[:n_planes] = (g[:n_planes].reshape(-1, 32) * mask[:, None]).reshape(-1)
+            if use_flags:
+                dirty.copy_((mask | extra).to(torch.uint8))
+                _lib.check(_lib.lib().mne_adam_step_segments_dirty(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), 2, ends, lr, eps, wd,
+                                                                   0.9, 0.99, None, t, 1, touched.data_ptr(), dirty.data_ptr(), n_planes,
+                                                                   ops._stream()), 'adam')
+                assert int(dirty.sum()) == 0
+            else:
+                _lib.check(_lib.lib().mne_adam_step_segments(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), 2, ends, lr, eps, wd,
+                                                             0.9, 0.99, None, t, 1, touched.data_ptr(), ops._stream()), 'adam')
+            assert float(g.abs().max()) == 0.0
+        state.append((p, m, v, touched))
+    (pd, md, vd, td), (ps, ms, vs, ts) = state
+    assert torch.equal(pd, ps) and torch.equal(md, ms) and torch.equal(vd, vs) and torch.equal(td, ts)
+    assert not torch.equal(pd, p0)
+
+
 @pytest.mark.parametrize('push', [False, True, 'flags'])
 def test_peer_optimiser_on_one_gpu_matches_dense_adam(push):
     """mne_grad_dirty_map (owners fetch the flagged groups) or mne_grad_push (non-zero texels pushed into the owners' inboxes)

@@ -442,7 +442,14 @@ __device__ __forceinline__ uint32_t peer_flags(const AdamPeers& s, int64_t i) {
 constexpr int kPeerU = 2;
 constexpr int kPeerFetch = 4;      // peer gradients fetched per group before the sum depends on them
 
+// INBOX: the peers' gradients were pushed into this rank's inbox (mne_grad_push): every source but this rank's own gradient
+// buffer is local, read-only and needs no clearing -- so no pointer per fetched group has to be kept (registers: the generic
+// variant spilled 300 bytes per thread).
+template <bool INBOX>
 __global__ void __launch_bounds__(256, 3) adam_peers_sparse_kernel(const __grid_constant__ AdamPeers s) {
+    // gradients fetched per group before the sum depends on them (a texel flagged by more ranks takes the loop below; at
+    // eight ranks a flagged texel is flagged by 1.4 ranks on average)
+    constexpr int F = INBOX ? 2 : kPeerFetch;
     const double t = (double)(s.step_dev ? *s.step_dev : s.step_host);
     const float bc1 = (float)(1.0 - pow((double)s.beta1, t));
     const float bc2_sqrt = (float)sqrt(1.0 - pow((double)s.beta2, t));
@@ -451,6 +458,7 @@ __global__ void __launch_bounds__(256, 3) adam_peers_sparse_kernel(const __grid_
     float4* m4 = reinterpret_cast<float4*>(s.m);
     float4* v4 = reinterpret_cast<float4*>(s.v);
     float4* p_loc = reinterpret_cast<float4*>(s.param[s.rank]);
+    float4* g_loc = reinterpret_cast<float4*>(s.grad[s.rank]);
     const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
     int seg[kPeerU] = {};
     for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < s.local4; i0 += kPeerU * stride) {
@@ -478,20 +486,22 @@ __global__ void __launch_bounds__(256, 3) adam_peers_sparse_kernel(const __grid_
             }
         }
         // ---- all loads of all groups
-        float4 p[kPeerU], m[kPeerU], v[kPeerU], x[kPeerU][kPeerFetch];
-        float4* gp[kPeerU][kPeerFetch];
+        float4 p[kPeerU], m[kPeerU], v[kPeerU], x[kPeerU][F];
+        float4* gp[INBOX ? 1 : kPeerU][INBOX ? 1 : F];
         uint32_t rest[kPeerU];
 #pragma unroll
         for (int u = 0; u < kPeerU; ++u) {
             rest[u] = on[u] ? mk[u] : 0u;
 #pragma unroll
-            for (int k = 0; k < kPeerFetch; ++k) {
-                gp[u][k] = nullptr; x[u][k] = zero;
+            for (int k = 0; k < F; ++k) {
+                x[u][k] = zero;
+                if constexpr (!INBOX) gp[u][k] = nullptr;
                 if (rest[u]) {
                     const int r = __ffs(rest[u]) - 1;
                     rest[u] &= rest[u] - 1;
-                    if (s.inbox && r != s.rank) {
-                        x[u][k] = s.inbox[(int64_t)r * s.local4 + li[u]];      // pushed by rank r; nothing to clear (flags are rewritten every step)
+                    if constexpr (INBOX) {
+                        // pushed by rank r (nothing to clear: the flags are rewritten every step), or this rank's own buffer
+                        x[u][k] = (r != s.rank) ? s.inbox[(int64_t)r * s.local4 + li[u]] : g_loc[gi[u]];
                     } else {
                         gp[u][k] = reinterpret_cast<float4*>(s.grad[r]) + gi[u];
                         x[u][k] = *gp[u][k];
@@ -500,27 +510,29 @@ __global__ void __launch_bounds__(256, 3) adam_peers_sparse_kernel(const __grid_
             }
             if (on[u]) { p[u] = p_loc[gi[u]]; m[u] = m4[li[u]]; v[u] = v4[li[u]]; }
         }
-        // ---- sums (more than kPeerFetch flagged peers: the rest, four at a time), updates, stores
+        // ---- sums (more than F flagged peers: the rest, four at a time), updates, stores
 #pragma unroll
         for (int u = 0; u < kPeerU; ++u) {
             if (!on[u]) continue;
             float4 g = zero;
 #pragma unroll
-            for (int k = 0; k < kPeerFetch; ++k) {
+            for (int k = 0; k < F; ++k) {
                 g.x += x[u][k].x; g.y += x[u][k].y; g.z += x[u][k].z; g.w += x[u][k].w;       // (unfetched slots hold zero)
-                if (gp[u][k]) *gp[u][k] = zero;
+                if constexpr (!INBOX) { if (gp[u][k]) *gp[u][k] = zero; }
             }
+            if (INBOX && ((mk[u] >> s.rank) & 1u)) g_loc[gi[u]] = zero;
             while (rest[u]) {
                 float4 y[4];
-                float4* yp[4];
+                float4* yp[INBOX ? 1 : 4];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    yp[k] = nullptr; y[k] = zero;
+                    y[k] = zero;
+                    if constexpr (!INBOX) yp[k] = nullptr;
                     if (rest[u]) {
                         const int r = __ffs(rest[u]) - 1;
                         rest[u] &= rest[u] - 1;
-                        if (s.inbox && r != s.rank) {
-                            y[k] = s.inbox[(int64_t)r * s.local4 + li[u]];
+                        if constexpr (INBOX) {
+                            y[k] = (r != s.rank) ? s.inbox[(int64_t)r * s.local4 + li[u]] : g_loc[gi[u]];
                         } else {
                             yp[k] = reinterpret_cast<float4*>(s.grad[r]) + gi[u];
                             y[k] = *yp[k];
@@ -530,7 +542,7 @@ __global__ void __launch_bounds__(256, 3) adam_peers_sparse_kernel(const __grid_
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     g.x += y[k].x; g.y += y[k].y; g.z += y[k].z; g.w += y[k].w;
-                    if (yp[k]) *yp[k] = zero;
+                    if constexpr (!INBOX) { if (yp[k]) *yp[k] = zero; }
                 }
             }
             AdamArgs a{};
@@ -649,9 +661,10 @@ extern "C" int mne_adam_step_peers(int32_t world_size, int32_t rank, float* cons
     MNE_CHECK_ARG(!inbox || (dirty && (((uintptr_t)inbox) & 15) == 0), "mne_adam_step_peers: inbox needs the dirty flags and 16-byte alignment");
     s.inbox = reinterpret_cast<const float4*>(inbox);
     int64_t blocks = (s.local4 + 255) / 256;
-    const int64_t cap = (int64_t)adam_sms() * (s.use_dirty ? resident_ctas(adam_peers_sparse_kernel, 256) : resident_ctas(adam_peers_kernel, 256));
+    const int64_t cap = (int64_t)adam_sms() * (!s.use_dirty ? resident_ctas(adam_peers_kernel, 256) : s.inbox ? resident_ctas(adam_peers_sparse_kernel<true>, 256) : resident_ctas(adam_peers_sparse_kernel<false>, 256));
     if (blocks > cap) blocks = cap;
-    if (s.use_dirty) adam_peers_sparse_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
+    if (s.use_dirty && s.inbox) adam_peers_sparse_kernel<true><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
+    else if (s.use_dirty) adam_peers_sparse_kernel<false><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
     else adam_peers_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;

@@ -52,7 +52,7 @@ def parse():
     ap.add_argument('--workload', default='room0', choices=['room0', 'scannet_hash'],
                     help='room0: BASELINE.json configs[1] (the default, the judged line); scannet_hash: configs[3] -- ScanNet scene0000 bound '
                          'and sampling (117 samples per ray) on the 16-level hash grid; use with --rays = 65536 / GPUs and --value-only')
-    ap.add_argument('--mark-dirty', action='store_true', help='multi-GPU: flag dirty texels in the backward kernel instead of deriving the flags from the gradient buffer')
+    ap.add_argument('--no-mark-dirty', action='store_true', help='multi-GPU: derive the flags of the non-zero gradient texels from a pass over the gradient buffer instead of setting them in the backward kernel')
     ap.add_argument('--spare-sms', type=int, default=8, help='SMs the optimiser kernels leave to the pipelined side stream')
     ap.add_argument('--value-only', action='store_true', help='print the graph-replayed step time only (side experiments)')
     args = ap.parse_args()
@@ -676,7 +676,7 @@ def run_ours(args):
     model = JointEncoding(cfg, bb).to(dev)
     model.train()
     # the map is replicated: same seed on every rank gives identical planes and decoder
-    mapper = FusedMapper(model, world_size=world, mark_dirty=args.mark_dirty)
+    mapper = FusedMapper(model, world_size=world, mark_dirty=False if args.no_mark_dirty else None)
     rays_cpu, poses_cpu = synthetic.make_keyframe_db(cfg, n_kf=N_KF, seed=0)
     current_cpu = synthetic.make_current_frame(cfg, poses_cpu[-1], seed=rank) if args.cur else None
     db = DeviceKeyframeRays(rays_cpu.to(dev), poses_cpu.to(dev), current=None if current_cpu is None else current_cpu.to(dev),

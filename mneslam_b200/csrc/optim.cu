@@ -27,8 +27,13 @@ __device__ __forceinline__ void adam_one(float& p, float& g, float& m, float& v,
     if (a.weight_decay != 0.0f) grad = fmaf(a.weight_decay, p, grad);
     m = m + (1.0f - a.beta1) * (grad - m);
     v = __fmaf_rn((1.0f - a.beta2) * grad, grad, a.beta2 * v);
+#ifdef MNE_FAST_ADAM_MATH      // diagnostic only: approximate division / square root
+    const float denom = __fdividef(__fsqrt_rn(v), bc2_sqrt) + a.eps;
+    p = p - step_size * __fdividef(m, denom);
+#else
     const float denom = sqrtf(v) / bc2_sqrt + a.eps;
     p = p - step_size * (m / denom);
+#endif
     if (a.zero_grad) g = 0.0f;
 }
 
@@ -92,8 +97,8 @@ struct AdamSegments {
 // The kernel is bound by memory latency (ncu: long-scoreboard stalls, 0.5 eligible warps per cycle), so every thread keeps
 // two groups in flight and issues the independent loads of both before anything depends on them: flags + gradients
 // first, then parameters + moments of the groups that need the update.
-template <bool DIRTY>
-__global__ void __launch_bounds__(256, 4) adam_segments_kernel(const __grid_constant__ AdamSegments s) {
+template <bool DIRTY, int U, int CTAS>
+__global__ void __launch_bounds__(256, CTAS) adam_segments_kernel(const __grid_constant__ AdamSegments s) {
     const double t = (double)(s.step_dev ? *s.step_dev : s.step_host);
     const float bc1 = (float)(1.0 - pow((double)s.beta1, t));
     const float bc2_sqrt = (float)sqrt(1.0 - pow((double)s.beta2, t));
@@ -104,7 +109,6 @@ __global__ void __launch_bounds__(256, 4) adam_segments_kernel(const __grid_cons
     float4* m4 = reinterpret_cast<float4*>(s.m);
     float4* v4 = reinterpret_cast<float4*>(s.v);
     const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
-    constexpr int U = 2;             // measured: 1 -> 119 us, 2 -> 108 us, 4 (2 CTAs / SM) -> 117 us
     int seg[U] = {};
     const int lane = threadIdx.x & 31;
     // (the loop condition is the WARP's first group, so that all 32 lanes reach the __syncwarp of the DIRTY variant together)
@@ -255,13 +259,16 @@ extern "C" int mne_adam_step_segments_dirty(float* param, float* grad, float* ex
     }
     int64_t blocks = ((prev >> 2) + 255) / 256;
     if (dirty) {
-        const int64_t cap = (int64_t)adam_sms() * resident_ctas(adam_segments_kernel<true>, 256);
+        const int64_t cap = (int64_t)adam_sms() * resident_ctas(adam_segments_kernel<true, 1, 6>, 256);
         if (blocks > cap) blocks = cap;
-        adam_segments_kernel<true><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
+        adam_segments_kernel<true, 1, 6><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
     } else {
-        const int64_t cap = (int64_t)adam_sms() * resident_ctas(adam_segments_kernel<false>, 256);
+        // one group per thread, eight CTAs per SM (64 warps): the pass is bound by loads in flight and by the ~200 instructions
+        // of IEEE division / square root per group, both of which more resident warps hide.  Measured on B200 (room0 step):
+        // (U groups per thread, CTAs per SM) = (2, 4) 0.236 ms, (1, 5) 0.241, (1, 6) 0.233, (1, 8) 0.227, (2, 5, spilling) 0.264
+        const int64_t cap = (int64_t)adam_sms() * resident_ctas(adam_segments_kernel<false, 1, 8>, 256);
         if (blocks > cap) blocks = cap;
-        adam_segments_kernel<false><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
+        adam_segments_kernel<false, 1, 8><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
     }
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
@@ -384,25 +391,44 @@ __global__ void __launch_bounds__(256) dirty_push_kernel(uint8_t* __restrict__ l
 // dirty_push_kernel + mne_grad_push in one: the flags the backward pass set say where the gradient is non-zero, so only those
 // texels (about a sixth of the map per iteration) are read, pushed into their owners' inboxes and cleared -- no pass over the
 // whole gradient buffer.  Eight lanes per texel (one float4 each).
+// A warp takes 32 texels per step: one coalesced load of their flags, the flags handed to the owners, then only the FLAGGED
+// texels owned by another rank are moved -- eight at a time (lane = (slot, 16-byte part); slot j takes the j-th and the
+// (j+4)-th flagged texel of the step), all their loads in flight before the first store.  (One texel per eight threads with
+// the flag load, the data load and the stores in a dependent chain took 42 us for the 1 MB map of room0: 28 serial round
+// trips per thread.)
 __global__ void __launch_bounds__(256) dirty_push_data_kernel(uint8_t* __restrict__ local_map, float4* __restrict__ g4,
                                                               const __grid_constant__ DirtyPush d) {
-    const int sub = threadIdx.x & 7;
-    const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 3;
+    const int lane = threadIdx.x & 31, sub = lane & 7, slot = lane >> 3;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int64_t tx = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3; tx < d.scan32; tx += stride) {
-        const uint8_t f = local_map[tx];
-        const uint32_t c = (uint32_t)(tx >> d.chunk_tx_log2);
-        const uint32_t owner = c % (uint32_t)d.world;
-        const int64_t lt = ((int64_t)(c / (uint32_t)d.world) << d.chunk_tx_log2) + (tx & ((1 << d.chunk_tx_log2) - 1));
-        __syncwarp();                                     // every lane of the texel has read the flag before it is cleared
-        if (sub == 0) {
+    for (int64_t t0 = warp * 32; t0 < d.scan32; t0 += n_warps * 32) {
+        const int64_t tx = t0 + lane;
+        uint8_t f = 0;
+        uint32_t owner = (uint32_t)d.rank;
+        int64_t lt = 0;
+        if (tx < d.scan32) {
+            f = local_map[tx];
+            const uint32_t c = (uint32_t)(tx >> d.chunk_tx_log2);
+            owner = c % (uint32_t)d.world;
+            lt = ((int64_t)(c / (uint32_t)d.world) << d.chunk_tx_log2) + (tx & ((1 << d.chunk_tx_log2) - 1));
             d.dst[owner][(int64_t)d.rank * d.local32 + lt] = f;
             if (f) local_map[tx] = 0;
         }
-        if (f && owner != (uint32_t)d.rank) {
-            const float4 v = g4[tx * 8 + sub];
-            d.inbox[owner][((int64_t)d.rank * d.local32 + lt) * 8 + sub] = v;
-            g4[tx * 8 + sub] = zero;
+        unsigned todo = __ballot_sync(0xffffffffu, f != 0 && owner != (uint32_t)d.rank);
+        while (todo) {                                    // warp-uniform
+            const unsigned src0 = __fns(todo, 0, slot + 1), src1 = __fns(todo, 0, slot + 5);     // 0xffffffff: no such bit
+#pragma unroll
+            for (int k = 0; k < 8; ++k) todo &= todo - 1;     // (todo - 1 of 0 wraps, but 0 & anything stays 0)
+            const uint32_t o0 = __shfl_sync(0xffffffffu, owner, src0 & 31), o1 = __shfl_sync(0xffffffffu, owner, src1 & 31);
+            const int64_t l0 = __shfl_sync(0xffffffffu, lt, src0 & 31), l1 = __shfl_sync(0xffffffffu, lt, src1 & 31);
+            float4 v0 = zero, v1 = zero;
+            float4* s0 = g4 + (t0 + (src0 & 31)) * 8 + sub;
+            float4* s1 = g4 + (t0 + (src1 & 31)) * 8 + sub;
+            if (src0 < 32u) v0 = *s0;
+            if (src1 < 32u) v1 = *s1;
+            if (src0 < 32u) { d.inbox[o0][((int64_t)d.rank * d.local32 + l0) * 8 + sub] = v0; *s0 = zero; }
+            if (src1 < 32u) { d.inbox[o1][((int64_t)d.rank * d.local32 + l1) * 8 + sub] = v1; *s1 = zero; }
         }
     }
 }
@@ -441,6 +467,111 @@ __device__ __forceinline__ uint32_t peer_flags(const AdamPeers& s, int64_t i) {
 // after the other (measured r01: 38 + 49 + 80 us at eight ranks); in flight together they overlap.
 constexpr int kPeerU = 2;
 constexpr int kPeerFetch = 4;      // peer gradients fetched per group before the sum depends on them
+
+// The same update when every peer gradient was PUSHED into this rank's inbox (mne_grad_push): all sources are local, only this
+// rank's own gradient buffer needs clearing.  Written for occupancy -- the kernel is bound by loads in flight (ncu on the
+// generic variant: 23 warps per SM, 8.7 long-scoreboard stalls per issue, 26 % of the DRAM peak): 32-bit indices, the
+// per-segment step sizes computed once per CTA, F gradients fetched per group before the sum depends on them (at eight ranks
+// a flagged texel is flagged by 1.4 ranks on average; more take the loop).  Sums run over the flagged ranks in ascending order.
+template <int U, int CTAS>
+__global__ void __launch_bounds__(256, CTAS) adam_peers_inbox_kernel(const __grid_constant__ AdamPeers s) {
+    constexpr int F = 1;
+    __shared__ float s_step[MNE_ADAM_MAX_SEGMENTS];
+    const double t = (double)(s.step_dev ? *s.step_dev : s.step_host);
+    const float bc2_sqrt = (float)sqrt(1.0 - pow((double)s.beta2, t));
+    if ((int)threadIdx.x < s.n_seg) {
+        const float bc1 = (float)(1.0 - pow((double)s.beta1, t));
+        s_step[threadIdx.x] = (float)((double)s.lr[threadIdx.x] / (double)bc1);
+    }
+    __syncthreads();
+    const int stride = (int)(gridDim.x * blockDim.x);
+    const int local4 = (int)s.local4, local32 = local4 >> 3, end_all = (int)s.end4[s.n_seg - 1];
+    const int cl = s.chunk4_log2, cmask = (1 << cl) - 1, world = s.world, rank = s.rank;
+    float4* __restrict__ m4 = reinterpret_cast<float4*>(s.m);
+    float4* __restrict__ v4 = reinterpret_cast<float4*>(s.v);
+    float4* p_loc = reinterpret_cast<float4*>(s.param[rank]);
+    float4* g_loc = reinterpret_cast<float4*>(s.grad[rank]);
+    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+    int seg[U] = {};
+    for (int i0 = (int)(blockIdx.x * blockDim.x + threadIdx.x); i0 < local4; i0 += U * stride) {
+        int li[U], gi[U];
+        uint32_t mk[U];
+        uint8_t tf[U];
+        bool on[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            li[u] = i0 + u * stride;
+            on[u] = li[u] < local4;
+            gi[u] = on[u] ? ((((li[u] >> cl) * world + rank) << cl) + (li[u] & cmask)) : end_all;
+            on[u] = on[u] && gi[u] < end_all;                 // beyond: padding
+            mk[u] = 0; tf[u] = 1;
+            if (on[u]) {
+                const uint8_t* f = s.dirty + (li[u] >> 3);
+#pragma unroll 4
+                for (int r = 0; r < world; ++r) mk[u] |= (uint32_t)(f[r * local32] != 0) << r;
+                if (s.touched) tf[u] = s.touched[li[u]];
+            }
+        }
+        float4 p[U], m[U], v[U], x[U][F];
+        uint32_t rest[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (on[u]) {
+                while (gi[u] >= (int)s.end4[seg[u]]) ++seg[u];
+                if (s.touched && s.wd[seg[u]] == 0.0f && !mk[u] && !tf[u]) on[u] = false;   // identity update: every replica holds this value
+            }
+            rest[u] = on[u] ? mk[u] : 0u;
+#pragma unroll
+            for (int k = 0; k < F; ++k) {
+                x[u][k] = zero;
+                if (rest[u]) {
+                    const int r = __ffs(rest[u]) - 1;
+                    rest[u] &= rest[u] - 1;
+                    x[u][k] = (r != rank) ? s.inbox[(int64_t)r * local4 + li[u]] : g_loc[gi[u]];
+                }
+            }
+            if (on[u]) { p[u] = p_loc[gi[u]]; m[u] = m4[li[u]]; v[u] = v4[li[u]]; }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (!on[u]) continue;
+            float4 g = x[u][0];
+#pragma unroll
+            for (int k = 1; k < F; ++k) { g.x += x[u][k].x; g.y += x[u][k].y; g.z += x[u][k].z; g.w += x[u][k].w; }
+            while (rest[u]) {
+                float4 y[2];
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    y[k] = zero;
+                    if (rest[u]) {
+                        const int r = __ffs(rest[u]) - 1;
+                        rest[u] &= rest[u] - 1;
+                        y[k] = (r != rank) ? s.inbox[(int64_t)r * local4 + li[u]] : g_loc[gi[u]];
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < 2; ++k) { g.x += y[k].x; g.y += y[k].y; g.z += y[k].z; g.w += y[k].w; }
+            }
+            if ((mk[u] >> rank) & 1u) g_loc[gi[u]] = zero;
+            AdamArgs a{};
+            a.beta1 = s.beta1; a.beta2 = s.beta2; a.eps = s.eps[seg[u]]; a.weight_decay = s.wd[seg[u]]; a.zero_grad = 0;
+            if (s.touched && a.weight_decay == 0.0f) {
+                const bool nz = g.x != 0.0f || g.y != 0.0f || g.z != 0.0f || g.w != 0.0f;
+                if (!nz && !tf[u]) continue;             // flagged texel, but this group of it carried no gradient
+                if (!tf[u]) s.touched[li[u]] = 1;
+            }
+            const float step_size = s_step[seg[u]];
+            adam_one(p[u].x, g.x, m[u].x, v[u].x, a, step_size, bc2_sqrt);
+            adam_one(p[u].y, g.y, m[u].y, v[u].y, a, step_size, bc2_sqrt);
+            adam_one(p[u].z, g.z, m[u].z, v[u].z, a, step_size, bc2_sqrt);
+            adam_one(p[u].w, g.w, m[u].w, v[u].w, a, step_size, bc2_sqrt);
+            m4[li[u]] = m[u]; v4[li[u]] = v[u];
+            if (s.mc_param) multimem_st(reinterpret_cast<float4*>(s.mc_param) + gi[u], p[u]);
+            else
+                for (int r = 0; r < world; ++r) reinterpret_cast<float4*>(s.param[r])[gi[u]] = p[u];
+        }
+    }
+}
 
 // INBOX: the peers' gradients were pushed into this rank's inbox (mne_grad_push): every source but this rank's own gradient
 // buffer is local, read-only and needs no clearing -- so no pointer per fetched group has to be kept (registers: the generic
@@ -661,7 +792,18 @@ extern "C" int mne_adam_step_peers(int32_t world_size, int32_t rank, float* cons
     MNE_CHECK_ARG(!inbox || (dirty && (((uintptr_t)inbox) & 15) == 0), "mne_adam_step_peers: inbox needs the dirty flags and 16-byte alignment");
     s.inbox = reinterpret_cast<const float4*>(inbox);
     int64_t blocks = (s.local4 + 255) / 256;
-    const int64_t cap = (int64_t)adam_sms() * (!s.use_dirty ? resident_ctas(adam_peers_kernel, 256) : s.inbox ? resident_ctas(adam_peers_sparse_kernel<true>, 256) : resident_ctas(adam_peers_sparse_kernel<false>, 256));
+    const bool lean = s.use_dirty && s.inbox && s.total4 < ((int64_t)1 << 30);       // (32-bit group indices)
+    if (lean) {
+        // (U groups per thread, CTAs per SM), two emulated ranks on one B200, room0: (2, 3) 97 us, (2, 4) 84, (3, 3) 99,
+        // (1, 6) 74, (1, 7) 74, (1, 8) 74 -- resident warps, not groups per thread, hide the latency
+        const int64_t cap = (int64_t)adam_sms() * resident_ctas(adam_peers_inbox_kernel<1, 6>, 256);
+        if (blocks > cap) blocks = cap;
+        adam_peers_inbox_kernel<1, 6><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
+        MNE_CHECK_CUDA(cudaGetLastError());
+        return 0;
+    }
+    const int64_t cap = (int64_t)adam_sms() * (!s.use_dirty ? resident_ctas(adam_peers_kernel, 256)
+                                                 : s.inbox ? resident_ctas(adam_peers_sparse_kernel<true>, 256) : resident_ctas(adam_peers_sparse_kernel<false>, 256));
     if (blocks > cap) blocks = cap;
     if (s.use_dirty && s.inbox) adam_peers_sparse_kernel<true><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);
     else if (s.use_dirty) adam_peers_sparse_kernel<false><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(s);

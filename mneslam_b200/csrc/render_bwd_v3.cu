@@ -63,10 +63,15 @@ __device__ __forceinline__ void scatter16_pq(const MneSceneDesc& sc, int grp, co
                         float* gp = Pl.grad + q * 4;
 #pragma unroll
                         for (int c = 0; c < 4; ++c) {
-                            if (ws[c] != 0.f) {
+                            if (ws[c] != 0.f)
                                 atomicAdd(reinterpret_cast<float4*>(gp + o[c]), make_float4(gv.x * ws[c], gv.y * ws[c], gv.z * ws[c], gv.w * ws[c]));
-                                if (q == 0 && sc.dirty) mark_dirty(sc.dirty, ((Pl.grad + o[c]) - sc.dirty_base) >> 5);
-                            }
+                        }
+                        // texel flags: lanes 0..3 of the point's octet flag one corner each -- ONE store instruction per tap
+                        // (a store per corner under `q == 0` serialised four divergent paths: +18 us on the kernel)
+                        if (sc.dirty && q < 4) {
+                            const unsigned oc = q == 0 ? o[0] : q == 1 ? o[1] : q == 2 ? o[2] : o[3];
+                            const float wc = q == 0 ? ws[0] : q == 1 ? ws[1] : q == 2 ? ws[2] : ws[3];
+                            if (wc != 0.f) mark_dirty(sc.dirty, ((Pl.grad - sc.dirty_base) >> 5) + (oc >> 5));
                         }
                     }
                     if (RAY) {

@@ -40,17 +40,18 @@ PEER_CHUNK = 1024      # floats per ownership chunk (4 KB) of the peer-memory op
 
 class FusedMapper:
     def __init__(self, model, is_co_sdf=None, process_group=None, world_size=1, adopt_parameters=True, skip_untouched=True,
-                 peer_memory=True, use_multicast=True, mark_dirty=False):
+                 peer_memory=True, use_multicast=True, mark_dirty=None):
         """``adopt_parameters``: move the planes and decoder weights into ONE flat buffer (each tensor keeps its
         Python identity, shape and strides; only its storage changes), with gradients and Adam moments laid out
         the same way, so that the optimiser is a single streaming launch.  ``skip_untouched``: exact skip of parameter
         groups that never received a gradient.  Several GPUs (``world_size`` > 1, rays sharded over ranks):
         ``peer_memory`` puts the flat buffers into NVLink peer-mapped memory and runs the optimiser as ONE kernel that
         reduces the gradient over the peers and writes the parameters back (else NCCL reduce-scatter / all-gather);
-        ``use_multicast`` lets that kernel store through the NVLink switch from 4 ranks up; owners fetch only the
-        texels a peer flagged as non-zero this step; the flags come from one pass over the gradient buffer
-        (``mne_grad_dirty_map``, 25 us for 129 MB) or, with ``mark_dirty``, from the backward kernels themselves
-        (``MneSceneDesc.dirty``; measured 5 us slower per iteration at two ranks, so off by default)."""
+        ``use_multicast`` lets that kernel store through the NVLink switch from 4 ranks up; the texels of the gradient that
+        are non-zero this step are pushed to their owners together with one flag byte each.  ``mark_dirty``: the flags come
+        from the backward kernels themselves (``MneSceneDesc.dirty``: +4.5 us on the backward kernel, then a pass over the
+        1 MB flag map, 22 us) instead of a pass over the 129 MB gradient buffer (``mne_grad_push``, 42 us); None = wherever
+        the kernels support it (channels-last planes; the hash grid adds 8-byte entries and takes the pass)."""
         ops.require_cuda()
         self.model, self.cfg = model, model.config
         self.world_size, self.group = world_size, process_group
@@ -187,6 +188,8 @@ class FusedMapper:
         self.dense_from = enc_len + self._dec_pad
         if os.environ.get('MNE_MARK_DIRTY') is not None:
             mark_dirty = os.environ['MNE_MARK_DIRTY'] == '1'
+        if mark_dirty is None:
+            mark_dirty = True
         vector_planes = model.hash_meta is None and len(planes) > 0 and all(p.stride(1) == 1 and p.shape[1] == 32 for p in planes)
         if self.peers is not None and mark_dirty and vector_planes:
             self.dirty_local = torch.zeros(padded // 32, dtype=torch.uint8, device=self.dev)

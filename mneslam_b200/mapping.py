@@ -606,6 +606,7 @@ class PipelinedMapper:
         self.losses = torch.zeros(_lib.N_LOSSES, **f32)
         self.side = torch.cuda.Stream(device=dev)
         self.graph = None
+        self.stream = None
 
     def _batch_size(self, n_rays):
         return self.db.batch_rays(n_rays)            # + the rays of the current frame, when the store has one
@@ -639,6 +640,7 @@ class PipelinedMapper:
                 self.losses.copy_(losses)
         else:
             self.losses.copy_(losses)
+        self._losses_ready(main)
         self.side.wait_stream(main)                 # the batch has been consumed: refill it under the optimiser
         with torch.cuda.stream(self.side):
             self._after_losses()
@@ -647,11 +649,14 @@ class PipelinedMapper:
         main.wait_stream(self.side)
         m.last_losses = self.losses
 
+    def _losses_ready(self, main):
+        """Hook on the main stream, once the iteration's losses have been queued (subclasses fork their read-back here)."""
+
     def _after_losses(self):
         """Hook on the side stream, once the iteration's losses exist (subclasses copy them to the host here)."""
 
     def capture(self):
-        stream = torch.cuda.Stream(device=self.mapper.dev)
+        stream = self.stream if self.stream is not None else torch.cuda.Stream(device=self.mapper.dev)
         stream.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(stream):
             self._draw()                             # prologue: the first batch
@@ -676,16 +681,34 @@ class PrefetchingHostMapper(PipelinedMapper):
     """``PipelinedMapper`` fed from HOST memory, data-loader style: every ``step(next_batch)`` trains on the batch handed over
     by the PREVIOUS call and, under its optimiser, uploads, assembles and samples ``next_batch`` (one CUDA-graph launch
     holding the H2D copies, the iteration and the D2H copy of the loss).  The ray batches of the reference come from the
-    host keyframe store (model/keyframe.py:91-103) and do not depend on the map, so the caller can always be one ahead."""
+    host keyframe store (model/keyframe.py:91-103) and do not depend on the map, so the caller can always be one ahead.
 
-    def __init__(self, mapper, db, n_rays, spare_sms=8):
+    ``async_loss``: the loss is read back one call late as well -- ``step`` launches its iteration and returns the loss of
+    the iteration launched by the previous call (None on the first call; ``flush()`` returns the last one).  The host then
+    never waits for the launch it has just made, so the device runs the iterations back to back (the reference loop itself
+    never reads the loss between ``backward()`` and ``step()``, mp_slam/mapper.py:155-162).  Two graphs with their own
+    pinned staging and loss buffers alternate, so that a buffer is only rewritten after its graph has finished."""
+
+    def __init__(self, mapper, db, n_rays, spare_sms=8, async_loss=False):
         super().__init__(mapper, db, n_rays, spare_sms)
         dev = mapper.dev
-        self.h_rays = torch.empty(n_rays, 7, dtype=torch.float32).pin_memory()
-        self.h_ids = torch.empty(n_rays, dtype=torch.int64).pin_memory()
-        self.h_loss = torch.zeros(1, dtype=torch.float32).pin_memory()
+        self.async_loss = bool(async_loss)
+        self.slots = []
+        for _ in range(2 if async_loss else 1):
+            self.slots.append({'h_rays': torch.empty(n_rays, 7, dtype=torch.float32).pin_memory(),
+                               'h_ids': torch.empty(n_rays, dtype=torch.int64).pin_memory(),
+                               'h_loss': torch.zeros(1, dtype=torch.float32).pin_memory(),
+                               'graph': None, 'done': torch.cuda.Event()})
+        self._use(0)
         self.d_rays = torch.empty(n_rays, 7, dtype=torch.float32, device=dev)
         self.d_ids = torch.empty(n_rays, dtype=torch.int64, device=dev)
+        self._calls, self._in_flight = 0, None
+        self._aux, self._forked = None, False
+
+    def _use(self, i):
+        slot = self.slots[i]
+        self.h_rays, self.h_ids, self.h_loss = slot['h_rays'], slot['h_ids'], slot['h_loss']
+        return slot
 
     def _batch_size(self, n_rays):
         return n_rays                                # the caller hands over whole batches (current-frame rays included)
@@ -697,27 +720,62 @@ class PrefetchingHostMapper(PipelinedMapper):
         self.ro.copy_(ro); self.rd.copy_(rd); self.rgb.copy_(rgb); self.d.copy_(d)
         self.mapper.sample_stage(self.d, z_out=self.z, acc_out=self.acc)
 
+    def _losses_ready(self, main):
+        # the weighted sum of the losses and its D2H copy run on a third stream beside the optimiser.  (On the side stream that
+        # uploads and samples the next batch they measured 25 us SLOWER per iteration -- that work then outlasts the optimiser;
+        # at the end of the main stream they sit on the critical path.)
+        self._forked = not self.mapper._loss_pending
+        if self._forked:
+            if self._aux is None:
+                self._aux = torch.cuda.Stream(device=self.mapper.dev)
+            self._aux.wait_stream(main)
+            with torch.cuda.stream(self._aux):
+                self.h_loss.copy_(self.mapper.total_loss(self.losses).reshape(1), non_blocking=True)
+
     def _iteration(self):
         super()._iteration()
-        # (issuing this copy on the side stream, under the optimiser, measured 25 us SLOWER per iteration: it delays the upload
-        #  and sampling of the next batch, which then outlast the optimiser)
-        self.h_loss.copy_(self.mapper.total_loss(self.losses).reshape(1), non_blocking=True)
+        if self._forked:
+            torch.cuda.current_stream().wait_stream(self._aux)
+        else:       # several GPUs: the losses are finalised on the mapper's own side stream, joined by optimizer_step
+            self.h_loss.copy_(self.mapper.total_loss(self.losses).reshape(1), non_blocking=True)
 
     def prime(self, rays7, kf_ids):
-        """Hand over the first batch (uploaded and sampled right away; also warms up and captures the graph, which costs
-        two real iterations on this batch)."""
-        self.h_rays.copy_(rays7); self.h_ids.copy_(kf_ids)
-        self.capture()
+        """Hand over the first batch (uploaded and sampled right away; also warms up and captures the graph(s), which costs
+        two real iterations on this batch per graph)."""
+        for i in range(len(self.slots)):
+            slot = self._use(i)
+            self.h_rays.copy_(rays7); self.h_ids.copy_(kf_ids)
+            self.graph = None
+            self.capture()
+            slot['graph'] = self.graph
         return self
 
     def step(self, next_rays7, next_kf_ids):
         """Train on the batch of the previous call (or of ``prime``); upload ``next_*`` (HOST tensors) under its optimiser.
-        Returns the loss of the trained batch as a Python float."""
+        Returns the loss of the trained batch as a Python float -- with ``async_loss`` the loss of the previous call's
+        iteration (None on the first call)."""
         if self.graph is None:
             raise RuntimeError('PrefetchingHostMapper: call prime(first_batch) first')
-        self.h_rays.copy_(next_rays7)
-        self.h_ids.copy_(next_kf_ids)
+        slot = self.slots[self._calls % len(self.slots)]
+        self._calls += 1
+        slot['h_rays'].copy_(next_rays7)
+        slot['h_ids'].copy_(next_kf_ids)
         with torch.cuda.stream(self.stream):
-            self.graph.replay()
-        self.stream.synchronize()
-        return float(self.h_loss[0])
+            slot['graph'].replay()
+            slot['done'].record()
+        if not self.async_loss:
+            slot['done'].synchronize()
+            return float(slot['h_loss'][0])
+        before, self._in_flight = self._in_flight, slot
+        if before is None:
+            return None
+        before['done'].synchronize()
+        return float(before['h_loss'][0])
+
+    def flush(self):
+        """``async_loss``: wait for the iteration still in flight and return its loss (None if there is none)."""
+        slot, self._in_flight = self._in_flight, None
+        if slot is None:
+            return None
+        slot['done'].synchronize()
+        return float(slot['h_loss'][0])

@@ -586,9 +586,11 @@ def test_optim_adam_is_a_drop_in_for_torch_adam():
     assert len(sd['state']) == 4 and sd['state'][0]['step'] == 5
 
 
-def test_prefetching_host_mapper_trains_on_the_previous_batch():
+@pytest.mark.parametrize('async_loss', [False, True])
+def test_prefetching_host_mapper_trains_on_the_previous_batch(async_loss):
     """PrefetchingHostMapper.step(next) = FusedMapper.step on the batch handed over one call earlier: same losses, same
-    parameters (prime() spends two real iterations on the first batch, as documented)."""
+    parameters (prime() spends two real iterations per captured graph on the first batch, as documented).  ``async_loss``:
+    the same iterations, each loss handed back one call later (two graphs alternate; the last loss comes from flush())."""
     from mneslam_b200.mapping import DeviceKeyframeRays, FusedMapper, PrefetchingHostMapper
     cfg, bb, planes, weights = _small_model(seed=9)
     cfg['cam'].update({'H': 40, 'W': 60, 'fx': 50.0, 'fy': 50.0, 'cx': 29.5, 'cy': 19.5})
@@ -607,11 +609,16 @@ def test_prefetching_host_mapper_trains_on_the_previous_batch():
         db = DeviceKeyframeRays(rays.cuda(), poses.cuda())
         losses = []
         if prefetch:
-            fed = PrefetchingHostMapper(mapper, db, 256).prime(*batches[0])
+            fed = PrefetchingHostMapper(mapper, db, 256, async_loss=async_loss).prime(*batches[0])
             for nxt in batches[1:]:
                 losses.append(fed.step(*nxt))                       # the loss of the batch given one call earlier
+            if async_loss:
+                assert losses[0] is None                            # nothing had been launched before the first call
+                losses = losses[1:] + [fed.flush()]
+                assert fed.flush() is None
+            fed.close()
         else:
-            for _ in range(2):
+            for _ in range(4 if async_loss else 2):
                 mapper.step(*db.assemble(batches[0][0].cuda(), batches[0][1].cuda()))
             for r7, ids in batches[:-1]:
                 losses.append(float(mapper.total_loss(mapper.step(*db.assemble(r7.cuda(), ids.cuda())))))

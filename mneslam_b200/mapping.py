@@ -47,7 +47,7 @@ class FusedMapper:
         groups that never received a gradient.  Several GPUs (``world_size`` > 1, rays sharded over ranks):
         ``peer_memory`` puts the flat buffers into NVLink peer-mapped memory and runs the optimiser as ONE kernel that
         reduces the gradient over the peers and writes the parameters back (else NCCL reduce-scatter / all-gather);
-        ``use_multicast`` lets that kernel store through the NVLink switch from 4 ranks up; the texels of the gradient that
+        ``use_multicast`` lets that kernel store through the NVLink switch from 8 ranks up; the texels of the gradient that
         are non-zero this step are pushed to their owners together with one flag byte each.  ``mark_dirty``: the flags come
         from the backward kernels themselves (``MneSceneDesc.dirty``: +4.5 us on the backward kernel, then a pass over the
         1 MB flag map, 22 us) instead of a pass over the 129 MB gradient buffer (``mne_grad_push``, 42 us); None = wherever
@@ -117,8 +117,9 @@ class FusedMapper:
                               # NVLink-switch multicast addresses (0 when the fabric has no multicast support)
                               'mc_grad': int(getattr(hg, 'multicast_ptr', 0) or 0) if use_multicast else 0,
                               'mc_param': int(getattr(hp, 'multicast_ptr', 0) or 0) if use_multicast else 0}
-                # measured (r01): multicast stores pay off from 4 ranks up; with 2 ranks plain peer stores are faster
-                if world_size < 4:
+                # measured (r02, room0): four ranks 0.264 ms per iteration with plain peer stores, 0.276 through the switch's multicast
+                # address; eight ranks 0.287 / 0.288 (a tie: the inbound side is the bound either way, multicast sends 1/7 of the bytes)
+                if world_size < int(os.environ.get('MNE_MULTICAST_FROM', '8')):
                     self.peers['mc_param'] = 0
                 self.peers['mc_grad'] = 0             # the gradient side uses the sparse (dirty-map) peer reduction
             except Exception as e:      # no peer access / no symmetric-memory support: NCCL collectives instead

@@ -213,6 +213,8 @@ class FusedMapper:
         self._wgrad_stream = None     # side stream: decoder weight gradients + decoder Adam beside the planes' Adam
         self._loss_stream = None      # side stream (several GPUs): all-reduce of the loss sums + loss finalisation
         self._loss_pending = False
+        self._tick_issued = False
+        self.losses_on_side = False   # one GPU too: finalise the losses and advance the step counter beside the backward (PipelinedMapper)
         self._act = None              # the per-sample record, forward -> backward (ops.act_floats per sample)
         self.last_losses = None
         self.global_rays_override = None
@@ -300,23 +302,28 @@ class FusedMapper:
         out = ops.render_forward(scene, rcfg, rays_o, rays_d, z_vals, target_rgb, td, acc, want_aux=False, act=self._act,
                                  ray_counters=self._ray_counters if self.single_launch_render else None,
                                  loss_grads=self.loss_grads, scratch=self._scratch)
-        ops.render_backward_points(self._scene(True, weight_grads=False), rays_o, rays_d, z_vals, self._scratch, act=self._act)
-        self._pending_wgrad = (n, s)
-        if not defer_wgrad or self.flat_param is None or (self.world_size > 1 and self.peers is None):
-            self._decoder_wgrad()     # (NCCL fallback: the reduce-scatter moves the whole flat buffer, nothing to overlap)
-        if self.world_size > 1:
-            # the loss VALUES need the global sums (slots 6..); nothing on the gradient path waits for them, so the reduction
-            # and the finalisation run on a side stream that is joined at the end of optimizer_step
+        if self.world_size > 1 or self.losses_on_side:
+            # the loss VALUES (and, several GPUs, the global sums they need: slots 6..) are not on the gradient path: their
+            # reduction and finalisation run on a side stream, forked here -- before the backward kernel is queued -- and joined
+            # in optimizer_step.  With ``losses_on_side`` (PipelinedMapper) the optimiser's step counter is advanced there too.
             main = torch.cuda.current_stream()
             if self._loss_stream is None:
                 self._loss_stream = torch.cuda.Stream(device=dev)
             self._loss_stream.wait_stream(main)
             with torch.cuda.stream(self._loss_stream):
-                self._small_allreduce('sums', acc[6:], 1)
+                if self.world_size > 1:
+                    self._small_allreduce('sums', acc[6:], 1)
                 losses = ops.loss_finalize(rcfg, s, acc)
+                if self.losses_on_side and not self._tick_issued:
+                    _lib.check(_lib.lib().mne_adam_tick(self.step_dev.data_ptr(), ops._stream()), 'mne_adam_tick')
+                    self._tick_issued = True
             self._loss_pending = True
         else:
             losses = ops.loss_finalize(rcfg, s, acc)
+        ops.render_backward_points(self._scene(True, weight_grads=False), rays_o, rays_d, z_vals, self._scratch, act=self._act)
+        self._pending_wgrad = (n, s)
+        if not defer_wgrad or self.flat_param is None or (self.world_size > 1 and self.peers is None):
+            self._decoder_wgrad()     # (NCCL fallback: the reduce-scatter moves the whole flat buffer, nothing to overlap)
         self.last_render = out
         return losses
 
@@ -359,7 +366,11 @@ class FusedMapper:
         (``mneslam_b200.distributed``)."""
         lib = _lib.lib()
         st = ops._stream()
-        _lib.check(lib.mne_adam_tick(self.step_dev.data_ptr(), st), 'mne_adam_tick')
+        if self._tick_issued:        # the step counter was advanced on the loss stream, under the backward kernel
+            torch.cuda.current_stream().wait_stream(self._loss_stream)
+            self._tick_issued = False
+        else:
+            _lib.check(lib.mne_adam_tick(self.step_dev.data_ptr(), st), 'mne_adam_tick')
         if self.world_size > 1 and self.peers is not None:
             # The decoder (6 208 weights) stays out of the peer exchange: on a side stream its weight gradients are computed,
             # all-reduced (25 KB) and applied by every rank's own Adam step (identical sums and moments -> identical weights),
@@ -617,6 +628,7 @@ class PipelinedMapper:
         if self._spare_before is not None:
             _lib.lib().mne_set_option(b'adam_spare_sms', int(self._spare_before))
             self._spare_before = None
+            self.mapper.losses_on_side = False
 
     def __del__(self):
         try:
@@ -632,17 +644,15 @@ class PipelinedMapper:
     def _iteration(self):
         m = self.mapper
         main = torch.cuda.current_stream()
-        # acc is consumed (and added to) by the forward of this iteration: work on a private copy so that the side stream
-        # may refill the shared one
-        acc = self.acc.clone()
-        losses = m.forward_backward(self.ro, self.rd, self.rgb, self.d, sampled=(self.z, acc), defer_wgrad=True)
-        if m._loss_pending:                          # several GPUs: the losses are finalised on the mapper's side stream
-            with torch.cuda.stream(m._loss_stream):
-                self.losses.copy_(losses)
-        else:
+        # acc (mask counts from the sampling stage; the forward adds the loss sums) is read by the forward on this stream and by
+        # the loss finalisation on the mapper's loss stream: the side stream refills it only after both (below)
+        m.losses_on_side = True
+        losses = m.forward_backward(self.ro, self.rd, self.rgb, self.d, sampled=(self.z, self.acc), defer_wgrad=True)
+        with torch.cuda.stream(m._loss_stream):      # (the losses are finalised there, beside the backward kernel)
             self.losses.copy_(losses)
-        self._losses_ready(main)
+            self._losses_ready()
         self.side.wait_stream(main)                 # the batch has been consumed: refill it under the optimiser
+        self.side.wait_stream(m._loss_stream)
         with torch.cuda.stream(self.side):
             self._after_losses()
             self._draw()
@@ -650,8 +660,8 @@ class PipelinedMapper:
         main.wait_stream(self.side)
         m.last_losses = self.losses
 
-    def _losses_ready(self, main):
-        """Hook on the main stream, once the iteration's losses have been queued (subclasses fork their read-back here)."""
+    def _losses_ready(self):
+        """Hook on the loss stream, once the iteration's losses exist (subclasses queue their read-back here)."""
 
     def _after_losses(self):
         """Hook on the side stream, once the iteration's losses exist (subclasses copy them to the host here)."""
@@ -704,7 +714,6 @@ class PrefetchingHostMapper(PipelinedMapper):
         self.d_rays = torch.empty(n_rays, 7, dtype=torch.float32, device=dev)
         self.d_ids = torch.empty(n_rays, dtype=torch.int64, device=dev)
         self._calls, self._in_flight = 0, None
-        self._aux, self._forked = None, False
 
     def _use(self, i):
         slot = self.slots[i]
@@ -721,24 +730,11 @@ class PrefetchingHostMapper(PipelinedMapper):
         self.ro.copy_(ro); self.rd.copy_(rd); self.rgb.copy_(rgb); self.d.copy_(d)
         self.mapper.sample_stage(self.d, z_out=self.z, acc_out=self.acc)
 
-    def _losses_ready(self, main):
-        # the weighted sum of the losses and its D2H copy run on a third stream beside the optimiser.  (On the side stream that
-        # uploads and samples the next batch they measured 25 us SLOWER per iteration -- that work then outlasts the optimiser;
-        # at the end of the main stream they sit on the critical path.)
-        self._forked = not self.mapper._loss_pending
-        if self._forked:
-            if self._aux is None:
-                self._aux = torch.cuda.Stream(device=self.mapper.dev)
-            self._aux.wait_stream(main)
-            with torch.cuda.stream(self._aux):
-                self.h_loss.copy_(self.mapper.total_loss(self.losses).reshape(1), non_blocking=True)
-
-    def _iteration(self):
-        super()._iteration()
-        if self._forked:
-            torch.cuda.current_stream().wait_stream(self._aux)
-        else:       # several GPUs: the losses are finalised on the mapper's own side stream, joined by optimizer_step
-            self.h_loss.copy_(self.mapper.total_loss(self.losses).reshape(1), non_blocking=True)
+    def _losses_ready(self):
+        # the weighted sum of the losses and its D2H copy, on the loss stream beside the backward kernel and the optimiser.  (On the
+        # side stream that uploads and samples the next batch they measured 25 us SLOWER per iteration -- that work then outlasts
+        # the optimiser; at the end of the main stream they sit on the critical path.)
+        self.h_loss.copy_(self.mapper.total_loss(self.losses).reshape(1), non_blocking=True)
 
     def prime(self, rays7, kf_ids):
         """Hand over the first batch (uploaded and sampled right away; also warms up and captures the graph(s), which costs

@@ -445,7 +445,8 @@ def self_check_record(world, rank, dev, iters=4):
         err_ok = err < 2e-3 and moved > 0
     else:
         err_ok = True
-    rec = {'ok': bool(identical and err_ok and loss_err < 1e-3), 'ranks_identical': identical,
+    timeouts = mapper.barrier_timeouts() if hasattr(mapper, 'barrier_timeouts') else 0
+    rec = {'ok': bool(identical and err_ok and loss_err < 1e-3 and timeouts == 0), 'ranks_identical': identical, 'barrier_timeouts': timeouts,
            'param_rel_err_vs_single_gpu': err, 'loss_rel_err_vs_single_gpu': loss_err if single is not None else None,
            'iterations': iters, 'rays_per_rank': n,
            'what': 'room0 map, %d sharded iterations on %d ranks; flat parameter buffers compared bit for bit across ranks '

@@ -400,6 +400,18 @@ int mne_peer_scatter(const float* src, int32_t n_floats, float* const* dst_ptrs,
                      mne_stream_t stream);
 int mne_peer_sum(const void* slots, int32_t n, int32_t world_size, void* out, int32_t is_double, mne_stream_t stream);
 
+/* Cross-rank barrier over NVLink peer memory as one small kernel (replaces the barriers of the exchange above; a kernel per
+ * barrier that only stores to the peers and polls local memory).  pad_ptrs: HOST array of world_size peer-mapped device
+ * pointers, entry r = rank r's signal pad of MNE_PEER_PAD_WORDS(n_channels) uint32 words, zero-initialised by the caller and
+ * identical in layout on every rank: [n_channels][MNE_MAX_PEERS] arrival words, [n_channels] epochs, 1 error word.  Every
+ * rank calls it the same number of times per channel; different channels may be in flight on different streams.  Memory
+ * written by earlier work of the calling stream (to any GPU) is visible to the peers' work after their barrier returns.  The
+ * wait is bounded (~2^27 polls): a rank that never arrives raises the error word (last word of the pad) instead of hanging
+ * the device. */
+#define MNE_PEER_PAD_WORDS(n_channels) ((n_channels) * (MNE_MAX_PEERS + 1) + 1)
+int mne_peer_barrier(uint32_t* const* pad_ptrs, int32_t world_size, int32_t rank, int32_t channel, int32_t n_channels,
+                     mne_stream_t stream);
+
 /* ---- measurement aid (no counterpart in the reference): a kernel that ONLY gathers.  offsets [n_offsets] uint32 = float
  * offsets into table; mode 0: each offset names a 128-byte texel (a multiple of 32 floats), fetched by eight lanes with one
  * 128-bit load each -- the tri-plane taps of the forward pass, 24 per sample; mode 1: each offset names an 8-byte entry (a

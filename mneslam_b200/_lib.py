@@ -96,6 +96,7 @@ _SIGNATURES = {
     'mne_dirty_push_data': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     'mne_peer_scatter': (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
     'mne_peer_sum': (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p]),
+    'mne_peer_barrier': (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
     'mne_bench_gather': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
     'mne_grad_dirty_map': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     'mne_dirty_push': (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
@@ -104,6 +105,14 @@ _SIGNATURES = {
 }
 
 _lib = None
+
+
+MAX_PEERS = 16
+
+
+def peer_pad_words(n_channels):
+    """MNE_PEER_PAD_WORDS of include/mneslam_b200.h."""
+    return n_channels * (MAX_PEERS + 1) + 1
 
 
 def exported_symbols():

@@ -960,3 +960,60 @@ extern "C" int mne_peer_sum(const void* slots, int32_t n, int32_t world_size, vo
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Cross-rank barrier over peer memory, one tiny kernel: lane r stores this rank's epoch of the channel into slot [rank] of
+// rank r's signal pad (release, system scope: everything earlier kernels of this stream wrote -- to any GPU -- is visible
+// before the signal is) and then polls slot [r] of its OWN pad until rank r's epoch has arrived (acquire).  Epochs count the
+// barriers of a channel and live in device memory, so a CUDA-graph replay continues the sequence.  Stores and local polls
+// only: no remote atomics, no remote loads (each costs an NVLink round trip).  The wait is bounded: after ~2^27 polls the
+// kernel gives up and raises the pad's error word instead of hanging the GPU.
+// ---------------------------------------------------------------------------------------------------------
+namespace mne {
+struct PeerBarrier {
+    uint32_t* pad[MNE_MAX_PEERS];     // every rank's pad: [channels][MNE_MAX_PEERS] arrival words, then [channels] epochs, then 1 error word
+    int world, rank, channel, channels;
+};
+
+__global__ void peer_barrier_kernel(const __grid_constant__ PeerBarrier b) {
+    __shared__ uint32_t epoch_s;
+    uint32_t* mine = b.pad[b.rank];
+    if (threadIdx.x == 0) {
+        uint32_t* e = mine + b.channels * MNE_MAX_PEERS + b.channel;
+        epoch_s = *e + 1;
+        *e = epoch_s;
+    }
+    __syncthreads();
+    const uint32_t epoch = epoch_s;
+    const int r = threadIdx.x;
+    if (r < b.world) {
+        uint32_t* there = b.pad[r] + b.channel * MNE_MAX_PEERS + b.rank;
+        asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(there), "r"(epoch) : "memory");
+        const uint32_t* here = mine + b.channel * MNE_MAX_PEERS + r;
+        uint32_t seen;
+        unsigned polls = 0;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(here) : "memory");
+            if ((int32_t)(seen - epoch) >= 0) break;
+        } while (++polls < (1u << 27));
+        if ((int32_t)(seen - epoch) < 0) mine[b.channels * (MNE_MAX_PEERS + 1)] = 1u;       // timed out
+    }
+}
+}  // namespace mne
+
+extern "C" int mne_peer_barrier(uint32_t* const* pad_ptrs, int32_t world_size, int32_t rank, int32_t channel, int32_t n_channels,
+                                mne_stream_t stream) {
+    using namespace mne;
+    MNE_CHECK_ARG(pad_ptrs && world_size >= 1 && world_size <= MNE_MAX_PEERS && rank >= 0 && rank < world_size,
+                  "mne_peer_barrier: bad world / rank");
+    MNE_CHECK_ARG(channel >= 0 && channel < n_channels && n_channels <= 64, "mne_peer_barrier: bad channel %d of %d", channel, n_channels);
+    PeerBarrier b{};
+    for (int r = 0; r < world_size; ++r) {
+        MNE_CHECK_ARG(pad_ptrs[r] && (((uintptr_t)pad_ptrs[r]) & 3) == 0, "mne_peer_barrier: null or misaligned pad");
+        b.pad[r] = pad_ptrs[r];
+    }
+    b.world = world_size; b.rank = rank; b.channel = channel; b.channels = n_channels;
+    peer_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(b);
+    MNE_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}

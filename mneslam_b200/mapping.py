@@ -38,6 +38,9 @@ def loss_weight_vector(cfg, is_co_sdf=None):
 PEER_CHUNK = 1024      # floats per ownership chunk (4 KB) of the peer-memory optimiser
 
 
+N_BARRIER_CHANNELS = 8
+
+
 class FusedMapper:
     def __init__(self, model, is_co_sdf=None, process_group=None, world_size=1, adopt_parameters=True, skip_untouched=True,
                  peer_memory=True, use_multicast=True, mark_dirty=None):
@@ -108,7 +111,17 @@ class FusedMapper:
                 x_buf = symm.empty(world_size * (32 + n_dec), dtype=torch.float32, device=self.dev)
                 hx = symm.rendezvous(x_buf, group.group_name)
                 x_buf.zero_()
-                self.peers = {'xchg': x_buf, 'hx': hx, 'x_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hx.buffer_ptrs]),
+                # signal pad of the library's own barrier kernel (mne_peer_barrier): channels 0-2 = the small all-reduces,
+                # 3 = gradients pushed, 4 = parameters landed
+                b_buf = symm.empty(_lib.peer_pad_words(N_BARRIER_CHANNELS), dtype=torch.int32, device=self.dev)
+                hb = symm.rendezvous(b_buf, group.group_name)
+                b_buf.zero_()
+                torch.cuda.synchronize(self.dev)
+                hb.barrier(channel=0)                  # every pad is zero before anybody signals
+                torch.cuda.synchronize(self.dev)
+                self._own_barrier = os.environ.get('MNE_OWN_BARRIER', '1') == '1'
+                self.peers = {'xchg': x_buf, 'hx': hx, 'pad': b_buf, 'hb': hb,
+                              'pad_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hb.buffer_ptrs]), 'x_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hx.buffer_ptrs]),
                               'grad': g_buf, 'param': p_buf, 'dirty': d_buf, 'hg': hg, 'hp': hp, 'hd': hd, 'inbox': i_buf, 'hi': hi,
                               'inbox_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hi.buffer_ptrs]),
                               'dirty_ptrs': (C.c_void_p * world_size)(*[int(x) for x in hd.buffer_ptrs]),
@@ -339,10 +352,28 @@ class FusedMapper:
         is_double = tensor.dtype == torch.float64
         assert tensor.is_contiguous() and tensor.numel() * (2 if is_double else 1) == n_f
         _lib.check(lib.mne_peer_scatter(tensor.data_ptr(), n_f, pr['x_ptrs'], off + rank * n_f, self.world_size, st), 'mne_peer_scatter')
-        pr['hx'].barrier(channel=channel)
+        self._barrier(channel)
         _lib.check(lib.mne_peer_sum(pr['xchg'].data_ptr() + 4 * off, tensor.numel(), self.world_size, tensor.data_ptr(),
                                     1 if is_double else 0, st), 'mne_peer_sum')
-        pr['hx'].barrier(channel=channel)     # nobody overwrites a slot that a slower rank is still summing
+        self._barrier(channel)     # nobody overwrites a slot that a slower rank is still summing
+
+    def _barrier(self, channel):
+        """Cross-rank barrier on the current stream: the library's own kernel over a signal pad in peer memory (stores to the
+        peers, polls of local memory), or torch's symmetric-memory barrier (MNE_OWN_BARRIER=0)."""
+        pr = self.peers
+        if self._own_barrier:
+            _lib.check(_lib.lib().mne_peer_barrier(pr['pad_ptrs'], self.world_size, self.shards.rank, channel, N_BARRIER_CHANNELS,
+                                                   ops._stream()), 'mne_peer_barrier')
+        elif channel < 3:
+            pr['hx'].barrier(channel=channel)
+        elif channel == 3:
+            pr['hg'].barrier(channel=0)
+        else:
+            pr['hp'].barrier(channel=1)
+
+    def barrier_timeouts(self):
+        """Non-zero if one of the library's barriers gave up waiting for a rank (the error word of the signal pad)."""
+        return 0 if self.peers is None else int(self.peers['pad'][-1].item())
 
     def _decoder_wgrad(self, max_ctas=0):
         if self._pending_wgrad is None:
@@ -401,14 +432,14 @@ class FusedMapper:
             else:                                     # flags only; the owners fetch the flagged groups themselves
                 _lib.check(lib.mne_grad_dirty_map(self.flat_grad.data_ptr(), self.flat_grad.numel(), PEER_CHUNK, self.world_size,
                                                   self.shards.rank, pr['dirty_ptrs'], st), 'mne_grad_dirty_map')
-            pr['hg'].barrier(channel=0)               # every rank's gradient and dirty map are complete
+            self._barrier(3)                          # every rank's gradient and dirty map are complete
             _lib.check(lib.mne_adam_step_peers(self.world_size, self.shards.rank, pr['param_ptrs'], pr['grad_ptrs'],
                                                self.flat_grad.numel(), PEER_CHUNK, self.flat_m.data_ptr(), self.flat_v.data_ptr(), n_seg, ends, lr,
                                                eps, wd, self.betas[0], self.betas[1], self.step_dev.data_ptr(), 0,
                                                ops._ptr(self.touched), pr['mc_param'] or None, pr['mc_grad'] or None, pr['dirty'].data_ptr(),
                                                pr['inbox'].data_ptr() if self.push_gradients else None, st),
                        'mne_adam_step_peers')
-            pr['hp'].barrier(channel=1)               # every rank's slice has landed in every parameter buffer
+            self._barrier(4)                          # every rank's slice has landed in every parameter buffer
             main.wait_stream(side)
             return
         if self.world_size > 1:

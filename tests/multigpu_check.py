@@ -51,6 +51,7 @@ def main():
     flat = mapper.flat_param.clone()
     dist.broadcast(flat, src=0)
     assert torch.equal(flat, mapper.flat_param), 'ranks diverged'
+    assert mapper.barrier_timeouts() == 0, 'a cross-rank barrier gave up waiting'
     dist.barrier()
     if rank == 0:
         print('multigpu_check ok')

@@ -203,11 +203,11 @@ def cpu_what():
     return "oracle port of the reference's torch-CPU path (F.grid_sample + matmul + torch Adam)"
 
 
-def cpu_baseline_record(cfg, n_rays, steps=5, warmup=1):
+def cpu_baseline_record(cfg, n_rays, steps=24, warmup=2):
     pts_s, med, total = time_cpu(cfg, n_rays, steps, warmup)
     threads = torch.get_num_threads()
     # the reference pins OMP_NUM_THREADS=3 (mneslam_mp.py:2): its own setting, reported beside the all-cores figure
-    pts_s3, med3, _ = time_cpu(cfg, n_rays, 3, 1, threads=3)
+    pts_s3, med3, _ = time_cpu(cfg, n_rays, 8, 1, threads=3)
     torch.set_num_threads(threads)
     return {'value': pts_s, 'unit': UNIT, 'cores': threads, 'kind': cpu_kind(),
             'sample': '%d mapping iterations (median) of the same %d-ray x %d-sample workload, %s, %d host threads of %d cores'

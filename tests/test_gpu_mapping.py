@@ -249,6 +249,40 @@ def test_touched_map_adam_is_bit_identical_to_dense():
     assert 0.2 < frac < 0.95, frac
 
 
+def test_peer_barrier_kernel_with_two_emulated_ranks():
+    """mne_peer_barrier with both "ranks" on ONE device (two pads, two streams): neither kernel returns before the other has
+    signalled, the epochs advance together, nothing times out; a rank whose partner never arrives raises the error word of
+    its pad instead of hanging."""
+    import ctypes as C
+    from mneslam_b200 import _lib
+    lib = _lib.lib()
+    n_ch = 4
+    words = _lib.peer_pad_words(n_ch)
+    pads = [torch.zeros(words, dtype=torch.int32, device='cuda') for _ in range(2)]
+    ptrs = (C.c_void_p * 2)(*[p.data_ptr() for p in pads])
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    marks = [torch.zeros(1, dtype=torch.int64, device='cuda') for _ in range(2)]
+    torch.cuda.synchronize()
+    for it in range(40):
+        ch = it % n_ch
+        for r in (0, 1) if it % 2 else (1, 0):
+            with torch.cuda.stream(streams[r]):
+                if r == 0:
+                    torch.cuda._sleep(200000)                     # rank 0 arrives late: rank 1 has to wait for it
+                marks[r] += 1
+                _lib.check(lib.mne_peer_barrier(ptrs, 2, r, ch, n_ch, streams[r].cuda_stream), 'mne_peer_barrier')
+    torch.cuda.synchronize()
+    for r in (0, 1):
+        epochs = pads[r][n_ch * (_lib.MAX_PEERS + 1) - n_ch:n_ch * (_lib.MAX_PEERS + 1)].tolist()
+        assert epochs == [10] * n_ch and int(pads[r][-1]) == 0
+        arrived = pads[r][:n_ch * _lib.MAX_PEERS].view(n_ch, _lib.MAX_PEERS)[:, :2]
+        assert bool((arrived == 10).all())
+    # the partner never calls: bounded wait, error word raised
+    _lib.check(lib.mne_peer_barrier(ptrs, 2, 0, 0, n_ch, None), 'mne_peer_barrier')
+    torch.cuda.synchronize()
+    assert int(pads[0][-1]) == 1 and int(pads[1][-1]) == 0
+
+
 def test_texel_flag_adam_is_bit_identical_to_dense():
     """mne_adam_step_segments_dirty: with the backward pass's texel flags (one byte per 32 floats of the plane range) the
     optimiser reads the gradient of flagged texels only.  Same bits as the dense kernel, gradients and flags cleared; flagged

@@ -88,6 +88,8 @@ static int g_adam_spare_sms = 0;
 int adam_spare_sms() { return g_adam_spare_sms; }
 static int g_hash_level0_smem = 0;
 int hash_level0_smem() { return g_hash_level0_smem; }
+static int g_peer_barrier_polls_log2 = 27;
+int peer_barrier_polls_log2() { return g_peer_barrier_polls_log2; }
 
 }  // namespace mne
 
@@ -113,6 +115,12 @@ extern "C" int mne_set_option(const char* key, int value) {
         g_hash_level0_smem = value;
         return 0;
     }
+    if (strcmp(key, "peer_barrier_polls_log2") == 0) {
+        // mne_peer_barrier gives up (and raises the pad's error word) after 2^value polls of a peer's arrival word
+        MNE_CHECK_ARG(value >= 10 && value <= 31, "mne_set_option: peer_barrier_polls_log2 must be in [10, 31]");
+        g_peer_barrier_polls_log2 = value;
+        return 0;
+    }
     set_error("mne_set_option: unknown option '%s'", key);
     return 1;
 }
@@ -123,6 +131,7 @@ extern "C" int mne_get_option(const char* key, int* value) {
     if (strcmp(key, "impl") == 0) { *value = g_impl; return 0; }
     if (strcmp(key, "adam_spare_sms") == 0) { *value = g_adam_spare_sms; return 0; }
     if (strcmp(key, "hash_level0_smem") == 0) { *value = g_hash_level0_smem; return 0; }
+    if (strcmp(key, "peer_barrier_polls_log2") == 0) { *value = g_peer_barrier_polls_log2; return 0; }
     set_error("mne_get_option: unknown option '%s'", key);
     return 1;
 }

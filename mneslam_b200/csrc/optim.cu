@@ -192,6 +192,7 @@ __global__ void tick_kernel(int64_t* step) { if (threadIdx.x == 0 && blockIdx.x 
 
 int sm_count();
 int adam_spare_sms();
+int peer_barrier_polls_log2();
 static int adam_sms() { return std::max(1, sm_count() - adam_spare_sms()); }
 
 }  // namespace mne
@@ -966,13 +967,14 @@ extern "C" int mne_peer_sum(const void* slots, int32_t n, int32_t world_size, vo
 // rank r's signal pad (release, system scope: everything earlier kernels of this stream wrote -- to any GPU -- is visible
 // before the signal is) and then polls slot [r] of its OWN pad until rank r's epoch has arrived (acquire).  Epochs count the
 // barriers of a channel and live in device memory, so a CUDA-graph replay continues the sequence.  Stores and local polls
-// only: no remote atomics, no remote loads (each costs an NVLink round trip).  The wait is bounded: after ~2^27 polls the
-// kernel gives up and raises the pad's error word instead of hanging the GPU.
+// only: no remote atomics, no remote loads (each costs an NVLink round trip).  The wait is bounded: after 2^27 polls (about
+// a minute; option peer_barrier_polls_log2) the kernel gives up and raises the pad's error word instead of hanging the GPU.
 // ---------------------------------------------------------------------------------------------------------
 namespace mne {
 struct PeerBarrier {
     uint32_t* pad[MNE_MAX_PEERS];     // every rank's pad: [channels][MNE_MAX_PEERS] arrival words, then [channels] epochs, then 1 error word
     int world, rank, channel, channels;
+    unsigned max_polls;
 };
 
 __global__ void peer_barrier_kernel(const __grid_constant__ PeerBarrier b) {
@@ -995,7 +997,7 @@ __global__ void peer_barrier_kernel(const __grid_constant__ PeerBarrier b) {
         do {
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(here) : "memory");
             if ((int32_t)(seen - epoch) >= 0) break;
-        } while (++polls < (1u << 27));
+        } while (++polls < b.max_polls);
         if ((int32_t)(seen - epoch) < 0) mine[b.channels * (MNE_MAX_PEERS + 1)] = 1u;       // timed out
     }
 }
@@ -1013,6 +1015,7 @@ extern "C" int mne_peer_barrier(uint32_t* const* pad_ptrs, int32_t world_size, i
         b.pad[r] = pad_ptrs[r];
     }
     b.world = world_size; b.rank = rank; b.channel = channel; b.channels = n_channels;
+    b.max_polls = 1u << peer_barrier_polls_log2();
     peer_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(b);
     MNE_CHECK_CUDA(cudaGetLastError());
     return 0;

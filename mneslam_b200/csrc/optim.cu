@@ -27,13 +27,10 @@ __device__ __forceinline__ void adam_one(float& p, float& g, float& m, float& v,
     if (a.weight_decay != 0.0f) grad = fmaf(a.weight_decay, p, grad);
     m = m + (1.0f - a.beta1) * (grad - m);
     v = __fmaf_rn((1.0f - a.beta2) * grad, grad, a.beta2 * v);
-#ifdef MNE_FAST_ADAM_MATH      // diagnostic only: approximate division / square root
-    const float denom = __fdividef(__fsqrt_rn(v), bc2_sqrt) + a.eps;
-    p = p - step_size * __fdividef(m, denom);
-#else
+    // IEEE division and square root, as torch's kernels compute them (~50 instructions per element; with approximate
+    // intrinsics the two-rank peer kernel measured 84 -> 79 us: not what bounds these kernels)
     const float denom = sqrtf(v) / bc2_sqrt + a.eps;
     p = p - step_size * (m / denom);
-#endif
     if (a.zero_grad) g = 0.0f;
 }
 

@@ -532,16 +532,20 @@ class DeviceKeyframeRays:
     def batch_rays(self, n_rays):
         return n_rays + self.n_current(n_rays)
 
-    def sample(self, n_rays, generator=None, return_rows=False):
+    def sample(self, n_rays, generator=None, return_rows=False, key=None):
         """``n_rays`` distinct stored rays (``random.sample`` of model/keyframe.py:98: without replacement) followed by
         ``n_current(n_rays)`` distinct pixels of the current frame, drawn and assembled in one launch.  The draw is keyed by one
-        device-side random integer, so a CUDA-graph replay draws a fresh batch."""
+        device-side random integer, so a CUDA-graph replay draws a fresh batch (``key``: that integer, a one-element int64
+        device tensor, for reproducible draws)."""
         dev = self.rays.device
         n_cur = self.n_current(n_rays)
         n = n_rays + n_cur
         if self.rays.dtype != torch.float32 or not self.rays.is_contiguous() or self.poses.dtype != torch.float32 or not self.poses.is_contiguous():
             raise TypeError('rays and poses must be contiguous float32 tensors')
-        key = torch.randint(0, 1 << 62, (1,), device=dev, generator=generator)
+        if key is None:
+            key = torch.randint(0, 1 << 62, (1,), device=dev, generator=generator)
+        elif key.dtype != torch.int64 or key.device != dev or key.numel() != 1:
+            raise TypeError('key must be a one-element int64 tensor on the device of the store')
         rows = torch.empty(n, dtype=torch.int64, device=dev) if return_rows else None
         ro, rd, rgb, d = (torch.empty(n, 3, dtype=torch.float32, device=dev), torch.empty(n, 3, dtype=torch.float32, device=dev),
                           torch.empty(n, 3, dtype=torch.float32, device=dev), torch.empty(n, 1, dtype=torch.float32, device=dev))

@@ -13,4 +13,6 @@ Parity status (see DESIGN.md "Oracle"):
   published algorithm of the un-vendored third-party dependency tiny-cuda-nn; the reference holds no
   test or golden vector for them and tiny-cuda-nn cannot be installed here: PARITY UNPINNED for
   these two functions.
+* The on-device batch draw (``oracle/draw.py``) restates this repository's own keyed permutation: the reference draws with
+  Python's ``random.sample``, whose stream cannot be reproduced on the device; the property (distinct rows) is what is tested.
 """

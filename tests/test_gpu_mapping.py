@@ -147,6 +147,12 @@ def test_device_draw_is_without_replacement_and_adds_the_current_frame():
         assert torch.equal(rgb.cpu(), r7[:, 3:6]) and torch.equal(d.cpu(), r7[:, 6:7])
         seen.append(rk)
     assert torch.equal(torch.sort(seen[1]).values, torch.arange(total))
+    # the rows are exactly those of the CPU restatement for the same key (index work: bit-exact)
+    from oracle import draw
+    for k in (0, 12345678901234567, (1 << 62) - 1):
+        key = torch.tensor([k], dtype=torch.int64, device='cuda')
+        rows = db.sample(200, return_rows=True, key=key)[4].cpu().tolist()
+        assert rows == draw.draw_rows(k, total, 200, current.shape[0], db.n_current(200))
     # a fresh key gives a fresh draw; the draw spreads over the whole store
     a = db.sample(256, return_rows=True)[4].cpu()
     b = db.sample(256, return_rows=True)[4].cpu()

@@ -160,3 +160,22 @@ def test_oracle_renders_the_reference_image_and_eval_forward():
     assert np.array_equal(e['z_vals'].numpy(), g['eval_ret_z_vals'])
     for k in ('rgb', 'depth', 'raw'):
         assert rel(e[k].numpy(), g['eval_ret_' + k]) < 1e-4, k
+
+
+def test_draw_oracle_is_a_bijection_of_the_row_range():
+    """oracle/draw.py (the function the device draw must compute): for every population size the first n elements of the keyed
+    sequence are a permutation of range(n) -- so any prefix holds distinct rows, like ``random.sample`` (model/keyframe.py:98);
+    different keys give different orders, and the two draws of a batch (keyframes / current frame) use different round keys."""
+    from oracle import draw
+    for n in (1, 2, 3, 5, 16, 17, 480, 1000, 4097):
+        for key in (0, 1, 0x123456789abcdef, (1 << 62) - 1):
+            rows = draw.draw_rows(key, n, n)
+            assert sorted(rows) == list(range(n)), (n, key)
+    a, b = draw.draw_rows(7, 1000, 64), draw.draw_rows(8, 1000, 64)
+    assert a != b and len(set(a)) == 64
+    both = draw.draw_rows(7, 1000, 32, 1000, 32)
+    assert both[:32] == a[:32] and both[32:] != both[:32] and len(set(both[32:])) == 32
+    # spread: a short prefix is not clustered at one end of the range
+    many = [r for key in range(50) for r in draw.draw_rows(key, 100000, 40)]
+    mean = sum(many) / len(many) / 100000
+    assert 0.45 < mean < 0.55

@@ -1139,6 +1139,9 @@ def run_ours(args):
             'last_loss': float(mapper.total_loss(static_losses if graph is not None else losses).item()),
         }
         line.update(extra)
+        if world > 1:
+            # (the library's cross-rank barriers wait a bounded time: non-zero = a rank gave up waiting somewhere in this run)
+            line['barrier_timeouts_at_end'] = mapper.barrier_timeouts()
         # the whole step against the gather roofline -- 6 144 algorithmic bytes per point (3 072 gathered + 3 072
         # of gradient contributions) x points/s over the measured HBM copy bandwidth of all GPUs
         line['roofline']['whole_step_frac_6144B_per_point'] = value * (ALG_BYTES_PER_POINT_FWD + ALG_BYTES_PER_POINT_BWD) / 1e9 / (peak * world)

@@ -133,7 +133,7 @@ const char* mne_last_error(void);
  * operands), 1 = the first-generation fp32 CUDA-core kernels, kept as an on-device cross-check.
  * "adam_spare_sms" (default 0, at most 64): SMs the persistent optimiser grids leave free, so that small kernels on
  * another stream can run under them.  "hash_level0_smem" (default 0): stage level 0 of the hash table(s) in shared memory
- * (measured slower on B200).  "peer_barrier_polls_log2" (default 27, 10..31): mne_peer_barrier gives up after 2^v polls. */
+ * (measured slower on B200).  "peer_barrier_polls_log2" (default 29, 10..31): mne_peer_barrier gives up after 2^v polls. */
 int mne_set_option(const char* key, int value);
 /* Current value of an option of mne_set_option (so that a caller can put it back). */
 int mne_get_option(const char* key, int* value);
@@ -407,7 +407,7 @@ int mne_peer_sum(const void* slots, int32_t n, int32_t world_size, void* out, in
  * identical in layout on every rank: [n_channels][MNE_MAX_PEERS] arrival words, [n_channels] epochs, 1 error word.  Every
  * rank calls it the same number of times per channel; different channels may be in flight on different streams.  Memory
  * written by earlier work of the calling stream (to any GPU) is visible to the peers' work after their barrier returns.  The
- * wait is bounded (2^27 polls, about a minute; mne_set_option("peer_barrier_polls_log2", v)): a rank that never arrives
+ * wait is bounded (2^29 polls, about two minutes; mne_set_option("peer_barrier_polls_log2", v)): a rank that never arrives
  * raises the error word (last word of the pad) instead of hanging the device. */
 #define MNE_PEER_PAD_WORDS(n_channels) ((n_channels) * (MNE_MAX_PEERS + 1) + 1)
 int mne_peer_barrier(uint32_t* const* pad_ptrs, int32_t world_size, int32_t rank, int32_t channel, int32_t n_channels,

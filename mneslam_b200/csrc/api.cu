@@ -88,7 +88,7 @@ static int g_adam_spare_sms = 0;
 int adam_spare_sms() { return g_adam_spare_sms; }
 static int g_hash_level0_smem = 0;
 int hash_level0_smem() { return g_hash_level0_smem; }
-static int g_peer_barrier_polls_log2 = 27;
+static int g_peer_barrier_polls_log2 = 29;
 int peer_barrier_polls_log2() { return g_peer_barrier_polls_log2; }
 
 }  // namespace mne

@@ -964,8 +964,8 @@ extern "C" int mne_peer_sum(const void* slots, int32_t n, int32_t world_size, vo
 // rank r's signal pad (release, system scope: everything earlier kernels of this stream wrote -- to any GPU -- is visible
 // before the signal is) and then polls slot [r] of its OWN pad until rank r's epoch has arrived (acquire).  Epochs count the
 // barriers of a channel and live in device memory, so a CUDA-graph replay continues the sequence.  Stores and local polls
-// only: no remote atomics, no remote loads (each costs an NVLink round trip).  The wait is bounded: after 2^27 polls (about
-// a minute; option peer_barrier_polls_log2) the kernel gives up and raises the pad's error word instead of hanging the GPU.
+// only: no remote atomics, no remote loads (each costs an NVLink round trip).  The wait is bounded: after 2^29 polls (about
+// two minutes; option peer_barrier_polls_log2) the kernel gives up and raises the pad's error word instead of hanging the GPU.
 // ---------------------------------------------------------------------------------------------------------
 namespace mne {
 struct PeerBarrier {

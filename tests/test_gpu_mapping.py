@@ -292,7 +292,7 @@ def test_peer_barrier_kernel_signals_and_bounded_wait():
             assert int(pads[0][-1]) == 0 and int(pads[1][2 * _lib.MAX_PEERS + 0]) == epoch
             assert int(pads[0][n_arr + 2]) == epoch and int(pads[1][n_arr + 2]) == epoch
     finally:
-        _lib.check(lib.mne_set_option(b'peer_barrier_polls_log2', 27), 'mne_set_option')
+        _lib.check(lib.mne_set_option(b'peer_barrier_polls_log2', 29), 'mne_set_option')
 
 
 def test_texel_flag_adam_is_bit_identical_to_dense():

@@ -331,7 +331,8 @@ int mne_adam_step_segments(float* param, float* grad, float* exp_avg, float* exp
  * gradient is zero by contract (everything that adds into it flags it, and this kernel clears what it read: zero_grad
  * must be set), so it is not read at all: ~80 % of the 129 MB gradient pass of a room0 iteration.  The flags are
  * cleared here for the next iteration.  Results are bit-identical to mne_adam_step_segments.  (Measured on B200: this pass
- * 111 -> 105 us, but setting the flags costs the backward kernel 18 us, so mapping.FusedMapper leaves it off.) */
+ * 111 -> 105 us and setting the flags costs the backward kernel 4.5 us -- a wash on one GPU, so mapping.FusedMapper leaves it
+ * off there; with several GPUs the same flags drive mne_dirty_push_data and are on by default.) */
 int mne_adam_step_segments_dirty(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int32_t n_segments,
                                  const int64_t* segment_ends, const float* lr, const float* eps, const float* weight_decay,
                                  float beta1, float beta2, const int64_t* step_dev, int64_t step_host, int32_t zero_grad,

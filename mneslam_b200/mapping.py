@@ -209,8 +209,8 @@ class FusedMapper:
             self.dirty_local = torch.zeros(padded // 32, dtype=torch.uint8, device=self.dev)
         # one GPU: the same flags can tell the optimiser which texels of the plane gradient are non-zero, so that it does not read
         # (nor clear) the other ~80 % of the 129 MB gradient buffer (mne_adam_step_segments_dirty).  Off by default -- measured on
-        # B200 (room0, 2150 rays): the optimiser pass 111 -> 105 us, but the flag stores cost the backward kernel 34 -> 52 us, the
-        # iteration 0.235 -> 0.249 ms
+        # B200 (room0, 2150 rays): the optimiser pass 111 -> 105 us, the flag stores cost the backward kernel 34 -> 38.5 us (one
+        # store per tap; 52 us when every corner stored its own flag): the iteration stays at 0.235 ms
         self.adam_dirty = world_size == 1 and vector_planes and os.environ.get('MNE_ADAM_DIRTY', '0') == '1' and enc_len % 32 == 0
         if self.adam_dirty:
             self.dirty_local = torch.zeros((padded + 31) // 32, dtype=torch.uint8, device=self.dev)
